@@ -1,0 +1,228 @@
+// Linear and BatchMatmul on top of the GEMM engine (gemm_sm100.cu).
+#include "gemm_sm100.cuh"
+
+namespace ffk {
+namespace {
+
+int run_gemm(gemm::Problem const &p, gemm::Epilogue const &e, cudaStream_t s, int path) {
+  switch (path) {
+    case FFK_GEMM_AUTO: return gemm::launch(p, e, s);
+    case FFK_GEMM_TENSOR: return gemm::launch_tc(p, e, s);
+    case FFK_GEMM_SIMT: return gemm::launch_simt(p, e, s);
+    default: set_error("gemm: unknown path %d", path); return FFK_ERR_INVALID;
+  }
+}
+
+// dY <- dY * act'(.) in place. `ref` is Y for relu/sigmoid/tanh and the
+// pre-activation for gelu.
+template <typename T>
+__global__ void __launch_bounds__(256)
+    act_backward_kernel(T *__restrict__ dy, T const *__restrict__ ref, size_t n, int act) {
+  constexpr int VN = Vec16<T>::N;
+  size_t nvec = n / VN;
+  size_t stride = size_t(gridDim.x) * blockDim.x;
+  for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < nvec; i += stride) {
+    Vec16<T> g = ld_vec(dy + i * VN);
+    Vec16<T> y = ld_stream(ref + i * VN);
+#pragma unroll
+    for (int j = 0; j < VN; ++j) {
+      float gv = to_f32(g.v[j]), yv = to_f32(y.v[j]), o;
+      if (act == FFK_ACT_RELU) o = yv > 0.f ? gv : 0.f;
+      else if (act == FFK_ACT_SIGMOID) o = gv * yv * (1.f - yv);
+      else if (act == FFK_ACT_TANH) o = gv * (1.f - yv * yv);
+      else {
+        constexpr float B = 0.7978845608028654f, C = 0.035677408136300125f;
+        float u = yv * (C * yv * yv + B);
+        float t = tanhf(u);
+        float du = B + 3.f * C * yv * yv;
+        o = gv * (0.5f + 0.5f * t + 0.5f * yv * (1.f - t * t) * du);
+      }
+      g.v[j] = from_f32<T>(o);
+    }
+    st_vec(dy + i * VN, g);
+  }
+  // tail
+  for (size_t i = nvec * VN + size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) {
+    float gv = to_f32(dy[i]), yv = to_f32(ref[i]), o;
+    if (act == FFK_ACT_RELU) o = yv > 0.f ? gv : 0.f;
+    else if (act == FFK_ACT_SIGMOID) o = gv * yv * (1.f - yv);
+    else if (act == FFK_ACT_TANH) o = gv * (1.f - yv * yv);
+    else {
+      constexpr float B = 0.7978845608028654f, C = 0.035677408136300125f;
+      float u = yv * (C * yv * yv + B);
+      float t = tanhf(u);
+      float du = B + 3.f * C * yv * yv;
+      o = gv * (0.5f + 0.5f * t + 0.5f * yv * (1.f - t * t) * du);
+    }
+    dy[i] = from_f32<T>(o);
+  }
+}
+
+// db[o] += sum_b dY[b][o]. One CTA owns a strip of 32 columns and walks every
+// row with 8 row-lanes; fixed summation order => run-to-run deterministic.
+template <typename T>
+__global__ void __launch_bounds__(256)
+    column_sum_accumulate_kernel(T const *__restrict__ dy, T *__restrict__ db, int rows,
+                                 int cols) {
+  __shared__ float part[8][33];
+  int const cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
+  int const col = blockIdx.x * 32 + cx;
+  float acc = 0.f;
+  if (col < cols) {
+    for (int r = ry; r < rows; r += 8) acc += to_f32(dy[size_t(r) * cols + col]);
+  }
+  part[ry][cx] = acc;
+  __syncthreads();
+  if (ry == 0 && col < cols) {
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s += part[i][cx];
+    db[col] = from_f32<T>(to_f32(db[col]) + s);
+  }
+}
+
+}  // namespace
+}  // namespace ffk
+
+using namespace ffk;
+
+extern "C" {
+
+int ffk_gemm(void *stream, void const *a, void const *b, void *d, int M, int N, int K, int batch,
+             long long lda, long long ldb, long long ldd, long long a_batch_stride,
+             long long b_batch_stride, long long d_batch_stride, int in_dtype, int out_dtype,
+             int a_mn_major, int b_mn_major, float alpha, int accumulate, void const *bias,
+             int activation, int path) {
+  FFK_REQUIRE(M >= 0 && N >= 0 && K >= 0 && batch >= 0, "ffk_gemm: negative extent");
+  if (M == 0 || N == 0 || batch == 0) return FFK_OK;
+  FFK_REQUIRE(a && b && d, "ffk_gemm: null operand");
+  gemm::Problem p{a, b, lda, ldb, a_batch_stride, b_batch_stride, M, N, K, batch,
+                  in_dtype, out_dtype, a_mn_major != 0, b_mn_major != 0};
+  gemm::Epilogue e{d, ldd, d_batch_stride, bias, activation, accumulate, alpha, 0.f, nullptr};
+  return run_gemm(p, e, as_stream(stream), path);
+}
+
+int ffk_linear_forward(void *stream, void const *input, void *output, void const *weight,
+                       void const *bias, int in_dim, int out_dim, int batch_size, int dtype,
+                       int activation, int path) {
+  FFK_REQUIRE(in_dim > 0 && out_dim > 0 && batch_size >= 0, "linear forward: bad extents");
+  if (batch_size == 0) return FFK_OK;
+  FFK_REQUIRE(input && output && weight, "linear forward: null tensor");
+  gemm::Problem p{input, weight, in_dim, in_dim, 0, 0, batch_size, out_dim, in_dim, 1,
+                  dtype, dtype, false, false};
+  gemm::Epilogue e{output, out_dim, 0, bias, activation, 0, 1.f, 0.f, nullptr};
+  return run_gemm(p, e, as_stream(stream), path);
+}
+
+int ffk_linear_backward(void *stream, void const *input, void *input_grad, void const *output,
+                        void *output_grad, void const *weight, void *weight_grad,
+                        void *bias_grad, int in_dim, int out_dim, int batch_size, int dtype,
+                        int activation, float l2_lambda, void const *preact, int path) {
+  FFK_REQUIRE(in_dim > 0 && out_dim > 0 && batch_size >= 0, "linear backward: bad extents");
+  if (batch_size == 0) return FFK_OK;
+  FFK_REQUIRE(input && output_grad && weight && weight_grad, "linear backward: null tensor");
+  cudaStream_t s = as_stream(stream);
+  size_t n_out = size_t(out_dim) * batch_size;
+
+  if (activation != FFK_ACT_NONE) {
+    void const *ref = output;
+    if (activation == FFK_ACT_GELU) {
+      if (!preact) {
+        set_error("linear backward: GELU gradient needs the pre-activation buffer");
+        return FFK_ERR_UNSUPPORTED;
+      }
+      ref = preact;
+    }
+    FFK_REQUIRE(ref, "linear backward: activation gradient needs `output`");
+    FFK_REQUIRE(aligned16(output_grad) && aligned16(ref), "linear backward: unaligned tensor");
+    FFK_DISPATCH_FLOAT(dtype, T, {
+      unsigned grid = stream_grid(n_out / Vec16<T>::N + 1, 256, 8);
+      act_backward_kernel<T><<<grid, 256, 0, s>>>(reinterpret_cast<T *>(output_grad),
+                                                  reinterpret_cast<T const *>(ref), n_out,
+                                                  activation);
+    });
+    FFK_LAUNCH_CHECK();
+  }
+
+  {  // weight gradient: dW[o][i] += sum_b dY[b][o] X[b][i]
+    gemm::Problem p{output_grad, input, out_dim, in_dim, 0, 0, out_dim, in_dim, batch_size, 1,
+                    dtype, dtype, true, true};
+    gemm::Epilogue e{weight_grad, in_dim, 0, nullptr, gemm::ACT_NONE, 1, 1.f,
+                     l2_lambda, l2_lambda != 0.f ? weight : nullptr};
+    int rc = run_gemm(p, e, s, path);
+    if (rc) return rc;
+  }
+  if (bias_grad) {
+    FFK_DISPATCH_FLOAT(dtype, T, {
+      column_sum_accumulate_kernel<T><<<(out_dim + 31) / 32, 256, 0, s>>>(
+          reinterpret_cast<T const *>(output_grad), reinterpret_cast<T *>(bias_grad), batch_size,
+          out_dim);
+    });
+    FFK_LAUNCH_CHECK();
+  }
+  if (input_grad) {  // data gradient: dX[b][i] += sum_o dY[b][o] W[o][i]
+    gemm::Problem p{output_grad, weight, out_dim, in_dim, 0, 0, batch_size, in_dim, out_dim, 1,
+                    dtype, dtype, false, true};
+    gemm::Epilogue e{input_grad, in_dim, 0, nullptr, gemm::ACT_NONE, 1, 1.f, 0.f, nullptr};
+    int rc = run_gemm(p, e, s, path);
+    if (rc) return rc;
+  }
+  return FFK_OK;
+}
+
+int ffk_batch_matmul_forward(void *stream, void *output, void const *a_input, void const *b_input,
+                             int m, int n, int k, int batch, int a_seq_length_dim,
+                             int b_seq_length_dim, int seq_length, int dtype, int path) {
+  FFK_REQUIRE(m >= 0 && n >= 0 && k >= 0 && batch >= 0, "batch_matmul: negative extent");
+  long long const lda = k, ldb = m, ldo = m;
+  long long const sa = 1LL * n * k, sb = 1LL * k * m, so = 1LL * n * m;
+  // sequence-length truncation, following the reference's rules
+  if (a_seq_length_dim == 0 && seq_length >= 0) {
+    FFK_REQUIRE(seq_length <= k && b_seq_length_dim == 1, "batch_matmul: bad seq_length for k");
+    k = seq_length;
+  } else if (a_seq_length_dim == 1 && seq_length >= 0) {
+    FFK_REQUIRE(seq_length <= n, "batch_matmul: seq_length > n");
+    n = seq_length;
+  } else {
+    FFK_REQUIRE(a_seq_length_dim < 0 || seq_length < 0, "batch_matmul: a_seq_length_dim must be 0/1");
+  }
+  if (b_seq_length_dim == 0 && seq_length >= 0) {
+    FFK_REQUIRE(seq_length <= m, "batch_matmul: seq_length > m");
+    m = seq_length;
+  } else if (b_seq_length_dim == 1 && seq_length >= 0) {
+    FFK_REQUIRE(a_seq_length_dim == 0 && k == seq_length, "batch_matmul: inconsistent seq dims");
+  } else {
+    FFK_REQUIRE(b_seq_length_dim < 0 || seq_length < 0, "batch_matmul: b_seq_length_dim must be 0/1");
+  }
+  if (m == 0 || n == 0 || batch == 0) return FFK_OK;
+  FFK_REQUIRE(output && a_input && b_input, "batch_matmul: null tensor");
+  gemm::Problem p{a_input, b_input, lda, ldb, sa, sb, n, m, k, batch, dtype, dtype, false, true};
+  gemm::Epilogue e{output, ldo, so, nullptr, gemm::ACT_NONE, 0, 1.f, 0.f, nullptr};
+  return run_gemm(p, e, as_stream(stream), path);
+}
+
+int ffk_batch_matmul_backward(void *stream, void const *o, void const *o_grad, void const *a,
+                              void *a_grad, void const *b, void *b_grad, int m, int n, int k,
+                              int batch, int dtype, int path) {
+  (void)o;
+  FFK_REQUIRE(m >= 0 && n >= 0 && k >= 0 && batch >= 0, "batch_matmul: negative extent");
+  if (m == 0 || n == 0 || k == 0 || batch == 0) return FFK_OK;
+  FFK_REQUIRE(o_grad && a && a_grad && b && b_grad, "batch_matmul backward: null tensor");
+  cudaStream_t s = as_stream(stream);
+  long long const sa = 1LL * n * k, sb = 1LL * k * m, so = 1LL * n * m;
+  {  // dA (n x k) += dO (n x m) * B^T   [B stored k x m: k-major over m for N = k]
+    gemm::Problem p{o_grad, b, m, m, so, sb, n, k, m, batch, dtype, dtype, false, false};
+    gemm::Epilogue e{a_grad, k, sa, nullptr, gemm::ACT_NONE, 1, 1.f, 0.f, nullptr};
+    int rc = run_gemm(p, e, s, path);
+    if (rc) return rc;
+  }
+  {  // dB (k x m) += A^T (k x n) * dO (n x m)
+    gemm::Problem p{a, o_grad, k, m, sa, so, k, m, n, batch, dtype, dtype, true, true};
+    gemm::Epilogue e{b_grad, m, sb, nullptr, gemm::ACT_NONE, 1, 1.f, 0.f, nullptr};
+    int rc = run_gemm(p, e, s, path);
+    if (rc) return rc;
+  }
+  return FFK_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,517 @@
+// tcgen05 / TMEM / TMA GEMM for sm_100a plus the CUDA-core fp32-exact GEMM.
+// See gemm_sm100.cuh for the contract.
+#include "gemm_sm100.cuh"
+
+#include <cudaTypedefs.h>
+#include <mutex>
+
+namespace ffk {
+namespace gemm {
+
+namespace {
+
+constexpr int BLOCK_M = 128;       // rows per CTA tile = TMEM lanes
+constexpr int SWIZZLE_BYTES = 128; // TMA / UMMA swizzle span
+constexpr int MMA_K_BYTES = 32;    // one tcgen05.mma consumes 32 bytes of K per row
+constexpr int K_STEPS = SWIZZLE_BYTES / MMA_K_BYTES;
+constexpr int GROUP_M = 8;         // tile rasterisation: 8 row-blocks share B columns in L2
+constexpr int NUM_THREADS = 192;   // warp0 TMA, warp1 MMA, warps 2..5 epilogue
+
+template <int BLOCK_N, int STAGES> struct SmemPlan {
+  static constexpr int A_BYTES = BLOCK_M * SWIZZLE_BYTES;
+  static constexpr int B_BYTES = BLOCK_N * SWIZZLE_BYTES;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int BAR_OFFSET = STAGES * STAGE_BYTES;
+  static constexpr int TOTAL = BAR_OFFSET + 256 + 1024;  // barriers + alignment slack
+};
+
+struct TileCoord {
+  int b, m_idx, n_idx;
+};
+
+__device__ __forceinline__ TileCoord decode_tile(int tile, int num_m, int num_n, int block_n) {
+  int per_batch = num_m * num_n;
+  int b = tile / per_batch;
+  int t = tile - b * per_batch;
+  int group_span = GROUP_M * num_n;
+  int g = t / group_span;
+  int first_m = g * GROUP_M;
+  int gsize = min(num_m - first_m, GROUP_M);
+  int in_g = t - g * group_span;
+  TileCoord c;
+  c.b = b;
+  c.m_idx = (first_m + in_g % gsize) * BLOCK_M;
+  c.n_idx = (in_g / gsize) * block_n;
+  return c;
+}
+
+template <typename T>
+__device__ __forceinline__ void epilogue_row_chunk(uint32_t const (&acc)[32], Epilogue const &ep,
+                                                   long long row_off, int col0, int ncols_valid,
+                                                   bool vec_ok) {
+  float v[32];
+#pragma unroll
+  for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(acc[i]) * ep.alpha;
+  T *drow = reinterpret_cast<T *>(ep.d) + row_off + col0;
+  if (ep.bias != nullptr) {
+    T const *bp = reinterpret_cast<T const *>(ep.bias) + col0;
+#pragma unroll
+    for (int i = 0; i < 32; ++i)
+      if (i < ncols_valid) v[i] += to_f32(__ldg(bp + i));
+  }
+  if (ep.act != ACT_NONE) {
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = apply_act(v[i], ep.act);
+  }
+  constexpr int VN = 16 / sizeof(T);
+  if (vec_ok && ncols_valid == 32) {
+    if (ep.r != nullptr) {
+      T const *rp = reinterpret_cast<T const *>(ep.r) + row_off + col0;
+#pragma unroll
+      for (int j = 0; j < 32 / VN; ++j) {
+        Vec16<T> t = ld_vec(rp + j * VN);
+#pragma unroll
+        for (int i = 0; i < VN; ++i) v[j * VN + i] += ep.lambda * to_f32(t.v[i]);
+      }
+    }
+    if (ep.accumulate) {
+#pragma unroll
+      for (int j = 0; j < 32 / VN; ++j) {
+        Vec16<T> t = ld_vec(drow + j * VN);
+#pragma unroll
+        for (int i = 0; i < VN; ++i) v[j * VN + i] += to_f32(t.v[i]);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 32 / VN; ++j) {
+      Vec16<T> t;
+#pragma unroll
+      for (int i = 0; i < VN; ++i) t.v[i] = from_f32<T>(v[j * VN + i]);
+      st_vec(drow + j * VN, t);
+    }
+  } else {
+    T const *rp = ep.r ? reinterpret_cast<T const *>(ep.r) + row_off + col0 : nullptr;
+#pragma unroll
+    for (int i = 0; i < 32; ++i) {
+      if (i < ncols_valid) {
+        float x = v[i];
+        if (rp) x += ep.lambda * to_f32(rp[i]);
+        if (ep.accumulate) x += to_f32(drow[i]);
+        drow[i] = from_f32<T>(x);
+      }
+    }
+  }
+}
+
+// ESIZE: bytes per input element (2: f16/bf16, 4: fp32 consumed as tf32).
+template <int ESIZE, bool A_MN, bool B_MN, int BLOCK_N, int STAGES>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+    gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a,
+                   const __grid_constant__ CUtensorMap map_b, Epilogue ep, int M, int N, int K,
+                   int batch, uint32_t idesc, int out_dtype, int vec_ok) {
+  using Plan = SmemPlan<BLOCK_N, STAGES>;
+  constexpr int BLOCK_K = SWIZZLE_BYTES / ESIZE;    // elements of K per stage
+  constexpr int ATOM_MN = SWIZZLE_BYTES / ESIZE;    // MN elements per swizzle row (MN-major)
+  constexpr uint32_t TMEM_COLS = 2 * BLOCK_N;       // double-buffered fp32 accumulator
+  static_assert(TMEM_COLS == 64 || TMEM_COLS == 128 || TMEM_COLS == 256 || TMEM_COLS == 512, "");
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t *smem = reinterpret_cast<uint8_t *>(
+      (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+  uint64_t *full_bar = reinterpret_cast<uint64_t *>(smem + Plan::BAR_OFFSET);
+  uint64_t *empty_bar = full_bar + STAGES;
+  uint64_t *tmem_full = empty_bar + STAGES;
+  uint64_t *tmem_empty = tmem_full + 2;
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tmem_empty + 2);
+
+  int const warp = threadIdx.x >> 5;
+  int const lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    ptx::prefetch_tensormap(&map_a);
+    ptx::prefetch_tensormap(&map_b);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      ptx::mbar_init(&full_bar[s], 1);
+      ptx::mbar_init(&empty_bar[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      ptx::mbar_init(&tmem_full[s], 1);
+      ptx::mbar_init(&tmem_empty[s], 4);  // one arrive per epilogue warp
+    }
+    ptx::fence_mbar_init();
+  }
+  if (warp == 2) {
+    ptx::tmem_alloc(tmem_slot, TMEM_COLS);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  uint32_t const tmem_base = *tmem_slot;
+
+  int const num_m = (M + BLOCK_M - 1) / BLOCK_M;
+  int const num_n = (N + BLOCK_N - 1) / BLOCK_N;
+  int const num_tiles = num_m * num_n * batch;
+  int const num_k = (K + BLOCK_K - 1) / BLOCK_K;
+
+  if (warp == 0 && lane == 0) {
+    // ------------------------------------------------------------ TMA producer
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      TileCoord tc = decode_tile(tile, num_m, num_n, BLOCK_N);
+      for (int kb = 0; kb < num_k; ++kb) {
+        ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+        uint8_t *sa = smem + stage * Plan::STAGE_BYTES;
+        uint8_t *sb = sa + Plan::A_BYTES;
+        ptx::mbar_arrive_expect_tx(&full_bar[stage], Plan::STAGE_BYTES);
+        int const k_idx = kb * BLOCK_K;
+        if constexpr (!A_MN) {
+          ptx::tma_load_3d(sa, &map_a, &full_bar[stage], k_idx, tc.m_idx, tc.b);
+        } else {
+#pragma unroll
+          for (int j = 0; j < BLOCK_M / ATOM_MN; ++j)
+            ptx::tma_load_3d(sa + j * BLOCK_K * SWIZZLE_BYTES, &map_a, &full_bar[stage],
+                             tc.m_idx + j * ATOM_MN, k_idx, tc.b);
+        }
+        if constexpr (!B_MN) {
+          ptx::tma_load_3d(sb, &map_b, &full_bar[stage], k_idx, tc.n_idx, tc.b);
+        } else {
+#pragma unroll
+          for (int j = 0; j < BLOCK_N / ATOM_MN; ++j)
+            ptx::tma_load_3d(sb + j * BLOCK_K * SWIZZLE_BYTES, &map_b, &full_bar[stage],
+                             tc.n_idx + j * ATOM_MN, k_idx, tc.b);
+        }
+        if (++stage == STAGES) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+    }
+  } else if (warp == 1 && lane == 0) {
+    // ------------------------------------------------------------ MMA issuer
+    // K-major operand: rows of 128 B, 8-row groups 1024 B apart; a k-step moves 32 B.
+    // MN-major operand: 128-B rows hold 128/ESIZE consecutive MN indices of one k;
+    //   8-k groups 1024 B apart (SBO), next MN atom BLOCK_K*128 B further (LBO);
+    //   a k-step moves (32/ESIZE) rows = (32/ESIZE)*128 B.
+    constexpr uint32_t A_LBO = A_MN ? BLOCK_K * SWIZZLE_BYTES : 0;
+    constexpr uint32_t B_LBO = B_MN ? BLOCK_K * SWIZZLE_BYTES : 0;
+    constexpr uint32_t A_KSTEP = A_MN ? (MMA_K_BYTES / ESIZE) * SWIZZLE_BYTES : MMA_K_BYTES;
+    constexpr uint32_t B_KSTEP = B_MN ? (MMA_K_BYTES / ESIZE) * SWIZZLE_BYTES : MMA_K_BYTES;
+    int stage = 0;
+    uint32_t phase = 0;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      ptx::mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+      ptx::tc_fence_after();
+      uint32_t const d_tmem = tmem_base + acc * BLOCK_N;
+      for (int kb = 0; kb < num_k; ++kb) {
+        ptx::mbar_wait(&full_bar[stage], phase);
+        ptx::tc_fence_after();
+        uint32_t const sa = ptx::smem_u32(smem + stage * Plan::STAGE_BYTES);
+        uint32_t const sb = sa + Plan::A_BYTES;
+#pragma unroll
+        for (int k = 0; k < K_STEPS; ++k) {
+          uint64_t da = ptx::make_smem_desc_sw128(sa + k * A_KSTEP, A_LBO, 1024);
+          uint64_t db = ptx::make_smem_desc_sw128(sb + k * B_KSTEP, B_LBO, 1024);
+          if constexpr (ESIZE == 2)
+            ptx::mma_f16_ss(d_tmem, da, db, idesc, (kb | k) != 0);
+          else
+            ptx::mma_tf32_ss(d_tmem, da, db, idesc, (kb | k) != 0);
+        }
+        ptx::mma_commit(&empty_bar[stage]);  // frees the smem slot when these MMAs retire
+        if (kb == num_k - 1) ptx::mma_commit(&tmem_full[acc]);
+        if (++stage == STAGES) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+      if (++acc == 2) {
+        acc = 0;
+        acc_phase ^= 1;
+      }
+    }
+  } else if (warp >= 2) {
+    // ------------------------------------------------------------ epilogue
+    int const q = warp & 3;  // TMEM lane quadrant this warp may read
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      TileCoord tc = decode_tile(tile, num_m, num_n, BLOCK_N);
+      ptx::mbar_wait(&tmem_full[acc], acc_phase);
+      ptx::tc_fence_after();
+      int const row = tc.m_idx + q * 32 + lane;
+      long long const row_off =
+          static_cast<long long>(tc.b) * ep.d_batch + static_cast<long long>(row) * ep.ldd;
+#pragma unroll 1
+      for (int c = 0; c < BLOCK_N / 32; ++c) {
+        uint32_t r[32];
+        ptx::tmem_ld_32x32(tmem_base + (uint32_t(q * 32) << 16) + acc * BLOCK_N + c * 32, r);
+        ptx::tmem_ld_wait();
+        if (c == BLOCK_N / 32 - 1) {
+          // accumulator fully in registers: hand the TMEM buffer back to the MMA warp
+          ptx::tc_fence_before();
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive(&tmem_empty[acc]);
+        }
+        int const col0 = tc.n_idx + c * 32;
+        int const valid = min(32, N - col0);
+        if (row < M && valid > 0) {
+          switch (out_dtype) {
+            case FFK_FLOAT: epilogue_row_chunk<float>(r, ep, row_off, col0, valid, vec_ok); break;
+            case FFK_BFLOAT16:
+              epilogue_row_chunk<__nv_bfloat16>(r, ep, row_off, col0, valid, vec_ok);
+              break;
+            default: epilogue_row_chunk<__half>(r, ep, row_off, col0, valid, vec_ok); break;
+          }
+        }
+      }
+      if (++acc == 2) {
+        acc = 0;
+        acc_phase ^= 1;
+      }
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
+// ------------------------------------------------------------------ host side
+PFN_cuTensorMapEncodeTiled_v12000 encode_fn() {
+  static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void *p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) ==
+            cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(p);
+  });
+  return fn;
+}
+
+// Stored matrix [batch][rows][inner], `ld` elements between rows.
+int make_map(CUtensorMap *out, void const *base, int dtype, uint64_t inner, uint64_t rows,
+             uint64_t batch, uint64_t ld, uint64_t batch_stride, uint32_t box_inner,
+             uint32_t box_rows) {
+  auto fn = encode_fn();
+  if (!fn) {
+    set_error("cuTensorMapEncodeTiled is not available from the driver");
+    return FFK_ERR_CUDA;
+  }
+  size_t es = dtype_size(dtype);
+  CUtensorMapDataType dt = dtype == FFK_BFLOAT16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16
+                           : dtype == FFK_HALF   ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16
+                                                 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
+  if (batch_stride == 0 || batch == 1) batch_stride = rows * ld;
+  cuuint64_t dims[3] = {inner, rows, batch};
+  cuuint64_t strides[2] = {ld * es, batch_stride * es};
+  cuuint32_t box[3] = {box_inner, box_rows, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = fn(out, dt, 3, const_cast<void *>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled failed (%d): inner=%llu rows=%llu batch=%llu ld=%llu",
+              (int)r, (unsigned long long)inner, (unsigned long long)rows,
+              (unsigned long long)batch, (unsigned long long)ld);
+    return FFK_ERR_CUDA;
+  }
+  return FFK_OK;
+}
+
+template <int ESIZE, bool A_MN, bool B_MN, int BLOCK_N, int STAGES>
+int launch_tc_inst(Problem const &p, Epilogue const &e, cudaStream_t stream) {
+  using Plan = SmemPlan<BLOCK_N, STAGES>;
+  constexpr int BLOCK_K = SWIZZLE_BYTES / ESIZE;
+  constexpr int ATOM = SWIZZLE_BYTES / ESIZE;
+  CUtensorMap ma, mb;
+  int rc;
+  if (!A_MN)
+    rc = make_map(&ma, p.a, p.in_dtype, p.K, p.M, p.batch, p.lda, p.a_batch, BLOCK_K, BLOCK_M);
+  else
+    rc = make_map(&ma, p.a, p.in_dtype, p.M, p.K, p.batch, p.lda, p.a_batch, ATOM, BLOCK_K);
+  if (rc) return rc;
+  if (!B_MN)
+    rc = make_map(&mb, p.b, p.in_dtype, p.K, p.N, p.batch, p.ldb, p.b_batch, BLOCK_K, BLOCK_N);
+  else
+    rc = make_map(&mb, p.b, p.in_dtype, p.N, p.K, p.batch, p.ldb, p.b_batch, ATOM, BLOCK_K);
+  if (rc) return rc;
+
+  auto kern = gemm_tc_kernel<ESIZE, A_MN, B_MN, BLOCK_N, STAGES>;
+  FFK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Plan::TOTAL));
+  uint32_t fmt = p.in_dtype == FFK_BFLOAT16 ? ptx::kFmtBF16
+                 : p.in_dtype == FFK_HALF   ? ptx::kFmtF16
+                                            : ptx::kFmtTF32;
+  uint32_t idesc = ptx::make_idesc(fmt, A_MN, B_MN, BLOCK_M, BLOCK_N);
+  int num_m = (p.M + BLOCK_M - 1) / BLOCK_M, num_n = (p.N + BLOCK_N - 1) / BLOCK_N;
+  long long tiles = 1LL * num_m * num_n * p.batch;
+  int grid = (int)std::min<long long>(tiles, device_info().sm_count);
+  size_t os = dtype_size(p.out_dtype);
+  int vec_ok = aligned16(e.d) && ((e.ldd * os) % 16 == 0) && ((e.d_batch * os) % 16 == 0) &&
+               (e.r == nullptr || aligned16(e.r));
+  kern<<<grid, NUM_THREADS, Plan::TOTAL, stream>>>(ma, mb, e, p.M, p.N, p.K, p.batch, idesc,
+                                                   p.out_dtype, vec_ok);
+  FFK_LAUNCH_CHECK();
+  return FFK_OK;
+}
+
+template <int ESIZE, int BLOCK_N, int STAGES>
+int launch_tc_layout(Problem const &p, Epilogue const &e, cudaStream_t s) {
+  if (!p.a_mn_major && !p.b_mn_major) return launch_tc_inst<ESIZE, false, false, BLOCK_N, STAGES>(p, e, s);
+  if constexpr (ESIZE == 4) return FFK_ERR_UNSUPPORTED;
+  if (!p.a_mn_major && p.b_mn_major) return launch_tc_inst<ESIZE, false, true, BLOCK_N, STAGES>(p, e, s);
+  if (p.a_mn_major && !p.b_mn_major) return launch_tc_inst<ESIZE, true, false, BLOCK_N, STAGES>(p, e, s);
+  return launch_tc_inst<ESIZE, true, true, BLOCK_N, STAGES>(p, e, s);
+}
+
+}  // namespace
+
+bool tc_eligible(Problem const &p, Epilogue const &e) {
+  size_t es = dtype_size(p.in_dtype);
+  if (!(p.in_dtype == FFK_BFLOAT16 || p.in_dtype == FFK_HALF || p.in_dtype == FFK_FLOAT))
+    return false;
+  if (!(p.out_dtype == FFK_BFLOAT16 || p.out_dtype == FFK_HALF || p.out_dtype == FFK_FLOAT))
+    return false;
+  if (p.M <= 0 || p.N <= 0 || p.K <= 0 || p.batch <= 0) return false;
+  if (!aligned16(p.a) || !aligned16(p.b)) return false;
+  if ((p.lda * es) % 16 || (p.ldb * es) % 16) return false;
+  if (p.batch > 1 && ((p.a_batch * es) % 16 || (p.b_batch * es) % 16)) return false;
+  (void)e;
+  return true;
+}
+
+int launch_tc(Problem const &p, Epilogue const &e, cudaStream_t stream) {
+  if (!tc_eligible(p, e)) {
+    set_error("gemm: operands do not satisfy TMA alignment (16-byte base and pitch)");
+    return FFK_ERR_UNSUPPORTED;
+  }
+  bool narrow = p.N <= 128;
+  if (p.in_dtype == FFK_FLOAT) {
+    if (p.a_mn_major || p.b_mn_major) {
+      // TF32 tiles are only wired for K-major operands; the fp32 products of the
+      // gradient GEMMs go through the exact CUDA-core path instead.
+      set_error("gemm: TF32 tensor path needs K-major operands");
+      return FFK_ERR_UNSUPPORTED;
+    }
+    return narrow ? launch_tc_layout<4, 128, 6>(p, e, stream)
+                  : launch_tc_layout<4, 256, 4>(p, e, stream);
+  }
+  return narrow ? launch_tc_layout<2, 128, 6>(p, e, stream)
+                : launch_tc_layout<2, 256, 4>(p, e, stream);
+}
+
+// ------------------------------------------------------------------ SIMT GEMM
+namespace {
+
+template <typename TIn, typename TOut>
+__global__ void __launch_bounds__(256)
+    gemm_simt_kernel(TIn const *__restrict__ a, TIn const *__restrict__ b, Epilogue ep, int M,
+                     int N, int K, long long sa_m, long long sa_k, long long sb_n, long long sb_k,
+                     long long a_batch, long long b_batch) {
+  constexpr int TM = 64, TN = 64, TK = 16;
+  __shared__ float As[TK][TM + 4];
+  __shared__ float Bs[TK][TN + 4];
+  int const bz = blockIdx.z;
+  a += bz * a_batch;
+  b += bz * b_batch;
+  int const m0 = blockIdx.y * TM, n0 = blockIdx.x * TN;
+  int const tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+  float acc[4][4] = {};
+  bool const a_kmajor = (sa_k == 1), b_kmajor = (sb_k == 1);
+  for (int k0 = 0; k0 < K; k0 += TK) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      int idx = threadIdx.x + i * 256;
+      int mm, kk;
+      if (a_kmajor) { mm = idx >> 4; kk = idx & 15; } else { kk = idx >> 6; mm = idx & 63; }
+      int gm = m0 + mm, gk = k0 + kk;
+      As[kk][mm] = (gm < M && gk < K) ? to_f32(a[gm * sa_m + gk * sa_k]) : 0.f;
+      int nn;
+      if (b_kmajor) { nn = idx >> 4; kk = idx & 15; } else { kk = idx >> 6; nn = idx & 63; }
+      int gn = n0 + nn;
+      gk = k0 + kk;
+      Bs[kk][nn] = (gn < N && gk < K) ? to_f32(b[gn * sb_n + gk * sb_k]) : 0.f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < TK; ++kk) {
+      float av[4], bv[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) av[i] = As[kk][ty * 4 + i];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) bv[j] = Bs[kk][tx * 4 + j];
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+  TOut *d = reinterpret_cast<TOut *>(ep.d) + bz * ep.d_batch;
+  TOut const *r = ep.r ? reinterpret_cast<TOut const *>(ep.r) + bz * ep.d_batch : nullptr;
+  TOut const *bias = reinterpret_cast<TOut const *>(ep.bias);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    int gm = m0 + ty * 4 + i;
+    if (gm >= M) continue;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      int gn = n0 + tx * 4 + j;
+      if (gn >= N) continue;
+      float v = acc[i][j] * ep.alpha;
+      if (bias) v += to_f32(bias[gn]);
+      v = apply_act(v, ep.act);
+      long long off = gm * ep.ldd + gn;
+      if (r) v += ep.lambda * to_f32(r[off]);
+      if (ep.accumulate) v += to_f32(d[off]);
+      d[off] = from_f32<TOut>(v);
+    }
+  }
+}
+
+template <typename TIn, typename TOut>
+int launch_simt_t(Problem const &p, Epilogue const &e, cudaStream_t stream) {
+  long long sa_m = p.a_mn_major ? 1 : p.lda, sa_k = p.a_mn_major ? p.lda : 1;
+  long long sb_n = p.b_mn_major ? 1 : p.ldb, sb_k = p.b_mn_major ? p.ldb : 1;
+  dim3 grid((p.N + 63) / 64, (p.M + 63) / 64, p.batch);
+  gemm_simt_kernel<TIn, TOut><<<grid, 256, 0, stream>>>(
+      reinterpret_cast<TIn const *>(p.a), reinterpret_cast<TIn const *>(p.b), e, p.M, p.N, p.K,
+      sa_m, sa_k, sb_n, sb_k, p.a_batch, p.b_batch);
+  FFK_LAUNCH_CHECK();
+  return FFK_OK;
+}
+
+}  // namespace
+
+int launch_simt(Problem const &p, Epilogue const &e, cudaStream_t stream) {
+  if (p.M <= 0 || p.N <= 0 || p.batch <= 0) return FFK_OK;
+  if (p.in_dtype == FFK_FLOAT && p.out_dtype == FFK_FLOAT) return launch_simt_t<float, float>(p, e, stream);
+  if (p.in_dtype == FFK_BFLOAT16 && p.out_dtype == FFK_BFLOAT16)
+    return launch_simt_t<__nv_bfloat16, __nv_bfloat16>(p, e, stream);
+  if (p.in_dtype == FFK_BFLOAT16 && p.out_dtype == FFK_FLOAT)
+    return launch_simt_t<__nv_bfloat16, float>(p, e, stream);
+  if (p.in_dtype == FFK_HALF && p.out_dtype == FFK_HALF) return launch_simt_t<__half, __half>(p, e, stream);
+  if (p.in_dtype == FFK_HALF && p.out_dtype == FFK_FLOAT) return launch_simt_t<__half, float>(p, e, stream);
+  set_error("gemm: unsupported dtype pair in=%d out=%d", p.in_dtype, p.out_dtype);
+  return FFK_ERR_DTYPE;
+}
+
+int launch(Problem const &p, Epilogue const &e, cudaStream_t stream) {
+  if (p.M <= 0 || p.N <= 0 || p.batch <= 0) return FFK_OK;
+  bool sixteen = p.in_dtype == FFK_BFLOAT16 || p.in_dtype == FFK_HALF;
+  if (sixteen && p.K > 0 && tc_eligible(p, e)) return launch_tc(p, e, stream);
+  return launch_simt(p, e, stream);
+}
+
+}  // namespace gemm
+}  // namespace ffk

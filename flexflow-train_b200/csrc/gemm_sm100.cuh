@@ -1,0 +1,76 @@
+// Dense contraction engine for sm_100a.
+//
+//   D[b][m][n] (+)= sum_k A(b,m,k) * B(b,n,k)   (+ bias[n]) (activation) (+ lambda * R[m][n])
+//
+// One warp-specialised persistent kernel: warp 0 drives TMA, warp 1 issues
+// tcgen05.mma into a double-buffered TMEM accumulator, warps 2..5 drain TMEM
+// with tcgen05.ld and run the fused epilogue. Operands may be K-major
+// (contraction index contiguous in memory) or MN-major (row/column index
+// contiguous), which covers forward (NT), data-gradient (NN) and
+// weight-gradient (TN) products without any transposed copies.
+//
+// This header is internal to csrc/; the C-ABI lives in include/ffk.h.
+#pragma once
+#include "common.cuh"
+#include "ptx_sm100.cuh"
+
+namespace ffk {
+namespace gemm {
+
+enum Act : int { ACT_NONE = -1, ACT_RELU = 0, ACT_SIGMOID = 1, ACT_TANH = 2, ACT_GELU = 3 };
+
+// What to do with an accumulator tile once it is in registers.
+struct Epilogue {
+  void *d;               // output, row-major [batch][M][ldd]
+  long long ldd;         // elements between rows of D
+  long long d_batch;     // elements between batches of D
+  void const *bias;      // optional, length N, same dtype as D
+  int act;               // Act
+  int accumulate;        // 1: D += result (beta = 1)
+  float alpha;           // scale on the product
+  float lambda;          // optional regulariser: D += lambda * R
+  void const *r;         // R, same layout/dtype as D (may be null)
+};
+
+// Problem in "logical" terms. a/b pointers are the stored matrices:
+//   K-major  operand: stored [batch][rows = MN][cols = K], ld = elements between rows
+//   MN-major operand: stored [batch][rows = K][cols = MN]
+struct Problem {
+  void const *a;
+  void const *b;
+  long long lda, ldb;
+  long long a_batch, b_batch;  // elements between batches
+  int M, N, K, batch;
+  int in_dtype;   // FFK_BFLOAT16 / FFK_HALF / FFK_FLOAT (tf32 on the tensor path)
+  int out_dtype;  // FFK_BFLOAT16 / FFK_HALF / FFK_FLOAT
+  bool a_mn_major, b_mn_major;
+};
+
+// Tensor-core path. Returns FFK_ERR_UNSUPPORTED (without launching) when the
+// operands break a TMA constraint (16-byte aligned base and row pitch).
+int launch_tc(Problem const &p, Epilogue const &e, cudaStream_t stream);
+bool tc_eligible(Problem const &p, Epilogue const &e);
+
+// CUDA-core path: any pitch, fp32 accumulate in strict k order per tile. This
+// is the fp32-exact path used for FLOAT tensors and the ragged fallback.
+int launch_simt(Problem const &p, Epilogue const &e, cudaStream_t stream);
+
+// Picks the tensor path for 16-bit inputs when eligible, else SIMT.
+int launch(Problem const &p, Epilogue const &e, cudaStream_t stream);
+
+__device__ __forceinline__ float apply_act(float v, int act) {
+  switch (act) {
+    case ACT_RELU: return fmaxf(v, 0.f);
+    case ACT_SIGMOID: return 1.f / (1.f + __expf(-v));
+    case ACT_TANH: return tanhf(v);
+    case ACT_GELU: {
+      // tanh form, as the reference's Linear uses (cuda_helper.cu:111-120)
+      constexpr float B = 0.7978845608028654f, C = 0.035677408136300125f;
+      return v * (0.5f + 0.5f * tanhf(v * (C * v * v + B)));
+    }
+    default: return v;
+  }
+}
+
+}  // namespace gemm
+}  // namespace ffk

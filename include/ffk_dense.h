@@ -1,0 +1,69 @@
+/* ffk_dense.h — tensor-core bound entry points: Linear, BatchMatmul and the GEMM they share.
+ * Included by ffk.h. */
+#ifndef FFK_DENSE_H_
+#define FFK_DENSE_H_
+#include "ffk.h"
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Which contraction engine a call uses. AUTO = tcgen05/TMEM/TMA tiles for 16-bit inputs
+ * whose pitches are 16-byte aligned, CUDA-core fp32 (exact fp32 products, fp32
+ * accumulation) otherwise. TENSOR on FLOAT inputs runs them as TF32 (10-bit mantissa). */
+typedef enum { FFK_GEMM_AUTO = 0, FFK_GEMM_TENSOR = 1, FFK_GEMM_SIMT = 2 } ffk_gemm_path_t;
+
+/* General strided-batched product, the building block under Linear / BatchMatmul / MHA:
+ *   D[b][m][n] = alpha * sum_k A(b,m,k) * B(b,n,k)  (+ bias[n]) (act)  (+ D if accumulate)
+ * A is stored [batch][M][lda>=K] when a_mn_major == 0 (k contiguous) or [batch][K][lda>=M]
+ * when a_mn_major == 1 (m contiguous); likewise B with N. D is [batch][M][ldd>=N].
+ * Replaces the cublasGemmEx / cublasSgemmStridedBatched calls at
+ * src/cuda/ops/linear_kernels.cu:131,231,303 and src/cuda/ops/batch_matmul_kernels.cu:66,105,123. */
+int ffk_gemm(void *stream, void const *a, void const *b, void *d, int M, int N, int K, int batch,
+             long long lda, long long ldb, long long ldd, long long a_batch_stride,
+             long long b_batch_stride, long long d_batch_stride, int in_dtype, int out_dtype,
+             int a_mn_major, int b_mn_major, float alpha, int accumulate, void const *bias,
+             int activation, int path);
+
+/* Kernels::Linear::forward_kernel — include/kernels/linear_kernels.h:52,
+ * src/cuda/ops/linear_kernels.cu:109-190.
+ *   Y[b][o] = act( sum_i X[b][i] * W[o][i] + bias[o] ),  W stored [out_dim][in_dim].
+ * bias may be NULL. GELU is the tanh form the reference's Linear uses. Accumulation is fp32
+ * (the reference asks cuBLAS for COMPUTE_16F; see DESIGN.md "deviations"). */
+int ffk_linear_forward(void *stream, void const *input, void *output, void const *weight,
+                       void const *bias, int in_dim, int out_dim, int batch_size, int dtype,
+                       int activation, int path);
+
+/* Kernels::Linear::backward_kernel — include/kernels/linear_kernels.h:62,
+ * src/cuda/ops/linear_kernels.cu:192-323. In this order, as the reference does:
+ *   dY <- dY (.) act'(Y) in place (RELU, SIGMOID as the reference; TANH and tanh-GELU added);
+ *   dW[o][i] += sum_b dY[b][o] X[b][i]  (+ l2_lambda * W[o][i] when l2_lambda != 0);
+ *   db[o]   += sum_b dY[b][o]           (bias_grad may be NULL);
+ *   dX[b][i] += sum_o dY[b][o] W[o][i]  (input_grad may be NULL).
+ * The activation gradient is evaluated from the post-activation `output` (Y) for
+ * RELU / SIGMOID / TANH. GELU needs the pre-activation values: pass them in `preact`
+ * (same shape as Y); with preact == NULL a GELU request fails with FFK_ERR_UNSUPPORTED
+ * (the reference asserts for anything but RELU / SIGMOID). */
+int ffk_linear_backward(void *stream, void const *input, void *input_grad, void const *output,
+                        void *output_grad, void const *weight, void *weight_grad,
+                        void *bias_grad, int in_dim, int out_dim, int batch_size, int dtype,
+                        int activation, float l2_lambda, void const *preact, int path);
+
+/* Kernels::BatchMatmul::forward_kernel — include/kernels/batch_matmul_kernels.h:12,
+ * src/cuda/ops/batch_matmul_kernels.cu:23-84 (argument order of the DEFINITION).
+ *   O[b] (n x m) = A[b] (n x k) * B[b] (k x m), all row-major; a/b_seq_length_dim and
+ *   seq_length truncate k / n / m exactly as the reference does (negative = off). */
+int ffk_batch_matmul_forward(void *stream, void *output, void const *a_input, void const *b_input,
+                             int m, int n, int k, int batch, int a_seq_length_dim,
+                             int b_seq_length_dim, int seq_length, int dtype, int path);
+
+/* Kernels::BatchMatmul::backward_kernel — include/kernels/batch_matmul_kernels.h:25,
+ * src/cuda/ops/batch_matmul_kernels.cu:86-141.
+ *   dA[b] += dO[b] * B[b]^T ;  dB[b] += A[b]^T * dO[b]. `o` is unused, as in the reference. */
+int ffk_batch_matmul_backward(void *stream, void const *o, void const *o_grad, void const *a,
+                              void *a_grad, void const *b, void *b_grad, int m, int n, int k,
+                              int batch, int dtype, int path);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

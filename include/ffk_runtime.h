@@ -1,0 +1,11 @@
+#ifndef FFK_RUNTIME_H_
+#define FFK_RUNTIME_H_
+#include "ffk.h"
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#ifdef __cplusplus
+}
+#endif
+#endif

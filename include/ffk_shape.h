@@ -1,0 +1,11 @@
+#ifndef FFK_SHAPE_H_
+#define FFK_SHAPE_H_
+#include "ffk.h"
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#ifdef __cplusplus
+}
+#endif
+#endif

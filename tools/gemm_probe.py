@@ -1,0 +1,78 @@
+"""Developer probe: checks the tcgen05 GEMM against torch on every operand layout and
+times the headline shapes. Not part of the test-suite (tests/ compares with the oracle)."""
+import sys, time
+from pathlib import Path
+sys.path.insert(0, str(Path(__file__).resolve().parents[1]))
+import torch
+import ffk_import
+ffk = ffk_import.load()
+L = ffk.lib()
+DT = {torch.float32: 4, torch.bfloat16: 6, torch.float16: 3}
+
+def gemm(a, b, M, N, K, batch, a_mn, b_mn, out_dtype, path, accumulate=False, bias=None, act=-1, d=None):
+    if d is None:
+        d = torch.zeros(batch, M, N, dtype=out_dtype, device="cuda")
+    lda = a.shape[-1]; ldb = b.shape[-1]
+    L.call("ffk_gemm", 0, a.data_ptr(), b.data_ptr(), d.data_ptr(), M, N, K, batch, lda, ldb, N,
+           a.shape[-2] * lda, b.shape[-2] * ldb, M * N, DT[a.dtype], DT[out_dtype], int(a_mn), int(b_mn),
+           1.0, int(accumulate), bias.data_ptr() if bias is not None else None, act, path)
+    return d
+
+def check(M, N, K, batch, a_mn, b_mn, dt, path=1):
+    g = torch.Generator(device="cuda").manual_seed(M * 7 + N * 3 + K)
+    A = (torch.rand(batch, M, K, device="cuda", generator=g) * 2 - 1).to(dt)
+    B = (torch.rand(batch, N, K, device="cuda", generator=g) * 2 - 1).to(dt)
+    a = A.transpose(1, 2).contiguous() if a_mn else A
+    b = B.transpose(1, 2).contiguous() if b_mn else B
+    out_dt = torch.float32
+    d = gemm(a, b, M, N, K, batch, a_mn, b_mn, out_dt, path)
+    torch.cuda.synchronize()
+    ref = torch.matmul(A.double(), B.double().transpose(1, 2))
+    err = (d.double() - ref).abs().max().item()
+    scale = ref.abs().max().item()
+    tol = (2e-2 if dt == torch.float32 and path == 1 else 1e-3) * max(scale, 1.0)
+    ok = err <= tol
+    print(f"{'OK ' if ok else 'BAD'} M={M} N={N} K={K} b={batch} a_mn={int(a_mn)} b_mn={int(b_mn)} {dt} path={path} err={err:.3e} scale={scale:.2e}", flush=True)
+    return ok
+
+def bench(M, N, K, a_mn, b_mn, dt=torch.bfloat16, iters=20):
+    A = (torch.rand(1, K if a_mn else M, M if a_mn else K, device="cuda") - 0.5).to(dt)
+    B = (torch.rand(1, K if b_mn else N, N if b_mn else K, device="cuda") - 0.5).to(dt)
+    d = torch.zeros(1, M, N, dtype=dt, device="cuda")
+    for _ in range(3):
+        gemm(A, B, M, N, K, 1, a_mn, b_mn, dt, 1, d=d)
+    e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize(); e0.record()
+    for _ in range(iters):
+        gemm(A, B, M, N, K, 1, a_mn, b_mn, dt, 1, d=d)
+    e1.record(); torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / iters
+    print(f"bench M={M} N={N} K={K} a_mn={int(a_mn)} b_mn={int(b_mn)} {dt}: {ms*1e3:.1f} us  {2*M*N*K/ms/1e9:.1f} TFLOP/s", flush=True)
+    # torch/cuBLAS for context
+    At = A[0].t() if a_mn else A[0]; Bt = B[0].t() if b_mn else B[0]
+    for _ in range(3): torch.matmul(At, Bt.t())
+    torch.cuda.synchronize(); e0.record()
+    for _ in range(iters): torch.matmul(At, Bt.t())
+    e1.record(); torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / iters
+    print(f"   cuBLAS same shape: {ms*1e3:.1f} us  {2*M*N*K/ms/1e9:.1f} TFLOP/s", flush=True)
+
+if __name__ == "__main__":
+    ok = True
+    for dt in (torch.bfloat16, torch.float16, torch.float32):
+        for a_mn in (False, True):
+            for b_mn in (False, True):
+                if dt == torch.float32 and (a_mn or b_mn):
+                    continue  # TF32 tiles are K-major only
+                ok &= check(128, 256, 64, 1, a_mn, b_mn, dt)
+                ok &= check(256, 512, 256, 1, a_mn, b_mn, dt)
+                ok &= check(200, 136, 104, 3, a_mn, b_mn, dt)
+                ok &= check(1024, 1024, 1024, 1, a_mn, b_mn, dt)
+    ok &= check(100, 10, 784, 1, False, False, torch.float32, path=2)
+    ok &= check(64, 512, 10, 1, False, True, torch.float32, path=2)
+    ok &= check(77, 33, 19, 2, True, True, torch.bfloat16, path=2)
+    print("ALL OK" if ok else "SOME BAD")
+    if ok:
+        bench(8192, 4096, 4096, False, False)
+        bench(8192, 4096, 4096, False, True)
+        bench(4096, 4096, 8192, True, True)
