@@ -32,7 +32,7 @@ _CTYPES = {
 }
 
 _PROTO_RE = re.compile(
-    r"^\s*(int|char const \*|void)\s*(ffk_[a-z0-9_]+)\s*\(([^;{]*?)\)\s*;", re.M | re.S
+    r"^\s*(int|size_t|char const \*|void)\s*(ffk_[a-z0-9_]+)\s*\(([^;{]*?)\)\s*;", re.M | re.S
 )
 
 
@@ -63,7 +63,9 @@ def parse_headers(include_dir: Path = INCLUDE_DIR):
         for m in _PROTO_RE.finditer(text):
             ret, name, args = m.group(1), m.group(2), m.group(3)
             argtypes = [t for t in (_arg_ctype(a) for a in args.split(",")) if t is not None]
-            restype = {"int": ctypes.c_int, "void": None}.get(ret, ctypes.c_char_p)
+            restype = {"int": ctypes.c_int, "size_t": ctypes.c_size_t, "void": None}.get(
+                ret, ctypes.c_char_p
+            )
             protos[name] = (restype, argtypes)
     return protos
 

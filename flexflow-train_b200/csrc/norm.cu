@@ -1,0 +1,689 @@
+// Softmax, LayerNorm and BatchNorm for sm_100a. Rows are read ONCE into registers as
+// 16-byte packets (up to 8 packets per thread), reduced with warp shuffles and written
+// back; rows that do not fit or are not 16-byte aligned take a generic looped kernel.
+#include "common.cuh"
+
+namespace ffk {
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kMaxP = 8;  // packets per thread held in registers
+
+__device__ __forceinline__ void block_sum2(float &a, float &b, float *red /* >= 64 floats */) {
+  int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  a = warp_sum(a);
+  b = warp_sum(b);
+  __syncthreads();
+  if (lane == 0) {
+    red[w] = a;
+    red[32 + w] = b;
+  }
+  __syncthreads();
+  int nw = (blockDim.x + 31) >> 5;
+  float ra = (lane < nw) ? red[lane] : 0.f, rb = (lane < nw) ? red[32 + lane] : 0.f;
+  a = warp_sum(ra);
+  b = warp_sum(rb);
+}
+
+inline int pick_p(long long nvec) {
+  long long need = (nvec + kThreads - 1) / kThreads;
+  if (need <= 1) return 1;
+  if (need <= 2) return 2;
+  if (need <= 4) return 4;
+  if (need <= 8) return 8;
+  return 0;
+}
+
+#define FFK_DISPATCH_P(p, P, ...)                                              \
+  switch (p) {                                                                 \
+    case 1: { constexpr int P = 1; __VA_ARGS__; break; }                       \
+    case 2: { constexpr int P = 2; __VA_ARGS__; break; }                       \
+    case 4: { constexpr int P = 4; __VA_ARGS__; break; }                       \
+    default: { constexpr int P = 8; __VA_ARGS__; break; }                      \
+  }
+
+// ================================================================== softmax
+template <typename T, int P>
+__global__ void __launch_bounds__(kThreads)
+    softmax_rows_kernel(T const *__restrict__ x, T *__restrict__ y, long long rows, int nvec) {
+  constexpr int VN = Vec16<T>::N;
+  __shared__ float red[32];
+  for (long long r = blockIdx.x; r < rows; r += gridDim.x) {
+    T const *xr = x + r * (long long)nvec * VN;
+    T *yr = y + r * (long long)nvec * VN;
+    float v[P][VN];
+    float mx = -INFINITY;
+#pragma unroll
+    for (int p = 0; p < P; ++p) {
+      int i = threadIdx.x + p * kThreads;
+      if (i < nvec) {
+        Vec16<T> t = ld_stream(xr + i * VN);
+#pragma unroll
+        for (int j = 0; j < VN; ++j) {
+          v[p][j] = to_f32(t.v[j]);
+          mx = fmaxf(mx, v[p][j]);
+        }
+      }
+    }
+    mx = block_max(mx, red);
+    float sum = 0.f;
+#pragma unroll
+    for (int p = 0; p < P; ++p) {
+      int i = threadIdx.x + p * kThreads;
+      if (i < nvec) {
+#pragma unroll
+        for (int j = 0; j < VN; ++j) {
+          v[p][j] = __expf(v[p][j] - mx);
+          sum += v[p][j];
+        }
+      }
+    }
+    sum = block_sum(sum, red);
+    float inv = 1.f / sum;
+#pragma unroll
+    for (int p = 0; p < P; ++p) {
+      int i = threadIdx.x + p * kThreads;
+      if (i < nvec) {
+        Vec16<T> o;
+#pragma unroll
+        for (int j = 0; j < VN; ++j) o.v[j] = from_f32<T>(v[p][j] * inv);
+        st_stream(yr + i * VN, o);
+      }
+    }
+  }
+}
+
+// Generic: one warp per (outer, inner) line, element stride `inner`.
+template <typename T>
+__global__ void __launch_bounds__(kThreads)
+    softmax_lines_kernel(T const *__restrict__ x, T *__restrict__ y, long long outer,
+                         long long dim, long long inner) {
+  long long const lines = outer * inner;
+  int const lane = threadIdx.x & 31;
+  long long const warp0 = (long long)blockIdx.x * (kThreads / 32) + (threadIdx.x >> 5);
+  long long const wstride = (long long)gridDim.x * (kThreads / 32);
+  for (long long l = warp0; l < lines; l += wstride) {
+    long long o = l / inner, in = l - o * inner;
+    T const *xl = x + o * dim * inner + in;
+    T *yl = y + o * dim * inner + in;
+    float mx = -INFINITY;
+    for (long long k = lane; k < dim; k += 32) mx = fmaxf(mx, to_f32(xl[k * inner]));
+    mx = warp_max(mx);
+    float sum = 0.f;
+    for (long long k = lane; k < dim; k += 32) sum += __expf(to_f32(xl[k * inner]) - mx);
+    sum = warp_sum(sum);
+    float inv = 1.f / sum;
+    for (long long k = lane; k < dim; k += 32)
+      yl[k * inner] = from_f32<T>(__expf(to_f32(xl[k * inner]) - mx) * inv);
+  }
+}
+
+// Strided case with a wide inner extent: one thread per (outer, inner) line so that
+// consecutive threads touch consecutive addresses.
+template <typename T>
+__global__ void __launch_bounds__(kThreads)
+    softmax_strided_kernel(T const *__restrict__ x, T *__restrict__ y, long long outer,
+                           long long dim, long long inner) {
+  long long const lines = outer * inner;
+  long long const stride = (long long)gridDim.x * blockDim.x;
+  for (long long l = (long long)blockIdx.x * blockDim.x + threadIdx.x; l < lines; l += stride) {
+    long long o = l / inner, in = l - o * inner;
+    T const *xl = x + o * dim * inner + in;
+    T *yl = y + o * dim * inner + in;
+    float mx = -INFINITY;
+    for (long long k = 0; k < dim; ++k) mx = fmaxf(mx, to_f32(xl[k * inner]));
+    float sum = 0.f;
+    for (long long k = 0; k < dim; ++k) sum += __expf(to_f32(xl[k * inner]) - mx);
+    float inv = 1.f / sum;
+    for (long long k = 0; k < dim; ++k)
+      yl[k * inner] = from_f32<T>(__expf(to_f32(xl[k * inner]) - mx) * inv);
+  }
+}
+
+// dx = y * (dy - sum(dy*y)) along dim; one warp per line (generic strides).
+template <typename T>
+__global__ void __launch_bounds__(kThreads)
+    softmax_jacobian_kernel(T *__restrict__ dx, T const *__restrict__ dy, T const *__restrict__ y,
+                            long long outer, long long dim, long long inner) {
+  long long const lines = outer * inner;
+  int const lane = threadIdx.x & 31;
+  long long const warp0 = (long long)blockIdx.x * (kThreads / 32) + (threadIdx.x >> 5);
+  long long const wstride = (long long)gridDim.x * (kThreads / 32);
+  for (long long l = warp0; l < lines; l += wstride) {
+    long long o = l / inner, in = l - o * inner;
+    long long base = o * dim * inner + in;
+    float dot = 0.f;
+    for (long long k = lane; k < dim; k += 32)
+      dot += to_f32(dy[base + k * inner]) * to_f32(y[base + k * inner]);
+    dot = warp_sum(dot);
+    for (long long k = lane; k < dim; k += 32) {
+      long long i = base + k * inner;
+      dx[i] = from_f32<T>(to_f32(y[i]) * (to_f32(dy[i]) - dot));
+    }
+  }
+}
+
+// ================================================================== layer norm
+template <typename T, int P>
+__global__ void __launch_bounds__(kThreads)
+    layer_norm_fwd_rows_kernel(T const *__restrict__ x, T *__restrict__ y,
+                               T const *__restrict__ gamma, T const *__restrict__ beta,
+                               float *__restrict__ mean, float *__restrict__ rstd, long long rows,
+                               int nvec, float eps) {
+  constexpr int VN = Vec16<T>::N;
+  __shared__ float red[64];
+  float const invn = 1.f / float(nvec * VN);
+  for (long long r = blockIdx.x; r < rows; r += gridDim.x) {
+    T const *xr = x + r * (long long)nvec * VN;
+    T *yr = y + r * (long long)nvec * VN;
+    float v[P][VN];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int p = 0; p < P; ++p) {
+      int i = threadIdx.x + p * kThreads;
+      if (i < nvec) {
+        Vec16<T> t = ld_stream(xr + i * VN);
+#pragma unroll
+        for (int j = 0; j < VN; ++j) {
+          v[p][j] = to_f32(t.v[j]);
+          s1 += v[p][j];
+          s2 += v[p][j] * v[p][j];
+        }
+      }
+    }
+    block_sum2(s1, s2, red);
+    float mu = s1 * invn;
+    float var = fmaxf(s2 * invn - mu * mu, 0.f);
+    float rs = rsqrtf(var + eps);
+    if (threadIdx.x == 0) {
+      mean[r] = mu;
+      rstd[r] = rs;
+    }
+#pragma unroll
+    for (int p = 0; p < P; ++p) {
+      int i = threadIdx.x + p * kThreads;
+      if (i < nvec) {
+        Vec16<T> o, g, b;
+        if (gamma) g = ld_vec(gamma + i * VN);
+        if (beta) b = ld_vec(beta + i * VN);
+#pragma unroll
+        for (int j = 0; j < VN; ++j) {
+          float t = (v[p][j] - mu) * rs;
+          if (gamma) t *= to_f32(g.v[j]);
+          if (beta) t += to_f32(b.v[j]);
+          o.v[j] = from_f32<T>(t);
+        }
+        st_stream(yr + i * VN, o);
+      }
+    }
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kThreads)
+    layer_norm_fwd_generic_kernel(T const *__restrict__ x, T *__restrict__ y,
+                                  T const *__restrict__ gamma, T const *__restrict__ beta,
+                                  float *__restrict__ mean, float *__restrict__ rstd,
+                                  long long rows, long long N, float eps) {
+  __shared__ float red[64];
+  for (long long r = blockIdx.x; r < rows; r += gridDim.x) {
+    T const *xr = x + r * N;
+    T *yr = y + r * N;
+    float s1 = 0.f, s2 = 0.f;
+    for (long long j = threadIdx.x; j < N; j += blockDim.x) {
+      float t = to_f32(xr[j]);
+      s1 += t;
+      s2 += t * t;
+    }
+    block_sum2(s1, s2, red);
+    float mu = s1 / float(N);
+    float var = fmaxf(s2 / float(N) - mu * mu, 0.f);
+    float rs = rsqrtf(var + eps);
+    if (threadIdx.x == 0) {
+      mean[r] = mu;
+      rstd[r] = rs;
+    }
+    for (long long j = threadIdx.x; j < N; j += blockDim.x) {
+      float t = (to_f32(xr[j]) - mu) * rs;
+      if (gamma) t *= to_f32(gamma[j]);
+      if (beta) t += to_f32(beta[j]);
+      yr[j] = from_f32<T>(t);
+    }
+  }
+}
+
+// Fused backward: one pass over dY and X gives dX (accumulated) and, when `part` is
+// non-null, this CTA's partial column sums for dgamma / dbeta:
+//   part[(blockIdx.x*2 + 0)*N + j] = sum over this CTA's rows of dy*(x-mean)*rstd
+//   part[(blockIdx.x*2 + 1)*N + j] = sum over this CTA's rows of dy
+template <typename T, int P>
+__global__ void __launch_bounds__(kThreads, 2)
+    layer_norm_bwd_rows_kernel(T const *__restrict__ dy, T const *__restrict__ x,
+                               T *__restrict__ dx, T const *__restrict__ gamma,
+                               float const *__restrict__ mean, float const *__restrict__ rstd,
+                               float *__restrict__ part, long long rows, int nvec) {
+  constexpr int VN = Vec16<T>::N;
+  __shared__ float red[64];
+  long long const N = (long long)nvec * VN;
+  float const invn = 1.f / float(N);
+  float g[P][VN], pg[P][VN], pb[P][VN];
+#pragma unroll
+  for (int p = 0; p < P; ++p) {
+    int i = threadIdx.x + p * kThreads;
+#pragma unroll
+    for (int j = 0; j < VN; ++j) {
+      g[p][j] = 1.f;
+      pg[p][j] = 0.f;
+      pb[p][j] = 0.f;
+    }
+    if (gamma && i < nvec) {
+      Vec16<T> t = ld_vec(gamma + i * VN);
+#pragma unroll
+      for (int j = 0; j < VN; ++j) g[p][j] = to_f32(t.v[j]);
+    }
+  }
+  for (long long r = blockIdx.x; r < rows; r += gridDim.x) {
+    T const *dyr = dy + r * N;
+    T const *xr = x + r * N;
+    float dv[P][VN], xv[P][VN];
+    float ds = 0.f, db = 0.f;
+#pragma unroll
+    for (int p = 0; p < P; ++p) {
+      int i = threadIdx.x + p * kThreads;
+      if (i < nvec) {
+        Vec16<T> a = ld_stream(dyr + i * VN), b = ld_stream(xr + i * VN);
+#pragma unroll
+        for (int j = 0; j < VN; ++j) {
+          dv[p][j] = to_f32(a.v[j]);
+          xv[p][j] = to_f32(b.v[j]);
+          ds += dv[p][j] * xv[p][j] * g[p][j];
+          db += dv[p][j] * g[p][j];
+        }
+      }
+    }
+    block_sum2(ds, db, red);
+    float const mu = mean[r], rs = rstd[r];
+    float const c1 = (db * mu - ds) * rs * rs * rs * invn;
+    float const c2 = -(c1 * mu + db * rs * invn);
+#pragma unroll
+    for (int p = 0; p < P; ++p) {
+      int i = threadIdx.x + p * kThreads;
+      if (i < nvec) {
+        if (dx) {
+          T *dxr = dx + r * N;
+          Vec16<T> o = ld_vec(dxr + i * VN);
+#pragma unroll
+          for (int j = 0; j < VN; ++j)
+            o.v[j] = from_f32<T>(to_f32(o.v[j]) + rs * dv[p][j] * g[p][j] + c1 * xv[p][j] + c2);
+          st_vec(dxr + i * VN, o);
+        }
+#pragma unroll
+        for (int j = 0; j < VN; ++j) {
+          pg[p][j] += dv[p][j] * (xv[p][j] - mu) * rs;
+          pb[p][j] += dv[p][j];
+        }
+      }
+    }
+  }
+  if (part) {
+    float *pgr = part + (size_t(blockIdx.x) * 2 + 0) * N;
+    float *pbr = part + (size_t(blockIdx.x) * 2 + 1) * N;
+#pragma unroll
+    for (int p = 0; p < P; ++p) {
+      int i = threadIdx.x + p * kThreads;
+      if (i < nvec) {
+#pragma unroll
+        for (int j = 0; j < VN; ++j) {
+          pgr[i * VN + j] = pg[p][j];
+          pbr[i * VN + j] = pb[p][j];
+        }
+      }
+    }
+  }
+}
+
+// Sum the per-CTA partials in CTA order (deterministic) and write / accumulate.
+template <typename T>
+__global__ void __launch_bounds__(kThreads)
+    layer_norm_param_reduce_kernel(float const *__restrict__ part, int nparts, long long N,
+                                   T *__restrict__ dgamma, T *__restrict__ dbeta,
+                                   bool accumulate) {
+  long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= N) return;
+  float sg = 0.f, sb = 0.f;
+  for (int p = 0; p < nparts; ++p) {
+    sg += part[(size_t(p) * 2 + 0) * N + j];
+    sb += part[(size_t(p) * 2 + 1) * N + j];
+  }
+  if (dgamma) dgamma[j] = from_f32<T>(accumulate ? to_f32(dgamma[j]) + sg : sg);
+  if (dbeta) dbeta[j] = from_f32<T>(accumulate ? to_f32(dbeta[j]) + sb : sb);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kThreads)
+    layer_norm_bwd_generic_kernel(T const *__restrict__ dy, T const *__restrict__ x,
+                                  T *__restrict__ dx, T const *__restrict__ gamma,
+                                  float const *__restrict__ mean, float const *__restrict__ rstd,
+                                  long long rows, long long N) {
+  __shared__ float red[64];
+  for (long long r = blockIdx.x; r < rows; r += gridDim.x) {
+    T const *dyr = dy + r * N;
+    T const *xr = x + r * N;
+    float ds = 0.f, db = 0.f;
+    for (long long j = threadIdx.x; j < N; j += blockDim.x) {
+      float gv = gamma ? to_f32(gamma[j]) : 1.f;
+      float d = to_f32(dyr[j]);
+      ds += d * to_f32(xr[j]) * gv;
+      db += d * gv;
+    }
+    block_sum2(ds, db, red);
+    float const mu = mean[r], rs = rstd[r], invn = 1.f / float(N);
+    float const c1 = (db * mu - ds) * rs * rs * rs * invn;
+    float const c2 = -(c1 * mu + db * rs * invn);
+    T *dxr = dx + r * N;
+    for (long long j = threadIdx.x; j < N; j += blockDim.x) {
+      float gv = gamma ? to_f32(gamma[j]) : 1.f;
+      dxr[j] = from_f32<T>(to_f32(dxr[j]) + rs * to_f32(dyr[j]) * gv + c1 * to_f32(xr[j]) + c2);
+    }
+  }
+}
+
+// Column reduction for dgamma / dbeta without scratch: a CTA owns 32 columns, 8 row-lanes.
+template <typename T>
+__global__ void __launch_bounds__(kThreads)
+    layer_norm_param_columns_kernel(T const *__restrict__ dy, T const *__restrict__ x,
+                                    float const *__restrict__ mean,
+                                    float const *__restrict__ rstd, T *__restrict__ dgamma,
+                                    T *__restrict__ dbeta, long long rows, long long N,
+                                    bool accumulate) {
+  __shared__ float sg[8][33], sb[8][33];
+  int const cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
+  long long const col = (long long)blockIdx.x * 32 + cx;
+  float ag = 0.f, ab = 0.f;
+  if (col < N) {
+    for (long long r = ry; r < rows; r += 8) {
+      float d = to_f32(dy[r * N + col]);
+      ag += d * (to_f32(x[r * N + col]) - mean[r]) * rstd[r];
+      ab += d;
+    }
+  }
+  sg[ry][cx] = ag;
+  sb[ry][cx] = ab;
+  __syncthreads();
+  if (ry == 0 && col < N) {
+    float tg = 0.f, tb = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      tg += sg[i][cx];
+      tb += sb[i][cx];
+    }
+    if (dgamma) dgamma[col] = from_f32<T>(accumulate ? to_f32(dgamma[col]) + tg : tg);
+    if (dbeta) dbeta[col] = from_f32<T>(accumulate ? to_f32(dbeta[col]) + tb : tb);
+  }
+}
+
+// ================================================================== batch norm (NCHW, fp32)
+// One CTA per channel. The channel's data (n * h*w floats, strided by c*h*w between
+// samples) is walked three times; after the first walk it is L2 resident.
+__global__ void __launch_bounds__(kThreads)
+    batch_norm_fwd_kernel(float const *__restrict__ x, float *__restrict__ y,
+                          float const *__restrict__ scale, float const *__restrict__ bias,
+                          float *__restrict__ run_mean, float *__restrict__ run_var,
+                          float *__restrict__ save_mean, float *__restrict__ save_invstd, int n,
+                          int c, long long hw, float eps, float factor) {
+  __shared__ float red[32];
+  int const ch = blockIdx.x;
+  long long const m = (long long)n * hw;
+  float s = 0.f;
+  for (long long i = threadIdx.x; i < m; i += blockDim.x) {
+    long long b = i / hw, p = i - b * hw;
+    s += x[(b * c + ch) * hw + p];
+  }
+  float const mu = block_sum(s, red) / float(m);
+  float q = 0.f;
+  for (long long i = threadIdx.x; i < m; i += blockDim.x) {
+    long long b = i / hw, p = i - b * hw;
+    float d = x[(b * c + ch) * hw + p] - mu;
+    q += d * d;
+  }
+  float const ssq = block_sum(q, red);
+  float const var = ssq / float(m);
+  float const invstd = rsqrtf(var + eps);
+  if (threadIdx.x == 0) {
+    save_mean[ch] = mu;
+    save_invstd[ch] = invstd;
+    float const unbiased = m > 1 ? ssq / float(m - 1) : var;
+    if (run_mean) run_mean[ch] = factor * mu + (1.f - factor) * run_mean[ch];
+    if (run_var) run_var[ch] = factor * unbiased + (1.f - factor) * run_var[ch];
+  }
+  float const g = scale[ch], be = bias[ch];
+  for (long long i = threadIdx.x; i < m; i += blockDim.x) {
+    long long b = i / hw, p = i - b * hw;
+    long long idx = (b * c + ch) * hw + p;
+    y[idx] = (x[idx] - mu) * invstd * g + be;
+  }
+}
+
+__global__ void __launch_bounds__(kThreads)
+    batch_norm_bwd_kernel(float const *__restrict__ x, float *__restrict__ dy,
+                          float const *__restrict__ y, float *__restrict__ dx,
+                          float const *__restrict__ scale, float *__restrict__ dscale,
+                          float *__restrict__ dbias, float const *__restrict__ save_mean,
+                          float const *__restrict__ save_invstd, int n, int c, long long hw,
+                          int relu) {
+  __shared__ float red[64];
+  int const ch = blockIdx.x;
+  long long const m = (long long)n * hw;
+  float const mu = save_mean[ch], invstd = save_invstd[ch];
+  float sdy = 0.f, sdyx = 0.f;
+  for (long long i = threadIdx.x; i < m; i += blockDim.x) {
+    long long b = i / hw, p = i - b * hw;
+    long long idx = (b * c + ch) * hw + p;
+    float d = dy[idx];
+    if (relu) {
+      d = y[idx] > 0.f ? d : 0.f;
+      dy[idx] = d;
+    }
+    sdy += d;
+    sdyx += d * (x[idx] - mu) * invstd;
+  }
+  block_sum2(sdy, sdyx, red);
+  float const g = scale[ch];
+  if (threadIdx.x == 0) {
+    if (dscale) dscale[ch] += sdyx;
+    if (dbias) dbias[ch] += sdy;
+  }
+  if (dx) {
+    float const k = g * invstd / float(m);
+    for (long long i = threadIdx.x; i < m; i += blockDim.x) {
+      long long b = i / hw, p = i - b * hw;
+      long long idx = (b * c + ch) * hw + p;
+      float xh = (x[idx] - mu) * invstd;
+      dx[idx] += k * (float(m) * dy[idx] - sdy - xh * sdyx);
+    }
+  }
+}
+
+unsigned rows_grid(long long rows, int per_sm) {
+  long long cap = (long long)device_info().sm_count * per_sm;
+  return (unsigned)std::max<long long>(1, std::min(rows, cap));
+}
+
+}  // namespace
+}  // namespace ffk
+
+using namespace ffk;
+
+extern "C" {
+
+int ffk_softmax_forward(void *stream, void const *input, void *output, long long outer,
+                        long long dim, long long inner, int dtype) {
+  FFK_REQUIRE(outer >= 0 && dim >= 0 && inner >= 0, "softmax: negative extent");
+  if (outer == 0 || dim == 0 || inner == 0) return FFK_OK;
+  FFK_REQUIRE(input && output, "softmax: null tensor");
+  cudaStream_t s = as_stream(stream);
+  FFK_DISPATCH_FLOAT(dtype, T, {
+    constexpr int VN = Vec16<T>::N;
+    bool vec = inner == 1 && dim % VN == 0 && aligned16(input) && aligned16(output) &&
+               pick_p(dim / VN) != 0 && dim / VN >= 64;
+    if (vec) {
+      int nvec = int(dim / VN), p = pick_p(nvec);
+      FFK_DISPATCH_P(p, P, {
+        softmax_rows_kernel<T, P><<<rows_grid(outer, 8), kThreads, 0, s>>>(
+            reinterpret_cast<T const *>(input), reinterpret_cast<T *>(output), outer, nvec);
+      });
+    } else if (inner >= 32) {
+      unsigned grid = stream_grid(size_t(outer * inner), kThreads, 8);
+      softmax_strided_kernel<T><<<grid, kThreads, 0, s>>>(
+          reinterpret_cast<T const *>(input), reinterpret_cast<T *>(output), outer, dim, inner);
+    } else {
+      unsigned grid = stream_grid(size_t(outer * inner) * 32, kThreads, 8);
+      softmax_lines_kernel<T><<<grid, kThreads, 0, s>>>(
+          reinterpret_cast<T const *>(input), reinterpret_cast<T *>(output), outer, dim, inner);
+    }
+  });
+  FFK_LAUNCH_CHECK();
+  return FFK_OK;
+}
+
+int ffk_softmax_backward(void *stream, void *input_grad, void const *output_grad,
+                         void const *output, long long outer, long long dim, long long inner,
+                         int dtype, int mode) {
+  FFK_REQUIRE(outer >= 0 && dim >= 0 && inner >= 0, "softmax: negative extent");
+  FFK_REQUIRE(mode == 0 || mode == 1, "softmax backward: mode must be 0 or 1");
+  size_t n = size_t(outer) * size_t(dim) * size_t(inner);
+  if (n == 0) return FFK_OK;
+  FFK_REQUIRE(input_grad && output_grad, "softmax backward: null tensor");
+  if (mode == 0) return ffk_copy(stream, input_grad, output_grad, n, dtype);
+  FFK_REQUIRE(output, "softmax backward: Jacobian mode needs `output`");
+  FFK_DISPATCH_FLOAT(dtype, T, {
+    unsigned grid = stream_grid(size_t(outer * inner) * 32, kThreads, 8);
+    softmax_jacobian_kernel<T><<<grid, kThreads, 0, as_stream(stream)>>>(
+        reinterpret_cast<T *>(input_grad), reinterpret_cast<T const *>(output_grad),
+        reinterpret_cast<T const *>(output), outer, dim, inner);
+  });
+  FFK_LAUNCH_CHECK();
+  return FFK_OK;
+}
+
+int ffk_layer_norm_forward(void *stream, void const *input, void *output, void const *gamma,
+                           void const *beta, float *mean, float *rstd, long long M, long long N,
+                           float eps, int dtype) {
+  FFK_REQUIRE(M >= 0 && N >= 0, "layer_norm: negative extent");
+  if (M == 0 || N == 0) return FFK_OK;
+  FFK_REQUIRE(input && output && mean && rstd, "layer_norm: null tensor");
+  cudaStream_t s = as_stream(stream);
+  FFK_DISPATCH_FLOAT(dtype, T, {
+    constexpr int VN = Vec16<T>::N;
+    bool vec = N % VN == 0 && aligned16(input) && aligned16(output) &&
+               (!gamma || aligned16(gamma)) && (!beta || aligned16(beta)) && pick_p(N / VN) != 0;
+    if (vec) {
+      int nvec = int(N / VN), p = pick_p(nvec);
+      FFK_DISPATCH_P(p, P, {
+        layer_norm_fwd_rows_kernel<T, P><<<rows_grid(M, 6), kThreads, 0, s>>>(
+            reinterpret_cast<T const *>(input), reinterpret_cast<T *>(output),
+            reinterpret_cast<T const *>(gamma), reinterpret_cast<T const *>(beta), mean, rstd, M,
+            nvec, eps);
+      });
+    } else {
+      layer_norm_fwd_generic_kernel<T><<<rows_grid(M, 8), kThreads, 0, s>>>(
+          reinterpret_cast<T const *>(input), reinterpret_cast<T *>(output),
+          reinterpret_cast<T const *>(gamma), reinterpret_cast<T const *>(beta), mean, rstd, M, N,
+          eps);
+    }
+  });
+  FFK_LAUNCH_CHECK();
+  return FFK_OK;
+}
+
+size_t ffk_layer_norm_backward_workspace_bytes(long long N) {
+  if (N <= 0) return 0;
+  return size_t(device_info().sm_count) * 2 /*CTAs per SM*/ * 2 /*dgamma,dbeta*/ * size_t(N) *
+         sizeof(float);
+}
+
+int ffk_layer_norm_backward(void *stream, void const *output_grad, void const *input,
+                            void *input_grad, void const *gamma, void *gamma_grad,
+                            void *beta_grad, float const *mean, float const *rstd, long long M,
+                            long long N, int dtype, int accumulate_param_grads, void *workspace,
+                            size_t workspace_bytes) {
+  FFK_REQUIRE(M >= 0 && N >= 0, "layer_norm: negative extent");
+  if (M == 0 || N == 0) return FFK_OK;
+  FFK_REQUIRE(output_grad && input && mean && rstd, "layer_norm backward: null tensor");
+  cudaStream_t s = as_stream(stream);
+  bool want_params = gamma_grad || beta_grad;
+  FFK_DISPATCH_FLOAT(dtype, T, {
+    constexpr int VN = Vec16<T>::N;
+    bool vec = N % VN == 0 && aligned16(output_grad) && aligned16(input) &&
+               (!input_grad || aligned16(input_grad)) && (!gamma || aligned16(gamma)) &&
+               pick_p(N / VN) != 0;
+    size_t per_part = size_t(2) * size_t(N) * sizeof(float);
+    size_t parts_fit = (workspace && want_params) ? workspace_bytes / per_part : 0;
+    bool fused = vec && want_params && parts_fit >= 1;
+    if (vec && (input_grad || fused)) {
+      int nvec = int(N / VN), p = pick_p(nvec);
+      unsigned grid = rows_grid(M, 2);
+      if (fused) grid = (unsigned)std::min<size_t>(grid, parts_fit);
+      FFK_DISPATCH_P(p, P, {
+        layer_norm_bwd_rows_kernel<T, P><<<grid, kThreads, 0, s>>>(
+            reinterpret_cast<T const *>(output_grad), reinterpret_cast<T const *>(input),
+            reinterpret_cast<T *>(input_grad), reinterpret_cast<T const *>(gamma), mean, rstd,
+            fused ? reinterpret_cast<float *>(workspace) : nullptr, M, nvec);
+      });
+      FFK_LAUNCH_CHECK();
+      if (fused) {
+        layer_norm_param_reduce_kernel<T><<<unsigned((N + kThreads - 1) / kThreads), kThreads, 0, s>>>(
+            reinterpret_cast<float const *>(workspace), int(grid), N,
+            reinterpret_cast<T *>(gamma_grad), reinterpret_cast<T *>(beta_grad),
+            accumulate_param_grads != 0);
+        FFK_LAUNCH_CHECK();
+      }
+    } else if (input_grad) {
+      layer_norm_bwd_generic_kernel<T><<<rows_grid(M, 8), kThreads, 0, s>>>(
+          reinterpret_cast<T const *>(output_grad), reinterpret_cast<T const *>(input),
+          reinterpret_cast<T *>(input_grad), reinterpret_cast<T const *>(gamma), mean, rstd, M, N);
+      FFK_LAUNCH_CHECK();
+    }
+    if (want_params && !fused) {
+      layer_norm_param_columns_kernel<T><<<unsigned((N + 31) / 32), kThreads, 0, s>>>(
+          reinterpret_cast<T const *>(output_grad), reinterpret_cast<T const *>(input), mean, rstd,
+          reinterpret_cast<T *>(gamma_grad), reinterpret_cast<T *>(beta_grad), M, N,
+          accumulate_param_grads != 0);
+      FFK_LAUNCH_CHECK();
+    }
+  });
+  return FFK_OK;
+}
+
+int ffk_batch_norm_forward(void *stream, float const *input, float *output, float const *scale,
+                           float const *bias, float *running_mean, float *running_var,
+                           float *save_mean, float *save_invstd, int n, int c, int h, int w,
+                           float eps, float factor) {
+  FFK_REQUIRE(n >= 0 && c >= 0 && h >= 0 && w >= 0, "batch_norm: negative extent");
+  if (n == 0 || c == 0 || h == 0 || w == 0) return FFK_OK;
+  FFK_REQUIRE(input && output && scale && bias && save_mean && save_invstd,
+              "batch_norm: null tensor");
+  batch_norm_fwd_kernel<<<c, kThreads, 0, as_stream(stream)>>>(
+      input, output, scale, bias, running_mean, running_var, save_mean, save_invstd, n, c,
+      (long long)h * w, eps, factor);
+  FFK_LAUNCH_CHECK();
+  return FFK_OK;
+}
+
+int ffk_batch_norm_backward(void *stream, float const *input, float *output_grad,
+                            float const *output, float *input_grad, float const *scale,
+                            float *scale_grad, float *bias_grad, float const *save_mean,
+                            float const *save_invstd, int n, int c, int h, int w, int relu) {
+  FFK_REQUIRE(n >= 0 && c >= 0 && h >= 0 && w >= 0, "batch_norm: negative extent");
+  if (n == 0 || c == 0 || h == 0 || w == 0) return FFK_OK;
+  FFK_REQUIRE(input && output_grad && scale && save_mean && save_invstd,
+              "batch_norm backward: null tensor");
+  FFK_REQUIRE(!relu || output, "batch_norm backward: relu needs `output`");
+  batch_norm_bwd_kernel<<<c, kThreads, 0, as_stream(stream)>>>(
+      input, output_grad, output, input_grad, scale, scale_grad, bias_grad, save_mean,
+      save_invstd, n, c, (long long)h * w, relu);
+  FFK_LAUNCH_CHECK();
+  return FFK_OK;
+}
+
+}  // extern "C"

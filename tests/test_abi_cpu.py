@@ -1,0 +1,61 @@
+"""CPU-side checks of the drop-in boundary: the C-ABI library loads without a GPU and
+exports every symbol that include/*.h declares; compute entry points fail loudly (no CPU
+fallback) when no CUDA device exists."""
+import ctypes
+import re
+
+import pytest
+import torch
+
+
+def test_library_exports_every_declared_symbol(ffk):
+    protos = ffk.parse_headers()
+    assert len(protos) >= 25
+    cdll = ctypes.CDLL(str(ffk.LIB_PATH))
+    missing = [n for n in protos if not hasattr(cdll, n)]
+    assert not missing, f"declared in include/*.h but not exported: {missing}"
+
+
+def test_every_exported_ffk_symbol_is_declared(ffk):
+    import subprocess
+
+    out = subprocess.run(["nm", "-D", "--defined-only", str(ffk.LIB_PATH)], capture_output=True,
+                         text=True, check=True).stdout
+    exported = set(re.findall(r"\sT\s+(ffk_[a-z0-9_]+)$", out, re.M))
+    declared = set(ffk.parse_headers())
+    assert exported <= declared, f"exported but undeclared: {sorted(exported - declared)}"
+
+
+def test_header_cites_reference_for_each_entry_point(ffk):
+    """Every compute prototype is preceded by a comment naming a reference file."""
+    from pathlib import Path
+
+    inc = Path(ffk.LIB_PATH).parents[1] / "include"
+    text = "".join(p.read_text() for p in sorted(inc.glob("*.h")))
+    assert "src/cuda/ops/linear_kernels.cu" in text
+    assert "include/kernels/" in text
+
+
+def test_abi_version_and_error_string(ffk):
+    L = ffk.lib()
+    assert L.cdll.ffk_abi_version() >= 1
+    assert isinstance(L.last_error(), str)
+
+
+@pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-GPU behaviour")
+def test_compute_fails_loudly_without_gpu(ffk):
+    L = ffk.lib()
+    buf = (ctypes.c_float * 64)()
+    p = ctypes.cast(buf, ctypes.c_void_p)
+    with pytest.raises(ffk.FFKError) as e:
+        L.call("ffk_copy", None, p, p.value + 128, 8, 4)
+    assert e.value.code < 0 and "CUDA" in str(e.value)
+
+
+def test_bad_arguments_are_rejected_without_touching_the_device(ffk):
+    L = ffk.lib()
+    with pytest.raises(ffk.FFKError) as e:
+        L.call("ffk_element_unary_forward", None, 9999, 0.0, None, None, 16, 4)
+    assert e.value.code == -1
+    with pytest.raises(ffk.FFKError):
+        L.call("ffk_linear_forward", None, None, None, None, None, -1, 4, 4, 4, -1, 0)

@@ -1,0 +1,134 @@
+"""GPU parity: Linear / BatchMatmul / GEMM through the C ABI vs the CPU oracle.
+fp32 tensors take the exact CUDA-core path (rtol 1e-4); bf16/half take the tcgen05 tiles
+(rtol 2e-2). Inputs: U(-1,1) activations (seed 1234), weights scaled by 1/sqrt(K) (seed 4321)."""
+import numpy as np
+import pytest
+import torch
+
+from helpers import SEED_ACT, SEED_W, assert_close, to_dev, uniform
+
+pytestmark = pytest.mark.gpu
+
+ACTS = {"none": -1, "relu": 0, "sigmoid": 1, "tanh": 2, "gelu": 3}
+
+
+def _linear_case(K, oracle, dtype, batch, in_dim, out_dim, act, use_bias, l2=0.0, path=0):
+    x, xn = to_dev(uniform((batch, in_dim), SEED_ACT), dtype)
+    w, wn = to_dev(uniform((out_dim, in_dim), SEED_W) / np.sqrt(in_dim), dtype)
+    b, bn = to_dev(uniform((out_dim,), SEED_W + 1), dtype) if use_bias else (None, None)
+    y = torch.zeros(batch, out_dim, dtype=dtype, device="cuda")
+    m = K.Linear.init_kernel(ACTS[act], l2, use_bias, path)
+    K.Linear.forward_kernel(None, m, x, y, w, b, in_dim, out_dim, batch)
+    yref = np.zeros((batch, out_dim), np.float32)
+    oracle.linear_forward(xn, wn, bn, yref, in_dim, out_dim, batch, ACTS[act])
+    assert_close(y, yref, dtype, what=f"linear fwd {dtype} {batch}x{in_dim}x{out_dim} {act}")
+
+    # backward: grads start non-zero to check the accumulate convention
+    dy, dyn = to_dev(uniform((batch, out_dim), SEED_ACT + 7), dtype)
+    dx, dxn = to_dev(uniform((batch, in_dim), SEED_ACT + 8) * 0.1, dtype)
+    dw, dwn = to_dev(uniform((out_dim, in_dim), SEED_W + 9) * 0.1, dtype)
+    db, dbn = to_dev(uniform((out_dim,), SEED_W + 10) * 0.1, dtype) if use_bias else (None, None)
+    preact = pre_n = None
+    if act == "gelu":
+        pre_n = np.zeros((batch, out_dim), np.float32)
+        oracle.linear_forward(xn, wn, bn, pre_n, in_dim, out_dim, batch, -1)
+        preact, pre_n = to_dev(pre_n, dtype)
+    yq, yn = to_dev(yref, dtype)  # both sides see the same stored activations
+    K.Linear.backward_kernel(None, m, x, dx, yq, dy, w, dw, db, in_dim, out_dim, batch, preact)
+    dyn2 = dyn.copy()
+    oracle.linear_backward(xn, dxn, yn, dyn2, wn, dwn, dbn, in_dim, out_dim, batch, ACTS[act],
+                           float(l2), pre_n)
+    tag = f"linear bwd {dtype} {batch}x{in_dim}x{out_dim} {act}"
+    assert_close(dy, dyn2, dtype, what=tag + " dY(in place)")
+    assert_close(dw, dwn, dtype, what=tag + " dW")
+    assert_close(dx, dxn, dtype, what=tag + " dX")
+    if use_bias:
+        assert_close(db, dbn, dtype, what=tag + " db")
+
+
+@pytest.mark.parametrize("act", ["none", "relu", "sigmoid", "tanh", "gelu"])
+def test_linear_fp32_mlp_shapes(K, oracle, act):
+    # config[0]: MLP 784-512-512-10, batch 64 (ragged 784 and 10 included)
+    _linear_case(K, oracle, torch.float32, 64, 784, 512, act, True)
+    _linear_case(K, oracle, torch.float32, 64, 512, 10, act, True, l2=1e-4)
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("act", ["none", "relu", "gelu"])
+def test_linear_16bit_tensor_core(K, oracle, dtype, act):
+    _linear_case(K, oracle, dtype, 256, 512, 384, act, True, path=1)
+    _linear_case(K, oracle, dtype, 200, 136, 104, act, False, l2=1e-3, path=1)  # ragged tiles
+
+
+def test_linear_bf16_unaligned_falls_back_to_simt(K, oracle):
+    _linear_case(K, oracle, torch.bfloat16, 33, 70, 10, "relu", True)
+
+
+def test_linear_empty_batch_is_a_no_op(K):
+    m = K.Linear.init_kernel()
+    x = torch.zeros(0, 16, device="cuda")
+    y = torch.zeros(0, 8, device="cuda")
+    w = torch.zeros(8, 16, device="cuda")
+    K.Linear.forward_kernel(None, m, x, y, w, None, 16, 8, 0)
+
+
+def test_linear_full_size_bf16_linearity(K):
+    """BASELINE config[1] size (8192x4096x4096 bf16), checked through size-independent
+    properties: exact row-selection (a one-hot activation row returns a weight column),
+    zero input -> bias, and homogeneity f(2x) = 2 f(x) (exact in binary floating point)."""
+    M, Kd, N = 8192, 4096, 4096
+    g = torch.Generator(device="cuda").manual_seed(SEED_W)
+    w = ((torch.rand(N, Kd, device="cuda", generator=g) * 2 - 1) / 64).to(torch.bfloat16)
+    x = torch.zeros(M, Kd, device="cuda", dtype=torch.bfloat16)
+    rows = torch.arange(M, device="cuda")
+    x[rows, (rows * 7) % Kd] = 1.0
+    y = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+    m = K.Linear.init_kernel(path=1)
+    K.Linear.forward_kernel(None, m, x, y, w, None, Kd, N, M)
+    expect = w[:, (rows * 7) % Kd].t().contiguous()
+    assert torch.equal(y, expect), "one-hot rows must return weight columns exactly"
+    xr = ((torch.rand(M, Kd, device="cuda", generator=g) * 2 - 1)).to(torch.bfloat16)
+    y1 = torch.empty_like(y)
+    y2 = torch.empty_like(y)
+    K.Linear.forward_kernel(None, m, xr, y1, w, None, Kd, N, M)
+    K.Linear.forward_kernel(None, m, (xr * 2).contiguous(), y2, w, None, Kd, N, M)
+    assert torch.equal(y2.float(), y1.float() * 2)
+    # spot-check 64 random outputs against fp64 dot products
+    idx = torch.randint(0, M, (64,), device="cuda", generator=g)
+    jdx = torch.randint(0, N, (64,), device="cuda", generator=g)
+    ref = (xr[idx].double() * w[jdx].double()).sum(1)
+    assert_close(y1[idx, jdx], ref.float().cpu().numpy(), torch.bfloat16, what="full-size spot check")
+
+
+@pytest.mark.parametrize("dtype,path", [(torch.float32, 0), (torch.bfloat16, 1)])
+def test_batch_matmul(K, oracle, dtype, path):
+    # reference fixture shape: m=10 n=10 k=10 batch=5 (lib/kernels/test/src/test_batch_matmul_kernel.cc:9-13)
+    for (m, n, k, batch) in [(10, 10, 10, 5), (64, 48, 40, 3), (128, 256, 64, 2)]:
+        if path == 1 and (m % 8 or k % 8):
+            continue
+        a, an = to_dev(uniform((batch, n, k), SEED_ACT), dtype)
+        b, bn = to_dev(uniform((batch, k, m), SEED_W) / np.sqrt(k), dtype)
+        o = torch.zeros(batch, n, m, dtype=dtype, device="cuda")
+        K.BatchMatmul.forward_kernel(None, o, a, b, m, n, k, batch, path=path)
+        oref = np.zeros((batch, n, m), np.float32)
+        oracle.batch_matmul_forward(oref, an, bn, m, n, k, batch, -1, -1, -1)
+        assert_close(o, oref, dtype, what=f"bmm fwd {m},{n},{k},{batch}")
+        do, don = to_dev(uniform((batch, n, m), SEED_ACT + 3), dtype)
+        da, dan = to_dev(uniform((batch, n, k), SEED_ACT + 4) * 0.1, dtype)
+        db, dbn = to_dev(uniform((batch, k, m), SEED_ACT + 5) * 0.1, dtype)
+        K.BatchMatmul.backward_kernel(None, o, do, a, da, b, db, m, n, k, batch, path=path)
+        oracle.batch_matmul_backward(don, an, dan, bn, dbn, m, n, k, batch)
+        assert_close(da, dan, dtype, what="bmm dA")
+        assert_close(db, dbn, dtype, what="bmm dB")
+
+
+def test_batch_matmul_seq_length_truncation(K, oracle):
+    m, n, k, batch = 12, 10, 8, 2
+    a, an = to_dev(uniform((batch, n, k), SEED_ACT))
+    b, bn = to_dev(uniform((batch, k, m), SEED_W))
+    for (ad, bd, sl) in [(1, -1, 6), (0, 1, 8), (-1, 0, 5)]:
+        o = torch.full((batch, n, m), 7.0, device="cuda")
+        oref = np.full((batch, n, m), 7.0, np.float32)
+        K.BatchMatmul.forward_kernel(None, o, a, b, m, n, k, batch, ad, bd, sl)
+        oracle.batch_matmul_forward(oref, an, bn, m, n, k, batch, ad, bd, sl)
+        assert_close(o, oref, what=f"bmm truncation {ad},{bd},{sl}")

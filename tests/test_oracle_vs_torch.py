@@ -1,0 +1,175 @@
+"""CPU: the oracle restatement is cross-checked against PyTorch's CPU implementations of the
+same math (the convention of the reference's legacy alignment tests, tests/align/align_utils.py:
+seeded random inputs, torch.testing.assert_close). The reference pins none of these ops
+numerically, so agreement of two independent statements is the pin we have."""
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+from helpers import SEED_ACT, SEED_W, uniform
+
+TOL = dict(rtol=1e-5, atol=1e-6)
+
+
+def t(a):
+    return torch.from_numpy(np.array(a, copy=True))
+
+
+@pytest.mark.parametrize("act,fn", [(-1, lambda v: v), (0, torch.relu), (1, torch.sigmoid), (2, torch.tanh),
+                                    (3, lambda v: F.gelu(v, approximate="tanh"))])
+def test_linear(oracle, act, fn):
+    B, I, O = 16, 40, 24
+    x, w, b = uniform((B, I), SEED_ACT), uniform((O, I), SEED_W), uniform((O,), 3)
+    y = np.zeros((B, O), np.float32)
+    oracle.linear_forward(x, w, b, y, I, O, B, act)
+    tx, tw, tb = t(x).requires_grad_(), t(w).requires_grad_(), t(b).requires_grad_()
+    pre = F.linear(tx, tw, tb)
+    ty = fn(pre)
+    torch.testing.assert_close(t(y), ty.detach(), **TOL)
+    dy = uniform((B, O), 5)
+    ty.backward(t(dy))
+    dx, dw, db = np.zeros_like(x), np.zeros_like(w), np.zeros_like(b)
+    dy2 = dy.copy()
+    oracle.linear_backward(x, dx, y, dy2, w, dw, db, I, O, B, act, 0.0, pre.detach().numpy().copy())
+    torch.testing.assert_close(t(dx), tx.grad, **TOL)
+    torch.testing.assert_close(t(dw), tw.grad, **TOL)
+    torch.testing.assert_close(t(db), tb.grad, **TOL)
+
+
+def test_linear_backward_accumulates_and_regularises(oracle):
+    B, I, O = 4, 6, 5
+    x, w = uniform((B, I), 1), uniform((O, I), 2)
+    dy = uniform((B, O), 3)
+    dw0 = uniform((O, I), 4)
+    dw = dw0.copy()
+    oracle.linear_backward(x, None, None, dy.copy(), w, dw, None, I, O, B, -1, 0.5, None)
+    np.testing.assert_allclose(dw, dw0 + dy.T @ x + 0.5 * w, rtol=1e-5, atol=1e-6)
+
+
+def test_batch_matmul(oracle):
+    b, n, k, m = 3, 7, 5, 6
+    A, Bm = uniform((b, n, k), 1), uniform((b, k, m), 2)
+    o = np.zeros((b, n, m), np.float32)
+    oracle.batch_matmul_forward(o, A, Bm, m, n, k, b, -1, -1, -1)
+    ta, tb = t(A).requires_grad_(), t(Bm).requires_grad_()
+    to = torch.bmm(ta, tb)
+    torch.testing.assert_close(t(o), to.detach(), **TOL)
+    do = uniform((b, n, m), 3)
+    to.backward(t(do))
+    da, db = np.zeros_like(A), np.zeros_like(Bm)
+    oracle.batch_matmul_backward(do, A, da, Bm, db, m, n, k, b)
+    torch.testing.assert_close(t(da), ta.grad, **TOL)
+    torch.testing.assert_close(t(db), tb.grad, **TOL)
+
+
+UNARY = {
+    8: lambda v, s: v * s, 9: lambda v, s: v + s, 12: lambda v, s: v - s, 11: lambda v, s: v / s,
+    71: lambda v, s: v ** s, 13: lambda v, s: torch.relu(v), 15: lambda v, s: torch.sigmoid(v),
+    16: lambda v, s: torch.tanh(v), 17: lambda v, s: F.elu(v, alpha=s), 56: lambda v, s: torch.exp(v),
+    14: lambda v, s: v * 1.0, 67: lambda v, s: F.gelu(v), 70: lambda v, s: torch.rsqrt(v),
+    61: lambda v, s: torch.sin(v), 62: lambda v, s: torch.cos(v),
+}
+
+
+@pytest.mark.parametrize("op", sorted(UNARY))
+def test_element_unary(oracle, op):
+    n = 257
+    x = uniform((n,), SEED_ACT, 0.2, 2.0) if op in (70, 71) else uniform((n,), SEED_ACT)
+    s = 1.5 if op != 17 else 1.0
+    y = np.zeros(n, np.float32)
+    assert oracle.element_unary_forward(op, s, x, y, n) == 0
+    tx = t(x).requires_grad_()
+    ty = UNARY[op](tx, s)
+    torch.testing.assert_close(t(y), ty.detach(), **TOL)
+    dy = uniform((n,), 9)
+    ty.backward(t(dy))
+    dx = np.zeros(n, np.float32)
+    oracle.element_unary_backward(op, s, x, dx, y, dy, n)
+    torch.testing.assert_close(t(dx), tx.grad, rtol=1e-5, atol=1e-5)
+
+
+BIN = {28: torch.add, 35: torch.sub, 29: torch.mul, 36: torch.div, 40: torch.maximum, 41: torch.minimum}
+
+
+@pytest.mark.parametrize("op", sorted(BIN))
+@pytest.mark.parametrize("ls,rs", [((3, 4, 5), (3, 4, 5)), ((3, 1, 5), (1, 4, 1)), ((1, 1, 5), (3, 4, 5))])
+def test_element_binary(oracle, op, ls, rs):
+    os_ = tuple(max(a, b) for a, b in zip(ls, rs))
+    l, r = uniform(ls, 1), uniform(rs, 2)
+    if op == 36:
+        r = np.sign(r) * (np.abs(r) + 0.5)
+    o = np.zeros(os_, np.float32)
+    oracle.element_binary_forward(op, l, r, o, 3, ls, rs, os_)
+    tl, tr = t(l).requires_grad_(), t(r).requires_grad_()
+    to = BIN[op](tl, tr)
+    torch.testing.assert_close(t(o), to.detach(), **TOL)
+    dy = uniform(os_, 3)
+    to.backward(t(dy))
+    dl, dr = np.zeros_like(l), np.zeros_like(r)
+    oracle.element_binary_backward(op, dy, l, r, dl, dr, 3, ls, rs, os_)
+    # continuous random inputs: no ties, so max/min subgradients agree with torch
+    torch.testing.assert_close(t(dl), tl.grad, rtol=1e-5, atol=1e-5)
+    torch.testing.assert_close(t(dr), tr.grad, rtol=1e-5, atol=1e-5)
+
+
+@pytest.mark.parametrize("outer,dim,inner", [(4, 10, 1), (2, 7, 3)])
+def test_softmax(oracle, outer, dim, inner):
+    x = uniform((outer, dim, inner), SEED_ACT) * 3
+    y = np.zeros_like(x)
+    oracle.softmax_forward(x, y, outer, dim, inner)
+    tx = t(x).requires_grad_()
+    ty = torch.softmax(tx, dim=1)
+    torch.testing.assert_close(t(y), ty.detach(), **TOL)
+    dy = uniform(x.shape, 2)
+    ty.backward(t(dy))
+    dx = np.zeros_like(x)
+    oracle.softmax_backward_jacobian(dx, dy, y, outer, dim, inner)
+    torch.testing.assert_close(t(dx), tx.grad, rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("affine", [True, False])
+def test_layer_norm(oracle, affine):
+    M, N, eps = 10, 10, 1e-5  # the reference's fixture size
+    x = uniform((M, N), SEED_ACT)
+    g = uniform((N,), 2) + 1 if affine else None
+    b = uniform((N,), 3) if affine else None
+    y, mean, rstd = np.zeros_like(x), np.zeros(M, np.float32), np.zeros(M, np.float32)
+    oracle.layer_norm_forward(x, y, g, b, mean, rstd, M, N, eps)
+    tx = t(x).requires_grad_()
+    tg = t(g).requires_grad_() if affine else None
+    tb = t(b).requires_grad_() if affine else None
+    ty = F.layer_norm(tx, (N,), tg, tb, eps)
+    torch.testing.assert_close(t(y), ty.detach(), rtol=1e-5, atol=1e-5)
+    dy = uniform((M, N), 4)
+    ty.backward(t(dy))
+    dx, dg, db = np.zeros_like(x), np.zeros(N, np.float32), np.zeros(N, np.float32)
+    oracle.layer_norm_backward(dy, x, dx, g, dg, db, mean, rstd, M, N, 0)
+    torch.testing.assert_close(t(dx), tx.grad, rtol=1e-4, atol=1e-5)
+    if affine:
+        torch.testing.assert_close(t(dg), tg.grad, rtol=1e-4, atol=1e-5)
+        torch.testing.assert_close(t(db), tb.grad, rtol=1e-4, atol=1e-5)
+
+
+@pytest.mark.parametrize("relu", [False, True])
+def test_batch_norm(oracle, relu):
+    n, c, h, w, eps = 4, 6, 5, 3, 1e-5
+    x = uniform((n, c, h, w), 1)
+    sc, bi = uniform((c,), 2) + 1, uniform((c,), 3)
+    y = np.zeros_like(x)
+    rm, rv, sm, si = (np.zeros(c, np.float32) for _ in range(4))
+    oracle.batch_norm_forward(x, y, sc, bi, rm, rv, sm, si, n, c, h, w, eps, 1.0)
+    tx, tsc, tbi = t(x).requires_grad_(), t(sc).requires_grad_(), t(bi).requires_grad_()
+    trm, trv = torch.zeros(c), torch.zeros(c)
+    ty = F.batch_norm(tx, trm, trv, tsc, tbi, training=True, momentum=1.0, eps=eps)
+    torch.testing.assert_close(t(y), ty.detach(), rtol=1e-5, atol=1e-5)
+    torch.testing.assert_close(t(rm), trm, rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(t(rv), trv, rtol=1e-5, atol=1e-6)
+    dy = uniform(x.shape, 4)
+    out = torch.relu(ty) if relu else ty
+    out.backward(t(dy))
+    dx, dsc, dbi = np.zeros_like(x), np.zeros(c, np.float32), np.zeros(c, np.float32)
+    oracle.batch_norm_backward(x, dy.copy(), y, dx, sc, dsc, dbi, sm, si, n, c, h, w, int(relu))
+    torch.testing.assert_close(t(dx), tx.grad, rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(t(dsc), tsc.grad, rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(t(dbi), tbi.grad, rtol=1e-4, atol=1e-5)
