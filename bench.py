@@ -1,0 +1,458 @@
+#!/usr/bin/env python
+"""bench.py — the measurement contract of this repository.
+
+Workload (BASELINE.json configs[1], "per-op microbench on 1 B200"): one STEP is one pass of
+the per-operator hot path over one batch of 8192 samples:
+
+    Linear 8192x4096x4096 bf16 (+bias, ReLU)  forward + backward (act-grad, wgrad, bias-grad, dgrad)
+    Softmax 8192x4096 fp32                     forward
+    LayerNorm 8192x4096 fp32                   forward + backward (dX, dgamma, dbeta)
+    ElementBinary add 8192x4096 fp32           forward + backward
+    Embedding 1,000,000 x 256 fp32, 65536 i64  forward + backward
+
+all through the C ABI of libffk.so (include/*.h). metric = training samples/sec =
+8192 * n_gpus / step time. With --gpus N > 1 every rank runs the step on its own batch (weak
+scaling) and the weight gradients (Linear dW/db, LayerNorm dgamma/dbeta) are summed over ranks
+with one NCCL all-reduce per step — the Replicate-backward exchange of data parallelism.
+
+The JSON line also carries: roofline (the tcgen05 GEMM of Linear forward against the measured
+bf16 peak), cpu_baseline (the CPU oracle on a bounded sample of the same step, rank 0, N=1),
+e2e (the same step fed from pinned HOST memory each step, result read back), clocks.
+
+`--impl reference` times the reference arm: the CPU restatement of the reference kernels
+(oracle/, the reference itself has no CPU path and cannot be built — DESIGN.md) on all host
+threads, on a bounded sample of the same step.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+M, KDIM, N = 8192, 4096, 4096          # Linear: batch, in, out
+ROWS, COLS = 8192, 4096                # Softmax / LayerNorm / ElementBinary
+ENTRIES, EDIM, EBATCH = 1_000_000, 256, 65536
+SAMPLES_PER_STEP = M
+GEMM_FLOP = 2.0 * M * N * KDIM         # algorithmic FLOP of one Linear-forward launch
+
+# kernels launched by one step, per C-ABI call (bench's own count, reported as gpu_launches)
+LAUNCHES_PER_STEP = {
+    "copy_dy": 1, "linear_forward": 1, "linear_backward": 5, "softmax_forward": 1, "layer_norm_forward": 1,
+    "layer_norm_backward": 2, "element_binary_forward": 1, "element_binary_backward": 1,
+    "embedding_forward": 1, "embedding_backward": 1,
+}
+
+
+def load_peaks():
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        d = json.loads(p.read_text())
+        return d.get("bf16_tflops", 1590.0), d.get("hbm_gbs", 6650.0), "measured"
+    return 1590.0, 6650.0, "fallback"
+
+
+# ----------------------------------------------------------------------------- clocks
+class ClockSampler:
+    """Samples nvidia-smi during the timed region (B200_PROFILING.md clocks line)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.gpu = gpu_index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                 "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None,
+                "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ----------------------------------------------------------------------------- GPU arm
+class Workload:
+    """Device buffers of one step and the C-ABI calls that make it up."""
+
+    def __init__(self, torch, Kmod, device):
+        self.torch, self.K = torch, Kmod
+        g = torch.Generator(device=device).manual_seed(1234)
+        bf = torch.bfloat16
+        r = lambda *s: torch.rand(*s, device=device, generator=g) * 2 - 1
+        # Linear
+        self.x = r(M, KDIM).to(bf)
+        self.w = (r(N, KDIM) / 64).to(bf)
+        self.b = r(N).to(bf)
+        self.y = torch.empty(M, N, dtype=bf, device=device)
+        self.dy_src = r(M, N).to(bf)
+        self.dy = torch.empty_like(self.dy_src)
+        self.dx = torch.zeros(M, KDIM, dtype=bf, device=device)
+        self.dw = torch.zeros(N, KDIM, dtype=bf, device=device)
+        self.db = torch.zeros(N, dtype=bf, device=device)
+        self.lin = Kmod.Linear.init_kernel(Kmod.ACT_RELU, 0.0, True, Kmod.GEMM_TENSOR, out_dim=N, device=device)
+        # Softmax / LayerNorm / ElementBinary (fp32)
+        self.a = r(ROWS, COLS)
+        self.c = r(ROWS, COLS)
+        self.o = torch.empty(ROWS, COLS, device=device)
+        self.ga = torch.zeros(ROWS, COLS, device=device)
+        self.gc = torch.zeros(ROWS, COLS, device=device)
+        self.gamma = r(COLS) + 1
+        self.beta = r(COLS)
+        self.dgamma = torch.zeros(COLS, device=device)
+        self.dbeta = torch.zeros(COLS, device=device)
+        self.ln = Kmod.LayerNorm.init_kernel(True, ROWS, COLS, 1e-5, device=device)
+        # Embedding
+        self.table = r(ENTRIES, EDIM)
+        self.dtable = torch.zeros(ENTRIES, EDIM, device=device)
+        self.idx = torch.randint(0, ENTRIES, (EBATCH,), device=device, generator=g, dtype=torch.int64)
+        self.eout = torch.empty(EBATCH, EDIM, device=device)
+        self.ev_a = torch.cuda.Event(enable_timing=True)
+        self.ev_b = torch.cuda.Event(enable_timing=True)
+        self.gemm_events = []
+
+    def grads_for_sync(self):
+        return [self.dw, self.db, self.dgamma, self.dbeta]
+
+    def step(self, time_gemm=False):
+        K, t = self.K, self.torch
+        K.copy(None, self.dy, self.dy_src)  # backward rewrites dY in place (ReLU gradient)
+        if time_gemm:
+            a, b = t.cuda.Event(enable_timing=True), t.cuda.Event(enable_timing=True)
+            a.record()
+        K.Linear.forward_kernel(None, self.lin, self.x, self.y, self.w, self.b, KDIM, N, M)
+        if time_gemm:
+            b.record()
+            self.gemm_events.append((a, b))
+        K.Linear.backward_kernel(None, self.lin, self.x, self.dx, self.y, self.dy, self.w, self.dw,
+                                 self.db, KDIM, N, M)
+        K.Softmax.forward_kernel(None, self.a, self.o, ROWS, COLS, 1)
+        K.LayerNorm.forward_kernel(None, self.ln, self.a, self.o, self.gamma, self.beta)
+        K.LayerNorm.backward_kernel(None, self.ln, self.c, self.a, self.ga, self.gamma, self.dgamma,
+                                    self.dbeta)
+        K.ElementBinary.forward_kernel(None, K.OperatorType.EW_ADD, self.a, self.c, self.o)
+        K.ElementBinary.backward_kernel(None, K.OperatorType.EW_ADD, self.o, self.a, self.c,
+                                        self.ga, self.gc)
+        K.Embedding.forward_kernel(None, self.idx, self.eout, self.table, K.AGGR_NONE, 1, EDIM, EBATCH)
+        K.Embedding.backward_kernel(None, self.idx, self.eout, self.dtable, K.AGGR_NONE, 1, EDIM, EBATCH)
+
+
+def run_gpu(args):
+    import torch
+    import torch.distributed as dist
+    import ffk_import
+
+    ffk_import.load()
+    import importlib
+    Kmod = importlib.import_module("flexflow_train_b200.kernels")
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=device)
+    n_gpus = world
+
+    wl = Workload(torch, Kmod, device)
+    lib = ffk_import.load().lib()
+
+    def sync_grads():
+        if world > 1:
+            flat = torch.cat([g.reshape(-1).float() for g in wl.grads_for_sync()])
+            dist.all_reduce(flat)  # Replicate-backward: sum of replica gradients over NVLink
+            off = 0
+            for g in wl.grads_for_sync():
+                n = g.numel()
+                g.copy_(flat[off:off + n].view_as(g))
+                off += n
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def full_step(time_gemm=False):
+        wl.step(time_gemm)
+        sync_grads()
+
+    for _ in range(args.warmup):
+        full_step()
+    barrier()
+
+    clocks = ClockSampler(local_rank)
+    if rank == 0:
+        clocks.start()
+    launches0 = lib.launches
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        full_step(time_gemm=True)
+    e1.record()
+    barrier()
+    ms_total = e0.elapsed_time(e1)
+    abi_calls = lib.launches - launches0
+    clock_info = clocks.stop() if rank == 0 else None
+    gemm_ms = [a.elapsed_time(b) for a, b in wl.gemm_events]
+
+    # ---- e2e: the same step, inputs from pinned HOST memory every step, result read back
+    hx = torch.empty(M, KDIM, dtype=torch.bfloat16).pin_memory()
+    hx.copy_(wl.x.cpu())
+    hidx = torch.empty(EBATCH, dtype=torch.int64).pin_memory()
+    hidx.copy_(wl.idx.cpu())
+    hres = torch.empty(N, dtype=torch.bfloat16).pin_memory()
+    h2d = hx.numel() * hx.element_size() + hidx.numel() * hidx.element_size()
+    d2h = hres.numel() * hres.element_size()
+
+    def e2e_step():
+        wl.x.copy_(hx, non_blocking=True)
+        wl.idx.copy_(hidx, non_blocking=True)
+        full_step()
+        hres.copy_(wl.db, non_blocking=True)
+        torch.cuda.current_stream().synchronize()  # the caller consumes the result
+
+    for _ in range(min(args.warmup, 3)):
+        e2e_step()
+    barrier()
+    e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e2.record()
+    for _ in range(args.steps):
+        e2e_step()
+    e3.record()
+    barrier()
+    ms_e2e = e2.elapsed_time(e3)
+
+    # max over ranks, as the contract asks
+    if world > 1:
+        t = torch.tensor([ms_total, ms_e2e], device=device, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_total, ms_e2e = t.tolist()
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    tf_peak, hbm_peak, peak_src = load_peaks()
+    ms_per_step = ms_total / args.steps
+    value = SAMPLES_PER_STEP * n_gpus / (ms_per_step * 1e-3)
+    gemm_avg_ms = sum(gemm_ms) / len(gemm_ms)
+    achieved = GEMM_FLOP / (gemm_avg_ms * 1e-3) / 1e12
+    traffic = None
+    tr = ROOT / "profiles" / "gemm_traffic_bytes.json"
+    if tr.exists():
+        try:
+            traffic = json.loads(tr.read_text()).get("dram_bytes_per_launch")
+        except Exception:
+            traffic = None
+
+    out = {
+        "metric": "training samples/sec (per-op microbench step, fwd+bwd)",
+        "value": value,
+        "unit": "samples/s",
+        "n_gpus": n_gpus,
+        "steps": args.steps,
+        "warmup": args.warmup,
+        "ms_per_step": ms_per_step,
+        "higher_is_better": True,
+        "scaling": "weak",
+        "vs_baseline": None,
+        "dtype": "bf16 (Linear, fp32 accumulate) + fp32 (Softmax/LayerNorm/ElementBinary/Embedding)",
+        "data": "synthetic",
+        "config": {
+            "workload": "BASELINE configs[1]: Linear 8192x4096x4096 bf16 fwd+bwd; Softmax fwd, LayerNorm "
+                        "fwd+bwd, ElementBinary add fwd+bwd on 8192x4096 fp32; Embedding 1Mx256 fp32 "
+                        "fwd+bwd with 65536 int64 indices",
+            "samples_per_step": SAMPLES_PER_STEP,
+            "l2": "inputs larger than L2 (step touches >2 GB; L2 is 126 MB), no explicit flush",
+            "parallelism": f"dp{n_gpus}" if n_gpus > 1 else "single",
+            "grad_sync": "NCCL all-reduce of dW/db/dgamma/dbeta per step" if n_gpus > 1 else "none",
+        },
+        "roofline": {
+            "kernel": "gemm_tc_kernel (tcgen05, Linear forward 8192x4096x4096 bf16, fused bias+ReLU)",
+            "bound": "tensor",
+            "achieved": achieved,
+            "peak": tf_peak,
+            "peak_source": f"{peak_src} MEASURED_PEAKS.json bf16_tflops (burst: the timed region is tens of ms)",
+            "unit": "TFLOP/s",
+            "frac": achieved / tf_peak,
+            "traffic": traffic,
+            "avg_launch_ms": gemm_avg_ms,
+            "launches_timed": len(gemm_ms),
+        },
+        "e2e": {
+            "value": SAMPLES_PER_STEP * n_gpus / (ms_e2e / args.steps * 1e-3),
+            "unit": "samples/s",
+            "h2d_bytes_per_step": h2d,
+            "d2h_bytes_per_step": d2h,
+            "ms_per_step": ms_e2e / args.steps,
+        },
+        "gpu_launches": args.steps * sum(LAUNCHES_PER_STEP.values()),
+        "abi_calls_timed": abi_calls,
+        "clocks": clock_info,
+    }
+    if n_gpus == 1 and not args.no_cpu_baseline:
+        out["cpu_baseline"] = cpu_baseline(threads=os.cpu_count() or 1, budget_s=20.0, kind_note="port")
+    print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+# ----------------------------------------------------------------------------- CPU arm
+def oracle_step(o, np, rows, erows, bufs=None):
+    """The same step on the CPU oracle at `rows` of the 8192 samples (erows embedding indices)."""
+    if bufs is None:
+        rng = np.random.default_rng(1234)
+        u = lambda *s: rng.uniform(-1, 1, size=s).astype(np.float32)
+        bufs = dict(x=u(rows, KDIM), w=u(N, KDIM) / 64, b=u(N), y=np.zeros((rows, N), np.float32),
+                    dy=u(rows, N), dx=np.zeros((rows, KDIM), np.float32), dw=np.zeros((N, KDIM), np.float32),
+                    db=np.zeros(N, np.float32), a=u(rows, COLS), c=u(rows, COLS),
+                    o=np.zeros((rows, COLS), np.float32), ga=np.zeros((rows, COLS), np.float32),
+                    gc=np.zeros((rows, COLS), np.float32), gamma=u(COLS) + 1, beta=u(COLS),
+                    dgamma=np.zeros(COLS, np.float32), dbeta=np.zeros(COLS, np.float32),
+                    mean=np.zeros(rows, np.float32), rstd=np.zeros(rows, np.float32),
+                    table=u(20000, EDIM), dtable=np.zeros((20000, EDIM), np.float32),
+                    idx=rng.integers(0, 20000, erows, dtype=np.int64), eout=np.zeros((erows, EDIM), np.float32))
+    B = bufs
+    dy = B["dy"].copy()
+    o.linear_forward(B["x"], B["w"], B["b"], B["y"], KDIM, N, rows, 0)
+    o.linear_backward(B["x"], B["dx"], B["y"], dy, B["w"], B["dw"], B["db"], KDIM, N, rows, 0, 0.0, None)
+    o.softmax_forward(B["a"], B["o"], rows, COLS, 1)
+    o.layer_norm_forward(B["a"], B["o"], B["gamma"], B["beta"], B["mean"], B["rstd"], rows, COLS, 1e-5)
+    o.layer_norm_backward(B["c"], B["a"], B["ga"], B["gamma"], B["dgamma"], B["dbeta"], B["mean"], B["rstd"], rows, COLS, 0)
+    shp = [rows, COLS]
+    o.element_binary_forward(28, B["a"], B["c"], B["o"], 2, shp, shp, shp)
+    o.element_binary_backward(28, B["o"], B["a"], B["c"], B["ga"], B["gc"], 2, shp, shp, shp)
+    o.embedding_forward(B["idx"], B["eout"], B["table"], -1, 1, EDIM, erows)
+    o.embedding_backward(B["idx"], B["eout"], B["dtable"], -1, 1, EDIM, erows)
+    return bufs
+
+
+def cpu_baseline(threads, budget_s, kind_note):
+    import numpy as np
+    sys.path.insert(0, str(ROOT / "tests"))
+    import oracle as oracle_mod
+
+    os.environ["OMP_NUM_THREADS"] = str(threads)
+    o = oracle_mod.load()
+    rows = 128
+    bufs = oracle_step(o, np, rows, rows * 8)  # warm-up + allocation
+    t0 = time.perf_counter()
+    n = 0
+    while True:
+        oracle_step(o, np, rows, rows * 8, bufs)
+        n += 1
+        if time.perf_counter() - t0 > budget_s / 2 or n >= 5:
+            break
+    dt = (time.perf_counter() - t0) / n
+    return {"value": rows / dt, "unit": "samples/s", "cores": threads, "kind": kind_note,
+            "sample": f"{rows} of {M} rows of the same step ({rows * 8} of {EBATCH} embedding indices, "
+                      f"20000-row table) on the CPU oracle (OpenMP, {threads} threads); {n} repeats, "
+                      f"{dt:.2f} s each"}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import numpy as np
+    sys.path.insert(0, str(ROOT / "tests"))
+    import oracle as oracle_mod
+
+    threads = os.cpu_count() or 1
+    os.environ["OMP_NUM_THREADS"] = str(threads)
+    o = oracle_mod.load()
+    rows = 128
+    bufs = oracle_step(o, np, rows, rows * 8)
+    for _ in range(min(args.warmup, 1)):
+        oracle_step(o, np, rows, rows * 8, bufs)
+    steps = max(1, min(args.steps, 5))
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        oracle_step(o, np, rows, rows * 8, bufs)
+    dt = (time.perf_counter() - t0) / steps
+    value = rows / dt
+    sample = (f"each step = {rows} of {M} rows of the workload step ({rows * 8} embedding indices, 20000-row "
+              f"table); {steps} timed steps of {dt:.2f} s")
+    out = {
+        "impl": "reference",
+        "metric": "training samples/sec (per-op microbench step, fwd+bwd)",
+        "value": value, "unit": "samples/s", "n_gpus": args.gpus, "steps": steps, "warmup": min(args.warmup, 1),
+        "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32 (double accumulation)", "data": "synthetic",
+        "config": {"workload": "BASELINE configs[1] step, bounded sample on host cores", "samples_per_step": rows},
+        "cpu_baseline": {"value": value, "unit": "samples/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "note": "the reference has no CPU op kernels and cannot be compiled here (SURVEY F1/F2): this arm times "
+                "oracle/cpu_ref.cc, the CPU restatement of its .cu bodies",
+    }
+    print(json.dumps(out), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "ours":
+        args.warmup = 3  # timing rule: at least 3 warm-up steps
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_gpu(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -81,6 +81,57 @@ __global__ void __launch_bounds__(256)
   }
 }
 
+
+// Bias gradient at HBM speed: phase 1 sums a slab of rows per CTA into fp32 partials
+// part[split][col] (16-byte loads, 32 lanes x 8 row-lanes), phase 2 adds the partials to db
+// in split order. Deterministic; needs split*cols floats of scratch.
+template <typename T>
+__global__ void __launch_bounds__(256)
+    column_sum_partial_kernel(T const *__restrict__ dy, float *__restrict__ part, int rows,
+                              int cols, int rows_per_split) {
+  constexpr int VN = Vec16<T>::N;
+  __shared__ float sm[8][32 * VN + 1];
+  int const cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
+  int const col = (blockIdx.x * 32 + cx) * VN;
+  int const r0 = blockIdx.y * rows_per_split;
+  int const r1 = min(rows, r0 + rows_per_split);
+  float acc[VN];
+#pragma unroll
+  for (int j = 0; j < VN; ++j) acc[j] = 0.f;
+  if (col < cols) {
+    for (int r = r0 + ry; r < r1; r += 8) {
+      Vec16<T> v = ld_stream(dy + size_t(r) * cols + col);
+#pragma unroll
+      for (int j = 0; j < VN; ++j) acc[j] += to_f32(v.v[j]);
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < VN; ++j) sm[ry][cx * VN + j] = acc[j];
+  __syncthreads();
+  for (int c = threadIdx.x; c < 32 * VN; c += 256) {
+    int gc = blockIdx.x * 32 * VN + c;
+    if (gc < cols) {
+      float t = 0.f;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) t += sm[i][c];
+      part[size_t(blockIdx.y) * cols + gc] = t;
+    }
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+    column_sum_finish_kernel(float const *__restrict__ part, T *__restrict__ db, int cols,
+                             int splits) {
+  int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= cols) return;
+  float t = 0.f;
+  for (int s = 0; s < splits; ++s) t += part[size_t(s) * cols + c];
+  db[c] = from_f32<T>(to_f32(db[c]) + t);
+}
+
+constexpr int kBiasGradSplits = 32;
+
 }  // namespace
 }  // namespace ffk
 
@@ -117,7 +168,8 @@ int ffk_linear_forward(void *stream, void const *input, void *output, void const
 int ffk_linear_backward(void *stream, void const *input, void *input_grad, void const *output,
                         void *output_grad, void const *weight, void *weight_grad,
                         void *bias_grad, int in_dim, int out_dim, int batch_size, int dtype,
-                        int activation, float l2_lambda, void const *preact, int path) {
+                        int activation, float l2_lambda, void const *preact, int path,
+                        void *workspace, size_t workspace_bytes) {
   FFK_REQUIRE(in_dim > 0 && out_dim > 0 && batch_size >= 0, "linear backward: bad extents");
   if (batch_size == 0) return FFK_OK;
   FFK_REQUIRE(input && output_grad && weight && weight_grad, "linear backward: null tensor");
@@ -154,9 +206,25 @@ int ffk_linear_backward(void *stream, void const *input, void *input_grad, void 
   }
   if (bias_grad) {
     FFK_DISPATCH_FLOAT(dtype, T, {
-      column_sum_accumulate_kernel<T><<<(out_dim + 31) / 32, 256, 0, s>>>(
-          reinterpret_cast<T const *>(output_grad), reinterpret_cast<T *>(bias_grad), batch_size,
-          out_dim);
+      constexpr int VN = Vec16<T>::N;
+      int splits = workspace ? int(std::min<size_t>(kBiasGradSplits,
+                                                    workspace_bytes / (size_t(out_dim) * 4)))
+                             : 0;
+      splits = std::min(splits, (batch_size + 63) / 64);
+      if (splits >= 2 && out_dim % VN == 0 && aligned16(output_grad)) {
+        int rps = (batch_size + splits - 1) / splits;
+        dim3 grid((out_dim / VN + 31) / 32, splits);
+        column_sum_partial_kernel<T><<<grid, 256, 0, s>>>(
+            reinterpret_cast<T const *>(output_grad), reinterpret_cast<float *>(workspace),
+            batch_size, out_dim, rps);
+        column_sum_finish_kernel<T><<<(out_dim + 255) / 256, 256, 0, s>>>(
+            reinterpret_cast<float const *>(workspace), reinterpret_cast<T *>(bias_grad), out_dim,
+            splits);
+      } else {
+        column_sum_accumulate_kernel<T><<<(out_dim + 31) / 32, 256, 0, s>>>(
+            reinterpret_cast<T const *>(output_grad), reinterpret_cast<T *>(bias_grad),
+            batch_size, out_dim);
+      }
     });
     FFK_LAUNCH_CHECK();
   }
@@ -168,6 +236,10 @@ int ffk_linear_backward(void *stream, void const *input, void *input_grad, void 
     if (rc) return rc;
   }
   return FFK_OK;
+}
+
+size_t ffk_linear_backward_workspace_bytes(int out_dim) {
+  return out_dim > 0 ? size_t(kBiasGradSplits) * size_t(out_dim) * sizeof(float) : 0;
 }
 
 int ffk_batch_matmul_forward(void *stream, void *output, void const *a_input, void const *b_input,

@@ -53,18 +53,32 @@ __device__ __forceinline__ void epilogue_row_chunk(uint32_t const (&acc)[32], Ep
 #pragma unroll
   for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(acc[i]) * ep.alpha;
   T *drow = reinterpret_cast<T *>(ep.d) + row_off + col0;
+  constexpr int VN = 16 / sizeof(T);
+  bool const full = vec_ok && ncols_valid == 32;
   if (ep.bias != nullptr) {
     T const *bp = reinterpret_cast<T const *>(ep.bias) + col0;
+    if (full && ep.bias_vec_ok) {
 #pragma unroll
-    for (int i = 0; i < 32; ++i)
-      if (i < ncols_valid) v[i] += to_f32(__ldg(bp + i));
+      for (int j = 0; j < 32 / VN; ++j) {
+        Vec16<T> t = ld_vec(bp + j * VN);
+#pragma unroll
+        for (int i = 0; i < VN; ++i) v[j * VN + i] += to_f32(t.v[i]);
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < 32; ++i)
+        if (i < ncols_valid) v[i] += to_f32(bp[i]);
+    }
   }
-  if (ep.act != ACT_NONE) {
+  // one branch per chunk, not per element
+  if (ep.act == ACT_RELU) {
 #pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = fmaxf(v[i], 0.f);
+  } else if (ep.act != ACT_NONE) {
+#pragma unroll 4
     for (int i = 0; i < 32; ++i) v[i] = apply_act(v[i], ep.act);
   }
-  constexpr int VN = 16 / sizeof(T);
-  if (vec_ok && ncols_valid == 32) {
+  if (full) {
     if (ep.r != nullptr) {
       T const *rp = reinterpret_cast<T const *>(ep.r) + row_off + col0;
 #pragma unroll
@@ -359,7 +373,9 @@ int launch_tc_inst(Problem const &p, Epilogue const &e, cudaStream_t stream) {
   size_t os = dtype_size(p.out_dtype);
   int vec_ok = aligned16(e.d) && ((e.ldd * os) % 16 == 0) && ((e.d_batch * os) % 16 == 0) &&
                (e.r == nullptr || aligned16(e.r));
-  kern<<<grid, NUM_THREADS, Plan::TOTAL, stream>>>(ma, mb, e, p.M, p.N, p.K, p.batch, idesc,
+  Epilogue e2 = e;
+  e2.bias_vec_ok = e.bias != nullptr && aligned16(e.bias) && vec_ok;
+  kern<<<grid, NUM_THREADS, Plan::TOTAL, stream>>>(ma, mb, e2, p.M, p.N, p.K, p.batch, idesc,
                                                    p.out_dtype, vec_ok);
   FFK_LAUNCH_CHECK();
   return FFK_OK;

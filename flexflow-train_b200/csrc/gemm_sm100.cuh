@@ -30,6 +30,7 @@ struct Epilogue {
   float alpha;           // scale on the product
   float lambda;          // optional regulariser: D += lambda * R
   void const *r;         // R, same layout/dtype as D (may be null)
+  int bias_vec_ok = 0;   // set by the launcher: bias readable as 16-byte packets
 };
 
 // Problem in "logical" terms. a/b pointers are the stored matrices:

@@ -256,32 +256,47 @@ __global__ void __launch_bounds__(kThreads)
 // non-null, this CTA's partial column sums for dgamma / dbeta:
 //   part[(blockIdx.x*2 + 0)*N + j] = sum over this CTA's rows of dy*(x-mean)*rstd
 //   part[(blockIdx.x*2 + 1)*N + j] = sum over this CTA's rows of dy
+// gamma and the two running column sums live in shared memory (3*N floats, accessed as
+// float4 so a warp touches consecutive banks); each thread owns fixed columns, so no
+// synchronisation is needed on them. Registers hold only the current row's dY and X
+// packets, which keeps 3-4 CTAs resident per SM to overlap one row's reduction with the
+// next row's loads.
 template <typename T, int P>
-__global__ void __launch_bounds__(kThreads, 2)
+__global__ void __launch_bounds__(kThreads)
     layer_norm_bwd_rows_kernel(T const *__restrict__ dy, T const *__restrict__ x,
                                T *__restrict__ dx, T const *__restrict__ gamma,
                                float const *__restrict__ mean, float const *__restrict__ rstd,
                                float *__restrict__ part, long long rows, int nvec) {
   constexpr int VN = Vec16<T>::N;
+  constexpr int Q = VN / 4;  // float4 groups per packet
+  extern __shared__ float4 ln_smem[];
   __shared__ float red[64];
   long long const N = (long long)nvec * VN;
+  float4 *sg = ln_smem;                 // gamma
+  float4 *spg = ln_smem + N / 4;        // running sum for dgamma
+  float4 *spb = ln_smem + 2 * (N / 4);  // running sum for dbeta
   float const invn = 1.f / float(N);
-  float g[P][VN], pg[P][VN], pb[P][VN];
 #pragma unroll
   for (int p = 0; p < P; ++p) {
     int i = threadIdx.x + p * kThreads;
+    if (i < nvec) {
+      float gv[VN];
 #pragma unroll
-    for (int j = 0; j < VN; ++j) {
-      g[p][j] = 1.f;
-      pg[p][j] = 0.f;
-      pb[p][j] = 0.f;
-    }
-    if (gamma && i < nvec) {
-      Vec16<T> t = ld_vec(gamma + i * VN);
+      for (int j = 0; j < VN; ++j) gv[j] = 1.f;
+      if (gamma) {
+        Vec16<T> t = ld_vec(gamma + i * VN);
 #pragma unroll
-      for (int j = 0; j < VN; ++j) g[p][j] = to_f32(t.v[j]);
+        for (int j = 0; j < VN; ++j) gv[j] = to_f32(t.v[j]);
+      }
+#pragma unroll
+      for (int q = 0; q < Q; ++q) {
+        sg[i * Q + q] = make_float4(gv[q * 4], gv[q * 4 + 1], gv[q * 4 + 2], gv[q * 4 + 3]);
+        spg[i * Q + q] = make_float4(0.f, 0.f, 0.f, 0.f);
+        spb[i * Q + q] = make_float4(0.f, 0.f, 0.f, 0.f);
+      }
     }
   }
+  // no barrier needed: every thread only ever touches the shared slots it just wrote
   for (long long r = blockIdx.x; r < rows; r += gridDim.x) {
     T const *dyr = dy + r * N;
     T const *xr = x + r * N;
@@ -293,11 +308,17 @@ __global__ void __launch_bounds__(kThreads, 2)
       if (i < nvec) {
         Vec16<T> a = ld_stream(dyr + i * VN), b = ld_stream(xr + i * VN);
 #pragma unroll
-        for (int j = 0; j < VN; ++j) {
-          dv[p][j] = to_f32(a.v[j]);
-          xv[p][j] = to_f32(b.v[j]);
-          ds += dv[p][j] * xv[p][j] * g[p][j];
-          db += dv[p][j] * g[p][j];
+        for (int q = 0; q < Q; ++q) {
+          float4 g4 = sg[i * Q + q];
+          float gq[4] = {g4.x, g4.y, g4.z, g4.w};
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            float d = to_f32(a.v[q * 4 + j]), xx = to_f32(b.v[q * 4 + j]);
+            dv[p][q * 4 + j] = d;
+            xv[p][q * 4 + j] = xx;
+            ds += d * xx * gq[j];
+            db += d * gq[j];
+          }
         }
       }
     }
@@ -313,50 +334,82 @@ __global__ void __launch_bounds__(kThreads, 2)
           T *dxr = dx + r * N;
           Vec16<T> o = ld_vec(dxr + i * VN);
 #pragma unroll
-          for (int j = 0; j < VN; ++j)
-            o.v[j] = from_f32<T>(to_f32(o.v[j]) + rs * dv[p][j] * g[p][j] + c1 * xv[p][j] + c2);
+          for (int q = 0; q < Q; ++q) {
+            float4 g4 = sg[i * Q + q];
+            float gq[4] = {g4.x, g4.y, g4.z, g4.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              o.v[q * 4 + j] = from_f32<T>(to_f32(o.v[q * 4 + j]) + rs * dv[p][q * 4 + j] * gq[j] +
+                                           c1 * xv[p][q * 4 + j] + c2);
+          }
           st_vec(dxr + i * VN, o);
         }
+        if (part) {
 #pragma unroll
-        for (int j = 0; j < VN; ++j) {
-          pg[p][j] += dv[p][j] * (xv[p][j] - mu) * rs;
-          pb[p][j] += dv[p][j];
+          for (int q = 0; q < Q; ++q) {
+            float4 a4 = spg[i * Q + q], b4 = spb[i * Q + q];
+            a4.x += dv[p][q * 4 + 0] * (xv[p][q * 4 + 0] - mu) * rs;
+            a4.y += dv[p][q * 4 + 1] * (xv[p][q * 4 + 1] - mu) * rs;
+            a4.z += dv[p][q * 4 + 2] * (xv[p][q * 4 + 2] - mu) * rs;
+            a4.w += dv[p][q * 4 + 3] * (xv[p][q * 4 + 3] - mu) * rs;
+            b4.x += dv[p][q * 4 + 0];
+            b4.y += dv[p][q * 4 + 1];
+            b4.z += dv[p][q * 4 + 2];
+            b4.w += dv[p][q * 4 + 3];
+            spg[i * Q + q] = a4;
+            spb[i * Q + q] = b4;
+          }
         }
       }
     }
   }
   if (part) {
-    float *pgr = part + (size_t(blockIdx.x) * 2 + 0) * N;
-    float *pbr = part + (size_t(blockIdx.x) * 2 + 1) * N;
+    float4 *pgr = reinterpret_cast<float4 *>(part + (size_t(blockIdx.x) * 2 + 0) * N);
+    float4 *pbr = reinterpret_cast<float4 *>(part + (size_t(blockIdx.x) * 2 + 1) * N);
 #pragma unroll
     for (int p = 0; p < P; ++p) {
       int i = threadIdx.x + p * kThreads;
       if (i < nvec) {
 #pragma unroll
-        for (int j = 0; j < VN; ++j) {
-          pgr[i * VN + j] = pg[p][j];
-          pbr[i * VN + j] = pb[p][j];
+        for (int q = 0; q < Q; ++q) {
+          pgr[i * Q + q] = spg[i * Q + q];
+          pbr[i * Q + q] = spb[i * Q + q];
         }
       }
     }
   }
 }
 
-// Sum the per-CTA partials in CTA order (deterministic) and write / accumulate.
+// Sum the per-CTA partials in CTA order (deterministic) and write / accumulate. A CTA owns
+// 32 columns; its 8 row-lanes stride over the partial rows and are combined in lane order.
 template <typename T>
 __global__ void __launch_bounds__(kThreads)
     layer_norm_param_reduce_kernel(float const *__restrict__ part, int nparts, long long N,
                                    T *__restrict__ dgamma, T *__restrict__ dbeta,
                                    bool accumulate) {
-  long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (j >= N) return;
-  float sg = 0.f, sb = 0.f;
-  for (int p = 0; p < nparts; ++p) {
-    sg += part[(size_t(p) * 2 + 0) * N + j];
-    sb += part[(size_t(p) * 2 + 1) * N + j];
+  __shared__ float sg[8][33], sb[8][33];
+  int const cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
+  long long const j = (long long)blockIdx.x * 32 + cx;
+  float ag = 0.f, ab = 0.f;
+  if (j < N) {
+    for (int p = ry; p < nparts; p += 8) {
+      ag += part[(size_t(p) * 2 + 0) * N + j];
+      ab += part[(size_t(p) * 2 + 1) * N + j];
+    }
   }
-  if (dgamma) dgamma[j] = from_f32<T>(accumulate ? to_f32(dgamma[j]) + sg : sg);
-  if (dbeta) dbeta[j] = from_f32<T>(accumulate ? to_f32(dbeta[j]) + sb : sb);
+  sg[ry][cx] = ag;
+  sb[ry][cx] = ab;
+  __syncthreads();
+  if (ry == 0 && j < N) {
+    float tg = 0.f, tb = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      tg += sg[i][cx];
+      tb += sb[i][cx];
+    }
+    if (dgamma) dgamma[j] = from_f32<T>(accumulate ? to_f32(dgamma[j]) + tg : tg);
+    if (dbeta) dbeta[j] = from_f32<T>(accumulate ? to_f32(dbeta[j]) + tb : tb);
+  }
 }
 
 template <typename T>
@@ -598,7 +651,7 @@ int ffk_layer_norm_forward(void *stream, void const *input, void *output, void c
 
 size_t ffk_layer_norm_backward_workspace_bytes(long long N) {
   if (N <= 0) return 0;
-  return size_t(device_info().sm_count) * 2 /*CTAs per SM*/ * 2 /*dgamma,dbeta*/ * size_t(N) *
+  return size_t(device_info().sm_count) * 4 /*CTAs per SM*/ * 2 /*dgamma,dbeta*/ * size_t(N) *
          sizeof(float);
 }
 
@@ -622,17 +675,21 @@ int ffk_layer_norm_backward(void *stream, void const *output_grad, void const *i
     bool fused = vec && want_params && parts_fit >= 1;
     if (vec && (input_grad || fused)) {
       int nvec = int(N / VN), p = pick_p(nvec);
-      unsigned grid = rows_grid(M, 2);
+      size_t smem = size_t(3) * size_t(N) * sizeof(float);
+      int per_sm = (int)std::max<size_t>(1, std::min<size_t>(4, (200 * 1024) / (smem + 1024)));
+      unsigned grid = rows_grid(M, per_sm);
       if (fused) grid = (unsigned)std::min<size_t>(grid, parts_fit);
       FFK_DISPATCH_P(p, P, {
-        layer_norm_bwd_rows_kernel<T, P><<<grid, kThreads, 0, s>>>(
+        FFK_CUDA(cudaFuncSetAttribute(layer_norm_bwd_rows_kernel<T, P>,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        layer_norm_bwd_rows_kernel<T, P><<<grid, kThreads, smem, s>>>(
             reinterpret_cast<T const *>(output_grad), reinterpret_cast<T const *>(input),
             reinterpret_cast<T *>(input_grad), reinterpret_cast<T const *>(gamma), mean, rstd,
             fused ? reinterpret_cast<float *>(workspace) : nullptr, M, nvec);
       });
       FFK_LAUNCH_CHECK();
       if (fused) {
-        layer_norm_param_reduce_kernel<T><<<unsigned((N + kThreads - 1) / kThreads), kThreads, 0, s>>>(
+        layer_norm_param_reduce_kernel<T><<<unsigned((N + 31) / 32), kThreads, 0, s>>>(
             reinterpret_cast<float const *>(workspace), int(grid), N,
             reinterpret_cast<T *>(gamma_grad), reinterpret_cast<T *>(beta_grad),
             accumulate_param_grads != 0);

@@ -1,0 +1,452 @@
+// Layout kernels: strided block copy/add (Concat, Split), Transpose, Reverse, Reduce, Pool2D.
+#include "common.cuh"
+
+namespace ffk {
+namespace {
+
+constexpr int kThreads = 256;
+
+template <typename T, bool ADD>
+__global__ void __launch_bounds__(kThreads)
+    stride_block_kernel(T *__restrict__ out, T const *__restrict__ in, long long num_blocks,
+                        long long out_blk, long long in_blk) {
+  long long const mb = out_blk < in_blk ? out_blk : in_blk;
+  long long const n = num_blocks * mb, gs = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gs) {
+    long long b = i / mb, o = i - b * mb;
+    if (ADD) out[b * out_blk + o] = from_f32<T>(to_f32(out[b * out_blk + o]) + to_f32(in[b * in_blk + o]));
+    else out[b * out_blk + o] = in[b * in_blk + o];
+  }
+}
+
+// 16-byte packets when both block sizes and pointers allow it (rows of >= 1 packet).
+template <bool ADD>
+__global__ void __launch_bounds__(kThreads)
+    stride_block_vec_kernel(float *__restrict__ out, float const *__restrict__ in,
+                            long long num_blocks, long long out_blk4, long long in_blk4) {
+  long long const mb = out_blk4 < in_blk4 ? out_blk4 : in_blk4;
+  long long const n = num_blocks * mb, gs = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gs) {
+    long long b = i / mb, o = i - b * mb;
+    Vec16<float> v = ld_stream(in + (b * in_blk4 + o) * 4);
+    float *dst = out + (b * out_blk4 + o) * 4;
+    if (ADD) {
+      Vec16<float> d = ld_vec(dst);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) v.v[j] += d.v[j];
+    }
+    st_vec(dst, v);
+  }
+}
+
+struct Perm {
+  int nd;
+  long long out_dims[5];
+  long long in_strides[5];  // stride in the input of output dimension i
+};
+
+template <typename T>
+__global__ void __launch_bounds__(kThreads)
+    transpose_kernel(T const *__restrict__ in, T *__restrict__ out, long long n, Perm p,
+                     bool accumulate) {
+  long long const gs = (long long)gridDim.x * blockDim.x;
+  for (long long o = (long long)blockIdx.x * blockDim.x + threadIdx.x; o < n; o += gs) {
+    long long rem = o, src = 0;
+#pragma unroll
+    for (int d = 4; d >= 0; --d) {
+      if (d < p.nd) {
+        long long c = rem % p.out_dims[d];
+        rem /= p.out_dims[d];
+        src += c * p.in_strides[d];
+      }
+    }
+    if (accumulate) out[o] = from_f32<T>(to_f32(out[o]) + to_f32(in[src]));
+    else out[o] = in[src];
+  }
+}
+
+// Tiled 2-D transpose for the common "swap the two innermost dims" case: coalesced both ways.
+template <typename T>
+__global__ void __launch_bounds__(256)
+    transpose2d_kernel(T const *__restrict__ in, T *__restrict__ out, long long batch, int rows,
+                       int cols, bool accumulate) {
+  __shared__ T tile[32][33];
+  long long b = blockIdx.z;
+  int const c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+  int const tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  T const *src = in + b * (long long)rows * cols;
+  T *dst = out + b * (long long)rows * cols;
+  for (int j = ty; j < 32; j += 8)
+    if (r0 + j < rows && c0 + tx < cols) tile[j][tx] = src[(long long)(r0 + j) * cols + c0 + tx];
+  __syncthreads();
+  for (int j = ty; j < 32; j += 8) {
+    int oc = r0 + tx, orow = c0 + j;  // output is [cols][rows]
+    if (orow < cols && oc < rows) {
+      long long o = (long long)orow * rows + oc;
+      dst[o] = accumulate ? from_f32<T>(to_f32(dst[o]) + to_f32(tile[tx][j])) : tile[tx][j];
+    }
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kThreads)
+    reverse_kernel(T const *__restrict__ in, T *__restrict__ out, long long blks, long long rsize,
+                   long long inner) {
+  long long const n = blks * rsize * inner, gs = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gs) {
+    long long b = i / (rsize * inner), rem = i - b * rsize * inner;
+    long long r = rem / inner, k = rem - r * inner;
+    out[i] = in[b * rsize * inner + (rsize - 1 - r) * inner + k];
+  }
+}
+
+struct RedGeom {
+  int nd;
+  long long in_dims[5], out_dims[5];
+  long long in_strides[5];
+};
+
+// One CTA per output element (grid-strided): sums the input elements that collapse onto it.
+template <typename T>
+__global__ void __launch_bounds__(kThreads)
+    reduce_fwd_kernel(T const *__restrict__ in, T *__restrict__ out, long long out_n,
+                      long long red_n, float scale, RedGeom g) {
+  __shared__ float red[32];
+  for (long long e = blockIdx.x; e < out_n; e += gridDim.x) {
+    long long base = 0, rem = e;
+#pragma unroll
+    for (int d = 4; d >= 0; --d)
+      if (d < g.nd) {
+        long long c = rem % g.out_dims[d];
+        rem /= g.out_dims[d];
+        base += c * g.in_strides[d];
+      }
+    float acc = 0.f;
+    for (long long k = threadIdx.x; k < red_n; k += blockDim.x) {
+      long long kr = k, off = 0;
+#pragma unroll
+      for (int d = 4; d >= 0; --d)
+        if (d < g.nd && g.out_dims[d] == 1 && g.in_dims[d] != 1) {
+          long long c = kr % g.in_dims[d];
+          kr /= g.in_dims[d];
+          off += c * g.in_strides[d];
+        }
+      acc += to_f32(in[base + off]);
+    }
+    float tot = block_sum(acc, red);
+    if (threadIdx.x == 0) out[e] = from_f32<T>(tot * scale);
+    __syncthreads();
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kThreads)
+    reduce_bwd_kernel(T const *__restrict__ dout, T *__restrict__ din, long long in_n, float alpha,
+                      RedGeom g) {
+  long long const gs = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < in_n; i += gs) {
+    long long rem = i, o = 0, ostride = 1;
+#pragma unroll
+    for (int d = 4; d >= 0; --d)
+      if (d < g.nd) {
+        long long c = rem % g.in_dims[d];
+        rem /= g.in_dims[d];
+        if (g.out_dims[d] != 1) o += c * ostride;
+        ostride *= g.out_dims[d];
+      }
+    din[i] = from_f32<T>(to_f32(din[i]) + alpha * to_f32(dout[o]));
+  }
+}
+
+__global__ void __launch_bounds__(kThreads)
+    pool2d_fwd_kernel(float const *__restrict__ x, float *__restrict__ y, long long total, int ih,
+                      int iw, int oh, int ow, int kh, int kw, int sh, int sw, int ph, int pw,
+                      int type) {
+  long long const gs = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gs) {
+    int wo = int(i % ow);
+    int ho = int((i / ow) % oh);
+    long long nc = i / ((long long)ow * oh);
+    float const *plane = x + nc * (long long)ih * iw;
+    int h0 = ho * sh - ph, w0 = wo * sw - pw;
+    float acc = type == FFK_POOL_MAX ? -INFINITY : 0.f;
+    int cnt = 0;
+    for (int a = 0; a < kh; ++a) {
+      int h = h0 + a;
+      if (h < 0 || h >= ih) continue;
+      for (int b = 0; b < kw; ++b) {
+        int w = w0 + b;
+        if (w < 0 || w >= iw) continue;
+        float v = plane[h * iw + w];
+        if (type == FFK_POOL_MAX) acc = fmaxf(acc, v);
+        else acc += v;
+        ++cnt;
+      }
+    }
+    y[i] = type == FFK_POOL_MAX ? acc : (cnt ? acc / float(cnt) : 0.f);
+  }
+}
+
+__global__ void __launch_bounds__(kThreads)
+    pool2d_bwd_kernel(float const *__restrict__ x, float *__restrict__ dx,
+                      float const *__restrict__ y, float const *__restrict__ dy, long long total,
+                      int ih, int iw, int oh, int ow, int kh, int kw, int sh, int sw, int ph,
+                      int pw, int type) {
+  long long const gs = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gs) {
+    int wo = int(i % ow);
+    int ho = int((i / ow) % oh);
+    long long nc = i / ((long long)ow * oh);
+    float const *plane = x + nc * (long long)ih * iw;
+    float *gplane = dx + nc * (long long)ih * iw;
+    int h0 = ho * sh - ph, w0 = wo * sw - pw;
+    float g = dy[i];
+    if (type == FFK_POOL_MAX) {
+      float m = y[i];
+      bool done = false;
+      for (int a = 0; a < kh && !done; ++a) {
+        int h = h0 + a;
+        if (h < 0 || h >= ih) continue;
+        for (int b = 0; b < kw; ++b) {
+          int w = w0 + b;
+          if (w < 0 || w >= iw) continue;
+          if (plane[h * iw + w] == m) {
+            atomicAdd(gplane + h * iw + w, g);
+            done = true;
+            break;
+          }
+        }
+      }
+    } else {
+      int cnt = 0;
+      for (int a = 0; a < kh; ++a) {
+        int h = h0 + a;
+        if (h < 0 || h >= ih) continue;
+        for (int b = 0; b < kw; ++b) {
+          int w = w0 + b;
+          if (w >= 0 && w < iw) ++cnt;
+        }
+      }
+      if (!cnt) continue;
+      float share = g / float(cnt);
+      for (int a = 0; a < kh; ++a) {
+        int h = h0 + a;
+        if (h < 0 || h >= ih) continue;
+        for (int b = 0; b < kw; ++b) {
+          int w = w0 + b;
+          if (w >= 0 && w < iw) atomicAdd(gplane + h * iw + w, share);
+        }
+      }
+    }
+  }
+}
+
+template <bool ADD>
+int stride_block(void *stream, void *output, void const *input, long long num_blocks,
+                 long long out_blk, long long in_blk, int dtype) {
+  FFK_REQUIRE(num_blocks >= 0 && out_blk >= 0 && in_blk >= 0, "copy_with_stride: negative extent");
+  long long mb = out_blk < in_blk ? out_blk : in_blk;
+  if (num_blocks * mb == 0) return FFK_OK;
+  FFK_REQUIRE(output && input, "copy_with_stride: null tensor");
+  cudaStream_t s = as_stream(stream);
+  if (dtype == FFK_FLOAT && out_blk % 4 == 0 && in_blk % 4 == 0 && aligned16(output) &&
+      aligned16(input)) {
+    unsigned grid = stream_grid(size_t(num_blocks * mb / 4), kThreads, 8);
+    stride_block_vec_kernel<ADD><<<grid, kThreads, 0, s>>>((float *)output, (float const *)input,
+                                                           num_blocks, out_blk / 4, in_blk / 4);
+    FFK_LAUNCH_CHECK();
+    return FFK_OK;
+  }
+  FFK_DISPATCH_FLOAT(dtype, T, {
+    unsigned grid = stream_grid(size_t(num_blocks * mb), kThreads, 8);
+    stride_block_kernel<T, ADD><<<grid, kThreads, 0, s>>>((T *)output, (T const *)input,
+                                                          num_blocks, out_blk, in_blk);
+  });
+  FFK_LAUNCH_CHECK();
+  return FFK_OK;
+}
+
+int fill_red(int ndims, long long const *id, long long const *od, RedGeom &g, long long &in_n,
+             long long &out_n) {
+  FFK_REQUIRE(ndims >= 1 && ndims <= 5, "reduce: ndims must be 1..5");
+  FFK_REQUIRE(id && od, "reduce: null shape");
+  g.nd = ndims;
+  in_n = out_n = 1;
+  long long st = 1;
+  for (int d = ndims - 1; d >= 0; --d) {
+    FFK_REQUIRE(id[d] > 0 && (od[d] == id[d] || od[d] == 1), "reduce: dim %d: out %lld vs in %lld",
+                d, od[d], id[d]);
+    g.in_dims[d] = id[d];
+    g.out_dims[d] = od[d];
+    g.in_strides[d] = st;
+    st *= id[d];
+    in_n *= id[d];
+    out_n *= od[d];
+  }
+  return FFK_OK;
+}
+
+}  // namespace
+}  // namespace ffk
+
+using namespace ffk;
+
+extern "C" {
+
+int ffk_copy_with_stride(void *stream, void *output, void const *input, long long num_blocks,
+                         long long output_blk_size, long long input_blk_size, int dtype) {
+  return stride_block<false>(stream, output, input, num_blocks, output_blk_size, input_blk_size, dtype);
+}
+int ffk_add_with_stride(void *stream, void *output, void const *input, long long num_blocks,
+                        long long output_blk_size, long long input_blk_size, int dtype) {
+  return stride_block<true>(stream, output, input, num_blocks, output_blk_size, input_blk_size, dtype);
+}
+
+int ffk_transpose(void *stream, void const *input, void *output, int ndims,
+                  long long const *input_dims_host, int const *perm_host, int accumulate,
+                  int dtype) {
+  FFK_REQUIRE(ndims >= 1 && ndims <= 5, "transpose: ndims must be 1..5");
+  FFK_REQUIRE(input_dims_host && perm_host, "transpose: null shape/perm");
+  long long in_strides[5], n = 1;
+  bool seen[5] = {false, false, false, false, false};
+  for (int d = ndims - 1; d >= 0; --d) {
+    FFK_REQUIRE(input_dims_host[d] >= 0, "transpose: negative extent");
+    in_strides[d] = n;
+    n *= input_dims_host[d];
+  }
+  Perm p{};
+  p.nd = ndims;
+  for (int i = 0; i < ndims; ++i) {
+    int s = perm_host[i];
+    FFK_REQUIRE(s >= 0 && s < ndims && !seen[s], "transpose: perm is not a permutation");
+    seen[s] = true;
+    p.out_dims[i] = input_dims_host[s];
+    p.in_strides[i] = in_strides[s];
+  }
+  if (n == 0) return FFK_OK;
+  FFK_REQUIRE(input && output, "transpose: null tensor");
+  cudaStream_t s = as_stream(stream);
+  // innermost-two swap (leading dims untouched): tiled path
+  bool swap2 = ndims >= 2 && perm_host[ndims - 1] == ndims - 2 && perm_host[ndims - 2] == ndims - 1;
+  for (int i = 0; i < ndims - 2 && swap2; ++i) swap2 = perm_host[i] == i;
+  long long batch = 1;
+  for (int i = 0; i < ndims - 2; ++i) batch *= input_dims_host[i];
+  if (swap2 && batch <= 65535) {
+    int rows = (int)input_dims_host[ndims - 2], cols = (int)input_dims_host[ndims - 1];
+    dim3 grid((cols + 31) / 32, (rows + 31) / 32, (unsigned)batch);
+    if (grid.y <= 65535) {
+      FFK_DISPATCH_FLOAT(dtype, T, {
+        transpose2d_kernel<T><<<grid, 256, 0, s>>>((T const *)input, (T *)output, batch, rows,
+                                                   cols, accumulate != 0);
+      });
+      FFK_LAUNCH_CHECK();
+      return FFK_OK;
+    }
+  }
+  FFK_DISPATCH_FLOAT(dtype, T, {
+    unsigned grid = stream_grid(size_t(n), kThreads, 8);
+    transpose_kernel<T><<<grid, kThreads, 0, s>>>((T const *)input, (T *)output, n, p,
+                                                  accumulate != 0);
+  });
+  FFK_LAUNCH_CHECK();
+  return FFK_OK;
+}
+
+int ffk_reverse(void *stream, void const *input, void *output, long long num_out_blks,
+                long long reverse_dim_size, long long in_blk_size, int dtype) {
+  FFK_REQUIRE(num_out_blks >= 0 && reverse_dim_size >= 0 && in_blk_size >= 0, "reverse: negative extent");
+  long long n = num_out_blks * reverse_dim_size * in_blk_size;
+  if (n == 0) return FFK_OK;
+  FFK_REQUIRE(input && output && input != output, "reverse: null or aliased tensors");
+  FFK_DISPATCH_FLOAT(dtype, T, {
+    unsigned grid = stream_grid(size_t(n), kThreads, 8);
+    reverse_kernel<T><<<grid, kThreads, 0, as_stream(stream)>>>((T const *)input, (T *)output,
+                                                                num_out_blks, reverse_dim_size,
+                                                                in_blk_size);
+  });
+  FFK_LAUNCH_CHECK();
+  return FFK_OK;
+}
+
+int ffk_reduce_forward(void *stream, void const *input, void *output, int ndims,
+                       long long const *input_dims_host, long long const *output_dims_host,
+                       int op_type, int dtype) {
+  FFK_REQUIRE(op_type == FFK_OP_REDUCE_SUM || op_type == FFK_OP_REDUCE_MEAN,
+              "reduce: op_type must be REDUCE_SUM or REDUCE_MEAN");
+  RedGeom g{};
+  long long in_n, out_n;
+  int rc = fill_red(ndims, input_dims_host, output_dims_host, g, in_n, out_n);
+  if (rc) return rc;
+  if (out_n == 0) return FFK_OK;
+  FFK_REQUIRE(input && output, "reduce: null tensor");
+  long long red_n = in_n / out_n;
+  float scale = op_type == FFK_OP_REDUCE_MEAN ? 1.f / float(red_n) : 1.f;
+  FFK_DISPATCH_FLOAT(dtype, T, {
+    unsigned grid = (unsigned)std::min<long long>(out_n, (long long)device_info().sm_count * 8);
+    reduce_fwd_kernel<T><<<grid, kThreads, 0, as_stream(stream)>>>((T const *)input, (T *)output,
+                                                                   out_n, red_n, scale, g);
+  });
+  FFK_LAUNCH_CHECK();
+  return FFK_OK;
+}
+
+int ffk_reduce_backward(void *stream, void const *output_grad, void *input_grad, int ndims,
+                        long long const *input_dims_host, long long const *output_dims_host,
+                        int op_type, int dtype) {
+  FFK_REQUIRE(op_type == FFK_OP_REDUCE_SUM || op_type == FFK_OP_REDUCE_MEAN,
+              "reduce: op_type must be REDUCE_SUM or REDUCE_MEAN");
+  RedGeom g{};
+  long long in_n, out_n;
+  int rc = fill_red(ndims, input_dims_host, output_dims_host, g, in_n, out_n);
+  if (rc) return rc;
+  if (in_n == 0) return FFK_OK;
+  FFK_REQUIRE(output_grad && input_grad, "reduce backward: null tensor");
+  float alpha = op_type == FFK_OP_REDUCE_MEAN ? 1.f / float(in_n / out_n) : 1.f;
+  FFK_DISPATCH_FLOAT(dtype, T, {
+    unsigned grid = stream_grid(size_t(in_n), kThreads, 8);
+    reduce_bwd_kernel<T><<<grid, kThreads, 0, as_stream(stream)>>>(
+        (T const *)output_grad, (T *)input_grad, in_n, alpha, g);
+  });
+  FFK_LAUNCH_CHECK();
+  return FFK_OK;
+}
+
+int ffk_pool2d_forward(void *stream, float const *input, float *output, int n, int c, int in_h,
+                       int in_w, int out_h, int out_w, int kernel_h, int kernel_w, int stride_h,
+                       int stride_w, int pad_h, int pad_w, int pool_type) {
+  FFK_REQUIRE(n >= 0 && c >= 0 && in_h > 0 && in_w > 0 && out_h > 0 && out_w > 0 && kernel_h > 0 &&
+                  kernel_w > 0 && stride_h > 0 && stride_w > 0 && pad_h >= 0 && pad_w >= 0,
+              "pool2d: bad geometry");
+  FFK_REQUIRE(pool_type == FFK_POOL_MAX || pool_type == FFK_POOL_AVG, "pool2d: bad pool_type");
+  long long total = (long long)n * c * out_h * out_w;
+  if (total == 0) return FFK_OK;
+  FFK_REQUIRE(input && output, "pool2d: null tensor");
+  unsigned grid = stream_grid(size_t(total), kThreads, 8);
+  pool2d_fwd_kernel<<<grid, kThreads, 0, as_stream(stream)>>>(input, output, total, in_h, in_w,
+                                                              out_h, out_w, kernel_h, kernel_w,
+                                                              stride_h, stride_w, pad_h, pad_w,
+                                                              pool_type);
+  FFK_LAUNCH_CHECK();
+  return FFK_OK;
+}
+
+int ffk_pool2d_backward(void *stream, float const *input, float *input_grad, float const *output,
+                        float const *output_grad, int n, int c, int in_h, int in_w, int out_h,
+                        int out_w, int kernel_h, int kernel_w, int stride_h, int stride_w,
+                        int pad_h, int pad_w, int pool_type) {
+  FFK_REQUIRE(n >= 0 && c >= 0 && in_h > 0 && in_w > 0 && out_h > 0 && out_w > 0 && kernel_h > 0 &&
+                  kernel_w > 0 && stride_h > 0 && stride_w > 0 && pad_h >= 0 && pad_w >= 0,
+              "pool2d: bad geometry");
+  FFK_REQUIRE(pool_type == FFK_POOL_MAX || pool_type == FFK_POOL_AVG, "pool2d: bad pool_type");
+  long long total = (long long)n * c * out_h * out_w;
+  if (total == 0) return FFK_OK;
+  FFK_REQUIRE(input && input_grad && output && output_grad, "pool2d backward: null tensor");
+  unsigned grid = stream_grid(size_t(total), kThreads, 8);
+  pool2d_bwd_kernel<<<grid, kThreads, 0, as_stream(stream)>>>(
+      input, input_grad, output, output_grad, total, in_h, in_w, out_h, out_w, kernel_h, kernel_w,
+      stride_h, stride_w, pad_h, pad_w, pool_type);
+  FFK_LAUNCH_CHECK();
+  return FFK_OK;
+}
+
+}  // extern "C"

@@ -86,14 +86,20 @@ class LinearPerDeviceState:
     l2_lambda: float = 0.0
     use_bias: bool = True
     path: int = GEMM_AUTO
+    workspace: Optional[torch.Tensor] = None  # PerDeviceFFHandle::workSpace stand-in
 
 
 class Linear:
     """linear_kernels.h"""
 
     @staticmethod
-    def init_kernel(activation=ACT_NONE, regularizer_lambda=0.0, use_bias=True, path=GEMM_AUTO):
-        return LinearPerDeviceState(activation, regularizer_lambda, use_bias, path)
+    def init_kernel(activation=ACT_NONE, regularizer_lambda=0.0, use_bias=True, path=GEMM_AUTO,
+                    out_dim=0, device="cuda"):
+        ws = None
+        if out_dim and use_bias:
+            nbytes = lib().cdll.ffk_linear_backward_workspace_bytes(out_dim)
+            ws = torch.empty(nbytes // 4, dtype=torch.float32, device=device)
+        return LinearPerDeviceState(activation, regularizer_lambda, use_bias, path, ws)
 
     @staticmethod
     def forward_kernel(stream, m, input, output, weight, bias, in_dim, out_dim, batch_size):
@@ -105,7 +111,8 @@ class Linear:
                         bias_grad, in_dim, out_dim, batch_size, preact=None):
         _call("ffk_linear_backward", _stream(stream), _ptr(input), _ptr(input_grad), _ptr(output),
               _ptr(output_grad), _ptr(weight), _ptr(weight_grad), _ptr(bias_grad), in_dim, out_dim,
-              batch_size, dtype_code(input), m.activation, m.l2_lambda, _ptr(preact), m.path)
+              batch_size, dtype_code(input), m.activation, m.l2_lambda, _ptr(preact), m.path,
+              _ptr(m.workspace), m.workspace.numel() * 4 if m.workspace is not None else 0)
 
 
 class BatchMatmul:
@@ -357,3 +364,267 @@ class BatchNorm:
         _call("ffk_batch_norm_backward", _stream(stream), _ptr(input), _ptr(output_grad),
               _ptr(output), _ptr(input_grad), _ptr(scale), _ptr(scale_grad), _ptr(bias_grad),
               _ptr(m.save_mean), _ptr(m.save_invstd), m.n, m.c, m.h, m.w, int(m.relu))
+
+
+# ------------------------------------------------------------------ index-driven
+AGGR_NONE, AGGR_SUM, AGGR_AVG = -1, 0, 1
+
+
+class Embedding:
+    """embedding_kernels.h"""
+
+    @staticmethod
+    def forward_kernel(stream, input, output, weight, aggr, in_dim, out_dim, batch_size):
+        _call("ffk_embedding_forward", _stream(stream), _ptr(input), _ptr(output), _ptr(weight),
+              dtype_code(input), dtype_code(weight), aggr, in_dim, out_dim, batch_size)
+
+    @staticmethod
+    def backward_kernel(stream, input, output_grad, weight_grad, aggr, in_dim, out_dim, batch_size):
+        _call("ffk_embedding_backward", _stream(stream), _ptr(input), _ptr(output_grad),
+              _ptr(weight_grad), dtype_code(input), dtype_code(weight_grad), aggr, in_dim, out_dim,
+              batch_size)
+
+    @staticmethod
+    def rand_generate_int(stream, t, p):
+        _call("ffk_rand_generate_int", _stream(stream), _ptr(t), t.numel(), p, dtype_code(t))
+
+
+class Gather:
+    """gather_kernels.h — `dim` is the FF (torch) dimension gathered along."""
+
+    @staticmethod
+    def _geom(input, output, dim):
+        stride = 1
+        for s in output.shape[dim + 1:]:
+            stride *= s
+        return output.numel(), stride, input.shape[dim], output.shape[dim]
+
+    @staticmethod
+    def forward_kernel(stream, dim, input, index, output):
+        n, stride, idim, odim = Gather._geom(input, output, dim)
+        _call("ffk_gather_forward", _stream(stream), _ptr(input), _ptr(index), _ptr(output), n,
+              stride, idim, odim, dtype_code(index), dtype_code(input))
+
+    @staticmethod
+    def backward_kernel(stream, dim, output_grad, index, input_grad):
+        n, stride, idim, odim = Gather._geom(input_grad, output_grad, dim)
+        _call("ffk_gather_backward", _stream(stream), _ptr(output_grad), _ptr(index),
+              _ptr(input_grad), n, stride, idim, odim, dtype_code(index), dtype_code(input_grad))
+
+
+class TopK:
+    """topk_kernels.h"""
+
+    @staticmethod
+    def forward_kernel(stream, input, output, indices, batch_size, length, k, sorted=True):
+        _call("ffk_topk_forward", _stream(stream), _ptr(input), _ptr(output), _ptr(indices),
+              batch_size, length, k, int(sorted))
+
+    @staticmethod
+    def backward_kernel(stream, out_grad, indices, in_grad, batch_size, length, k):
+        _call("ffk_topk_backward", _stream(stream), _ptr(out_grad), _ptr(indices), _ptr(in_grad),
+              batch_size, length, k)
+
+
+# ------------------------------------------------------------------ loss / optimizer / metrics
+def sparse_categorical_crossentropy_loss_backward_kernel(stream, logit_grad, logit, label,
+                                                         num_samples, num_classes, k, scale_factor):
+    _call("ffk_sparse_categorical_crossentropy_loss_backward", _stream(stream), _ptr(logit_grad),
+          _ptr(logit), _ptr(label), num_samples, num_classes, k, scale_factor, dtype_code(logit))
+
+
+def categorical_crossentropy_loss_backward_kernel(stream, logit_grad, logit, label, scale_factor):
+    _call("ffk_categorical_crossentropy_loss_backward", _stream(stream), _ptr(logit_grad),
+          _ptr(logit), _ptr(label), logit.numel(), scale_factor, dtype_code(logit))
+
+
+def mean_squared_error_avg_loss_backward_kernel(stream, logit_grad, logit, label, scale_factor):
+    _call("ffk_mean_squared_error_avg_loss_backward", _stream(stream), _ptr(logit_grad),
+          _ptr(logit), _ptr(label), logit.numel(), scale_factor, dtype_code(logit))
+
+
+def identity_loss_backward_kernel(stream, loss_grad, loss, scale_factor):
+    _call("ffk_identity_loss_backward", _stream(stream), _ptr(loss_grad), _ptr(loss),
+          loss_grad.numel(), scale_factor, dtype_code(loss_grad))
+
+
+def sgd_ps_update_task_gpu(stream, lr, momentum, nesterov, weight_decay, weight_grad, size,
+                           num_replicas, weight, sgd_v, master_weight=None):
+    _call("ffk_sgd_update", _stream(stream), lr, momentum, int(nesterov), weight_decay,
+          _ptr(weight_grad), size, num_replicas, _ptr(weight), _ptr(sgd_v), dtype_code(weight),
+          _ptr(master_weight))
+
+
+def adam_ps_update_task_gpu(stream, alpha_t, beta1, beta2, weight_decay, epsilon, weight_grad,
+                            size, num_replicas, adam_m, adam_v, weight, master_weight=None):
+    _call("ffk_adam_update", _stream(stream), alpha_t, beta1, beta2, weight_decay, epsilon,
+          _ptr(weight_grad), size, num_replicas, _ptr(adam_m), _ptr(adam_v), _ptr(weight),
+          dtype_code(weight), _ptr(master_weight))
+
+
+METRIC_ACCURACY, METRIC_CCE, METRIC_SPARSE_CCE, METRIC_MSE, METRIC_RMSE, METRIC_MAE = 1, 2, 4, 8, 16, 32
+
+
+class PerfMetrics:
+    """Device-side accumulator (ffk_perf_metrics_t) with the reference's accessors."""
+
+    def __init__(self, device="cuda"):
+        self.buf = torch.zeros(7, dtype=torch.int32, device=device)
+
+    def read(self):
+        raw = self.buf.cpu()
+        f = raw.view(torch.float32)
+        return dict(train_all=int(raw[0]), train_correct=int(raw[1]), cce_loss=float(f[2]),
+                    sparse_cce_loss=float(f[3]), mse_loss=float(f[4]), rmse_loss=float(f[5]),
+                    mae_loss=float(f[6]))
+
+
+def update_metrics_sparse_label_kernel(stream, metrics, logit, label, num_samples, num_classes, perf):
+    _call("ffk_update_metrics_sparse_label", _stream(stream), metrics, _ptr(logit), _ptr(label),
+          num_samples, num_classes, _ptr(perf.buf))
+
+
+def update_metrics_label_kernel(stream, metrics, logit, label, num_samples, num_classes, perf):
+    _call("ffk_update_metrics_label", _stream(stream), metrics, _ptr(logit), _ptr(label),
+          num_samples, num_classes, _ptr(perf.buf))
+
+
+# ------------------------------------------------------------------ layout ops
+def _ints(vals):
+    return (ctypes.c_int * len(vals))(*vals)
+
+
+class Concat:
+    """concat_kernels.h — `axis` is the FF (torch) dimension."""
+
+    @staticmethod
+    def _blocks(shape, axis):
+        num_blocks = 1
+        for s in shape[:axis]:
+            num_blocks *= s
+        blk = 1
+        for s in shape[axis:]:
+            blk *= s
+        return num_blocks, blk
+
+    @staticmethod
+    def forward_kernel(stream, output, inputs, axis):
+        nb, oblk = Concat._blocks(output.shape, axis)
+        off = 0
+        for t in inputs:
+            _, iblk = Concat._blocks(t.shape, axis)
+            _call("ffk_copy_with_stride", _stream(stream), output.data_ptr() + off * output.element_size(),
+                  _ptr(t), nb, oblk, iblk, dtype_code(t))
+            off += iblk
+
+    @staticmethod
+    def backward_kernel(stream, output_grad, input_grads, axis):
+        nb, oblk = Concat._blocks(output_grad.shape, axis)
+        off = 0
+        for g in input_grads:
+            _, iblk = Concat._blocks(g.shape, axis)
+            _call("ffk_add_with_stride", _stream(stream), _ptr(g),
+                  output_grad.data_ptr() + off * output_grad.element_size(), nb, iblk, oblk,
+                  dtype_code(g))
+            off += iblk
+
+
+class Split:
+    """split_kernels.h"""
+
+    @staticmethod
+    def forward_kernel(stream, outputs, input, out_blk_sizes, in_blk_size, num_blks):
+        off = 0
+        for t, blk in zip(outputs, out_blk_sizes):
+            _call("ffk_copy_with_stride", _stream(stream), _ptr(t),
+                  input.data_ptr() + off * input.element_size(), num_blks, blk, in_blk_size,
+                  dtype_code(t))
+            off += blk
+
+    @staticmethod
+    def backward_kernel(stream, input_grad, output_grads, out_blk_sizes, in_blk_size, num_blks):
+        off = 0
+        for g, blk in zip(output_grads, out_blk_sizes):
+            _call("ffk_add_with_stride", _stream(stream),
+                  input_grad.data_ptr() + off * input_grad.element_size(), _ptr(g), num_blks,
+                  in_blk_size, blk, dtype_code(g))
+            off += blk
+
+
+class Transpose:
+    """transpose_kernels.h — perm in FF order, torch.permute semantics."""
+
+    @staticmethod
+    def init_kernel(num_dim, perm):
+        assert len(perm) == num_dim
+        return list(perm)
+
+    @staticmethod
+    def forward_kernel(stream, m, input, output):
+        _call("ffk_transpose", _stream(stream), _ptr(input), _ptr(output), input.dim(),
+              _dims(input.shape), _ints(m), 0, dtype_code(input))
+
+    @staticmethod
+    def backward_kernel(stream, m, in_grad, out_grad):
+        inv = [0] * len(m)
+        for i, p in enumerate(m):
+            inv[p] = i
+        _call("ffk_transpose", _stream(stream), _ptr(out_grad), _ptr(in_grad), out_grad.dim(),
+              _dims(out_grad.shape), _ints(inv), 1, dtype_code(out_grad))
+
+
+class Reverse:
+    """reverse_kernels.h"""
+
+    @staticmethod
+    def forward_kernel(stream, in_t, out_t, num_out_blks, reverse_dim_size, in_blk_size):
+        _call("ffk_reverse", _stream(stream), _ptr(in_t), _ptr(out_t), num_out_blks,
+              reverse_dim_size, in_blk_size, dtype_code(in_t))
+
+    backward_kernel = forward_kernel
+
+
+class Reduce:
+    """reduce_kernels.h"""
+
+    @staticmethod
+    def forward_kernel(stream, op_type, input, output):
+        _call("ffk_reduce_forward", _stream(stream), _ptr(input), _ptr(output), input.dim(),
+              _dims(input.shape), _dims(output.shape), op_type, dtype_code(input))
+
+    @staticmethod
+    def backward_kernel(stream, op_type, output_grad, input_grad):
+        _call("ffk_reduce_backward", _stream(stream), _ptr(output_grad), _ptr(input_grad),
+              input_grad.dim(), _dims(input_grad.shape), _dims(output_grad.shape), op_type,
+              dtype_code(input_grad))
+
+
+POOL_MAX, POOL_AVG = 0, 1
+
+
+@dataclass
+class Pool2DPerDeviceState:
+    geom: tuple  # (n, c, ih, iw, oh, ow, kh, kw, sh, sw, ph, pw)
+    pool_type: int
+
+
+class Pool2D:
+    """pool_2d_kernels.h"""
+
+    @staticmethod
+    def init_kernel(input_w, input_h, input_c, input_n, output_w, output_h, output_c, output_n,
+                    pad_h, pad_w, kernel_h, kernel_w, stride_h, stride_w, pool_type):
+        assert output_h == (input_h + 2 * pad_h - kernel_h) // stride_h + 1
+        assert output_w == (input_w + 2 * pad_w - kernel_w) // stride_w + 1
+        assert output_c == input_c and output_n == input_n
+        return Pool2DPerDeviceState((input_n, input_c, input_h, input_w, output_h, output_w,
+                                     kernel_h, kernel_w, stride_h, stride_w, pad_h, pad_w), pool_type)
+
+    @staticmethod
+    def forward_kernel(stream, m, input, output):
+        _call("ffk_pool2d_forward", _stream(stream), _ptr(input), _ptr(output), *m.geom, m.pool_type)
+
+    @staticmethod
+    def backward_kernel(stream, m, input, input_grad, output, output_grad):
+        _call("ffk_pool2d_backward", _stream(stream), _ptr(input), _ptr(input_grad), _ptr(output),
+              _ptr(output_grad), *m.geom, m.pool_type)

@@ -42,11 +42,18 @@ int ffk_linear_forward(void *stream, void const *input, void *output, void const
  * The activation gradient is evaluated from the post-activation `output` (Y) for
  * RELU / SIGMOID / TANH. GELU needs the pre-activation values: pass them in `preact`
  * (same shape as Y); with preact == NULL a GELU request fails with FFK_ERR_UNSUPPORTED
- * (the reference asserts for anything but RELU / SIGMOID). */
+ * (the reference asserts for anything but RELU / SIGMOID).
+ * `workspace` (device scratch, optional — the reference keeps one in
+ * PerDeviceFFHandle::workSpace, include/kernels/ff_handle.h:17-18) lets the bias gradient run
+ * as a two-phase column reduction at HBM speed: ffk_linear_backward_workspace_bytes(out_dim)
+ * bytes; with NULL a single-pass kernel without scratch is used. Its contents are not
+ * preserved between calls. */
+size_t ffk_linear_backward_workspace_bytes(int out_dim);
 int ffk_linear_backward(void *stream, void const *input, void *input_grad, void const *output,
                         void *output_grad, void const *weight, void *weight_grad,
                         void *bias_grad, int in_dim, int out_dim, int batch_size, int dtype,
-                        int activation, float l2_lambda, void const *preact, int path);
+                        int activation, float l2_lambda, void const *preact, int path,
+                        void *workspace, size_t workspace_bytes);
 
 /* Kernels::BatchMatmul::forward_kernel — include/kernels/batch_matmul_kernels.h:12,
  * src/cuda/ops/batch_matmul_kernels.cu:23-84 (argument order of the DEFINITION).

@@ -543,3 +543,305 @@ ORACLE_API void oracle_batch_norm_backward(float const *x, float *dy, float cons
     }
   }
 }
+
+// ===================================================================== Embedding
+// lib/kernels/src/cuda/embedding_kernels.cu:63-141. aggr: -1 none, 0 SUM, 1 AVG (= mean over
+// the bag; the reference rescales inside the loop, :106-114 — SURVEY App. A). Indices int64.
+ORACLE_API void oracle_embedding_forward(int64_t const *idx, float *out, float const *table,
+                                         int aggr, int in_dim, int out_dim, int batch) {
+  int bag = aggr < 0 ? 1 : in_dim;
+#pragma omp parallel for schedule(static)
+  for (int b = 0; b < batch; ++b)
+    for (int o = 0; o < out_dim; ++o) {
+      if (aggr < 0) {
+        out[(size_t)b * out_dim + o] = table[(size_t)idx[b] * out_dim + o];
+      } else {
+        float acc = 0.f;
+        for (int j = 0; j < bag; ++j) acc += table[(size_t)idx[(size_t)b * bag + j] * out_dim + o];
+        if (aggr == 1) acc *= (float)(1.0 / (double)bag);
+        out[(size_t)b * out_dim + o] = acc;
+      }
+    }
+}
+// lib/kernels/src/cuda/embedding_kernels.cu:143-335: table_grad[idx] += grad (x 1/in_dim for AVG).
+// Sequential order here; the GPU uses atomics, so duplicates are compared with a tolerance.
+ORACLE_API void oracle_embedding_backward(int64_t const *idx, float const *dout, float *dtable,
+                                          int aggr, int in_dim, int out_dim, int batch) {
+  int bag = aggr < 0 ? 1 : in_dim;
+  float scale = aggr == 1 ? (float)(1.0 / (double)bag) : 1.f;
+  for (int b = 0; b < batch; ++b)
+    for (int j = 0; j < bag; ++j) {
+      size_t row = (size_t)idx[(size_t)b * bag + j];
+      for (int o = 0; o < out_dim; ++o)
+        dtable[row * out_dim + o] += dout[(size_t)b * out_dim + o] * scale;
+    }
+}
+
+// ===================================================================== Gather
+// lib/kernels/src/cuda/ops/gather_kernels.cu:26-77.
+ORACLE_API void oracle_gather_forward(float const *in, int64_t const *index, float *out,
+                                      long long n, long long stride, long long in_dim,
+                                      long long out_dim) {
+  for (long long o = 0; o < n; ++o) {
+    long long outer = o / (stride * out_dim), rest = o % stride;
+    out[o] = in[outer * stride * in_dim + index[o] * stride + rest];
+  }
+}
+ORACLE_API void oracle_gather_backward(float const *dout, int64_t const *index, float *din,
+                                       long long n, long long stride, long long in_dim,
+                                       long long out_dim) {
+  for (long long o = 0; o < n; ++o) {
+    long long outer = o / (stride * out_dim), rest = o % stride;
+    din[outer * stride * in_dim + index[o] * stride + rest] += dout[o];
+  }
+}
+
+// ===================================================================== TopK
+// lib/kernels/src/cuda/ops/topk_kernels.cu:342-437 (TensorFlow-derived heaps): k largest per
+// row, descending, ties -> lower index first; bwd scatter-add.
+ORACLE_API void oracle_topk_forward(float const *in, float *out, int *indices, size_t batch,
+                                    int length, int k) {
+  for (size_t b = 0; b < batch; ++b) {
+    std::vector<int> order(length);
+    for (int i = 0; i < length; ++i) order[i] = i;
+    float const *row = in + b * length;
+    std::stable_sort(order.begin(), order.end(), [&](int x, int y) { return row[x] > row[y]; });
+    for (int r = 0; r < k; ++r) {
+      out[b * k + r] = row[order[r]];
+      indices[b * k + r] = order[r];
+    }
+  }
+}
+ORACLE_API void oracle_topk_backward(float const *dout, int const *indices, float *din,
+                                     size_t batch, int length, int k) {
+  for (size_t i = 0; i < batch * (size_t)k; ++i) din[(i / k) * length + indices[i]] += dout[i];
+}
+
+// ===================================================================== losses
+// lib/kernels/src/cuda/loss_function_kernels.cu:21-31,59-84.
+ORACLE_API void oracle_sparse_cce_loss_backward(float *g, float const *p, int const *label,
+                                                int num_samples, int num_classes, int k,
+                                                float scale) {
+  size_t n = (size_t)num_samples * num_classes;
+  for (size_t i = 0; i < n; ++i) g[i] = p[i];
+  for (int i = 0; i < num_samples; ++i) g[(size_t)i * num_classes + label[i / k]] -= 1.0f;
+  float b = scale * k;
+  for (size_t i = 0; i < n; ++i) g[i] = (b - 0.f) * g[i] + 0.f;  // scale_kernel, cuda_helper.cu:32-36
+}
+// :33-49,86-122 (CCE and MSE-avg share the expression).
+ORACLE_API void oracle_diff_loss_backward(float *g, float const *p, float const *y, size_t n,
+                                          float scale) {
+  for (size_t i = 0; i < n; ++i) g[i] = (p[i] - y[i]) * scale;
+}
+
+// ===================================================================== optimizers
+// lib/kernels/src/cuda/optimizer_kernel.cu:20-41 (+ replica fold :52-57).
+ORACLE_API void oracle_sgd_update(float lr, float momentum, int nesterov, float wd,
+                                  float const *grad, size_t n, int reps, float *W, float *V) {
+  for (size_t i = 0; i < n; ++i) {
+    float g = grad[i];
+    for (int r = 1; r < reps; ++r) g += grad[(size_t)r * n + i];
+    float gt = g + wd * W[i];
+    if (momentum > 0.0f) {
+      V[i] = V[i] * momentum + gt;
+      gt = nesterov ? gt + momentum * V[i] : V[i];
+    }
+    W[i] -= lr * gt;
+  }
+}
+// lib/kernels/src/cuda/optimizer_kernel.cu:123-145.
+ORACLE_API void oracle_adam_update(float alpha_t, float b1, float b2, float wd, float eps,
+                                   float const *grad, size_t n, int reps, float *M, float *V,
+                                   float *W) {
+  for (size_t i = 0; i < n; ++i) {
+    float g = grad[i];
+    for (int r = 1; r < reps; ++r) g += grad[(size_t)r * n + i];
+    float gt = g + wd * W[i];
+    float mt = b1 * M[i] + (1 - b1) * gt;
+    float vt = b2 * V[i] + (1 - b2) * gt * gt;
+    M[i] = mt;
+    V[i] = vt;
+    W[i] -= alpha_t * mt / (std::sqrt(vt) + eps);
+  }
+}
+
+// ===================================================================== metrics
+// lib/kernels/src/cuda/metrics_functions.cu:23-71 (sparse labels) and :73-137 (dense labels).
+// out[7] = {train_all, train_correct, cce, sparse_cce, mse, rmse, mae} accumulated in double.
+ORACLE_API void oracle_metrics_sparse(int metrics, float const *logits, int const *labels,
+                                      int samples, int classes, double *out) {
+  for (int b = 0; b < samples; ++b) {
+    float const *row = logits + (size_t)b * classes;
+    if (metrics & 1) {
+      float mx = -1.0f;
+      int arg = -1;
+      for (int i = 0; i < classes; ++i)
+        if (row[i] > mx) { mx = row[i]; arg = i; }
+      out[0] += 1;
+      if (labels[b] == arg) out[1] += 1;
+    }
+    if (metrics & 4) out[3] += -std::log(std::max(row[labels[b]], 0.00000001f));
+    if (metrics & (8 | 16 | 32)) {
+      float mse = 0.f, mae = 0.f;
+      for (int i = 0; i < classes; ++i) {
+        float d = row[i] - (labels[b] == i ? 1.0f : 0.0f);
+        mse += d * d;
+        mae += std::fabs(d);
+      }
+      if (metrics & 8) out[4] += mse;
+      if (metrics & 16) out[5] += std::sqrt(mse);
+      if (metrics & 32) out[6] += mae;
+    }
+  }
+}
+ORACLE_API void oracle_metrics_label(int metrics, float const *logits, float const *labels,
+                                     int samples, int classes, double *out) {
+  for (int b = 0; b < samples; ++b) {
+    float const *row = logits + (size_t)b * classes;
+    float const *lab = labels + (size_t)b * classes;
+    out[0] += 1;
+    if (metrics & 1) {
+      if (classes == 1) {
+        out[0] += 1;
+        out[1] += 1;
+      } else {
+        float mx = 0.f;
+        int arg = -1, truth = -1;
+        for (int i = 0; i < classes; ++i) {
+          if (arg == -1 || row[i] > mx) { mx = row[i]; arg = i; }
+          if (lab[i] > 0.9f) truth = i;
+        }
+        if (truth == arg) out[1] += 1;
+      }
+    }
+    if (metrics & 2) {
+      float cce = 0.f;
+      for (int i = 0; i < classes; ++i)
+        if (lab[i] > 0.f) cce += lab[i] * -std::log(std::max(row[i], 0.00000001f));
+      out[2] += cce;
+    }
+    if (metrics & (8 | 16 | 32)) {
+      float mse = 0.f, mae = 0.f;
+      for (int i = 0; i < classes; ++i) {
+        float d = row[i] - lab[i];
+        mse += d * d;
+        mae += std::fabs(d);
+      }
+      if (metrics & 8) out[4] += mse;
+      if (metrics & 16) out[5] += std::sqrt(mse);
+      if (metrics & 32) out[6] += mae;
+    }
+  }
+}
+
+// ===================================================================== Concat / Split
+// lib/kernels/src/cuda/cuda_helper.cu:144-172 (copy_with_stride / add_with_stride), used by
+// concat_kernels.cu:33-88 and split_kernels.cu:23-58.
+ORACLE_API void oracle_copy_with_stride(float *out, float const *in, long long num_blocks,
+                                        long long out_blk, long long in_blk, int add) {
+  long long mb = std::min(out_blk, in_blk);
+  for (long long b = 0; b < num_blocks; ++b)
+    for (long long o = 0; o < mb; ++o) {
+      if (add) out[b * out_blk + o] += in[b * in_blk + o];
+      else out[b * out_blk + o] = in[b * in_blk + o];
+    }
+}
+
+// ===================================================================== Transpose
+// lib/kernels/src/cuda/ops/transpose_kernels.cu:45-120 — intended permutation
+// (out.shape[i] = in.shape[perm[i]], FF order); accumulate for the backward form.
+ORACLE_API void oracle_transpose(float const *in, float *out, int nd, long long const *in_dims,
+                                 long long const *perm, int accumulate) {
+  long long in_strides[5], out_dims[5], src_stride[5], n = 1;
+  for (int d = nd - 1; d >= 0; --d) { in_strides[d] = n; n *= in_dims[d]; }
+  for (int i = 0; i < nd; ++i) { out_dims[i] = in_dims[perm[i]]; src_stride[i] = in_strides[perm[i]]; }
+  for (long long o = 0; o < n; ++o) {
+    long long rem = o, src = 0;
+    for (int d = nd - 1; d >= 0; --d) { src += (rem % out_dims[d]) * src_stride[d]; rem /= out_dims[d]; }
+    if (accumulate) out[o] += in[src]; else out[o] = in[src];
+  }
+}
+
+// ===================================================================== Reverse
+// lib/kernels/src/cuda/ops/reverse_kernels.cu:24-37 — intended reversal along the middle axis.
+ORACLE_API void oracle_reverse(float const *in, float *out, long long blks, long long rsize,
+                               long long inner) {
+  for (long long b = 0; b < blks; ++b)
+    for (long long r = 0; r < rsize; ++r)
+      for (long long k = 0; k < inner; ++k)
+        out[(b * rsize + r) * inner + k] = in[(b * rsize + (rsize - 1 - r)) * inner + k];
+}
+
+// ===================================================================== Reduce
+// lib/kernels/src/cuda/ops/reduce_kernels.cu:47-92. mean != 0 -> REDUCE_MEAN.
+ORACLE_API void oracle_reduce_forward(float const *in, float *out, int nd, long long const *id,
+                                      long long const *od, int mean) {
+  long long in_n = 1, out_n = 1;
+  for (int d = 0; d < nd; ++d) { in_n *= id[d]; out_n *= od[d]; }
+  std::vector<double> acc(out_n, 0.0);
+  for (long long i = 0; i < in_n; ++i) {
+    long long rem = i, o = 0, ostride = 1;
+    for (int d = nd - 1; d >= 0; --d) {
+      long long c = rem % id[d];
+      rem /= id[d];
+      if (od[d] != 1) o += c * ostride;
+      ostride *= od[d];
+    }
+    acc[o] += in[i];
+  }
+  double scale = mean ? 1.0 / (double)(in_n / out_n) : 1.0;
+  for (long long o = 0; o < out_n; ++o) out[o] = (float)(acc[o] * scale);
+}
+ORACLE_API void oracle_reduce_backward(float const *dout, float *din, int nd, long long const *id,
+                                       long long const *od, int mean) {
+  long long in_n = 1, out_n = 1;
+  for (int d = 0; d < nd; ++d) { in_n *= id[d]; out_n *= od[d]; }
+  float alpha = mean ? 1.0f / (float)(in_n / out_n) : 1.0f;
+  for (long long i = 0; i < in_n; ++i) {
+    long long rem = i, o = 0, ostride = 1;
+    for (int d = nd - 1; d >= 0; --d) {
+      long long c = rem % id[d];
+      rem /= id[d];
+      if (od[d] != 1) o += c * ostride;
+      ostride *= od[d];
+    }
+    din[i] += alpha * dout[o];
+  }
+}
+
+// ===================================================================== Pool2D
+// lib/kernels/src/cuda/ops/pool_2d_kernels.cu:94-135: cudnnPoolingForward / Backward, MAX or
+// AVERAGE_COUNT_EXCLUDE_PADDING, NCHW; backward accumulates (beta = 1), MAX -> first maximum.
+ORACLE_API void oracle_pool2d(float const *x, float *y, float *dx, float const *dy, int n, int c,
+                              int ih, int iw, int oh, int ow, int kh, int kw, int sh, int sw,
+                              int ph, int pw, int type, int backward) {
+  for (long long nc = 0; nc < (long long)n * c; ++nc)
+    for (int ho = 0; ho < oh; ++ho)
+      for (int wo = 0; wo < ow; ++wo) {
+        float const *plane = x + nc * ih * iw;
+        long long oi = (nc * oh + ho) * ow + wo;
+        float best = -INFINITY, sum = 0.f;
+        int bh = -1, bw = -1, cnt = 0;
+        for (int a = 0; a < kh; ++a)
+          for (int b = 0; b < kw; ++b) {
+            int h = ho * sh - ph + a, w = wo * sw - pw + b;
+            if (h < 0 || h >= ih || w < 0 || w >= iw) continue;
+            float v = plane[h * iw + w];
+            if (v > best) { best = v; bh = h; bw = w; }
+            sum += v;
+            ++cnt;
+          }
+        if (!backward) {
+          y[oi] = type == 0 ? best : (cnt ? sum / cnt : 0.f);
+        } else if (type == 0) {
+          if (bh >= 0) dx[nc * ih * iw + bh * iw + bw] += dy[oi];
+        } else {
+          for (int a = 0; a < kh; ++a)
+            for (int b = 0; b < kw; ++b) {
+              int h = ho * sh - ph + a, w = wo * sw - pw + b;
+              if (h < 0 || h >= ih || w < 0 || w >= iw) continue;
+              dx[nc * ih * iw + h * iw + w] += dy[oi] / cnt;
+            }
+        }
+      }
+}

@@ -35,6 +35,24 @@ def check(M, N, K, batch, a_mn, b_mn, dt, path=1):
     print(f"{'OK ' if ok else 'BAD'} M={M} N={N} K={K} b={batch} a_mn={int(a_mn)} b_mn={int(b_mn)} {dt} path={path} err={err:.3e} scale={scale:.2e}", flush=True)
     return ok
 
+def bench_epilogues(M=8192, N=4096, K=4096, dt=torch.bfloat16, iters=20):
+    A = (torch.rand(1, M, K, device="cuda") - 0.5).to(dt)
+    B = (torch.rand(1, N, K, device="cuda") - 0.5).to(dt)
+    bias = torch.rand(N, device="cuda").to(dt)
+    d = torch.zeros(1, M, N, dtype=dt, device="cuda")
+    e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+    for name, kw in (("none", {}), ("bias", dict(bias=bias)), ("relu", dict(act=0)), ("bias+relu", dict(bias=bias, act=0)),
+                     ("bias+gelu", dict(bias=bias, act=3)), ("accumulate", dict(accumulate=True))):
+        for _ in range(3):
+            gemm(A, B, M, N, K, 1, False, False, dt, 1, d=d, **kw)
+        torch.cuda.synchronize(); e0.record()
+        for _ in range(iters):
+            gemm(A, B, M, N, K, 1, False, False, dt, 1, d=d, **kw)
+        e1.record(); torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / iters
+        print(f"epilogue {name:12s}: {ms*1e3:.1f} us  {2*M*N*K/ms/1e9:.1f} TFLOP/s", flush=True)
+
+
 def bench(M, N, K, a_mn, b_mn, dt=torch.bfloat16, iters=20):
     A = (torch.rand(1, K if a_mn else M, M if a_mn else K, device="cuda") - 0.5).to(dt)
     B = (torch.rand(1, K if b_mn else N, N if b_mn else K, device="cuda") - 0.5).to(dt)
@@ -73,6 +91,7 @@ if __name__ == "__main__":
     ok &= check(77, 33, 19, 2, True, True, torch.bfloat16, path=2)
     print("ALL OK" if ok else "SOME BAD")
     if ok:
+        bench_epilogues()
         bench(8192, 4096, 4096, False, False)
         bench(8192, 4096, 4096, False, True)
         bench(4096, 4096, 8192, True, True)
