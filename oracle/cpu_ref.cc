@@ -845,3 +845,166 @@ ORACLE_API void oracle_pool2d(float const *x, float *y, float *dx, float const *
         }
       }
 }
+
+// ===================================================================== MultiHeadAttention
+// lib/kernels/src/cuda/ops/attention_kernels.cu:59-334. The arithmetic is cuDNN's legacy
+// multi-head attention (cudnnMultiHeadAttnForward :255, BackwardData :292, BackwardWeights
+// :316) configured at :106-125: ALL_TO_ONE query map, smScalar = 1.0 (no 1/sqrt(d)), no
+// dropout, no projection biases, attention window [0, kvSeqLength) for every query,
+// sequence data laid out [batch][time][beam = 1][vect] (:134-137). cuDNN is closed source,
+// so this restatement follows its documented math and is PINNED against vectors produced by
+// those very cuDNN calls on the GPU box (oracle/cudnn_ref/mha_golden.cu ->
+// tests/golden/mha_*.npz). The packed weight buffer is the one cudnnGetMultiHeadAttnWeights
+// reports (recorded in the golden files' layout.json):
+//   Wq [qSize][H][qProj] | Wk [kSize][H][kProj] | Wv [vSize][H][vProj] | Wo [H][vProj][oProj]
+// Gradients: dq/dk/dv are OVERWRITTEN (cuDNN semantics; NULL skips), dW accumulates
+// (CUDNN_WGRAD_MODE_ADD, :318).
+namespace {
+struct MhaDims {
+  int N, H, qS, kS, vS, qP, kP, vP, oP, Sq, Sk;
+};
+struct MhaFwd {
+  std::vector<double> qp, kp, vp, p, oc;  // projections, probabilities, concatenated heads
+};
+void mha_forward_core(MhaDims const &d, float const *q, float const *k, float const *v,
+                      float const *w, MhaFwd &f) {
+  float const *wq = w;
+  float const *wk = wq + (size_t)d.qS * d.H * d.qP;
+  float const *wv = wk + (size_t)d.kS * d.H * d.kP;
+  int HQ = d.H * d.qP, HK = d.H * d.kP, HV = d.H * d.vP;
+  f.qp.assign((size_t)d.N * d.Sq * HQ, 0.0);
+  f.kp.assign((size_t)d.N * d.Sk * HK, 0.0);
+  f.vp.assign((size_t)d.N * d.Sk * HV, 0.0);
+  f.p.assign((size_t)d.N * d.H * d.Sq * d.Sk, 0.0);
+  f.oc.assign((size_t)d.N * d.Sq * HV, 0.0);
+  auto project = [](float const *x, float const *wm, std::vector<double> &out, size_t rows, int in,
+                    int cols) {
+#pragma omp parallel for schedule(static)
+    for (size_t r = 0; r < rows; ++r)
+      for (int i = 0; i < in; ++i) {
+        double xv = x[r * in + i];
+        for (int c = 0; c < cols; ++c) out[r * cols + c] += xv * wm[(size_t)i * cols + c];
+      }
+  };
+  project(q, wq, f.qp, (size_t)d.N * d.Sq, d.qS, HQ);
+  project(k, wk, f.kp, (size_t)d.N * d.Sk, d.kS, HK);
+  project(v, wv, f.vp, (size_t)d.N * d.Sk, d.vS, HV);
+#pragma omp parallel for collapse(2) schedule(static)
+  for (int n = 0; n < d.N; ++n)
+    for (int h = 0; h < d.H; ++h)
+      for (int s = 0; s < d.Sq; ++s) {
+        double *prow = &f.p[(((size_t)n * d.H + h) * d.Sq + s) * d.Sk];
+        double mx = -INFINITY;
+        for (int t = 0; t < d.Sk; ++t) {
+          double acc = 0.0;
+          for (int c = 0; c < d.qP; ++c)
+            acc += f.qp[((size_t)n * d.Sq + s) * HQ + h * d.qP + c] *
+                   f.kp[((size_t)n * d.Sk + t) * HK + h * d.kP + c];
+          prow[t] = acc;  // smScalar = 1.0
+          mx = std::max(mx, acc);
+        }
+        double sum = 0.0;
+        for (int t = 0; t < d.Sk; ++t) { prow[t] = std::exp(prow[t] - mx); sum += prow[t]; }
+        for (int t = 0; t < d.Sk; ++t) prow[t] /= sum;
+        for (int c = 0; c < d.vP; ++c) {
+          double acc = 0.0;
+          for (int t = 0; t < d.Sk; ++t)
+            acc += prow[t] * f.vp[((size_t)n * d.Sk + t) * HV + h * d.vP + c];
+          f.oc[((size_t)n * d.Sq + s) * HV + h * d.vP + c] = acc;
+        }
+      }
+}
+}  // namespace
+
+// dims: {N, H, qSize, kSize, vSize, qProj, kProj, vProj, oProj, qoSeq, kvSeq}
+ORACLE_API void oracle_mha_forward(long long const *dims, float const *q, float const *k,
+                                   float const *v, float const *w, float *out) {
+  MhaDims d{(int)dims[0], (int)dims[1], (int)dims[2], (int)dims[3], (int)dims[4], (int)dims[5],
+            (int)dims[6], (int)dims[7], (int)dims[8], (int)dims[9], (int)dims[10]};
+  MhaFwd f;
+  mha_forward_core(d, q, k, v, w, f);
+  int HV = d.H * d.vP;
+  float const *wo = w + (size_t)d.qS * d.H * d.qP + (size_t)d.kS * d.H * d.kP + (size_t)d.vS * d.H * d.vP;
+#pragma omp parallel for schedule(static)
+  for (size_t r = 0; r < (size_t)d.N * d.Sq; ++r)
+    for (int o = 0; o < d.oP; ++o) {
+      double acc = 0.0;
+      for (int c = 0; c < HV; ++c) acc += f.oc[r * HV + c] * wo[(size_t)c * d.oP + o];
+      out[r * d.oP + o] = (float)acc;
+    }
+}
+
+ORACLE_API void oracle_mha_backward(long long const *dims, float const *q, float *dq,
+                                    float const *k, float *dk, float const *v, float *dv,
+                                    float const *w, float *dw, float const *dout) {
+  MhaDims d{(int)dims[0], (int)dims[1], (int)dims[2], (int)dims[3], (int)dims[4], (int)dims[5],
+            (int)dims[6], (int)dims[7], (int)dims[8], (int)dims[9], (int)dims[10]};
+  MhaFwd f;
+  mha_forward_core(d, q, k, v, w, f);
+  int HQ = d.H * d.qP, HK = d.H * d.kP, HV = d.H * d.vP;
+  size_t oq = 0, ok = oq + (size_t)d.qS * HQ, ov = ok + (size_t)d.kS * HK, oo = ov + (size_t)d.vS * HV;
+  float const *wq = w + oq, *wk = w + ok, *wv = w + ov, *wo = w + oo;
+  size_t Rq = (size_t)d.N * d.Sq, Rk = (size_t)d.N * d.Sk;
+  std::vector<double> doc(Rq * HV, 0.0), dqp(Rq * HQ, 0.0), dkp(Rk * HK, 0.0), dvp(Rk * HV, 0.0);
+  // through the output projection
+  for (size_t r = 0; r < Rq; ++r)
+    for (int c = 0; c < HV; ++c) {
+      double acc = 0.0;
+      for (int o = 0; o < d.oP; ++o) acc += (double)dout[r * d.oP + o] * wo[(size_t)c * d.oP + o];
+      doc[r * HV + c] = acc;
+    }
+  for (int c = 0; c < HV; ++c)
+    for (int o = 0; o < d.oP; ++o) {
+      double acc = 0.0;
+      for (size_t r = 0; r < Rq; ++r) acc += f.oc[r * HV + c] * dout[r * d.oP + o];
+      dw[oo + (size_t)c * d.oP + o] += (float)acc;
+    }
+  // attention core
+  for (int n = 0; n < d.N; ++n)
+    for (int h = 0; h < d.H; ++h)
+      for (int s = 0; s < d.Sq; ++s) {
+        double const *prow = &f.p[(((size_t)n * d.H + h) * d.Sq + s) * d.Sk];
+        std::vector<double> dp(d.Sk);
+        double dot = 0.0;
+        for (int t = 0; t < d.Sk; ++t) {
+          double acc = 0.0;
+          for (int c = 0; c < d.vP; ++c)
+            acc += doc[((size_t)n * d.Sq + s) * HV + h * d.vP + c] *
+                   f.vp[((size_t)n * d.Sk + t) * HV + h * d.vP + c];
+          dp[t] = acc;
+          dot += acc * prow[t];
+        }
+        for (int t = 0; t < d.Sk; ++t) {
+          double ds = prow[t] * (dp[t] - dot);
+          for (int c = 0; c < d.vP; ++c)
+            dvp[((size_t)n * d.Sk + t) * HV + h * d.vP + c] +=
+                prow[t] * doc[((size_t)n * d.Sq + s) * HV + h * d.vP + c];
+          for (int c = 0; c < d.qP; ++c) {
+            dqp[((size_t)n * d.Sq + s) * HQ + h * d.qP + c] +=
+                ds * f.kp[((size_t)n * d.Sk + t) * HK + h * d.kP + c];
+            dkp[((size_t)n * d.Sk + t) * HK + h * d.kP + c] +=
+                ds * f.qp[((size_t)n * d.Sq + s) * HQ + h * d.qP + c];
+          }
+        }
+      }
+  // through the input projections: data gradients overwrite, weight gradients accumulate
+  auto back = [](float const *x, float *dx, float const *wm, float *dwm, std::vector<double> const &dproj,
+                 size_t rows, int in, int cols) {
+    if (dx)
+      for (size_t r = 0; r < rows; ++r)
+        for (int i = 0; i < in; ++i) {
+          double acc = 0.0;
+          for (int c = 0; c < cols; ++c) acc += dproj[r * cols + c] * wm[(size_t)i * cols + c];
+          dx[r * in + i] = (float)acc;
+        }
+    for (int i = 0; i < in; ++i)
+      for (int c = 0; c < cols; ++c) {
+        double acc = 0.0;
+        for (size_t r = 0; r < rows; ++r) acc += (double)x[r * in + i] * dproj[r * cols + c];
+        dwm[(size_t)i * cols + c] += (float)acc;
+      }
+  };
+  back(q, dq, wq, dw + oq, dqp, Rq, d.qS, HQ);
+  back(k, dk, wk, dw + ok, dkp, Rk, d.kS, HK);
+  back(v, dv, wv, dw + ov, dvp, Rk, d.vS, HV);
+}
