@@ -122,7 +122,7 @@ template <int ESIZE, bool A_MN, bool B_MN, int BLOCK_N, int STAGES>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
     gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a,
                    const __grid_constant__ CUtensorMap map_b, Epilogue ep, int M, int N, int K,
-                   int batch, uint32_t idesc, int out_dtype, int vec_ok) {
+                   int batch, int batch2, uint32_t idesc, int out_dtype, int vec_ok) {
   using Plan = SmemPlan<BLOCK_N, STAGES>;
   constexpr int BLOCK_K = SWIZZLE_BYTES / ESIZE;    // elements of K per stage
   constexpr int ATOM_MN = SWIZZLE_BYTES / ESIZE;    // MN elements per swizzle row (MN-major)
@@ -183,20 +183,20 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
         ptx::mbar_arrive_expect_tx(&full_bar[stage], Plan::STAGE_BYTES);
         int const k_idx = kb * BLOCK_K;
         if constexpr (!A_MN) {
-          ptx::tma_load_3d(sa, &map_a, &full_bar[stage], k_idx, tc.m_idx, tc.b);
+          ptx::tma_load_4d(sa, &map_a, &full_bar[stage], k_idx, tc.m_idx, tc.b % batch2, tc.b / batch2);
         } else {
 #pragma unroll
           for (int j = 0; j < BLOCK_M / ATOM_MN; ++j)
-            ptx::tma_load_3d(sa + j * BLOCK_K * SWIZZLE_BYTES, &map_a, &full_bar[stage],
-                             tc.m_idx + j * ATOM_MN, k_idx, tc.b);
+            ptx::tma_load_4d(sa + j * BLOCK_K * SWIZZLE_BYTES, &map_a, &full_bar[stage],
+                             tc.m_idx + j * ATOM_MN, k_idx, tc.b % batch2, tc.b / batch2);
         }
         if constexpr (!B_MN) {
-          ptx::tma_load_3d(sb, &map_b, &full_bar[stage], k_idx, tc.n_idx, tc.b);
+          ptx::tma_load_4d(sb, &map_b, &full_bar[stage], k_idx, tc.n_idx, tc.b % batch2, tc.b / batch2);
         } else {
 #pragma unroll
           for (int j = 0; j < BLOCK_N / ATOM_MN; ++j)
-            ptx::tma_load_3d(sb + j * BLOCK_K * SWIZZLE_BYTES, &map_b, &full_bar[stage],
-                             tc.n_idx + j * ATOM_MN, k_idx, tc.b);
+            ptx::tma_load_4d(sb + j * BLOCK_K * SWIZZLE_BYTES, &map_b, &full_bar[stage],
+                             tc.n_idx + j * ATOM_MN, k_idx, tc.b % batch2, tc.b / batch2);
         }
         if (++stage == STAGES) {
           stage = 0;
@@ -258,8 +258,9 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
       ptx::mbar_wait(&tmem_full[acc], acc_phase);
       ptx::tc_fence_after();
       int const row = tc.m_idx + q * 32 + lane;
-      long long const row_off =
-          static_cast<long long>(tc.b) * ep.d_batch + static_cast<long long>(row) * ep.ldd;
+      long long const row_off = static_cast<long long>(tc.b / batch2) * ep.d_batch +
+                                static_cast<long long>(tc.b % batch2) * ep.d_batch2 +
+                                static_cast<long long>(row) * ep.ldd;
 #pragma unroll 1
       for (int c = 0; c < BLOCK_N / 32; ++c) {
         uint32_t r[32];
@@ -313,10 +314,11 @@ PFN_cuTensorMapEncodeTiled_v12000 encode_fn() {
   return fn;
 }
 
-// Stored matrix [batch][rows][inner], `ld` elements between rows.
+// Stored matrix [batch_outer][batch2][rows][inner] with arbitrary element strides between
+// rows (`ld`), inner batches (`batch2_stride`) and outer batches (`batch_stride`).
 int make_map(CUtensorMap *out, void const *base, int dtype, uint64_t inner, uint64_t rows,
-             uint64_t batch, uint64_t ld, uint64_t batch_stride, uint32_t box_inner,
-             uint32_t box_rows) {
+             uint64_t batch_outer, uint64_t batch2, uint64_t ld, uint64_t batch_stride,
+             uint64_t batch2_stride, uint32_t box_inner, uint32_t box_rows) {
   auto fn = encode_fn();
   if (!fn) {
     set_error("cuTensorMapEncodeTiled is not available from the driver");
@@ -326,18 +328,21 @@ int make_map(CUtensorMap *out, void const *base, int dtype, uint64_t inner, uint
   CUtensorMapDataType dt = dtype == FFK_BFLOAT16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16
                            : dtype == FFK_HALF   ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16
                                                  : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
-  if (batch_stride == 0 || batch == 1) batch_stride = rows * ld;
-  cuuint64_t dims[3] = {inner, rows, batch};
-  cuuint64_t strides[2] = {ld * es, batch_stride * es};
-  cuuint32_t box[3] = {box_inner, box_rows, 1};
-  cuuint32_t estr[3] = {1, 1, 1};
-  CUresult r = fn(out, dt, 3, const_cast<void *>(base), dims, strides, box, estr,
+  if (batch2 <= 1) { batch2 = 1; batch2_stride = rows * ld; }
+  if (batch_outer <= 1) { batch_outer = 1; batch_stride = batch2_stride * batch2; }
+  if (batch2_stride == 0) batch2_stride = rows * ld;
+  if (batch_stride == 0) batch_stride = batch2_stride * batch2;
+  cuuint64_t dims[4] = {inner, rows, batch2, batch_outer};
+  cuuint64_t strides[3] = {ld * es, batch2_stride * es, batch_stride * es};
+  cuuint32_t box[4] = {box_inner, box_rows, 1, 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = fn(out, dt, 4, const_cast<void *>(base), dims, strides, box, estr,
                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
-    set_error("cuTensorMapEncodeTiled failed (%d): inner=%llu rows=%llu batch=%llu ld=%llu",
+    set_error("cuTensorMapEncodeTiled failed (%d): inner=%llu rows=%llu batch=%llux%llu ld=%llu",
               (int)r, (unsigned long long)inner, (unsigned long long)rows,
-              (unsigned long long)batch, (unsigned long long)ld);
+              (unsigned long long)batch_outer, (unsigned long long)batch2, (unsigned long long)ld);
     return FFK_ERR_CUDA;
   }
   return FFK_OK;
@@ -350,15 +355,16 @@ int launch_tc_inst(Problem const &p, Epilogue const &e, cudaStream_t stream) {
   constexpr int ATOM = SWIZZLE_BYTES / ESIZE;
   CUtensorMap ma, mb;
   int rc;
+  int const b2 = p.batch2 > 1 ? p.batch2 : 1, bo = p.batch / b2;
   if (!A_MN)
-    rc = make_map(&ma, p.a, p.in_dtype, p.K, p.M, p.batch, p.lda, p.a_batch, BLOCK_K, BLOCK_M);
+    rc = make_map(&ma, p.a, p.in_dtype, p.K, p.M, bo, b2, p.lda, p.a_batch, p.a_batch2, BLOCK_K, BLOCK_M);
   else
-    rc = make_map(&ma, p.a, p.in_dtype, p.M, p.K, p.batch, p.lda, p.a_batch, ATOM, BLOCK_K);
+    rc = make_map(&ma, p.a, p.in_dtype, p.M, p.K, bo, b2, p.lda, p.a_batch, p.a_batch2, ATOM, BLOCK_K);
   if (rc) return rc;
   if (!B_MN)
-    rc = make_map(&mb, p.b, p.in_dtype, p.K, p.N, p.batch, p.ldb, p.b_batch, BLOCK_K, BLOCK_N);
+    rc = make_map(&mb, p.b, p.in_dtype, p.K, p.N, bo, b2, p.ldb, p.b_batch, p.b_batch2, BLOCK_K, BLOCK_N);
   else
-    rc = make_map(&mb, p.b, p.in_dtype, p.N, p.K, p.batch, p.ldb, p.b_batch, ATOM, BLOCK_K);
+    rc = make_map(&mb, p.b, p.in_dtype, p.N, p.K, bo, b2, p.ldb, p.b_batch, p.b_batch2, ATOM, BLOCK_K);
   if (rc) return rc;
 
   auto kern = gemm_tc_kernel<ESIZE, A_MN, B_MN, BLOCK_N, STAGES>;
@@ -372,10 +378,11 @@ int launch_tc_inst(Problem const &p, Epilogue const &e, cudaStream_t stream) {
   int grid = (int)std::min<long long>(tiles, device_info().sm_count);
   size_t os = dtype_size(p.out_dtype);
   int vec_ok = aligned16(e.d) && ((e.ldd * os) % 16 == 0) && ((e.d_batch * os) % 16 == 0) &&
+               ((e.d_batch2 * os) % 16 == 0) &&
                (e.r == nullptr || aligned16(e.r));
   Epilogue e2 = e;
   e2.bias_vec_ok = e.bias != nullptr && aligned16(e.bias) && vec_ok;
-  kern<<<grid, NUM_THREADS, Plan::TOTAL, stream>>>(ma, mb, e2, p.M, p.N, p.K, p.batch, idesc,
+  kern<<<grid, NUM_THREADS, Plan::TOTAL, stream>>>(ma, mb, e2, p.M, p.N, p.K, p.batch, b2, idesc,
                                                    p.out_dtype, vec_ok);
   FFK_LAUNCH_CHECK();
   return FFK_OK;
@@ -402,6 +409,8 @@ bool tc_eligible(Problem const &p, Epilogue const &e) {
   if (!aligned16(p.a) || !aligned16(p.b)) return false;
   if ((p.lda * es) % 16 || (p.ldb * es) % 16) return false;
   if (p.batch > 1 && ((p.a_batch * es) % 16 || (p.b_batch * es) % 16)) return false;
+  if (p.batch2 > 1 && ((p.a_batch2 * es) % 16 || (p.b_batch2 * es) % 16)) return false;
+  if (p.batch2 > 1 && p.batch % p.batch2 != 0) return false;
   (void)e;
   return true;
 }
@@ -433,13 +442,14 @@ template <typename TIn, typename TOut>
 __global__ void __launch_bounds__(256)
     gemm_simt_kernel(TIn const *__restrict__ a, TIn const *__restrict__ b, Epilogue ep, int M,
                      int N, int K, long long sa_m, long long sa_k, long long sb_n, long long sb_k,
-                     long long a_batch, long long b_batch) {
+                     long long a_batch, long long b_batch, int batch2, long long a_batch2,
+                     long long b_batch2) {
   constexpr int TM = 64, TN = 64, TK = 16;
   __shared__ float As[TK][TM + 4];
   __shared__ float Bs[TK][TN + 4];
-  int const bz = blockIdx.z;
-  a += bz * a_batch;
-  b += bz * b_batch;
+  int const bo = blockIdx.z / batch2, bi = blockIdx.z % batch2;
+  a += bo * a_batch + bi * a_batch2;
+  b += bo * b_batch + bi * b_batch2;
   int const m0 = blockIdx.y * TM, n0 = blockIdx.x * TN;
   int const tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
   float acc[4][4] = {};
@@ -473,8 +483,9 @@ __global__ void __launch_bounds__(256)
     }
     __syncthreads();
   }
-  TOut *d = reinterpret_cast<TOut *>(ep.d) + bz * ep.d_batch;
-  TOut const *r = ep.r ? reinterpret_cast<TOut const *>(ep.r) + bz * ep.d_batch : nullptr;
+  long long const d_off = bo * ep.d_batch + bi * ep.d_batch2;
+  TOut *d = reinterpret_cast<TOut *>(ep.d) + d_off;
+  TOut const *r = ep.r ? reinterpret_cast<TOut const *>(ep.r) + d_off : nullptr;
   TOut const *bias = reinterpret_cast<TOut const *>(ep.bias);
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
@@ -502,7 +513,8 @@ int launch_simt_t(Problem const &p, Epilogue const &e, cudaStream_t stream) {
   dim3 grid((p.N + 63) / 64, (p.M + 63) / 64, p.batch);
   gemm_simt_kernel<TIn, TOut><<<grid, 256, 0, stream>>>(
       reinterpret_cast<TIn const *>(p.a), reinterpret_cast<TIn const *>(p.b), e, p.M, p.N, p.K,
-      sa_m, sa_k, sb_n, sb_k, p.a_batch, p.b_batch);
+      sa_m, sa_k, sb_n, sb_k, p.a_batch, p.b_batch, p.batch2 > 1 ? p.batch2 : 1, p.a_batch2,
+      p.b_batch2);
   FFK_LAUNCH_CHECK();
   return FFK_OK;
 }

@@ -31,6 +31,7 @@ struct Epilogue {
   float lambda;          // optional regulariser: D += lambda * R
   void const *r;         // R, same layout/dtype as D (may be null)
   int bias_vec_ok = 0;   // set by the launcher: bias readable as 16-byte packets
+  long long d_batch2 = 0;  // elements between inner batches of D (see Problem::batch2)
 };
 
 // Problem in "logical" terms. a/b pointers are the stored matrices:
@@ -45,6 +46,11 @@ struct Problem {
   int in_dtype;   // FFK_BFLOAT16 / FFK_HALF / FFK_FLOAT (tf32 on the tensor path)
   int out_dtype;  // FFK_BFLOAT16 / FFK_HALF / FFK_FLOAT
   bool a_mn_major, b_mn_major;
+  // Optional second (inner) batch level: the batch index b in [0, batch) is split as
+  // (b / batch2, b % batch2) with strides (x_batch, x_batch2). Used by attention, where a
+  // [sample][seq][head][dim] tensor is batched over (sample, head).
+  int batch2 = 1;
+  long long a_batch2 = 0, b_batch2 = 0;
 };
 
 // Tensor-core path. Returns FFK_ERR_UNSUPPORTED (without launching) when the

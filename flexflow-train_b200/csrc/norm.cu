@@ -45,9 +45,10 @@ inline int pick_p(long long nvec) {
 // ================================================================== softmax
 template <typename T, int P>
 __global__ void __launch_bounds__(kThreads)
-    softmax_rows_kernel(T const *__restrict__ x, T *__restrict__ y, long long rows, int nvec) {
+    softmax_rows_kernel(T const *x, T *y, long long rows, int nvec) {
   constexpr int VN = Vec16<T>::N;
   __shared__ float red[32];
+  bool const inplace = (x == y);  // attention normalises its score matrix in place
   for (long long r = blockIdx.x; r < rows; r += gridDim.x) {
     T const *xr = x + r * (long long)nvec * VN;
     T *yr = y + r * (long long)nvec * VN;
@@ -57,7 +58,7 @@ __global__ void __launch_bounds__(kThreads)
     for (int p = 0; p < P; ++p) {
       int i = threadIdx.x + p * kThreads;
       if (i < nvec) {
-        Vec16<T> t = ld_stream(xr + i * VN);
+        Vec16<T> t = inplace ? ld_vec(xr + i * VN) : ld_stream(xr + i * VN);
 #pragma unroll
         for (int j = 0; j < VN; ++j) {
           v[p][j] = to_f32(t.v[j]);
@@ -96,7 +97,7 @@ __global__ void __launch_bounds__(kThreads)
 // Generic: one warp per (outer, inner) line, element stride `inner`.
 template <typename T>
 __global__ void __launch_bounds__(kThreads)
-    softmax_lines_kernel(T const *__restrict__ x, T *__restrict__ y, long long outer,
+    softmax_lines_kernel(T const *x, T *y, long long outer,
                          long long dim, long long inner) {
   long long const lines = outer * inner;
   int const lane = threadIdx.x & 31;
@@ -122,7 +123,7 @@ __global__ void __launch_bounds__(kThreads)
 // consecutive threads touch consecutive addresses.
 template <typename T>
 __global__ void __launch_bounds__(kThreads)
-    softmax_strided_kernel(T const *__restrict__ x, T *__restrict__ y, long long outer,
+    softmax_strided_kernel(T const *x, T *y, long long outer,
                            long long dim, long long inner) {
   long long const lines = outer * inner;
   long long const stride = (long long)gridDim.x * blockDim.x;
@@ -143,7 +144,7 @@ __global__ void __launch_bounds__(kThreads)
 // dx = y * (dy - sum(dy*y)) along dim; one warp per line (generic strides).
 template <typename T>
 __global__ void __launch_bounds__(kThreads)
-    softmax_jacobian_kernel(T *__restrict__ dx, T const *__restrict__ dy, T const *__restrict__ y,
+    softmax_jacobian_kernel(T *dx, T const *dy, T const *__restrict__ y,
                             long long outer, long long dim, long long inner) {
   long long const lines = outer * inner;
   int const lane = threadIdx.x & 31;

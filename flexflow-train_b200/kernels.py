@@ -628,3 +628,57 @@ class Pool2D:
     def backward_kernel(stream, m, input, input_grad, output, output_grad):
         _call("ffk_pool2d_backward", _stream(stream), _ptr(input), _ptr(input_grad), _ptr(output),
               _ptr(output_grad), *m.geom, m.pool_type)
+
+
+# ------------------------------------------------------------------ attention
+class _MhaConfig(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_int) for n in (
+        "num_samples", "num_heads", "qSize", "kSize", "vSize", "qProjSize", "kProjSize",
+        "vProjSize", "oProjSize", "qoSeqLength", "kvSeqLength")]
+
+
+@dataclass
+class MHAPerDeviceState:
+    cfg: _MhaConfig
+    weightSize: int          # bytes, as the reference's field
+    reserveSpaceSize: int
+    reserveSpace: torch.Tensor
+    workSpace: torch.Tensor
+    dtype: torch.dtype
+    path: int = GEMM_AUTO
+
+
+class MultiHeadAttention:
+    """attention_kernels.h"""
+
+    @staticmethod
+    def init_kernel(num_samples, num_heads, qSize, kSize, vSize, qProjSize, kProjSize, vProjSize,
+                    oProjSize, qoSeqLength, kvSeqLength, add_bias_kv=False, dtype=torch.float32,
+                    device="cuda", path=GEMM_AUTO):
+        assert not add_bias_kv, "the reference asserts !add_bias_kv (attention_kernels.cu:93)"
+        cfg = _MhaConfig(num_samples, num_heads, qSize, kSize, vSize, qProjSize, kProjSize,
+                         vProjSize, oProjSize, qoSeqLength, kvSeqLength)
+        dt = _DT[dtype]
+        c = lib().cdll
+        ref = ctypes.byref(cfg)
+        wbytes = c.ffk_mha_weight_bytes(ref, dt)
+        rbytes = c.ffk_mha_reserve_bytes(ref, dt)
+        sbytes = c.ffk_mha_workspace_bytes(ref, dt)
+        if wbytes == 0:
+            from ._lib import FFKError
+            raise FFKError("ffk_mha_weight_bytes", -1, lib().last_error())
+        mk = lambda b: torch.empty(max(b, 16), dtype=torch.uint8, device=device)
+        return MHAPerDeviceState(cfg, wbytes, rbytes, mk(rbytes), mk(sbytes), dtype, path)
+
+    @staticmethod
+    def forward_kernel(stream, m, query, key, value, weight, output):
+        _call("ffk_mha_forward", _stream(stream), ctypes.byref(m.cfg), _ptr(query), _ptr(key),
+              _ptr(value), _ptr(weight), _ptr(output), _ptr(m.reserveSpace), _DT[m.dtype], m.path)
+
+    @staticmethod
+    def backward_kernel(stream, m, query, query_grad, key, key_grad, value, value_grad, weight,
+                        weight_grad, output_grad):
+        _call("ffk_mha_backward", _stream(stream), ctypes.byref(m.cfg), _ptr(query),
+              _ptr(query_grad), _ptr(key), _ptr(key_grad), _ptr(value), _ptr(value_grad),
+              _ptr(weight), _ptr(weight_grad), _ptr(output_grad), _ptr(m.reserveSpace),
+              _ptr(m.workSpace), m.workSpace.numel(), _DT[m.dtype], m.path)

@@ -70,6 +70,46 @@ int ffk_batch_matmul_backward(void *stream, void const *o, void const *o_grad, v
                               void *a_grad, void const *b, void *b_grad, int m, int n, int k,
                               int batch, int dtype, int path);
 
+/* Kernels::MultiHeadAttention — include/kernels/attention_kernels.h:70-106,
+ * src/cuda/ops/attention_kernels.cu:59-345 (cuDNN legacy multi-head attention: ALL_TO_ONE,
+ * smScalar 1.0 i.e. NO 1/sqrt(d) scaling, no biases, no dropout, full attention window,
+ * sequence data [batch][time][vect]). The fields are init_kernel's integer arguments. */
+typedef struct {
+  int num_samples, num_heads;
+  int qSize, kSize, vSize;
+  int qProjSize, kProjSize, vProjSize, oProjSize;
+  int qoSeqLength, kvSeqLength;
+} ffk_mha_config_t;
+
+/* Bytes of the packed weight buffer: what cudnnGetMultiHeadAttnBuffers reports as weightSize
+ * (attention_kernels.cu:127) for the same configuration, with the same layout —
+ *   Wq [qSize][heads][qProj] | Wk [kSize][heads][kProj] | Wv [vSize][heads][vProj] | Wo [heads][vProj][oProj]
+ * — verified against cudnnGetMultiHeadAttnWeights on a B200 (tests/golden/mha_*.npz). */
+size_t ffk_mha_weight_bytes(ffk_mha_config_t const *cfg_host, int dtype);
+/* Bytes the forward pass keeps for the backward pass (the role of MHAPerDeviceState::
+ * reserveSpace): projected Q/K/V, attention probabilities, concatenated head outputs. */
+size_t ffk_mha_reserve_bytes(ffk_mha_config_t const *cfg_host, int dtype);
+/* Scratch bytes backward needs (the role of PerDeviceFFHandle::workSpace). */
+size_t ffk_mha_workspace_bytes(ffk_mha_config_t const *cfg_host, int dtype);
+
+/* MultiHeadAttention::forward_kernel — attention_kernels.h:85, attention_kernels.cu:246-277.
+ * out[n][s][:] = concat_h( softmax(Qh Kh^T) Vh ) Wo with Qh = q Wq_h etc. `reserve` must hold
+ * ffk_mha_reserve_bytes() and is read by the backward call. */
+int ffk_mha_forward(void *stream, ffk_mha_config_t const *cfg_host, void const *query,
+                    void const *key, void const *value, void const *weight, void *output,
+                    void *reserve, int dtype, int path);
+
+/* MultiHeadAttention::backward_kernel — attention_kernels.h:93, attention_kernels.cu:279-334.
+ * query/key/value gradients are OVERWRITTEN (cuDNN's BackwardData semantics; key_grad and
+ * value_grad may be NULL, which the reference's wrapper passes for self-attention,
+ * lib/local-execution/src/ops/attention.cc:177-181); weight_grad accumulates
+ * (CUDNN_WGRAD_MODE_ADD). */
+int ffk_mha_backward(void *stream, ffk_mha_config_t const *cfg_host, void const *query,
+                     void *query_grad, void const *key, void *key_grad, void const *value,
+                     void *value_grad, void const *weight, void *weight_grad,
+                     void const *output_grad, void const *reserve, void *workspace,
+                     size_t workspace_bytes, int dtype, int path);
+
 #ifdef __cplusplus
 }
 #endif

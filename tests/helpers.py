@@ -48,3 +48,16 @@ def assert_equal_bits(got, ref, what=""):
     g = got.detach().cpu().contiguous().view(torch.uint8).numpy() if isinstance(got, torch.Tensor) else np.asarray(got).view(np.uint8)
     r = ref.detach().cpu().contiguous().view(torch.uint8).numpy() if isinstance(ref, torch.Tensor) else np.ascontiguousarray(ref).view(np.uint8)
     assert g.shape == r.shape and (g == r).all(), f"{what}: not bit-identical"
+
+
+def assert_close_l2(got, ref, rel=2e-2, max_rel=0.15, what=""):
+    """Bound for chains of 16-bit GEMMs (attention): every intermediate is rounded to 16 bits,
+    so single elements that cancel can miss an elementwise 2e-2; the tensor as a whole must
+    still agree to 2e-2 in relative L2 norm and no element may be off by more than
+    `max_rel` of the tensor's largest magnitude."""
+    got = to_np(got) if isinstance(got, torch.Tensor) else np.asarray(got, dtype=np.float32)
+    ref = np.asarray(ref, dtype=np.float32).reshape(got.shape)
+    l2 = np.linalg.norm((got - ref).ravel()) / max(np.linalg.norm(ref.ravel()), 1e-30)
+    worst = np.abs(got - ref).max() / max(np.abs(ref).max(), 1e-30)
+    assert l2 <= rel, f"{what}: relative L2 error {l2:.3e} > {rel}"
+    assert worst <= max_rel, f"{what}: worst element off by {worst:.3e} of the tensor scale"
