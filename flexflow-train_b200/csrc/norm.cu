@@ -3,6 +3,8 @@
 // back; rows that do not fit or are not 16-byte aligned take a generic looped kernel.
 #include "common.cuh"
 
+#include <mutex>
+
 namespace ffk {
 namespace {
 
@@ -742,6 +744,80 @@ int ffk_batch_norm_backward(void *stream, float const *input, float *output_grad
       save_invstd, n, c, (long long)h * w, relu);
   FFK_LAUNCH_CHECK();
   return FFK_OK;
+}
+
+
+// ------------------------------------------------------------------------------------------
+// LayerNorm backward for callers that cannot allocate.
+//
+// Who that is: code that runs as a task under a runtime which has already taken the GPU's
+// memory for its own pool — the reference's legacy Legion/Realm runtime reserves the
+// framebuffer when the process starts, so a cudaMalloc issued later from inside a task can
+// simply fail, and even when it succeeds it synchronises the whole device and stalls every
+// other task's stream — and callers that reach the backward call holding neither an
+// Allocator nor a PerDeviceFFHandle workspace to lend. For them the per-CTA partial sums of
+// dgamma / dbeta, which ffk_layer_norm_backward keeps in caller scratch, live here, in a
+// fixed array that is part of the library image. Every GPU that loads libffk.so carries these
+// 4 MiB until the process exits.
+//
+// The array's NAME is only a host-side handle: handing it to a kernel from host code would
+// pass a host address. Its device address is looked up once per device with
+// cudaGetSymbolAddress (below) and that pointer is what the kernels receive.
+constexpr size_t kStaticScratchFloats = size_t(1) << 20;   // 4 MiB
+constexpr long long kStaticMaxColumns = 16384;             // => at least 32 partial slabs
+constexpr int kStaticMaxDevices = 64;
+
+namespace {
+static __device__ __align__(256) float g_layer_norm_static_scratch[kStaticScratchFloats];
+float *g_static_scratch_addr[kStaticMaxDevices];  // device address per device ordinal, lazily filled
+std::mutex g_static_scratch_mutex;
+
+// Resolves (once per device, with that device current) the device address of the array.
+int static_scratch_of_current_device(float **out) {
+  int dev = -1;
+  FFK_CUDA(cudaGetDevice(&dev));
+  FFK_REQUIRE(dev >= 0 && dev < kStaticMaxDevices, "layer_norm static: device ordinal %d unsupported", dev);
+  std::lock_guard<std::mutex> lock(g_static_scratch_mutex);
+  if (g_static_scratch_addr[dev] == nullptr) {
+    float *addr = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(reinterpret_cast<void **>(&addr), g_layer_norm_static_scratch);
+    if (e != cudaSuccess) return ::ffk::cuda_fail(e, "cudaGetSymbolAddress(g_layer_norm_static_scratch)", __FILE__, __LINE__);
+    FFK_REQUIRE(addr != nullptr, "layer_norm static: symbol address resolved to null");
+    g_static_scratch_addr[dev] = addr;
+  }
+  *out = g_static_scratch_addr[dev];
+  return FFK_OK;
+}
+}  // namespace
+
+// Same arithmetic and the same kernels as ffk_layer_norm_backward; the only difference is
+// where the partial sums are kept. Nothing here (or below it) calls cudaMalloc, cudaFree or
+// any allocating library routine.
+//  * The first call on a device resolves the array's address (see above). Make that first
+//    call outside any stream capture.
+//  * Limit: N <= 16384 columns; larger rows are refused with FFK_ERR_LIMIT.
+//  * All calls on one GPU share the one array and it keeps whatever the previous call left
+//    there. That is harmless for sequential calls — each call's first kernel overwrites every
+//    slab that its second kernel reads, so nothing has to be cleared — but two calls whose
+//    kernels overlap on the GPU (different streams, no ordering between them) would trample
+//    each other's partial sums. Order such calls on one stream or with events.
+int ffk_layer_norm_backward_static(void *stream, void const *output_grad, void const *input,
+                                   void *input_grad, void const *gamma, void *gamma_grad,
+                                   void *beta_grad, float const *mean, float const *rstd,
+                                   long long M, long long N, int dtype,
+                                   int accumulate_param_grads) {
+  if (N > kStaticMaxColumns) {
+    set_error("layer_norm static: N = %lld exceeds the %lld columns the built-in 4 MiB scratch "
+              "is sized for; use ffk_layer_norm_backward with a caller workspace",
+              N, kStaticMaxColumns);
+    return FFK_ERR_LIMIT;
+  }
+  float *scratch = nullptr;
+  int rc = static_scratch_of_current_device(&scratch);
+  if (rc) return rc;
+  return ffk_layer_norm_backward(stream, output_grad, input, input_grad, gamma, gamma_grad,
+                                 beta_grad, mean, rstd, M, N, dtype, accumulate_param_grads,
+                                 scratch, kStaticScratchFloats * sizeof(float));
 }
 
 }  // extern "C"

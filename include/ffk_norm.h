@@ -49,6 +49,23 @@ int ffk_layer_norm_backward(void *stream, void const *output_grad, void const *i
                             long long N, int dtype, int accumulate_param_grads, void *workspace,
                             size_t workspace_bytes);
 
+/* No counterpart in the reference. LayerNorm backward for callers that cannot allocate device
+ * memory and have no workspace to pass: tasks running under a runtime that has already claimed
+ * the GPU's memory for its own pool (the reference's legacy Legion/Realm runtime does so at
+ * start-up, so a later cudaMalloc may fail, and in any case synchronises the device), or code
+ * that reaches the backward call without an Allocator / PerDeviceFFHandle workspace. Same
+ * arguments and results as ffk_layer_norm_backward without the workspace pair: the partial
+ * dgamma / dbeta sums are kept in a 4 MiB array built into libffk.so (held by every GPU that
+ * loads the library, until exit). Limit: N <= 16384, else FFK_ERR_LIMIT. It allocates nothing.
+ * The first call on a device looks up the array's device address — make that call before any
+ * stream capture. Calls on one GPU share the array: run them one after another (same stream
+ * or event-ordered); calls that overlap on the GPU race. */
+int ffk_layer_norm_backward_static(void *stream, void const *output_grad, void const *input,
+                                   void *input_grad, void const *gamma, void *gamma_grad,
+                                   void *beta_grad, float const *mean, float const *rstd,
+                                   long long M, long long N, int dtype,
+                                   int accumulate_param_grads);
+
 /* Kernels::BatchNorm::forward_kernel — include/kernels/batch_norm_kernels.h:49,
  * src/cuda/ops/batch_norm_kernels.cu:26-53 (cudnnBatchNormalizationForwardTraining, SPATIAL,
  * exponentialAverageFactor 1.0). NCHW fp32. Per channel: batch mean and biased variance,
