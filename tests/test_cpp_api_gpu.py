@@ -1,0 +1,32 @@
+"""Runs the C++ veneer test (tests/cpp/kernels_api_test.cc): the reference's own kernel tests
+(lib/kernels/test/src/test_*.cc — same shapes, fills and assertions) against
+FlexFlow::Kernels::<Op> as declared in flexflow-train_b200/include/kernels/*.h."""
+import subprocess
+from pathlib import Path
+
+import pytest
+
+ROOT = Path(__file__).resolve().parents[1]
+BIN = ROOT / "tests" / "cpp" / "kernels_api_test"
+
+
+def test_veneer_headers_keep_the_reference_include_paths():
+    names = ["accessor", "allocation", "array_shape", "attention_kernels", "batch_matmul_kernels",
+             "batch_norm_kernels", "cast_kernels", "combine_kernels", "concat_kernels", "dropout_kernels",
+             "element_binary_kernels", "element_unary_kernels", "embedding_kernels", "ff_handle",
+             "flat_kernels", "gather_kernels", "layer_norm_kernels", "linear_kernels",
+             "local_cuda_allocator", "loss_function_kernels", "managed_ff_stream",
+             "managed_per_device_ff_handle", "optimizer_kernels", "partition_kernels", "pool_2d_kernels",
+             "profiling", "reduce_kernels", "reduction_kernels", "replicate_kernels", "reshape_kernels",
+             "reverse_kernels", "softmax_kernels", "split_kernels", "topk_kernels", "transpose_kernels"]
+    inc = ROOT / "flexflow-train_b200" / "include" / "kernels"
+    missing = [n for n in names if not (inc / f"{n}.h").exists()]
+    assert not missing, missing
+
+
+@pytest.mark.gpu
+def test_reference_kernel_tests_on_the_cpp_veneer():
+    assert BIN.exists(), "build it with __graft_entry__.build()"
+    r = subprocess.run([str(BIN)], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert "0 failed" in r.stdout
