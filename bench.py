@@ -132,8 +132,10 @@ class Workload:
         self.dy_src = r(M, N).to(bf)
         self.dy = torch.empty_like(self.dy_src)
         self.dx = torch.zeros(M, KDIM, dtype=bf, device=device)
-        self.dw = torch.zeros(N, KDIM, dtype=bf, device=device)
-        self.db = torch.zeros(N, dtype=bf, device=device)
+        # weight gradients live in flat buckets so that data-parallel sync is one all-reduce each
+        self.flat16 = torch.zeros(N * KDIM + N, dtype=bf, device=device)
+        self.dw = self.flat16[: N * KDIM].view(N, KDIM)
+        self.db = self.flat16[N * KDIM:]
         self.lin = Kmod.Linear.init_kernel(Kmod.ACT_RELU, 0.0, True, Kmod.GEMM_TENSOR, out_dim=N, device=device)
         # Softmax / LayerNorm / ElementBinary (fp32)
         self.a = r(ROWS, COLS)
@@ -143,8 +145,9 @@ class Workload:
         self.gc = torch.zeros(ROWS, COLS, device=device)
         self.gamma = r(COLS) + 1
         self.beta = r(COLS)
-        self.dgamma = torch.zeros(COLS, device=device)
-        self.dbeta = torch.zeros(COLS, device=device)
+        self.flat32 = torch.zeros(2 * COLS, device=device)
+        self.dgamma = self.flat32[:COLS]
+        self.dbeta = self.flat32[COLS:]
         self.ln = Kmod.LayerNorm.init_kernel(True, ROWS, COLS, 1e-5, device=device)
         # Embedding
         self.table = r(ENTRIES, EDIM)
@@ -156,7 +159,7 @@ class Workload:
         self.gemm_events = []
 
     def grads_for_sync(self):
-        return [self.dw, self.db, self.dgamma, self.dbeta]
+        return [self.flat16, self.flat32]
 
     def step(self, time_gemm=False):
         K, t = self.K, self.torch
@@ -205,15 +208,14 @@ def run_gpu(args):
     wl = Workload(torch, Kmod, device)
     lib = ffk_import.load().lib()
 
+    pops = None
+    if world > 1:
+        pops = importlib.import_module("flexflow_train_b200.parallel_ops").ParallelOps()
+
     def sync_grads():
-        if world > 1:
-            flat = torch.cat([g.reshape(-1).float() for g in wl.grads_for_sync()])
-            dist.all_reduce(flat)  # Replicate-backward: sum of replica gradients over NVLink
-            off = 0
-            for g in wl.grads_for_sync():
-                n = g.numel()
-                g.copy_(flat[off:off + n].view_as(g))
-                off += n
+        if pops is not None:
+            # Replicate-backward / *_nccl_update gradient sync: SUM over ranks, two flat buckets
+            pops.allreduce_gradients(wl.grads_for_sync())
 
     def barrier():
         if world > 1:
@@ -315,7 +317,7 @@ def run_gpu(args):
             "samples_per_step": SAMPLES_PER_STEP,
             "l2": "inputs larger than L2 (step touches >2 GB; L2 is 126 MB), no explicit flush",
             "parallelism": f"dp{n_gpus}" if n_gpus > 1 else "single",
-            "grad_sync": "NCCL all-reduce of dW/db/dgamma/dbeta per step" if n_gpus > 1 else "none",
+            "grad_sync": "NCCL all-reduce (sum) of two flat gradient buckets per step: dW|db bf16 32 MiB, dgamma|dbeta fp32" if n_gpus > 1 else "none",
         },
         "roofline": {
             "kernel": "gemm_tc_kernel (tcgen05, Linear forward 8192x4096x4096 bf16, fused bias+ReLU)",

@@ -1,0 +1,135 @@
+"""Multi-GPU forms of the four parallel operators: one process per GPU,
+`torch.distributed` (NCCL over NVLink 5 / NVSwitch) moves the bytes, the local halves (slice,
+place, accumulate) run on the sm_100a kernels through the C ABI.
+
+    Replicate   fwd: broadcast from the owning rank (bit-exact)       bwd: all-reduce(sum) of the replica gradients
+    Reduction   fwd: all-reduce(sum) of the partial tensors            bwd: copy (bit-exact)
+    Repartition fwd: every rank keeps its slab along `dim` (bit-exact) bwd: all-gather the slab gradients, accumulate
+    Combine     fwd: all-gather the slabs along `dim` (bit-exact)      bwd: accumulate this rank's slab of the gradient
+
+The single-device forms (`kernels.Replicate` ...) are what the reference's kernels compute
+(`lib/kernels/src/cuda/ops/{replicate,reduction,partition,combine}_kernels.cu`); the movement
+between devices was Legion's job there and is NCCL's here. The reference sums gradients
+without dividing by the replica count (optimizer_kernel.cu:83-89), and so does this.
+
+`local` supplies copy / accumulate / strided copy. The default is the GPU kernels; there is
+no CPU implementation in the product — the CPU tests inject one built on the test oracle to
+exercise the rank arithmetic over gloo.
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Sequence
+
+import torch
+import torch.distributed as dist
+
+
+class GpuLocalOps:
+    """copy / accumulate / strided block copy on the device through libffk.so."""
+
+    def __init__(self):
+        from . import kernels as K  # raises if libffk.so is missing: no fallback
+
+        self.K = K
+
+    def copy(self, dst, src):
+        self.K.copy(None, dst, src)
+
+    def accumulate(self, dst, src):
+        self.K.accumulate(None, dst, src)
+
+    def copy_blocks(self, out, out_off, inp, in_off, num_blocks, out_blk, in_blk, add=False):
+        name = "ffk_add_with_stride" if add else "ffk_copy_with_stride"
+        es = out.element_size()
+        self.K._call(name, self.K._stream(None), out.data_ptr() + out_off * es,
+                     inp.data_ptr() + in_off * es, num_blocks, out_blk, in_blk, self.K.dtype_code(out))
+
+
+def _blocks(shape: Sequence[int], dim: int):
+    outer = 1
+    for s in shape[:dim]:
+        outer *= s
+    inner = 1
+    for s in shape[dim:]:
+        inner *= s
+    return outer, inner
+
+
+class ParallelOps:
+    def __init__(self, group: Optional[dist.ProcessGroup] = None, local=None):
+        self.group = group
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        self.local = local if local is not None else GpuLocalOps()
+
+    # ------------------------------------------------------------------ Replicate
+    def replicate_forward(self, tensor: torch.Tensor, src: int = 0) -> torch.Tensor:
+        dist.broadcast(tensor, src, group=self.group)
+        return tensor
+
+    def replicate_backward(self, input_grad: torch.Tensor, output_grad: torch.Tensor) -> None:
+        """input_grad += sum over ranks of output_grad. `output_grad` is used as the
+        communication buffer and holds the sum afterwards."""
+        dist.all_reduce(output_grad, op=dist.ReduceOp.SUM, group=self.group)
+        self.local.accumulate(input_grad, output_grad)
+
+    # ------------------------------------------------------------------ Reduction
+    def reduction_forward(self, partial: torch.Tensor, output: torch.Tensor) -> None:
+        self.local.copy(output, partial)
+        dist.all_reduce(output, op=dist.ReduceOp.SUM, group=self.group)
+
+    def reduction_backward(self, input_grad: torch.Tensor, output_grad: torch.Tensor) -> None:
+        self.local.copy(input_grad, output_grad)
+
+    # ------------------------------------------------------------------ Repartition
+    def slab_shape(self, full_shape: Sequence[int], dim: int) -> List[int]:
+        assert full_shape[dim] % self.world == 0, "dimension must divide evenly over the ranks"
+        s = list(full_shape)
+        s[dim] //= self.world
+        return s
+
+    def repartition_forward(self, input: torch.Tensor, output: torch.Tensor, dim: int) -> None:
+        """output = this rank's slab of the (replicated) input along `dim`."""
+        assert list(output.shape) == self.slab_shape(input.shape, dim)
+        outer, full_blk = _blocks(input.shape, dim)
+        _, slab_blk = _blocks(output.shape, dim)
+        self.local.copy_blocks(output, 0, input, self.rank * slab_blk, outer, slab_blk, full_blk)
+
+    def repartition_backward(self, input_grad: torch.Tensor, output_grad: torch.Tensor, dim: int) -> None:
+        """input_grad (full) += concatenation over ranks of the slab gradients along `dim`."""
+        gathered = torch.empty((self.world,) + tuple(output_grad.shape), dtype=output_grad.dtype,
+                               device=output_grad.device)
+        dist.all_gather_into_tensor(gathered.view(-1), output_grad.contiguous().view(-1), group=self.group)
+        outer, full_blk = _blocks(input_grad.shape, dim)
+        _, slab_blk = _blocks(output_grad.shape, dim)
+        n = output_grad.numel()
+        for r in range(self.world):
+            self.local.copy_blocks(input_grad, r * slab_blk, gathered, r * n, outer, full_blk, slab_blk, add=True)
+
+    # ------------------------------------------------------------------ Combine
+    def combine_forward(self, input: torch.Tensor, output: torch.Tensor, dim: int) -> None:
+        """output (full) = concatenation over ranks of the slabs `input` along `dim`."""
+        assert list(input.shape) == self.slab_shape(output.shape, dim)
+        outer, full_blk = _blocks(output.shape, dim)
+        _, slab_blk = _blocks(input.shape, dim)
+        if dim == 0 or outer == 1:
+            dist.all_gather_into_tensor(output.view(-1), input.contiguous().view(-1), group=self.group)
+            return
+        gathered = torch.empty((self.world,) + tuple(input.shape), dtype=input.dtype, device=input.device)
+        dist.all_gather_into_tensor(gathered.view(-1), input.contiguous().view(-1), group=self.group)
+        n = input.numel()
+        for r in range(self.world):
+            self.local.copy_blocks(output, r * slab_blk, gathered, r * n, outer, full_blk, slab_blk)
+
+    def combine_backward(self, output_grad: torch.Tensor, input_grad: torch.Tensor, dim: int) -> None:
+        """input_grad (slab) += this rank's slab of output_grad (full)."""
+        outer, full_blk = _blocks(output_grad.shape, dim)
+        _, slab_blk = _blocks(input_grad.shape, dim)
+        self.local.copy_blocks(input_grad, 0, output_grad, self.rank * slab_blk, outer, slab_blk, full_blk, add=True)
+
+    # ------------------------------------------------------------------ optimizer sync
+    def allreduce_gradients(self, flat_buffers: Sequence[torch.Tensor]) -> None:
+        """The `*_nccl_update_task_gpu` gradient sync (optimizer_kernel.cu:83-89,191-197):
+        SUM over ranks, no division; one collective per flat bucket."""
+        for b in flat_buffers:
+            dist.all_reduce(b, op=dist.ReduceOp.SUM, group=self.group)

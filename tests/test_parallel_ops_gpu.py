@@ -1,0 +1,72 @@
+"""GPU, 2 ranks over NCCL (skipped on a single-GPU box): the multi-GPU parallel operators with
+the real local kernels, checked against the single-process statement of the same math."""
+import os
+import socket
+import sys
+from pathlib import Path
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = Path(__file__).resolve().parents[1]
+pytestmark = pytest.mark.gpu
+
+
+def _worker(rank, world, port, results):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    sys.path.insert(0, str(ROOT))
+    import ffk_import
+
+    ffk_import.load()
+    from flexflow_train_b200.parallel_ops import ParallelOps
+
+    P = ParallelOps()
+    ok = {}
+    g = torch.Generator(device="cuda").manual_seed(1234)
+    for dtype in (torch.float32, torch.bfloat16):
+        full = torch.rand(8, 6, 64, generator=g, device="cuda").to(dtype)
+        x = full.clone() if rank == 0 else torch.zeros_like(full)
+        P.replicate_forward(x)
+        ok[f"replicate_fwd_{dtype}"] = torch.equal(x, full)
+        dx = torch.ones_like(full)
+        P.replicate_backward(dx, (full * (rank + 1)).contiguous())
+        ok[f"replicate_bwd_{dtype}"] = torch.allclose(dx.float(), 1 + full.float() * 3, rtol=2e-2)
+        out = torch.zeros_like(full)
+        P.reduction_forward((full * (rank + 1)).contiguous(), out)
+        ok[f"reduction_fwd_{dtype}"] = torch.allclose(out.float(), full.float() * 3, rtol=2e-2)
+        for dim in (0, 1, 2):
+            slab = torch.zeros(P.slab_shape(full.shape, dim), dtype=dtype, device="cuda")
+            P.repartition_forward(full, slab, dim)
+            expect = torch.chunk(full, world, dim=dim)[rank].contiguous()
+            ok[f"repartition_fwd_{dim}_{dtype}"] = torch.equal(slab, expect)
+            back = torch.zeros_like(full)
+            P.combine_forward(slab, back, dim)
+            ok[f"combine_fwd_{dim}_{dtype}"] = torch.equal(back, full)
+            gfull = torch.ones_like(full)
+            P.repartition_backward(gfull, slab, dim)
+            ok[f"repartition_bwd_{dim}_{dtype}"] = torch.equal(gfull, 1 + full)
+            gslab = torch.ones_like(slab)
+            P.combine_backward(full, gslab, dim)
+            ok[f"combine_bwd_{dim}_{dtype}"] = torch.equal(gslab, 1 + expect)
+    torch.cuda.synchronize()
+    results[rank] = ok
+    dist.destroy_process_group()
+
+
+def test_parallel_ops_two_gpus_nccl():
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (run with gpurun --gpus 2)")
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    mgr = mp.Manager()
+    results = mgr.dict()
+    mp.spawn(_worker, args=(2, port, results), nprocs=2, join=True)
+    for rank, ok in results.items():
+        bad = [k for k, v in ok.items() if not v]
+        assert not bad, f"rank {rank}: {bad}"
