@@ -78,6 +78,10 @@ struct Pool2DPerDeviceState {
   PoolOp pool_type;
   bool relu;
 };
+struct Conv2DPerDeviceState {
+  PerDeviceFFHandle handle;
+  ffk_conv2d_config_t config;
+};
 struct GatherPerDeviceState {
   PerDeviceFFHandle handle;
   legion_dim_t legion_dim;
@@ -445,6 +449,39 @@ inline void backward_kernel(ffStream_t stream, Pool2DPerDeviceState const &m, vo
                                 m.stride_w, m.pad_h, m.pad_w, static_cast<int>(m.pool_type)));
 }
 }  // namespace Pool2D
+
+// ------------------------------------------------------------------ conv_2d_kernels.h
+namespace Conv2D {
+// input / output accessors are NCHW in FF order, i.e. legion dims (w, h, c, n)
+inline Conv2DPerDeviceState init_kernel(PerDeviceFFHandle handle, std::optional<Activation> /*activation*/,
+                                        int kernel_h, int kernel_w, int groups, int padding_h,
+                                        int padding_w, int stride_h, int stride_w,
+                                        GenericTensorAccessorW const &input,
+                                        GenericTensorAccessorW const &output, float const * /*filter_ptr*/,
+                                        float * /*filter_grad_ptr*/) {
+  auto L = [](ArrayShape const &s, int i) { return (int)s[legion_dim_t{i}]; };
+  ffk_conv2d_config_t c{L(input.shape, 3), L(input.shape, 2), L(input.shape, 1), L(input.shape, 0),
+                        L(output.shape, 2), L(output.shape, 1), L(output.shape, 0),
+                        kernel_h, kernel_w, padding_h, padding_w, stride_h, stride_w, groups};
+  if (ffk_conv2d_workspace_bytes(&c) > handle.workSpaceSize)
+    FatalError("Conv2D: handle.workSpace is smaller than one im2col panel");
+  return Conv2DPerDeviceState{handle, c};
+}
+inline void forward_kernel(ffStream_t stream, Conv2DPerDeviceState const &m, float const *input_ptr,
+                           float *output_ptr, float const *filter_ptr, float const *bias_ptr,
+                           std::optional<Activation> activation) {
+  FFK_CHECK(ffk_conv2d_forward(stream, &m.config, input_ptr, output_ptr, filter_ptr, bias_ptr,
+                               activation.has_value(), m.handle.workSpace, m.handle.workSpaceSize));
+}
+inline void backward_kernel(ffStream_t stream, Conv2DPerDeviceState const &m, float const *input_ptr,
+                            float *input_grad_ptr, float const *output_ptr, float *output_grad_ptr,
+                            float const *filter_ptr, float *filter_grad_ptr, float *bias_grad_ptr,
+                            std::optional<Activation> activation) {
+  FFK_CHECK(ffk_conv2d_backward(stream, &m.config, input_ptr, input_grad_ptr, output_ptr, output_grad_ptr,
+                                filter_ptr, filter_grad_ptr, bias_grad_ptr, activation.has_value(),
+                                m.handle.workSpace, m.handle.workSpaceSize));
+}
+}  // namespace Conv2D
 
 // ------------------------------------------------------------------ cast / flat / reshape
 namespace Cast {

@@ -682,3 +682,46 @@ class MultiHeadAttention:
               _ptr(query_grad), _ptr(key), _ptr(key_grad), _ptr(value), _ptr(value_grad),
               _ptr(weight), _ptr(weight_grad), _ptr(output_grad), _ptr(m.reserveSpace),
               _ptr(m.workSpace), m.workSpace.numel(), _DT[m.dtype], m.path)
+
+
+# ------------------------------------------------------------------ conv
+class _Conv2DConfig(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_int) for n in (
+        "n", "in_c", "in_h", "in_w", "out_c", "out_h", "out_w", "kernel_h", "kernel_w", "pad_h",
+        "pad_w", "stride_h", "stride_w", "groups")]
+
+
+@dataclass
+class Conv2DPerDeviceState:
+    cfg: _Conv2DConfig
+    workspace: torch.Tensor
+    relu: bool
+
+
+class Conv2D:
+    """conv_2d_kernels.h"""
+
+    @staticmethod
+    def init_kernel(activation, kernel_h, kernel_w, groups, padding_h, padding_w, stride_h, stride_w,
+                    input_shape, output_shape, device="cuda"):
+        n, ci, ih, iw = input_shape
+        _, co, oh, ow = output_shape
+        cfg = _Conv2DConfig(n, ci, ih, iw, co, oh, ow, kernel_h, kernel_w, padding_h, padding_w,
+                            stride_h, stride_w, groups)
+        nbytes = lib().cdll.ffk_conv2d_workspace_bytes(ctypes.byref(cfg))
+        if nbytes == 0:
+            from ._lib import FFKError
+            raise FFKError("ffk_conv2d_workspace_bytes", -1, lib().last_error())
+        ws = torch.empty(nbytes // 4, dtype=torch.float32, device=device)
+        return Conv2DPerDeviceState(cfg, ws, activation is not None and activation != ACT_NONE)
+
+    @staticmethod
+    def forward_kernel(stream, m, input, output, filter, bias):
+        _call("ffk_conv2d_forward", _stream(stream), ctypes.byref(m.cfg), _ptr(input), _ptr(output),
+              _ptr(filter), _ptr(bias), int(m.relu), _ptr(m.workspace), m.workspace.numel() * 4)
+
+    @staticmethod
+    def backward_kernel(stream, m, input, input_grad, output, output_grad, filter, filter_grad, bias_grad):
+        _call("ffk_conv2d_backward", _stream(stream), ctypes.byref(m.cfg), _ptr(input), _ptr(input_grad),
+              _ptr(output), _ptr(output_grad), _ptr(filter), _ptr(filter_grad), _ptr(bias_grad),
+              int(m.relu), _ptr(m.workspace), m.workspace.numel() * 4)

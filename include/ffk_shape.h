@@ -70,6 +70,37 @@ int ffk_pool2d_backward(void *stream, float const *input, float *input_grad, flo
                         int out_w, int kernel_h, int kernel_w, int stride_h, int stride_w,
                         int pad_h, int pad_w, int pool_type);
 
+/* Conv2D geometry: the integer arguments of Kernels::Conv2D::init_kernel plus the tensor
+ * extents it reads from its accessors (include/kernels/conv_2d_kernels.h:47-59). NCHW fp32,
+ * cross-correlation (cuDNN's CUDNN_CROSS_CORRELATION, the reference's mode), dilation 1. */
+typedef struct {
+  int n, in_c, in_h, in_w;
+  int out_c, out_h, out_w;
+  int kernel_h, kernel_w, pad_h, pad_w, stride_h, stride_w, groups;
+} ffk_conv2d_config_t;
+
+/* Scratch bytes for the im2col panel of ONE sample (the minimum); more lets several samples
+ * share a GEMM launch. The reference passes handle.workSpace to cuDNN the same way
+ * (conv_2d_kernels.cu:286-287). */
+size_t ffk_conv2d_workspace_bytes(ffk_conv2d_config_t const *cfg_host);
+
+/* Kernels::Conv2D::forward_kernel — include/kernels/conv_2d_kernels.h:61,
+ * src/cuda/ops/conv_2d_kernels.cu:269-313: convolution, + bias (cudnnAddTensor) when bias is
+ * not NULL, then ReLU when `relu` (cudnnActivationForward with the RELU descriptor). Filter
+ * layout [out_c][in_c/groups][kernel_h][kernel_w]. */
+int ffk_conv2d_forward(void *stream, ffk_conv2d_config_t const *cfg_host, float const *input,
+                       float *output, float const *filter, float const *bias, int relu,
+                       void *workspace, size_t workspace_bytes);
+
+/* Kernels::Conv2D::backward_kernel — include/kernels/conv_2d_kernels.h:69,
+ * src/cuda/ops/conv_2d_kernels.cu:315-387: optional reluBackward on output_grad in place,
+ * then filter_grad, bias_grad and input_grad all ACCUMULATE (alpha = beta = 1). bias_grad and
+ * input_grad may be NULL. */
+int ffk_conv2d_backward(void *stream, ffk_conv2d_config_t const *cfg_host, float const *input,
+                        float *input_grad, float const *output, float *output_grad,
+                        float const *filter, float *filter_grad, float *bias_grad, int relu,
+                        void *workspace, size_t workspace_bytes);
+
 #ifdef __cplusplus
 }
 #endif

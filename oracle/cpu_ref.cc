@@ -1008,3 +1008,67 @@ ORACLE_API void oracle_mha_backward(long long const *dims, float const *q, float
   back(k, dk, wk, dw + ok, dkp, Rk, d.kS, HK);
   back(v, dv, wv, dw + ov, dvp, Rk, d.vS, HV);
 }
+
+// ===================================================================== Conv2D
+// lib/kernels/src/cuda/ops/conv_2d_kernels.cu:269-387: cudnnConvolutionForward (cross-correlation,
+// NCHW, groups) + cudnnAddTensor bias + RELU; backward: reluBackward, then filter / bias / data
+// gradients, all accumulated. geo = {n, ci, ih, iw, co, oh, ow, kh, kw, ph, pw, sh, sw, groups}.
+ORACLE_API void oracle_conv2d_forward(long long const *geo, float const *x, float *y, float const *w,
+                                      float const *bias, int relu) {
+  int n = geo[0], ci = geo[1], ih = geo[2], iw = geo[3], co = geo[4], oh = geo[5], ow = geo[6], kh = geo[7],
+      kw = geo[8], ph = geo[9], pw = geo[10], sh = geo[11], sw = geo[12], g = geo[13];
+  int cig = ci / g, cog = co / g;
+#pragma omp parallel for collapse(2) schedule(static)
+  for (int b = 0; b < n; ++b)
+    for (int o = 0; o < co; ++o) {
+      int grp = o / cog;
+      for (int ho = 0; ho < oh; ++ho)
+        for (int wo = 0; wo < ow; ++wo) {
+          double acc = 0.0;
+          for (int c = 0; c < cig; ++c)
+            for (int a = 0; a < kh; ++a)
+              for (int bb = 0; bb < kw; ++bb) {
+                int h = ho * sh - ph + a, ww = wo * sw - pw + bb;
+                if (h < 0 || h >= ih || ww < 0 || ww >= iw) continue;
+                acc += (double)x[(((size_t)b * ci + grp * cig + c) * ih + h) * iw + ww] *
+                       w[(((size_t)o * cig + c) * kh + a) * kw + bb];
+              }
+          float v = (float)acc;
+          if (bias) v += bias[o];
+          if (relu) v = v > 0.f ? v : 0.f;
+          y[(((size_t)b * co + o) * oh + ho) * ow + wo] = v;
+        }
+    }
+}
+ORACLE_API void oracle_conv2d_backward(long long const *geo, float const *x, float *dx, float const *y,
+                                       float *dy, float const *w, float *dw, float *db, int relu) {
+  int n = geo[0], ci = geo[1], ih = geo[2], iw = geo[3], co = geo[4], oh = geo[5], ow = geo[6], kh = geo[7],
+      kw = geo[8], ph = geo[9], pw = geo[10], sh = geo[11], sw = geo[12], g = geo[13];
+  int cig = ci / g, cog = co / g;
+  size_t ysz = (size_t)n * co * oh * ow;
+  if (relu)
+    for (size_t i = 0; i < ysz; ++i) dy[i] = y[i] > 0.f ? dy[i] : 0.f;
+  std::vector<double> aw((size_t)co * cig * kh * kw, 0.0), ax(dx ? (size_t)n * ci * ih * iw : 0, 0.0), ab(co, 0.0);
+  for (int b = 0; b < n; ++b)
+    for (int o = 0; o < co; ++o) {
+      int grp = o / cog;
+      for (int ho = 0; ho < oh; ++ho)
+        for (int wo = 0; wo < ow; ++wo) {
+          double gy = dy[(((size_t)b * co + o) * oh + ho) * ow + wo];
+          ab[o] += gy;
+          for (int c = 0; c < cig; ++c)
+            for (int a = 0; a < kh; ++a)
+              for (int bb = 0; bb < kw; ++bb) {
+                int h = ho * sh - ph + a, ww = wo * sw - pw + bb;
+                if (h < 0 || h >= ih || ww < 0 || ww >= iw) continue;
+                size_t xi = (((size_t)b * ci + grp * cig + c) * ih + h) * iw + ww;
+                size_t wi = (((size_t)o * cig + c) * kh + a) * kw + bb;
+                aw[wi] += gy * x[xi];
+                if (dx) ax[xi] += gy * w[wi];
+              }
+        }
+    }
+  for (size_t i = 0; i < aw.size(); ++i) dw[i] += (float)aw[i];
+  if (db) for (int o = 0; o < co; ++o) db[o] += (float)ab[o];
+  if (dx) for (size_t i = 0; i < ax.size(); ++i) dx[i] += (float)ax[i];
+}

@@ -261,3 +261,25 @@ def test_layout_ops(oracle):
         dx = np.zeros_like(xi)
         oracle.pool2d(xi, None, dx, dy, 2, 3, 9, 11, 5, 6, 3, 3, 2, 2, 1, 1, ptype, 1)
         torch.testing.assert_close(t(dx), tx.grad, rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("relu", [False, True])
+def test_conv2d(oracle, relu):
+    n, ci, ih, iw, co, k, s, p, g = 2, 4, 7, 6, 6, 3, 2, 1, 2
+    oh, ow = (ih + 2 * p - k) // s + 1, (iw + 2 * p - k) // s + 1
+    geo = [n, ci, ih, iw, co, oh, ow, k, k, p, p, s, s, g]
+    x, w, b = uniform((n, ci, ih, iw), 1), uniform((co, ci // g, k, k), 2), uniform((co,), 3)
+    y = np.zeros((n, co, oh, ow), np.float32)
+    oracle.conv2d_forward(geo, x, y, w, b, int(relu))
+    tx, tw, tb = t(x).requires_grad_(), t(w).requires_grad_(), t(b).requires_grad_()
+    ty = F.conv2d(tx, tw, tb, stride=s, padding=p, groups=g)
+    if relu:
+        ty = torch.relu(ty)
+    torch.testing.assert_close(t(y), ty.detach(), **TOL)
+    dy = uniform((n, co, oh, ow), 4)
+    ty.backward(t(dy))
+    dx, dw, db = np.zeros_like(x), np.zeros_like(w), np.zeros_like(b)
+    oracle.conv2d_backward(geo, x, dx, y, dy.copy(), w, dw, db, int(relu))
+    torch.testing.assert_close(t(dx), tx.grad, rtol=1e-5, atol=1e-5)
+    torch.testing.assert_close(t(dw), tw.grad, rtol=1e-5, atol=1e-5)
+    torch.testing.assert_close(t(db), tb.grad, rtol=1e-5, atol=1e-5)

@@ -116,3 +116,29 @@ def test_pool2d(K, oracle, ptype, n, c, ih, iw, k, s, p):
     K.Pool2D.backward_kernel(None, m, x, dx, y, dy)
     oracle.pool2d(xn, None, dxn, dyn, n, c, ih, iw, oh, ow, k, k, s, s, p, p, code, 1)
     assert_close(dx, dxn, rtol=1e-5, what=f"pool2d bwd {ptype}")
+
+
+@pytest.mark.parametrize("relu", [False, True])
+@pytest.mark.parametrize("n,ci,ih,iw,co,k,s,p,g", [(2, 3, 9, 11, 8, 3, 1, 1, 1), (3, 4, 8, 8, 6, 3, 2, 0, 2),
+                                                   (1, 16, 12, 12, 32, 1, 1, 0, 1), (2, 6, 7, 5, 6, 5, 2, 2, 3)])
+def test_conv2d(K, oracle, n, ci, ih, iw, co, k, s, p, g, relu):
+    oh, ow = (ih + 2 * p - k) // s + 1, (iw + 2 * p - k) // s + 1
+    geo = [n, ci, ih, iw, co, oh, ow, k, k, p, p, s, s, g]
+    x, xn = to_dev(uniform((n, ci, ih, iw), SEED_ACT))
+    w, wn = to_dev(uniform((co, ci // g, k, k), SEED_W) / np.sqrt(ci // g * k * k))
+    b, bn = to_dev(uniform((co,), SEED_W + 1))
+    m = K.Conv2D.init_kernel(K.ACT_RELU if relu else None, k, k, g, p, p, s, s, (n, ci, ih, iw), (n, co, oh, ow))
+    y = torch.zeros(n, co, oh, ow, device="cuda")
+    K.Conv2D.forward_kernel(None, m, x, y, w, b)
+    yref = np.zeros((n, co, oh, ow), np.float32)
+    oracle.conv2d_forward(geo, xn, yref, wn, bn, int(relu))
+    assert_close(y, yref, what="conv2d fwd")
+    dy, dyn = to_dev(uniform((n, co, oh, ow), SEED_ACT + 1))
+    dx, dxn = to_dev(uniform((n, ci, ih, iw), SEED_ACT + 2))
+    dw, dwn = to_dev(uniform((co, ci // g, k, k), SEED_W + 2))
+    db, dbn = to_dev(uniform((co,), SEED_W + 3))
+    K.Conv2D.backward_kernel(None, m, x, dx, y, dy, w, dw, db)
+    oracle.conv2d_backward(geo, xn, dxn, y.cpu().numpy(), dyn, wn, dwn, dbn, int(relu))
+    assert_close(dx, dxn, what="conv2d dX")
+    assert_close(dw, dwn, what="conv2d dW")
+    assert_close(db, dbn, what="conv2d db")
