@@ -84,7 +84,9 @@ struct UnaryBwd {
       case FFK_OP_RELU: return y > 0.f ? dy : 0.f;         // cudnnActivationBackward(RELU)
       case FFK_OP_SIGMOID: return dy * y * (1.f - y);
       case FFK_OP_TANH: return dy * (1.f - y * y);
-      case FFK_OP_ELU: return x > 0.f ? dy : dy * (y + s);  // d/dx s(e^x - 1) = y + s
+      // cuDNN's rule, which the reference inherits: branch on the OUTPUT (y >= 0), so with the
+      // reference's coefficient 0.0 the gradient is dy everywhere (tests/golden/cudnn_ops.npz)
+      case FFK_OP_ELU: return y >= 0.f ? dy : dy * (y + s);
       case FFK_OP_EXP: return dy * expf(x);
       case FFK_OP_GELU:
         return dy * (0.5f * erfcf(-x * 0.70710678118654752f) +

@@ -235,7 +235,7 @@ ORACLE_API int oracle_element_unary_backward(int op, float scalar, float const *
       case OP_RELU: r = o > 0.f ? g : 0.f; break;
       case OP_SIGMOID: r = g * o * (1.f - o); break;
       case OP_TANH: r = g * (1.f - o * o); break;
-      case OP_ELU: r = v > 0.f ? g : g * (o + scalar); break;
+      case OP_ELU: r = o >= 0.f ? g : g * (o + scalar); break;  // cuDNN branches on the output
       case OP_EXP: r = g * std::exp(v); break;
       case OP_GELU:
         r = (float)(g * (0.5 * std::erfc(-v * M_SQRT1_2) +

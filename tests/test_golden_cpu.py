@@ -89,3 +89,107 @@ def test_oracle_mha_against_torch(oracle):
     np.testing.assert_allclose(dk, tk.grad.numpy(), rtol=1e-5, atol=1e-6)
     np.testing.assert_allclose(dv, tv.grad.numpy(), rtol=1e-5, atol=1e-6)
     np.testing.assert_allclose(dw, 1 + tw.grad.numpy(), rtol=1e-5, atol=1e-5)  # accumulated
+
+
+# ---------------------------------------------------------------------------------------------
+# tests/golden/cudnn_ops.npz: results of the cuDNN calls the reference makes for Softmax,
+# ElementUnary (RELU/SIGMOID/TANH/ELU), ElementBinary, Reduce, BatchNorm, Pool2D and Dropout,
+# issued with the reference's descriptor settings on a B200 (oracle/cudnn_ref/ops_golden.cu,
+# tools/make_ops_golden.py). fp32 throughout; cuDNN's own rounding differs from an fp64
+# accumulation by a few ulp, hence rtol 1e-5 / atol 1e-6 unless noted.
+@pytest.fixture(scope="module")
+def G():
+    return np.load(GOLD / "cudnn_ops.npz")
+
+
+def near(got, ref, rtol=1e-5, atol=1e-6):
+    np.testing.assert_allclose(got, ref, rtol=rtol, atol=atol)
+
+
+def test_oracle_softmax_vs_cudnn(oracle, G):
+    x = np.ascontiguousarray(G["softmax_x"])
+    n, c, h, w = x.shape
+    y = np.zeros_like(x)
+    oracle.softmax_forward(x, y, n, c, h * w)
+    near(y, G["softmax_y"])
+
+
+@pytest.mark.parametrize("name,op", [("relu", 13), ("sigmoid", 15), ("tanh", 16), ("elu", 17)])
+def test_oracle_activations_vs_cudnn(oracle, G, name, op):
+    x = np.ascontiguousarray(G["act_x"])
+    y = np.zeros_like(x)
+    oracle.element_unary_forward(op, 0.0, x, y, x.size)  # ELU coefficient 0.0, as the reference sets
+    near(y, G[f"act_{name}_y"])
+    dx = np.array(G["act_dx0"], copy=True)
+    oracle.element_unary_backward(op, 0.0, x, dx, np.ascontiguousarray(G[f"act_{name}_y"]),
+                                  np.ascontiguousarray(G["act_dy"]), x.size)
+    near(dx, G[f"act_{name}_dx"])  # beta = 1: accumulates onto dx0
+
+
+@pytest.mark.parametrize("name,op", [("add", 28), ("sub", 35), ("mul", 29), ("max", 40), ("min", 41)])
+def test_oracle_element_binary_vs_cudnn(oracle, G, name, op):
+    a, b = np.ascontiguousarray(G["bin_lhs"]), np.ascontiguousarray(G["bin_rhs"])
+    o = np.zeros_like(a)
+    oracle.element_binary_forward(op, a, b, o, 4, list(a.shape), list(b.shape), list(a.shape))
+    near(o, G[f"bin_{name}"])
+
+
+def test_oracle_broadcast_gradient_vs_cudnn_reduce(oracle, G):
+    a, b, dy = (np.ascontiguousarray(G[k]) for k in ("bin_lhs", "bin_rhs", "bin_dy"))
+    dr = np.array(G["bin_drhs0"], copy=True)
+    oracle.element_binary_backward(28, dy, a, b, None, dr, 4, list(a.shape), list(b.shape), list(a.shape))
+    near(dr, G["bin_add_drhs"], rtol=1e-5, atol=1e-5)
+
+
+@pytest.mark.parametrize("name,mean", [("reduce_sum", 0), ("reduce_mean", 1)])
+def test_oracle_reduce_vs_cudnn(oracle, G, name, mean):
+    x = np.ascontiguousarray(G["reduce_x"])
+    out = np.zeros(G[name].shape, np.float32)
+    oracle.reduce_forward(x, out, 4, list(x.shape), list(out.shape), mean)
+    near(out, G[name], rtol=1e-5, atol=1e-5)
+
+
+def test_oracle_batch_norm_vs_cudnn(oracle, G):
+    x = np.ascontiguousarray(G["bn_x"])
+    n, c, h, w = x.shape
+    eps = float(G["bn_eps"][0])
+    y = np.zeros_like(x)
+    rm, rv, sm, si = (np.zeros(c, np.float32) for _ in range(4))
+    oracle.batch_norm_forward(x, y, np.ascontiguousarray(G["bn_scale"]), np.ascontiguousarray(G["bn_bias"]),
+                              rm, rv, sm, si, n, c, h, w, eps, 1.0)
+    near(y, G["bn_y"], rtol=1e-4, atol=1e-5)
+    near(rm, G["bn_running_mean"])
+    near(rv, G["bn_running_var"], rtol=1e-4)
+    near(sm, G["bn_save_mean"])
+    near(si, G["bn_save_invvar"], rtol=1e-4)  # cuDNN's "saved inverse variance" is 1/sqrt(var+eps)
+    dx, ds, db = (np.array(G[k], copy=True) for k in ("bn_dx0", "bn_dscale0", "bn_dbias0"))
+    oracle.batch_norm_backward(x, np.array(G["bn_dy"], copy=True), y, dx, np.ascontiguousarray(G["bn_scale"]),
+                               ds, db, sm, si, n, c, h, w, 0)
+    near(dx, G["bn_dx"], rtol=1e-3, atol=1e-4)
+    near(ds, G["bn_dscale"], rtol=1e-4, atol=1e-4)
+    near(db, G["bn_dbias"], rtol=1e-4, atol=1e-4)
+
+
+@pytest.mark.parametrize("name,ptype", [("pool_max", 0), ("pool_avg", 1)])
+def test_oracle_pool2d_vs_cudnn(oracle, G, name, ptype):
+    x = np.ascontiguousarray(G["pool_x"])
+    n, c, ih, iw = x.shape
+    _, _, oh, ow = G["pool_dy"].shape
+    y = np.zeros((n, c, oh, ow), np.float32)
+    oracle.pool2d(x, y, None, None, n, c, ih, iw, oh, ow, 3, 3, 2, 2, 1, 1, ptype, 0)
+    near(y, G[name + "_y"])
+    dx = np.array(G["pool_dx0"], copy=True)
+    oracle.pool2d(x, None, dx, np.ascontiguousarray(G["pool_dy"]), n, c, ih, iw, oh, ow, 3, 3, 2, 2, 1, 1, ptype, 1)
+    near(dx, G[name + "_dx"], rtol=1e-5, atol=1e-5)
+
+
+def test_dropout_value_rule_of_cudnn(G):
+    """cuDNN's mask cannot be reproduced; what it pins is the value rule our kernels share:
+    y is 0 or x/(1-p), the backward pass reuses the forward mask, about 1-p of entries survive."""
+    x, y, dy, dx = (G[k] for k in ("dropout_x", "dropout_y", "dropout_dy", "dropout_dx"))
+    p = float(G["dropout_rate"][0])
+    kept = y != 0
+    near(y[kept], x[kept] / (1 - p))
+    assert ((dx != 0) == kept).all()
+    near(dx[kept], dy[kept] / (1 - p))
+    assert abs(kept.mean() - (1 - p)) < 0.02
