@@ -3,6 +3,7 @@
 #include "gemm_sm100.cuh"
 
 #include <cudaTypedefs.h>
+#include <cstdlib>
 #include <mutex>
 
 namespace ffk {
@@ -299,6 +300,202 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
   }
 }
 
+// ------------------------------------------------------------------ CTA-pair kernel
+// Two CTAs of one cluster (one TPC) share a 256 x 256 output tile: CTA r owns rows
+// [r*128, r*128+128) and loads those rows of A plus columns [r*128, r*128+128) of B, so each
+// SM pulls 32 KB per k-block from L2 instead of 48 KB. The leader CTA (rank 0) issues
+// tcgen05.mma.cta_group::2 for both; TMA completions of both CTAs are counted on the
+// leader's full barrier; commits are multicast to both CTAs' empty / tmem-full barriers;
+// both epilogues release the accumulator through the leader's tmem-empty barrier.
+template <bool A_MN, bool B_MN, int STAGES>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
+    gemm_tc_pair_kernel(const __grid_constant__ CUtensorMap map_a,
+                        const __grid_constant__ CUtensorMap map_b, Epilogue ep, int M, int N, int K,
+                        int batch, int batch2, uint32_t idesc, int out_dtype, int vec_ok) {
+  constexpr int BLOCK_N = 256, HALF_N = 128, PAIR_M = 256, ESIZE = 2;
+  constexpr int BLOCK_K = SWIZZLE_BYTES / ESIZE, ATOM_MN = SWIZZLE_BYTES / ESIZE;
+  constexpr int A_BYTES = BLOCK_M * SWIZZLE_BYTES, B_BYTES = HALF_N * SWIZZLE_BYTES;
+  constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  constexpr uint32_t TMEM_COLS = 2 * BLOCK_N;
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t *smem = reinterpret_cast<uint8_t *>(
+      (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+  uint64_t *full_bar = reinterpret_cast<uint64_t *>(smem + STAGES * STAGE_BYTES);
+  uint64_t *empty_bar = full_bar + STAGES;
+  uint64_t *tmem_full = empty_bar + STAGES;
+  uint64_t *tmem_empty = tmem_full + 2;
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tmem_empty + 2);
+
+  int const warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  uint32_t const rank = ptx::cluster_ctarank();
+  bool const leader = rank == 0;
+
+  if (threadIdx.x == 0) {
+    ptx::prefetch_tensormap(&map_a);
+    ptx::prefetch_tensormap(&map_b);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      ptx::mbar_init(&full_bar[s], 2);   // leader's producer (with expect_tx) + peer's producer
+      ptx::mbar_init(&empty_bar[s], 1);  // one multicast commit
+    }
+    for (int s = 0; s < 2; ++s) {
+      ptx::mbar_init(&tmem_full[s], 1);
+      ptx::mbar_init(&tmem_empty[s], 8);  // 4 epilogue warps in each of the two CTAs
+    }
+    ptx::fence_mbar_init();
+  }
+  if (warp == 2) {
+    ptx::tmem_alloc_2cta(tmem_slot, TMEM_COLS);
+    ptx::tmem_relinquish_2cta();
+  }
+  ptx::tc_fence_before();
+  ptx::cluster_sync();
+  ptx::tc_fence_after();
+  uint32_t const tmem_base = *tmem_slot;
+
+  int const num_m = (M + PAIR_M - 1) / PAIR_M;
+  int const num_n = (N + BLOCK_N - 1) / BLOCK_N;
+  int const num_tiles = num_m * num_n * batch;
+  int const num_k = (K + BLOCK_K - 1) / BLOCK_K;
+  int const tile0 = ptx::cluster_id_x(), tile_step = ptx::num_clusters_x();
+
+  // tile -> (batch, pair row block, column block); 4 pair-row-blocks (1024 rows) share B in L2
+  auto decode = [&](int tile, int &b, int &m_idx, int &n_idx) {
+    int per_batch = num_m * num_n;
+    b = tile / per_batch;
+    int t = tile - b * per_batch;
+    constexpr int G = 4;
+    int span = G * num_n, g = t / span, first = g * G;
+    int gsize = min(num_m - first, G), in_g = t - g * span;
+    m_idx = (first + in_g % gsize) * PAIR_M;
+    n_idx = (in_g / gsize) * BLOCK_N;
+  };
+
+  if (warp == 0 && lane == 0) {
+    // ------------------------------------------------------------ TMA producer (both CTAs)
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int tile = tile0; tile < num_tiles; tile += tile_step) {
+      int b, m_idx, n_idx;
+      decode(tile, b, m_idx, n_idx);
+      int const my_m = m_idx + rank * BLOCK_M, my_n = n_idx + rank * HALF_N;
+      int const b_in = b % batch2, b_out = b / batch2;
+      for (int kb = 0; kb < num_k; ++kb) {
+        ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+        uint8_t *sa = smem + stage * STAGE_BYTES;
+        uint8_t *sb = sa + A_BYTES;
+        uint32_t const lead_full = ptx::map_to_cta(ptx::smem_u32(&full_bar[stage]), 0);
+        if (leader) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * STAGE_BYTES);
+        int const k_idx = kb * BLOCK_K;
+        if constexpr (!A_MN) {
+          ptx::tma_load_4d_2cta(sa, &map_a, lead_full, k_idx, my_m, b_in, b_out);
+        } else {
+#pragma unroll
+          for (int j = 0; j < BLOCK_M / ATOM_MN; ++j)
+            ptx::tma_load_4d_2cta(sa + j * BLOCK_K * SWIZZLE_BYTES, &map_a, lead_full,
+                                  my_m + j * ATOM_MN, k_idx, b_in, b_out);
+        }
+        if constexpr (!B_MN) {
+          ptx::tma_load_4d_2cta(sb, &map_b, lead_full, k_idx, my_n, b_in, b_out);
+        } else {
+#pragma unroll
+          for (int j = 0; j < HALF_N / ATOM_MN; ++j)
+            ptx::tma_load_4d_2cta(sb + j * BLOCK_K * SWIZZLE_BYTES, &map_b, lead_full,
+                                  my_n + j * ATOM_MN, k_idx, b_in, b_out);
+        }
+        if (!leader) ptx::mbar_arrive_cluster(lead_full);
+        if (++stage == STAGES) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+    }
+  } else if (warp == 1 && lane == 0 && leader) {
+    // ------------------------------------------------------------ MMA issuer (leader only)
+    constexpr uint32_t A_LBO = A_MN ? BLOCK_K * SWIZZLE_BYTES : 0;
+    constexpr uint32_t B_LBO = B_MN ? BLOCK_K * SWIZZLE_BYTES : 0;
+    constexpr uint32_t A_KSTEP = A_MN ? (MMA_K_BYTES / ESIZE) * SWIZZLE_BYTES : MMA_K_BYTES;
+    constexpr uint32_t B_KSTEP = B_MN ? (MMA_K_BYTES / ESIZE) * SWIZZLE_BYTES : MMA_K_BYTES;
+    int stage = 0, acc = 0;
+    uint32_t phase = 0, acc_phase = 0;
+    for (int tile = tile0; tile < num_tiles; tile += tile_step) {
+      ptx::mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+      ptx::tc_fence_after();
+      uint32_t const d_tmem = tmem_base + acc * BLOCK_N;
+      for (int kb = 0; kb < num_k; ++kb) {
+        ptx::mbar_wait(&full_bar[stage], phase);
+        ptx::tc_fence_after();
+        uint32_t const sa = ptx::smem_u32(smem + stage * STAGE_BYTES);
+        uint32_t const sb = sa + A_BYTES;
+#pragma unroll
+        for (int k = 0; k < K_STEPS; ++k) {
+          uint64_t da = ptx::make_smem_desc_sw128(sa + k * A_KSTEP, A_LBO, 1024);
+          uint64_t db = ptx::make_smem_desc_sw128(sb + k * B_KSTEP, B_LBO, 1024);
+          ptx::mma_f16_ss_2cta(d_tmem, da, db, idesc, (kb | k) != 0);
+        }
+        ptx::mma_commit_2cta(&empty_bar[stage], 0b11);
+        if (kb == num_k - 1) ptx::mma_commit_2cta(&tmem_full[acc], 0b11);
+        if (++stage == STAGES) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+      if (++acc == 2) {
+        acc = 0;
+        acc_phase ^= 1;
+      }
+    }
+  } else if (warp >= 2) {
+    // ------------------------------------------------------------ epilogue (both CTAs)
+    int const q = warp & 3;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = tile0; tile < num_tiles; tile += tile_step) {
+      int b, m_idx, n_idx;
+      decode(tile, b, m_idx, n_idx);
+      ptx::mbar_wait(&tmem_full[acc], acc_phase);
+      ptx::tc_fence_after();
+      int const row = m_idx + rank * BLOCK_M + q * 32 + lane;
+      long long const row_off = static_cast<long long>(b / batch2) * ep.d_batch +
+                                static_cast<long long>(b % batch2) * ep.d_batch2 +
+                                static_cast<long long>(row) * ep.ldd;
+#pragma unroll 1
+      for (int c = 0; c < BLOCK_N / 32; ++c) {
+        uint32_t r[32];
+        ptx::tmem_ld_32x32(tmem_base + (uint32_t(q * 32) << 16) + acc * BLOCK_N + c * 32, r);
+        ptx::tmem_ld_wait();
+        if (c == BLOCK_N / 32 - 1) {
+          ptx::tc_fence_before();
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive_cluster(ptx::map_to_cta(ptx::smem_u32(&tmem_empty[acc]), 0));
+        }
+        int const col0 = n_idx + c * 32;
+        int const valid = min(32, N - col0);
+        if (row < M && valid > 0) {
+          switch (out_dtype) {
+            case FFK_FLOAT: epilogue_row_chunk<float>(r, ep, row_off, col0, valid, vec_ok); break;
+            case FFK_BFLOAT16: epilogue_row_chunk<__nv_bfloat16>(r, ep, row_off, col0, valid, vec_ok); break;
+            default: epilogue_row_chunk<__half>(r, ep, row_off, col0, valid, vec_ok); break;
+          }
+        }
+      }
+      if (++acc == 2) {
+        acc = 0;
+        acc_phase ^= 1;
+      }
+    }
+  }
+
+  ptx::tc_fence_before();
+  ptx::cluster_sync();
+  if (warp == 2) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc_2cta(tmem_base, TMEM_COLS);
+  }
+}
+
 // ------------------------------------------------------------------ host side
 PFN_cuTensorMapEncodeTiled_v12000 encode_fn() {
   static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
@@ -397,6 +594,47 @@ int launch_tc_layout(Problem const &p, Epilogue const &e, cudaStream_t s) {
   return launch_tc_inst<ESIZE, true, true, BLOCK_N, STAGES>(p, e, s);
 }
 
+template <bool A_MN, bool B_MN>
+int launch_tc_pair_inst(Problem const &p, Epilogue const &e, cudaStream_t stream) {
+  constexpr int STAGES = 6, BLOCK_K = 64, ATOM = 64, HALF_N = 128;
+  constexpr int SMEM = STAGES * (BLOCK_M * SWIZZLE_BYTES + HALF_N * SWIZZLE_BYTES) + 256 + 1024;
+  CUtensorMap ma, mb;
+  int rc;
+  int const b2 = p.batch2 > 1 ? p.batch2 : 1, bo = p.batch / b2;
+  if (!A_MN)
+    rc = make_map(&ma, p.a, p.in_dtype, p.K, p.M, bo, b2, p.lda, p.a_batch, p.a_batch2, BLOCK_K, BLOCK_M);
+  else
+    rc = make_map(&ma, p.a, p.in_dtype, p.M, p.K, bo, b2, p.lda, p.a_batch, p.a_batch2, ATOM, BLOCK_K);
+  if (rc) return rc;
+  if (!B_MN)
+    rc = make_map(&mb, p.b, p.in_dtype, p.K, p.N, bo, b2, p.ldb, p.b_batch, p.b_batch2, BLOCK_K, HALF_N);
+  else
+    rc = make_map(&mb, p.b, p.in_dtype, p.N, p.K, bo, b2, p.ldb, p.b_batch, p.b_batch2, ATOM, BLOCK_K);
+  if (rc) return rc;
+  auto kern = gemm_tc_pair_kernel<A_MN, B_MN, STAGES>;
+  FFK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+  uint32_t fmt = p.in_dtype == FFK_BFLOAT16 ? ptx::kFmtBF16 : ptx::kFmtF16;
+  uint32_t idesc = ptx::make_idesc(fmt, A_MN, B_MN, 256, 256);
+  long long tiles = 1LL * ((p.M + 255) / 256) * ((p.N + 255) / 256) * p.batch;
+  int clusters = (int)std::min<long long>(tiles, device_info().sm_count / 2);
+  size_t os = dtype_size(p.out_dtype);
+  int vec_ok = aligned16(e.d) && ((e.ldd * os) % 16 == 0) && ((e.d_batch * os) % 16 == 0) &&
+               ((e.d_batch2 * os) % 16 == 0) && (e.r == nullptr || aligned16(e.r));
+  Epilogue e2 = e;
+  e2.bias_vec_ok = e.bias != nullptr && aligned16(e.bias) && vec_ok;
+  kern<<<clusters * 2, NUM_THREADS, SMEM, stream>>>(ma, mb, e2, p.M, p.N, p.K, p.batch, b2, idesc,
+                                                    p.out_dtype, vec_ok);
+  FFK_LAUNCH_CHECK();
+  return FFK_OK;
+}
+
+int launch_tc_pair(Problem const &p, Epilogue const &e, cudaStream_t s) {
+  if (!p.a_mn_major && !p.b_mn_major) return launch_tc_pair_inst<false, false>(p, e, s);
+  if (!p.a_mn_major && p.b_mn_major) return launch_tc_pair_inst<false, true>(p, e, s);
+  if (p.a_mn_major && !p.b_mn_major) return launch_tc_pair_inst<true, false>(p, e, s);
+  return launch_tc_pair_inst<true, true>(p, e, s);
+}
+
 }  // namespace
 
 bool tc_eligible(Problem const &p, Epilogue const &e) {
@@ -431,6 +669,10 @@ int launch_tc(Problem const &p, Epilogue const &e, cudaStream_t stream) {
     return narrow ? launch_tc_layout<4, 128, 6>(p, e, stream)
                   : launch_tc_layout<4, 256, 4>(p, e, stream);
   }
+  // CTA pairs (256 x 256 tiles) whenever a problem has at least one full pair tile; the
+  // single-CTA kernel serves small or narrow outputs. FFK_GEMM_NO_PAIR=1 forces the latter.
+  static bool const no_pair = std::getenv("FFK_GEMM_NO_PAIR") != nullptr;
+  if (!no_pair && !narrow && p.M > 128) return launch_tc_pair(p, e, stream);
   return narrow ? launch_tc_layout<2, 128, 6>(p, e, stream)
                 : launch_tc_layout<2, 256, 4>(p, e, stream);
 }

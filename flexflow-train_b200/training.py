@@ -1,0 +1,301 @@
+"""Step driver over the kernel API — the glue the reference's local-execution backend lacks
+(SURVEY §8f-1): `LocalTrainingBacking::execute_update` is NOT_IMPLEMENTED
+(lib/local-execution/src/local_training_backing.cc:107-109) and no loss task is wired, so
+nothing in the reference can run a full step. This driver walks a layer list exactly the
+way `execute_forward` / `execute_backward` do (topological order forward, reversed order
+backward: local_training_backing.cc:69-105), then calls the loss and optimizer kernels.
+
+Every arithmetic step is a C-ABI call into libffk.so (through `kernels.py`); torch owns the
+device buffers. Gradients follow the reference's convention: backward kernels accumulate, so
+the driver zeroes all gradient buffers at the start of a step (`ff.zero_gradients()` in the
+legacy loop, examples/cpp/Transformer/transformer.cc:192-197).
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+from typing import Dict, List, Optional
+
+import torch
+
+from . import kernels as K
+
+
+class Tensor:
+    """An activation with its gradient buffer (allocated on demand)."""
+
+    def __init__(self, shape, dtype, device, requires_grad=True):
+        self.data = torch.zeros(shape, dtype=dtype, device=device)
+        self.grad = torch.zeros(shape, dtype=dtype, device=device) if requires_grad else None
+
+    @property
+    def shape(self):
+        return self.data.shape
+
+
+def _fill0(t: torch.Tensor):
+    K._call("ffk_fill", K._stream(None), t.data_ptr(), t.numel(), 0.0, K.dtype_code(t))
+
+
+class Layer:
+    params: List[torch.Tensor] = []
+    grads: List[torch.Tensor] = []
+
+    def forward(self):
+        raise NotImplementedError
+
+    def backward(self):
+        raise NotImplementedError
+
+
+class Linear(Layer):
+    def __init__(self, x: Tensor, out_dim: int, activation=K.ACT_NONE, bias=True, seed=0):
+        self.x = x
+        dt, dev = x.data.dtype, x.data.device
+        self.in_dim = x.shape[-1]
+        self.batch = x.data.numel() // self.in_dim
+        self.out_dim = out_dim
+        g = torch.Generator(device=dev).manual_seed(4321 + seed)
+        bound = (6.0 / (self.in_dim + out_dim)) ** 0.5  # glorot uniform, the reference's default initializer
+        self.w = ((torch.rand(out_dim, self.in_dim, device=dev, generator=g) * 2 - 1) * bound).to(dt)
+        self.b = torch.zeros(out_dim, dtype=dt, device=dev) if bias else None
+        self.dw = torch.zeros_like(self.w)
+        self.db = torch.zeros_like(self.b) if bias else None
+        self.y = Tensor(tuple(x.shape[:-1]) + (out_dim,), dt, dev)
+        self.state = K.Linear.init_kernel(activation, 0.0, bias, K.GEMM_AUTO, out_dim=out_dim, device=dev)
+        self.preact = torch.zeros_like(self.y.data) if activation == K.ACT_GELU else None
+        self.plain = K.Linear.init_kernel(K.ACT_NONE, 0.0, bias, K.GEMM_AUTO)
+        self.params = [self.w] + ([self.b] if bias else [])
+        self.grads = [self.dw] + ([self.db] if bias else [])
+
+    def forward(self):
+        if self.preact is not None:
+            # GELU's gradient needs the pre-activation: one extra plain projection kept beside
+            # the activated output (the reference's Linear cannot differentiate GELU at all)
+            K.Linear.forward_kernel(None, self.plain, self.x.data, self.preact, self.w, self.b,
+                                    self.in_dim, self.out_dim, self.batch)
+        K.Linear.forward_kernel(None, self.state, self.x.data, self.y.data, self.w, self.b, self.in_dim,
+                                self.out_dim, self.batch)
+
+    def backward(self):
+        K.Linear.backward_kernel(None, self.state, self.x.data, self.x.grad, self.y.data, self.y.grad,
+                                 self.w, self.dw, self.db, self.in_dim, self.out_dim, self.batch, self.preact)
+
+
+class LayerNorm(Layer):
+    def __init__(self, x: Tensor, eps=1e-5):
+        self.x = x
+        dt, dev = x.data.dtype, x.data.device
+        N = x.shape[-1]
+        M = x.data.numel() // N
+        self.gamma = torch.ones(N, dtype=dt, device=dev)
+        self.beta = torch.zeros(N, dtype=dt, device=dev)
+        self.dgamma = torch.zeros_like(self.gamma)
+        self.dbeta = torch.zeros_like(self.beta)
+        self.y = Tensor(x.shape, dt, dev)
+        self.state = K.LayerNorm.init_kernel(True, M, N, eps, device=dev)
+        self.params = [self.gamma, self.beta]
+        self.grads = [self.dgamma, self.dbeta]
+
+    def forward(self):
+        K.LayerNorm.forward_kernel(None, self.state, self.x.data, self.y.data, self.gamma, self.beta)
+
+    def backward(self):
+        K.LayerNorm.backward_kernel(None, self.state, self.y.grad, self.x.data, self.x.grad, self.gamma,
+                                    self.dgamma, self.dbeta, accumulate_param_grads=True)
+
+
+class Add(Layer):
+    def __init__(self, a: Tensor, b: Tensor):
+        self.a, self.b = a, b
+        self.y = Tensor(a.shape, a.data.dtype, a.data.device)
+
+    def forward(self):
+        K.ElementBinary.forward_kernel(None, K.OperatorType.EW_ADD, self.a.data, self.b.data, self.y.data)
+
+    def backward(self):
+        K.ElementBinary.backward_kernel(None, K.OperatorType.EW_ADD, self.y.grad, self.a.data, self.b.data,
+                                        self.a.grad, self.b.grad)
+
+
+class Dropout(Layer):
+    def __init__(self, x: Tensor, rate: float, seed: int):
+        self.x = x
+        self.y = Tensor(x.shape, x.data.dtype, x.data.device)
+        self.state = K.Dropout.init_kernel(rate, seed, x.data.numel(), device=x.data.device)
+        self.scratch = torch.zeros_like(x.data)
+
+    def forward(self):
+        K.Dropout.forward_kernel(None, self.state, self.x.data, self.y.data)
+
+    def backward(self):
+        # the kernel overwrites (reference semantics); the driver accumulates into x.grad
+        K.Dropout.backward_kernel(None, self.state, self.y.grad, self.scratch)
+        K.accumulate(None, self.x.grad, self.scratch)
+
+
+class SelfAttention(Layer):
+    """MultiHeadAttention with q = k = v = x (what lib/models' encoder layer builds:
+    transformer.cc:32-45). The reference's wrapper passes NULL for dK/dV in this case and
+    thereby drops two thirds of the input gradient; the driver asks for all three and sums them."""
+
+    def __init__(self, x: Tensor, heads: int, kdim: int, vdim: int, seed=0):
+        self.x = x
+        dt, dev = x.data.dtype, x.data.device
+        N, S, E = x.shape
+        self.state = K.MultiHeadAttention.init_kernel(N, heads, E, E, E, kdim, kdim, vdim, E, S, S, dtype=dt, device=dev)
+        nw = self.state.weightSize // x.data.element_size()
+        g = torch.Generator(device=dev).manual_seed(977 + seed)
+        self.w = ((torch.rand(nw, device=dev, generator=g) * 2 - 1) * (1.0 / E ** 0.5)).to(dt)
+        self.dw = torch.zeros_like(self.w)
+        self.y = Tensor(x.shape, dt, dev)
+        self.dq, self.dk, self.dv = (torch.zeros_like(x.data) for _ in range(3))
+        self.params, self.grads = [self.w], [self.dw]
+
+    def forward(self):
+        K.MultiHeadAttention.forward_kernel(None, self.state, self.x.data, self.x.data, self.x.data, self.w, self.y.data)
+
+    def backward(self):
+        K.MultiHeadAttention.backward_kernel(None, self.state, self.x.data, self.dq, self.x.data, self.dk,
+                                             self.x.data, self.dv, self.w, self.dw, self.y.grad)
+        for g in (self.dq, self.dk, self.dv):
+            K.accumulate(None, self.x.grad, g)
+
+
+class Softmax(Layer):
+    def __init__(self, x: Tensor):
+        self.x = x
+        self.y = Tensor(x.shape, x.data.dtype, x.data.device)
+
+    def forward(self):
+        C = self.x.shape[-1]
+        K.Softmax.forward_kernel(None, self.x.data, self.y.data, self.x.data.numel() // C, C, 1)
+
+    def backward(self):
+        # the reference's softmax backward is a copy (it relies on the fused CE loss gradient)
+        K.Softmax.backward_kernel(None, self.x.grad, self.y.grad)
+
+
+@dataclass
+class SGD:
+    lr: float = 0.01
+    momentum: float = 0.0
+    nesterov: bool = False
+    weight_decay: float = 1e-4  # FFConfig default (lib/local-execution/include/local-execution/config.h)
+    velocity: Dict[int, torch.Tensor] = field(default_factory=dict)
+    master: Dict[int, torch.Tensor] = field(default_factory=dict)
+
+    def step(self, params, grads, num_replicas=1):
+        for p, g in zip(params, grads):
+            v = None
+            if self.momentum > 0:
+                v = self.velocity.setdefault(id(p), torch.zeros(p.numel(), dtype=torch.float32, device=p.device))
+            m = None
+            if p.dtype != torch.float32:
+                m = self.master.setdefault(id(p), p.detach().float().clone())
+            K.sgd_ps_update_task_gpu(None, self.lr, self.momentum, self.nesterov, self.weight_decay, g,
+                                     p.numel(), num_replicas, p, v, m)
+
+
+class Model:
+    def __init__(self, inp: Tensor, layers: List[Layer], out: Tensor):
+        self.input, self.layers, self.output = inp, layers, out
+        self.params = [p for l in layers for p in l.params]
+        self.grads = [g for l in layers for g in l.grads]
+
+    def activations(self):
+        seen, out = set(), []
+        for l in self.layers:
+            for name in ("x", "a", "b", "y"):
+                t = getattr(l, name, None)
+                if isinstance(t, Tensor) and id(t) not in seen:
+                    seen.add(id(t))
+                    out.append(t)
+        return out
+
+    def zero_gradients(self):
+        for g in self.grads:
+            _fill0(g)
+        for t in self.activations():
+            if t.grad is not None:
+                _fill0(t.grad)
+
+    def forward(self):
+        for l in self.layers:
+            l.forward()
+
+    def backward(self):
+        for l in reversed(self.layers):
+            l.backward()
+
+
+def sparse_cce_step(model: Model, labels: torch.Tensor, opt: SGD, pops=None, global_batch=None):
+    """One training step with softmax + sparse categorical cross-entropy:
+    zero grads, forward, loss gradient (scale 1/global batch, lib/runtime/src/loss_functions.cc:68-72),
+    backward, gradient sync (sum over ranks, no division), SGD."""
+    model.zero_gradients()
+    model.forward()
+    probs = model.output
+    rows = probs.data.numel() // probs.shape[-1]
+    scale = 1.0 / float(global_batch or rows)
+    K.sparse_categorical_crossentropy_loss_backward_kernel(None, probs.grad, probs.data, labels, rows,
+                                                           probs.shape[-1], 1, scale)
+    model.backward()
+    if pops is not None:
+        pops.allreduce_gradients(model.grads)
+    opt.step(model.params, model.grads)
+
+
+def mse_step(model: Model, target: torch.Tensor, opt: SGD, pops=None, global_batch=None):
+    """One step with the mean-squared-error (avg) loss: scale = 2 / global volume."""
+    model.zero_gradients()
+    model.forward()
+    out = model.output
+    per_rank = out.data.numel()
+    world = 1 if pops is None else pops.world
+    scale = 2.0 / float(per_rank * world)
+    K.mean_squared_error_avg_loss_backward_kernel(None, out.grad, out.data, target, scale)
+    model.backward()
+    if pops is not None:
+        pops.allreduce_gradients(model.grads)
+    opt.step(model.params, model.grads)
+
+
+def build_mlp(batch=64, dims=(784, 512, 512, 10), dtype=torch.float32, device="cuda"):
+    """BASELINE configs[0]: MLP 784-512-512-10, ReLU, softmax head."""
+    x = Tensor((batch, dims[0]), dtype, device, requires_grad=True)
+    layers: List[Layer] = []
+    cur = x
+    for i, d in enumerate(dims[1:]):
+        last = i == len(dims) - 2
+        lin = Linear(cur, d, K.ACT_NONE if last else K.ACT_RELU, bias=True, seed=i)
+        layers.append(lin)
+        cur = lin.y
+    sm = Softmax(cur)
+    layers.append(sm)
+    return Model(x, layers, sm.y)
+
+
+def build_transformer_encoder(num_layers=12, d_model=1024, heads=16, seq=512, batch=64, dim_ff=4096,
+                              head_dim: Optional[int] = None, dropout=0.1, dtype=torch.bfloat16,
+                              device="cuda", seed=0):
+    """BASELINE configs[2]: the encoder stack lib/models builds
+    (lib/models/src/models/transformer/transformer.cc:32-65): MHA(x,x,x) -> add -> LayerNorm ->
+    dense(dim_ff, ReLU) -> dropout -> dense(d_model) -> dropout -> add -> LayerNorm.
+    head_dim None reproduces the reference's kdim = vdim = dim_ff / heads."""
+    hd = head_dim if head_dim is not None else dim_ff // heads
+    x = Tensor((batch, seq, d_model), dtype, device)
+    layers: List[Layer] = []
+    cur = x
+    for i in range(num_layers):
+        att = SelfAttention(cur, heads, hd, hd, seed=seed + i)
+        add1 = Add(cur, att.y)
+        ln1 = LayerNorm(add1.y)
+        ff1 = Linear(ln1.y, dim_ff, K.ACT_RELU, True, seed=100 + i)
+        dp1 = Dropout(ff1.y, dropout, 12345 + 2 * i)
+        ff2 = Linear(dp1.y, d_model, K.ACT_NONE, True, seed=200 + i)
+        dp2 = Dropout(ff2.y, dropout, 12346 + 2 * i)
+        add2 = Add(ln1.y, dp2.y)
+        ln2 = LayerNorm(add2.y)
+        layers += [att, add1, ln1, ff1, dp1, ff2, dp2, add2, ln2]
+        cur = ln2.y
+    return Model(x, layers, cur)

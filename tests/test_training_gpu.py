@@ -1,0 +1,79 @@
+"""GPU parity of whole training steps through the step driver (flexflow-train_b200/training.py):
+BASELINE configs[0] — MLP 784-512-512-10, batch 64, fp32, softmax + sparse-CCE + SGD — against
+the same chain of CPU-oracle kernels, step by step; and a small encoder stack for finiteness and
+loss decrease."""
+import numpy as np
+import pytest
+import torch
+
+from helpers import assert_close, uniform
+
+pytestmark = pytest.mark.gpu
+
+
+def oracle_mlp_step(o, P, x, labels, lr, wd, batch):
+    """The same step on the CPU oracle. P: list of (W, b) numpy arrays (updated in place)."""
+    acts = [x]
+    dims = [x.shape[1]] + [w.shape[0] for w, _ in P]
+    for i, (w, b) in enumerate(P):
+        y = np.zeros((batch, w.shape[0]), np.float32)
+        o.linear_forward(acts[-1], w, b, y, w.shape[1], w.shape[0], batch, -1 if i == len(P) - 1 else 0)
+        acts.append(y)
+    probs = np.zeros_like(acts[-1])
+    o.softmax_forward(acts[-1], probs, batch, probs.shape[1], 1)
+    g = np.zeros_like(probs)
+    o.sparse_cce_loss_backward(g, probs, labels, batch, probs.shape[1], 1, 1.0 / batch)
+    # softmax backward = copy (reference semantics)
+    grads = []
+    for i in reversed(range(len(P))):
+        w, b = P[i]
+        dw, db = np.zeros_like(w), np.zeros_like(b)
+        dx = np.zeros_like(acts[i])
+        o.linear_backward(acts[i], dx, acts[i + 1], g, w, dw, db, w.shape[1], w.shape[0], batch,
+                          -1 if i == len(P) - 1 else 0, 0.0, None)
+        grads.append((dw, db))
+        g = dx
+    for (w, b), (dw, db) in zip(P, reversed(grads)):
+        o.sgd_update(lr, 0.0, 0, wd, dw, w.size, 1, w.reshape(-1), None)
+        o.sgd_update(lr, 0.0, 0, wd, db, b.size, 1, b, None)
+    return probs
+
+
+def test_mlp_config0_three_steps_match_the_oracle(ffk, oracle):
+    import importlib
+    T = importlib.import_module("flexflow_train_b200.training")
+    batch = 64
+    model = T.build_mlp(batch=batch)
+    opt = T.SGD(lr=0.01, weight_decay=1e-4)
+    lin = [l for l in model.layers if isinstance(l, T.Linear)]
+    P = [(l.w.cpu().numpy().copy(), l.b.cpu().numpy().copy()) for l in lin]
+    rng = np.random.default_rng(1234)
+    for step in range(3):
+        x = rng.uniform(0, 1, (batch, 784)).astype(np.float32)       # MNIST-shaped synthetic data
+        labels = rng.integers(0, 10, batch).astype(np.int32)
+        model.input.data.copy_(torch.from_numpy(x))
+        T.sparse_cce_step(model, torch.from_numpy(labels).cuda(), opt)
+        probs = oracle_mlp_step(oracle, P, x, labels, 0.01, 1e-4, batch)
+        assert_close(model.output.data, probs, what=f"step {step} probabilities")
+        for l, (w, b) in zip(lin, P):
+            assert_close(l.w, w, rtol=1e-4, what=f"step {step} weights")
+            assert_close(l.b, b, rtol=1e-4, what=f"step {step} bias")
+
+
+def test_small_encoder_trains(ffk):
+    import importlib
+    T = importlib.import_module("flexflow_train_b200.training")
+    for dtype in (torch.float32, torch.bfloat16):
+        model = T.build_transformer_encoder(num_layers=2, d_model=64, heads=4, seq=16, batch=4, dim_ff=128,
+                                            dropout=0.0, dtype=dtype)
+        opt = T.SGD(lr=0.05, weight_decay=0.0)
+        g = torch.Generator(device="cuda").manual_seed(1)
+        x = (torch.rand(4, 16, 64, device="cuda", generator=g) * 2 - 1).to(dtype)
+        target = (torch.rand(4, 16, 64, device="cuda", generator=g) * 2 - 1).to(dtype)
+        losses = []
+        for _ in range(8):
+            model.input.data.copy_(x)
+            T.mse_step(model, target, opt)
+            losses.append(((model.output.data.float() - target.float()) ** 2).mean().item())
+        assert all(np.isfinite(losses)), losses
+        assert losses[-1] < losses[0], losses

@@ -76,6 +76,9 @@ def bench(M, N, K, a_mn, b_mn, dt=torch.bfloat16, iters=20):
     print(f"   cuBLAS same shape: {ms*1e3:.1f} us  {2*M*N*K/ms/1e9:.1f} TFLOP/s", flush=True)
 
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "bench":
+        bench(8192, 4096, 4096, False, False, iters=5)
+        sys.exit(0)
     ok = True
     for dt in (torch.bfloat16, torch.float16, torch.float32):
         for a_mn in (False, True):
