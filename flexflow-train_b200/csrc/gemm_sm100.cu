@@ -76,8 +76,13 @@ __device__ __forceinline__ void epilogue_row_chunk(uint32_t const (&acc)[32], Ep
 #pragma unroll
     for (int i = 0; i < 32; ++i) v[i] = fmaxf(v[i], 0.f);
   } else if (ep.act != ACT_NONE) {
+    if constexpr (sizeof(T) == 2) {
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] = apply_act_fast(v[i], ep.act);
+    } else {
 #pragma unroll 4
-    for (int i = 0; i < 32; ++i) v[i] = apply_act(v[i], ep.act);
+      for (int i = 0; i < 32; ++i) v[i] = apply_act(v[i], ep.act);
+    }
   }
   if (full) {
     if (ep.r != nullptr) {
@@ -337,7 +342,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < STAGES; ++s) {
-      ptx::mbar_init(&full_bar[s], 2);   // leader's producer (with expect_tx) + peer's producer
+      ptx::mbar_init(&full_bar[s], 1);   // leader's producer; both CTAs' TMA bytes are counted on it
       ptx::mbar_init(&empty_bar[s], 1);  // one multicast commit
     }
     for (int s = 0; s < 2; ++s) {
@@ -405,7 +410,6 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
             ptx::tma_load_4d_2cta(sb + j * BLOCK_K * SWIZZLE_BYTES, &map_b, lead_full,
                                   my_n + j * ATOM_MN, k_idx, b_in, b_out);
         }
-        if (!leader) ptx::mbar_arrive_cluster(lead_full);
         if (++stage == STAGES) {
           stage = 0;
           phase ^= 1;

@@ -65,6 +65,26 @@ int launch_simt(Problem const &p, Epilogue const &e, cudaStream_t stream);
 // Picks the tensor path for 16-bit inputs when eligible, else SIMT.
 int launch(Problem const &p, Epilogue const &e, cudaStream_t stream);
 
+__device__ __forceinline__ float tanh_fast(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));  // MUFU.TANH, rel. error ~2^-11
+  return y;
+}
+// Activations for 16-bit outputs: hardware tanh / exp are exact to well below bf16/half
+// resolution (2^-8 / 2^-11) and keep the epilogue off the critical path.
+__device__ __forceinline__ float apply_act_fast(float v, int act) {
+  switch (act) {
+    case ACT_RELU: return fmaxf(v, 0.f);
+    case ACT_SIGMOID: return 0.5f * tanh_fast(0.5f * v) + 0.5f;
+    case ACT_TANH: return tanh_fast(v);
+    case ACT_GELU: {
+      constexpr float B = 0.7978845608028654f, C = 0.035677408136300125f;
+      return v * (0.5f + 0.5f * tanh_fast(v * (C * v * v + B)));
+    }
+    default: return v;
+  }
+}
+
 __device__ __forceinline__ float apply_act(float v, int act) {
   switch (act) {
     case ACT_RELU: return fmaxf(v, 0.f);

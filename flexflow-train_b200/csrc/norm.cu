@@ -383,19 +383,29 @@ __global__ void __launch_bounds__(kThreads)
   }
 }
 
-// Sum the per-CTA partials in CTA order (deterministic) and write / accumulate. A CTA owns
-// 32 columns; its 8 row-lanes stride over the partial rows and are combined in lane order.
+// Sum the per-CTA partials (deterministic order) and write / accumulate. A CTA owns 32
+// columns; its 32 row-lanes stride over the partial slabs four loads deep, then combine in
+// lane order through shared memory.
 template <typename T>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(1024)
     layer_norm_param_reduce_kernel(float const *__restrict__ part, int nparts, long long N,
                                    T *__restrict__ dgamma, T *__restrict__ dbeta,
                                    bool accumulate) {
-  __shared__ float sg[8][33], sb[8][33];
+  __shared__ float sg[32][33], sb[32][33];
   int const cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
   long long const j = (long long)blockIdx.x * 32 + cx;
   float ag = 0.f, ab = 0.f;
   if (j < N) {
-    for (int p = ry; p < nparts; p += 8) {
+    int p = ry;
+    for (; p + 96 < nparts; p += 128) {
+      float g0 = part[(size_t(p) * 2 + 0) * N + j], b0 = part[(size_t(p) * 2 + 1) * N + j];
+      float g1 = part[(size_t(p + 32) * 2 + 0) * N + j], b1 = part[(size_t(p + 32) * 2 + 1) * N + j];
+      float g2 = part[(size_t(p + 64) * 2 + 0) * N + j], b2 = part[(size_t(p + 64) * 2 + 1) * N + j];
+      float g3 = part[(size_t(p + 96) * 2 + 0) * N + j], b3 = part[(size_t(p + 96) * 2 + 1) * N + j];
+      ag += (g0 + g1) + (g2 + g3);
+      ab += (b0 + b1) + (b2 + b3);
+    }
+    for (; p < nparts; p += 32) {
       ag += part[(size_t(p) * 2 + 0) * N + j];
       ab += part[(size_t(p) * 2 + 1) * N + j];
     }
@@ -406,7 +416,7 @@ __global__ void __launch_bounds__(kThreads)
   if (ry == 0 && j < N) {
     float tg = 0.f, tb = 0.f;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
+    for (int i = 0; i < 32; ++i) {
       tg += sg[i][cx];
       tb += sb[i][cx];
     }
@@ -692,7 +702,7 @@ int ffk_layer_norm_backward(void *stream, void const *output_grad, void const *i
       });
       FFK_LAUNCH_CHECK();
       if (fused) {
-        layer_norm_param_reduce_kernel<T><<<unsigned((N + 31) / 32), kThreads, 0, s>>>(
+        layer_norm_param_reduce_kernel<T><<<unsigned((N + 31) / 32), 1024, 0, s>>>(
             reinterpret_cast<float const *>(workspace), int(grid), N,
             reinterpret_cast<T *>(gamma_grad), reinterpret_cast<T *>(beta_grad),
             accumulate_param_grads != 0);

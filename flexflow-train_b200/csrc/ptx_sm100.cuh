@@ -187,8 +187,12 @@ __device__ __forceinline__ uint32_t map_to_cta(uint32_t local, uint32_t rank) {
   asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local), "r"(rank));
   return r;
 }
+// Arrive on a barrier that may live in the peer CTA. Deliberately NOT `.release.cluster`: that
+// form compiles to MEMBAR.ALL.GPU + ERRBAR in front of the arrive (seen in the round-1 ncu
+// source page, where it throttled the producer); the data these barriers guard travels through
+// TMA / tcgen05 completion mechanisms, not through generic-proxy stores.
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
 __device__ __forceinline__ void tmem_alloc_2cta(uint32_t *smem_slot, uint32_t ncols) {
   asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_slot)),
