@@ -349,6 +349,130 @@ def run_gpu(args):
         dist.destroy_process_group()
 
 
+# ----------------------------------------------------------------------------- encoder workload
+def run_encoder(args):
+    """BASELINE configs[2]: lib/models' transformer encoder (12 layers, d 1024, 16 heads, seq 512,
+    batch 64 per GPU, bf16, dim_ff 4096 assumed) trained with MSE + SGD through the step driver
+    (flexflow-train_b200/training.py), data-parallel over --gpus ranks. Selected with
+    `--workload encoder`; the default workload stays configs[1]."""
+    import importlib
+
+    import torch
+    import torch.distributed as dist
+
+    import ffk_import
+
+    ffk_import.load()
+    T = importlib.import_module("flexflow_train_b200.training")
+    Kmod = importlib.import_module("flexflow_train_b200.kernels")
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    pops = None
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=device)
+        pops = importlib.import_module("flexflow_train_b200.parallel_ops").ParallelOps()
+    B, S, D, H, FF, L = args.batch, 512, 1024, 16, 4096, args.layers
+    hd = args.head_dim if args.head_dim > 0 else FF // H
+    model = T.build_transformer_encoder(L, D, H, S, B, FF, hd, dropout=0.1, dtype=torch.bfloat16, device=device)
+    opt = T.SGD(lr=1e-3, weight_decay=1e-4)
+    g = torch.Generator(device=device).manual_seed(1234 + rank)
+    hx = (torch.rand(B, S, D, generator=g, device=device) * 2 - 1).to(torch.bfloat16).cpu().pin_memory()
+    target = (torch.rand(B, S, D, generator=g, device=device) * 2 - 1).to(torch.bfloat16)
+    model.input.data.copy_(hx)
+    lib = ffk_import.load().lib()
+    perf = Kmod.PerfMetrics(device=device)
+    out32 = torch.empty(B * S, D, device=device)
+    tgt32 = target.float().view(B * S, D).contiguous()
+    hres = torch.empty(7, dtype=torch.int32).pin_memory()
+
+    def step():
+        T.mse_step(model, target, opt, pops)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    clocks = ClockSampler(local_rank)
+    if rank == 0:
+        clocks.start()
+    calls0 = lib.launches
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        step()
+    e1.record()
+    barrier()
+    ms_total = e0.elapsed_time(e1)
+    abi_calls = lib.launches - calls0
+    clock_info = clocks.stop() if rank == 0 else None
+
+    def e2e_step():
+        model.input.data.copy_(hx, non_blocking=True)          # the batch arrives from the host
+        step()
+        Kmod.Cast.forward_kernel(None, model.output.data.view(B * S, D), out32)
+        Kmod._call("ffk_fill", Kmod._stream(None), perf.buf.data_ptr(), 7, 0.0, Kmod.INT32)
+        Kmod.update_metrics_label_kernel(None, Kmod.METRIC_MSE, out32, tgt32, B * S, D, perf)
+        hres.copy_(perf.buf, non_blocking=True)                # the step's metric goes back
+        torch.cuda.current_stream().synchronize()
+
+    for _ in range(2):
+        e2e_step()
+    barrier()
+    e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e2.record()
+    for _ in range(args.steps):
+        e2e_step()
+    e3.record()
+    barrier()
+    ms_e2e = e2.elapsed_time(e3)
+    if world > 1:
+        t = torch.tensor([ms_total, ms_e2e], device=device, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_total, ms_e2e = t.tolist()
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    ms_per_step = ms_total / args.steps
+    params = sum(p.numel() for p in model.params)
+    # fwd+bwd FLOPs per sample: 3 x (projections + scores + FFN), SURVEY §8d
+    per_tok = 2 * (3 * D * H * hd + H * hd * D + 2 * S * H * hd + 2 * D * FF)
+    flops_per_sample = 3 * per_tok * S * L
+    tf_peak, _, peak_src = load_peaks()
+    achieved = flops_per_sample * B / (ms_per_step * 1e-3) / 1e12
+    out = {
+        "metric": "training samples/sec (transformer encoder, fwd+bwd+SGD)",
+        "value": B * world / (ms_per_step * 1e-3), "unit": "samples/s", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
+        "data": "synthetic",
+        "config": {"workload": f"BASELINE configs[2]: transformer encoder {L} layers, d {D}, {H} heads, head dim {hd}, "
+                               f"dim_ff {FF}, seq {S}, batch {B} per GPU, MSE + SGD",
+                   "global_batch": B * world, "seq_len": S, "parameters": params,
+                   "parallelism": f"dp{world}" if world > 1 else "single",
+                   "l2": "activations of one layer exceed L2 (>= 0.5 GB)"},
+        "roofline": {"kernel": "whole step (model FLOPs, all kernels)", "bound": "tensor", "achieved": achieved,
+                     "peak": tf_peak, "peak_source": f"{peak_src} bf16_tflops (burst)", "unit": "TFLOP/s",
+                     "frac": achieved / tf_peak, "traffic": None},
+        "e2e": {"value": B * world / (ms_e2e / args.steps * 1e-3), "unit": "samples/s",
+                "h2d_bytes_per_step": hx.numel() * 2, "d2h_bytes_per_step": 28,
+                "ms_per_step": ms_e2e / args.steps},
+        "gpu_launches": None, "abi_calls_timed": abi_calls, "clocks": clock_info,
+    }
+    print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
 # ----------------------------------------------------------------------------- CPU arm
 def oracle_step(o, np, rows, erows, bufs=None):
     """The same step on the CPU oracle at `rows` of the 8192 samples (erows embedding indices)."""
@@ -447,11 +571,17 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="microbench", choices=["microbench", "encoder"])
+    ap.add_argument("--layers", type=int, default=12)
+    ap.add_argument("--batch", type=int, default=64)
+    ap.add_argument("--head-dim", type=int, default=0, help="0 = the reference's dim_ff/heads (256)")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3  # timing rule: at least 3 warm-up steps
     if args.impl == "reference":
         run_reference(args)
+    elif args.workload == "encoder":
+        run_encoder(args)
     else:
         run_gpu(args)
 

@@ -138,11 +138,15 @@ class SelfAttention(Layer):
     transformer.cc:32-45). The reference's wrapper passes NULL for dK/dV in this case and
     thereby drops two thirds of the input gradient; the driver asks for all three and sums them."""
 
+    _shared_ws: Dict = {}  # backward scratch is dead between layers: one buffer per (device, size)
+
     def __init__(self, x: Tensor, heads: int, kdim: int, vdim: int, seed=0):
         self.x = x
         dt, dev = x.data.dtype, x.data.device
         N, S, E = x.shape
         self.state = K.MultiHeadAttention.init_kernel(N, heads, E, E, E, kdim, kdim, vdim, E, S, S, dtype=dt, device=dev)
+        key = (str(dev), self.state.workSpace.numel())
+        self.state.workSpace = SelfAttention._shared_ws.setdefault(key, self.state.workSpace)
         nw = self.state.weightSize // x.data.element_size()
         g = torch.Generator(device=dev).manual_seed(977 + seed)
         self.w = ((torch.rand(nw, device=dev, generator=g) * 2 - 1) * (1.0 / E ** 0.5)).to(dt)
@@ -199,8 +203,31 @@ class SGD:
 class Model:
     def __init__(self, inp: Tensor, layers: List[Layer], out: Tensor):
         self.input, self.layers, self.output = inp, layers, out
+        self._flatten_gradients()
         self.params = [p for l in layers for p in l.params]
         self.grads = [g for l in layers for g in l.grads]
+
+    def _flatten_gradients(self):
+        """Re-home every weight gradient in one flat bucket per dtype (16-byte aligned slots),
+        so that zeroing is one fill and data-parallel sync is one all-reduce per bucket."""
+        by_dtype: Dict[torch.dtype, List] = {}
+        for l in self.layers:
+            for g in l.grads:
+                by_dtype.setdefault(g.dtype, []).append((l, g))
+        self.grad_buckets: List[torch.Tensor] = []
+        for dt, items in by_dtype.items():
+            align = 16 // torch.empty(0, dtype=dt).element_size()
+            total = sum((g.numel() + align - 1) // align * align for _, g in items)
+            flat = torch.zeros(total, dtype=dt, device=items[0][1].device)
+            off = 0
+            for l, g in items:
+                view = flat[off:off + g.numel()].view(g.shape)
+                for name, val in list(vars(l).items()):
+                    if val is g:
+                        setattr(l, name, view)
+                l.grads = [view if x is g else x for x in l.grads]
+                off += (g.numel() + align - 1) // align * align
+            self.grad_buckets.append(flat)
 
     def activations(self):
         seen, out = set(), []
@@ -213,8 +240,8 @@ class Model:
         return out
 
     def zero_gradients(self):
-        for g in self.grads:
-            _fill0(g)
+        for b in self.grad_buckets:
+            _fill0(b)
         for t in self.activations():
             if t.grad is not None:
                 _fill0(t.grad)
@@ -241,7 +268,7 @@ def sparse_cce_step(model: Model, labels: torch.Tensor, opt: SGD, pops=None, glo
                                                            probs.shape[-1], 1, scale)
     model.backward()
     if pops is not None:
-        pops.allreduce_gradients(model.grads)
+        pops.allreduce_gradients(model.grad_buckets)
     opt.step(model.params, model.grads)
 
 
@@ -256,7 +283,7 @@ def mse_step(model: Model, target: torch.Tensor, opt: SGD, pops=None, global_bat
     K.mean_squared_error_avg_loss_backward_kernel(None, out.grad, out.data, target, scale)
     model.backward()
     if pops is not None:
-        pops.allreduce_gradients(model.grads)
+        pops.allreduce_gradients(model.grad_buckets)
     opt.step(model.params, model.grads)
 
 
