@@ -96,6 +96,110 @@ __global__ void __launch_bounds__(kThreads)
   }
 }
 
+// Short rows (<= 8 packets per lane): one WARP per row, no block barrier. A row of 512 bf16
+// (the attention score rows) is 64 packets = 2 per lane.
+template <typename T, int PW>
+__global__ void __launch_bounds__(kThreads)
+    softmax_warp_rows_kernel(T const *x, T *y, long long rows, int nvec) {
+  constexpr int VN = Vec16<T>::N;
+  int const lane = threadIdx.x & 31;
+  long long const warp0 = (long long)blockIdx.x * (kThreads / 32) + (threadIdx.x >> 5);
+  long long const wstride = (long long)gridDim.x * (kThreads / 32);
+  bool const inplace = (x == y);
+  for (long long r = warp0; r < rows; r += wstride) {
+    T const *xr = x + r * (long long)nvec * VN;
+    T *yr = y + r * (long long)nvec * VN;
+    float v[PW][VN];
+    float mx = -INFINITY;
+#pragma unroll
+    for (int p = 0; p < PW; ++p) {
+      int i = lane + p * 32;
+      if (i < nvec) {
+        Vec16<T> t = inplace ? ld_vec(xr + i * VN) : ld_stream(xr + i * VN);
+#pragma unroll
+        for (int j = 0; j < VN; ++j) {
+          v[p][j] = to_f32(t.v[j]);
+          mx = fmaxf(mx, v[p][j]);
+        }
+      }
+    }
+    mx = warp_max(mx);
+    float sum = 0.f;
+#pragma unroll
+    for (int p = 0; p < PW; ++p) {
+      int i = lane + p * 32;
+      if (i < nvec) {
+#pragma unroll
+        for (int j = 0; j < VN; ++j) {
+          v[p][j] = __expf(v[p][j] - mx);
+          sum += v[p][j];
+        }
+      }
+    }
+    sum = warp_sum(sum);
+    float inv = 1.f / sum;
+#pragma unroll
+    for (int p = 0; p < PW; ++p) {
+      int i = lane + p * 32;
+      if (i < nvec) {
+        Vec16<T> o;
+#pragma unroll
+        for (int j = 0; j < VN; ++j) o.v[j] = from_f32<T>(v[p][j] * inv);
+        st_stream(yr + i * VN, o);
+      }
+    }
+  }
+}
+
+// dx = y (.) (dy - sum(dy (.) y)) for contiguous short rows, one warp per row; dx may alias dy.
+template <typename T, int PW>
+__global__ void __launch_bounds__(kThreads)
+    softmax_jacobian_warp_rows_kernel(T *dx, T const *dy, T const *__restrict__ y, long long rows,
+                                      int nvec) {
+  constexpr int VN = Vec16<T>::N;
+  int const lane = threadIdx.x & 31;
+  long long const warp0 = (long long)blockIdx.x * (kThreads / 32) + (threadIdx.x >> 5);
+  long long const wstride = (long long)gridDim.x * (kThreads / 32);
+  for (long long r = warp0; r < rows; r += wstride) {
+    long long const base = r * (long long)nvec * VN;
+    float g[PW][VN], p_[PW][VN];
+    float dot = 0.f;
+#pragma unroll
+    for (int p = 0; p < PW; ++p) {
+      int i = lane + p * 32;
+      if (i < nvec) {
+        Vec16<T> a = ld_vec(dy + base + i * VN), b = ld_stream(y + base + i * VN);
+#pragma unroll
+        for (int j = 0; j < VN; ++j) {
+          g[p][j] = to_f32(a.v[j]);
+          p_[p][j] = to_f32(b.v[j]);
+          dot += g[p][j] * p_[p][j];
+        }
+      }
+    }
+    dot = warp_sum(dot);
+#pragma unroll
+    for (int p = 0; p < PW; ++p) {
+      int i = lane + p * 32;
+      if (i < nvec) {
+        Vec16<T> o;
+#pragma unroll
+        for (int j = 0; j < VN; ++j) o.v[j] = from_f32<T>(p_[p][j] * (g[p][j] - dot));
+        st_vec(dx + base + i * VN, o);
+      }
+    }
+  }
+}
+
+inline int pick_pw(long long nvec) {
+  long long need = (nvec + 31) / 32;
+  if (need <= 1) return 1;
+  if (need <= 2) return 2;
+  if (need <= 4) return 4;
+  if (need <= 8) return 8;
+  return 0;
+}
+
 // Generic: one warp per (outer, inner) line, element stride `inner`.
 template <typename T>
 __global__ void __launch_bounds__(kThreads)
@@ -264,8 +368,8 @@ __global__ void __launch_bounds__(kThreads)
 // synchronisation is needed on them. Registers hold only the current row's dY and X
 // packets, which keeps 3-4 CTAs resident per SM to overlap one row's reduction with the
 // next row's loads.
-template <typename T, int P>
-__global__ void __launch_bounds__(kThreads)
+template <typename T, int P, int TPB>
+__global__ void __launch_bounds__(TPB)
     layer_norm_bwd_rows_kernel(T const *__restrict__ dy, T const *__restrict__ x,
                                T *__restrict__ dx, T const *__restrict__ gamma,
                                float const *__restrict__ mean, float const *__restrict__ rstd,
@@ -281,7 +385,7 @@ __global__ void __launch_bounds__(kThreads)
   float const invn = 1.f / float(N);
 #pragma unroll
   for (int p = 0; p < P; ++p) {
-    int i = threadIdx.x + p * kThreads;
+    int i = threadIdx.x + p * TPB;
     if (i < nvec) {
       float gv[VN];
 #pragma unroll
@@ -307,7 +411,7 @@ __global__ void __launch_bounds__(kThreads)
     float ds = 0.f, db = 0.f;
 #pragma unroll
     for (int p = 0; p < P; ++p) {
-      int i = threadIdx.x + p * kThreads;
+      int i = threadIdx.x + p * TPB;
       if (i < nvec) {
         Vec16<T> a = ld_stream(dyr + i * VN), b = ld_stream(xr + i * VN);
 #pragma unroll
@@ -331,7 +435,7 @@ __global__ void __launch_bounds__(kThreads)
     float const c2 = -(c1 * mu + db * rs * invn);
 #pragma unroll
     for (int p = 0; p < P; ++p) {
-      int i = threadIdx.x + p * kThreads;
+      int i = threadIdx.x + p * TPB;
       if (i < nvec) {
         if (dx) {
           T *dxr = dx + r * N;
@@ -371,7 +475,7 @@ __global__ void __launch_bounds__(kThreads)
     float4 *pbr = reinterpret_cast<float4 *>(part + (size_t(blockIdx.x) * 2 + 1) * N);
 #pragma unroll
     for (int p = 0; p < P; ++p) {
-      int i = threadIdx.x + p * kThreads;
+      int i = threadIdx.x + p * TPB;
       if (i < nvec) {
 #pragma unroll
         for (int q = 0; q < Q; ++q) {
@@ -488,6 +592,170 @@ __global__ void __launch_bounds__(kThreads)
   }
 }
 
+// Short rows: one warp per row for LayerNorm as well (a d_model = 1024 bf16 row is 128 packets).
+template <typename T, int PW>
+__global__ void __launch_bounds__(kThreads)
+    layer_norm_fwd_warp_rows_kernel(T const *__restrict__ x, T *__restrict__ y,
+                                    T const *__restrict__ gamma, T const *__restrict__ beta,
+                                    float *__restrict__ mean, float *__restrict__ rstd,
+                                    long long rows, int nvec, float eps) {
+  constexpr int VN = Vec16<T>::N;
+  int const lane = threadIdx.x & 31;
+  long long const warp0 = (long long)blockIdx.x * (kThreads / 32) + (threadIdx.x >> 5);
+  long long const wstride = (long long)gridDim.x * (kThreads / 32);
+  float const invn = 1.f / float(nvec * VN);
+  for (long long r = warp0; r < rows; r += wstride) {
+    T const *xr = x + r * (long long)nvec * VN;
+    T *yr = y + r * (long long)nvec * VN;
+    float v[PW][VN];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int p = 0; p < PW; ++p) {
+      int i = lane + p * 32;
+      if (i < nvec) {
+        Vec16<T> t = ld_stream(xr + i * VN);
+#pragma unroll
+        for (int j = 0; j < VN; ++j) {
+          v[p][j] = to_f32(t.v[j]);
+          s1 += v[p][j];
+          s2 += v[p][j] * v[p][j];
+        }
+      }
+    }
+    s1 = warp_sum(s1);
+    s2 = warp_sum(s2);
+    float mu = s1 * invn;
+    float var = fmaxf(s2 * invn - mu * mu, 0.f);
+    float rs = rsqrtf(var + eps);
+    if (lane == 0) {
+      mean[r] = mu;
+      rstd[r] = rs;
+    }
+#pragma unroll
+    for (int p = 0; p < PW; ++p) {
+      int i = lane + p * 32;
+      if (i < nvec) {
+        Vec16<T> o, g, b;
+        if (gamma) g = ld_vec(gamma + i * VN);
+        if (beta) b = ld_vec(beta + i * VN);
+#pragma unroll
+        for (int j = 0; j < VN; ++j) {
+          float t = (v[p][j] - mu) * rs;
+          if (gamma) t *= to_f32(g.v[j]);
+          if (beta) t += to_f32(b.v[j]);
+          o.v[j] = from_f32<T>(t);
+        }
+        st_stream(yr + i * VN, o);
+      }
+    }
+  }
+}
+
+// Fused backward for short rows, one warp per row. Each lane owns fixed columns, keeps gamma
+// and its running dgamma / dbeta sums in registers over all the rows its warp visits; the 8
+// warps of a CTA are combined through shared memory into this CTA's partial slab.
+template <typename T, int PW>
+__global__ void __launch_bounds__(kThreads)
+    layer_norm_bwd_warp_rows_kernel(T const *__restrict__ dy, T const *__restrict__ x,
+                                    T *__restrict__ dx, T const *__restrict__ gamma,
+                                    float const *__restrict__ mean, float const *__restrict__ rstd,
+                                    float *__restrict__ part, long long rows, int nvec) {
+  constexpr int VN = Vec16<T>::N;
+  extern __shared__ float4 ln_smem[];  // [2][N] floats, accumulated warp after warp
+  int const lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  long long const N = (long long)nvec * VN;
+  long long const warp0 = (long long)blockIdx.x * (kThreads / 32) + warp;
+  long long const wstride = (long long)gridDim.x * (kThreads / 32);
+  float const invn = 1.f / float(N);
+  float g[PW][VN], pg[PW][VN], pb[PW][VN];
+#pragma unroll
+  for (int p = 0; p < PW; ++p) {
+    int i = lane + p * 32;
+#pragma unroll
+    for (int j = 0; j < VN; ++j) {
+      g[p][j] = 1.f;
+      pg[p][j] = 0.f;
+      pb[p][j] = 0.f;
+    }
+    if (gamma && i < nvec) {
+      Vec16<T> t = ld_vec(gamma + i * VN);
+#pragma unroll
+      for (int j = 0; j < VN; ++j) g[p][j] = to_f32(t.v[j]);
+    }
+  }
+  for (long long r = warp0; r < rows; r += wstride) {
+    T const *dyr = dy + r * N;
+    T const *xr = x + r * N;
+    float dv[PW][VN], xv[PW][VN];
+    float ds = 0.f, db = 0.f;
+#pragma unroll
+    for (int p = 0; p < PW; ++p) {
+      int i = lane + p * 32;
+      if (i < nvec) {
+        Vec16<T> a = ld_stream(dyr + i * VN), b = ld_stream(xr + i * VN);
+#pragma unroll
+        for (int j = 0; j < VN; ++j) {
+          dv[p][j] = to_f32(a.v[j]);
+          xv[p][j] = to_f32(b.v[j]);
+          ds += dv[p][j] * xv[p][j] * g[p][j];
+          db += dv[p][j] * g[p][j];
+        }
+      }
+    }
+    ds = warp_sum(ds);
+    db = warp_sum(db);
+    float const mu = mean[r], rs = rstd[r];
+    float const c1 = (db * mu - ds) * rs * rs * rs * invn;
+    float const c2 = -(c1 * mu + db * rs * invn);
+#pragma unroll
+    for (int p = 0; p < PW; ++p) {
+      int i = lane + p * 32;
+      if (i < nvec) {
+        if (dx) {
+          T *dxr = dx + r * N;
+          Vec16<T> o = ld_vec(dxr + i * VN);
+#pragma unroll
+          for (int j = 0; j < VN; ++j)
+            o.v[j] = from_f32<T>(to_f32(o.v[j]) + rs * dv[p][j] * g[p][j] + c1 * xv[p][j] + c2);
+          st_vec(dxr + i * VN, o);
+        }
+#pragma unroll
+        for (int j = 0; j < VN; ++j) {
+          pg[p][j] += dv[p][j] * (xv[p][j] - mu) * rs;
+          pb[p][j] += dv[p][j];
+        }
+      }
+    }
+  }
+  if (part) {
+    float *sg = reinterpret_cast<float *>(ln_smem);
+    float *sb = sg + N;
+    for (int w = 0; w < kThreads / 32; ++w) {  // fixed warp order => deterministic
+      if (warp == w) {
+#pragma unroll
+        for (int p = 0; p < PW; ++p) {
+          int i = lane + p * 32;
+          if (i < nvec) {
+#pragma unroll
+            for (int j = 0; j < VN; ++j) {
+              int c = i * VN + j;
+              sg[c] = (w == 0 ? 0.f : sg[c]) + pg[p][j];
+              sb[c] = (w == 0 ? 0.f : sb[c]) + pb[p][j];
+            }
+          }
+        }
+      }
+      __syncthreads();
+    }
+    float *pgr = part + (size_t(blockIdx.x) * 2 + 0) * N;
+    float *pbr = part + (size_t(blockIdx.x) * 2 + 1) * N;
+    for (long long c = threadIdx.x; c < N; c += blockDim.x) {
+      pgr[c] = sg[c];
+      pbr[c] = sb[c];
+    }
+  }
+}
+
 // ================================================================== batch norm (NCHW, fp32)
 // One CTA per channel. The channel's data (n * h*w floats, strided by c*h*w between
 // samples) is walked three times; after the first walk it is L2 resident.
@@ -592,7 +860,16 @@ int ffk_softmax_forward(void *stream, void const *input, void *output, long long
     constexpr int VN = Vec16<T>::N;
     bool vec = inner == 1 && dim % VN == 0 && aligned16(input) && aligned16(output) &&
                pick_p(dim / VN) != 0 && dim / VN >= 64;
-    if (vec) {
+    bool warp_rows = inner == 1 && dim % VN == 0 && aligned16(input) && aligned16(output) &&
+                     pick_pw(dim / VN) != 0;
+    if (warp_rows) {
+      int nvec = int(dim / VN), p = pick_pw(nvec);
+      unsigned grid = rows_grid((outer + 7) / 8, 8);
+      FFK_DISPATCH_P(p, P, {
+        softmax_warp_rows_kernel<T, P><<<grid, kThreads, 0, s>>>(
+            reinterpret_cast<T const *>(input), reinterpret_cast<T *>(output), outer, nvec);
+      });
+    } else if (vec) {
       int nvec = int(dim / VN), p = pick_p(nvec);
       FFK_DISPATCH_P(p, P, {
         softmax_rows_kernel<T, P><<<rows_grid(outer, 8), kThreads, 0, s>>>(
@@ -623,10 +900,23 @@ int ffk_softmax_backward(void *stream, void *input_grad, void const *output_grad
   if (mode == 0) return ffk_copy(stream, input_grad, output_grad, n, dtype);
   FFK_REQUIRE(output, "softmax backward: Jacobian mode needs `output`");
   FFK_DISPATCH_FLOAT(dtype, T, {
-    unsigned grid = stream_grid(size_t(outer * inner) * 32, kThreads, 8);
-    softmax_jacobian_kernel<T><<<grid, kThreads, 0, as_stream(stream)>>>(
-        reinterpret_cast<T *>(input_grad), reinterpret_cast<T const *>(output_grad),
-        reinterpret_cast<T const *>(output), outer, dim, inner);
+    constexpr int VN = Vec16<T>::N;
+    bool warp_rows = inner == 1 && dim % VN == 0 && aligned16(input_grad) && aligned16(output_grad) &&
+                     aligned16(output) && pick_pw(dim / VN) != 0;
+    if (warp_rows) {
+      int nvec = int(dim / VN), p = pick_pw(nvec);
+      unsigned grid = rows_grid((outer + 7) / 8, 8);
+      FFK_DISPATCH_P(p, P, {
+        softmax_jacobian_warp_rows_kernel<T, P><<<grid, kThreads, 0, as_stream(stream)>>>(
+            reinterpret_cast<T *>(input_grad), reinterpret_cast<T const *>(output_grad),
+            reinterpret_cast<T const *>(output), outer, nvec);
+      });
+    } else {
+      unsigned grid = stream_grid(size_t(outer * inner) * 32, kThreads, 8);
+      softmax_jacobian_kernel<T><<<grid, kThreads, 0, as_stream(stream)>>>(
+          reinterpret_cast<T *>(input_grad), reinterpret_cast<T const *>(output_grad),
+          reinterpret_cast<T const *>(output), outer, dim, inner);
+    }
   });
   FFK_LAUNCH_CHECK();
   return FFK_OK;
@@ -643,7 +933,16 @@ int ffk_layer_norm_forward(void *stream, void const *input, void *output, void c
     constexpr int VN = Vec16<T>::N;
     bool vec = N % VN == 0 && aligned16(input) && aligned16(output) &&
                (!gamma || aligned16(gamma)) && (!beta || aligned16(beta)) && pick_p(N / VN) != 0;
-    if (vec) {
+    if (vec && pick_pw(N / VN) != 0 && pick_pw(N / VN) <= 4) {
+      int nvec = int(N / VN), p = pick_pw(nvec);
+      unsigned grid = rows_grid((M + 7) / 8, 8);
+      FFK_DISPATCH_P(p, P, {
+        layer_norm_fwd_warp_rows_kernel<T, P><<<grid, kThreads, 0, s>>>(
+            reinterpret_cast<T const *>(input), reinterpret_cast<T *>(output),
+            reinterpret_cast<T const *>(gamma), reinterpret_cast<T const *>(beta), mean, rstd, M,
+            nvec, eps);
+      });
+    } else if (vec) {
       int nvec = int(N / VN), p = pick_p(nvec);
       FFK_DISPATCH_P(p, P, {
         layer_norm_fwd_rows_kernel<T, P><<<rows_grid(M, 6), kThreads, 0, s>>>(
@@ -664,7 +963,7 @@ int ffk_layer_norm_forward(void *stream, void const *input, void *output, void c
 
 size_t ffk_layer_norm_backward_workspace_bytes(long long N) {
   if (N <= 0) return 0;
-  return size_t(device_info().sm_count) * 4 /*CTAs per SM*/ * 2 /*dgamma,dbeta*/ * size_t(N) *
+  return size_t(device_info().sm_count) * 12 /*CTAs per SM*/ * 2 /*dgamma,dbeta*/ * size_t(N) *
          sizeof(float);
 }
 
@@ -686,20 +985,54 @@ int ffk_layer_norm_backward(void *stream, void const *output_grad, void const *i
     size_t per_part = size_t(2) * size_t(N) * sizeof(float);
     size_t parts_fit = (workspace && want_params) ? workspace_bytes / per_part : 0;
     bool fused = vec && want_params && parts_fit >= 1;
-    if (vec && (input_grad || fused)) {
-      int nvec = int(N / VN), p = pick_p(nvec);
+    bool short_rows = vec && pick_pw(N / VN) != 0 && pick_pw(N / VN) <= 2;
+    if (short_rows && (input_grad || fused)) {
+      int nvec = int(N / VN), p = pick_pw(nvec);
+      size_t smem = size_t(2) * size_t(N) * sizeof(float);
+      unsigned grid = rows_grid((M + 7) / 8, 3);
+      if (fused) grid = (unsigned)std::min<size_t>(grid, parts_fit);
+      float *wpart = fused ? reinterpret_cast<float *>(workspace) : nullptr;
+      if (p == 1) {
+        layer_norm_bwd_warp_rows_kernel<T, 1><<<grid, kThreads, smem, s>>>(
+            reinterpret_cast<T const *>(output_grad), reinterpret_cast<T const *>(input),
+            reinterpret_cast<T *>(input_grad), reinterpret_cast<T const *>(gamma), mean, rstd, wpart, M, nvec);
+      } else {
+        layer_norm_bwd_warp_rows_kernel<T, 2><<<grid, kThreads, smem, s>>>(
+            reinterpret_cast<T const *>(output_grad), reinterpret_cast<T const *>(input),
+            reinterpret_cast<T *>(input_grad), reinterpret_cast<T const *>(gamma), mean, rstd, wpart, M, nvec);
+      }
+      FFK_LAUNCH_CHECK();
+      if (fused) {
+        layer_norm_param_reduce_kernel<T><<<unsigned((N + 31) / 32), 1024, 0, s>>>(
+            reinterpret_cast<float const *>(workspace), int(grid), N,
+            reinterpret_cast<T *>(gamma_grad), reinterpret_cast<T *>(beta_grad),
+            accumulate_param_grads != 0);
+        FFK_LAUNCH_CHECK();
+      }
+    } else if (vec && (input_grad || fused)) {
+      int nvec = int(N / VN);
+      bool narrow = nvec <= 128;  // rows of <= 128 packets: 128-thread CTAs keep every lane busy
+      int p = narrow ? 1 : pick_p(nvec);
       size_t smem = size_t(3) * size_t(N) * sizeof(float);
-      int per_sm = (int)std::max<size_t>(1, std::min<size_t>(4, (200 * 1024) / (smem + 1024)));
+      int per_sm = (int)std::max<size_t>(1, std::min<size_t>(narrow ? 12 : 4, (200 * 1024) / (smem + 1024)));
       unsigned grid = rows_grid(M, per_sm);
       if (fused) grid = (unsigned)std::min<size_t>(grid, parts_fit);
-      FFK_DISPATCH_P(p, P, {
-        FFK_CUDA(cudaFuncSetAttribute(layer_norm_bwd_rows_kernel<T, P>,
+      float *part = fused ? reinterpret_cast<float *>(workspace) : nullptr;
+      if (narrow) {
+        FFK_CUDA(cudaFuncSetAttribute(layer_norm_bwd_rows_kernel<T, 1, 128>,
                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        layer_norm_bwd_rows_kernel<T, P><<<grid, kThreads, smem, s>>>(
+        layer_norm_bwd_rows_kernel<T, 1, 128><<<grid, 128, smem, s>>>(
             reinterpret_cast<T const *>(output_grad), reinterpret_cast<T const *>(input),
-            reinterpret_cast<T *>(input_grad), reinterpret_cast<T const *>(gamma), mean, rstd,
-            fused ? reinterpret_cast<float *>(workspace) : nullptr, M, nvec);
-      });
+            reinterpret_cast<T *>(input_grad), reinterpret_cast<T const *>(gamma), mean, rstd, part, M, nvec);
+      } else {
+        FFK_DISPATCH_P(p, P, {
+          FFK_CUDA(cudaFuncSetAttribute(layer_norm_bwd_rows_kernel<T, P, kThreads>,
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+          layer_norm_bwd_rows_kernel<T, P, kThreads><<<grid, kThreads, smem, s>>>(
+              reinterpret_cast<T const *>(output_grad), reinterpret_cast<T const *>(input),
+              reinterpret_cast<T *>(input_grad), reinterpret_cast<T const *>(gamma), mean, rstd, part, M, nvec);
+        });
+      }
       FFK_LAUNCH_CHECK();
       if (fused) {
         layer_norm_param_reduce_kernel<T><<<unsigned((N + 31) / 32), 1024, 0, s>>>(
