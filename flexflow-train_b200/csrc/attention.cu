@@ -81,6 +81,7 @@ int mm(Ctx const &c, void const *a, long long lda, bool a_mn, void const *b, lon
   switch (c.path) {
     case FFK_GEMM_TENSOR: return gemm::launch_tc(p, e, c.s);
     case FFK_GEMM_SIMT: return gemm::launch_simt(p, e, c.s);
+    case FFK_GEMM_SPLIT_BF16: return gemm::launch_split_bf16_registered(p, e, c.s);
     default: return gemm::launch(p, e, c.s);
   }
 }

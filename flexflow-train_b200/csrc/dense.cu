@@ -9,6 +9,7 @@ int run_gemm(gemm::Problem const &p, gemm::Epilogue const &e, cudaStream_t s, in
     case FFK_GEMM_AUTO: return gemm::launch(p, e, s);
     case FFK_GEMM_TENSOR: return gemm::launch_tc(p, e, s);
     case FFK_GEMM_SIMT: return gemm::launch_simt(p, e, s);
+    case FFK_GEMM_SPLIT_BF16: return gemm::launch_split_bf16_registered(p, e, s);
     default: set_error("gemm: unknown path %d", path); return FFK_ERR_INVALID;
   }
 }
@@ -138,6 +139,12 @@ constexpr int kBiasGradSplits = 32;
 using namespace ffk;
 
 extern "C" {
+
+int ffk_set_gemm_workspace(void *workspace, size_t workspace_bytes) {
+  FFK_REQUIRE(workspace == nullptr || aligned16(workspace), "gemm workspace must be 16-byte aligned");
+  gemm::set_workspace(workspace, workspace ? workspace_bytes : 0);
+  return FFK_OK;
+}
 
 int ffk_gemm(void *stream, void const *a, void const *b, void *d, int M, int N, int K, int batch,
              long long lda, long long ldb, long long ldd, long long a_batch_stride,

@@ -56,6 +56,20 @@ __device__ __forceinline__ void epilogue_row_chunk(uint32_t const (&acc)[32], Ep
   T *drow = reinterpret_cast<T *>(ep.d) + row_off + col0;
   constexpr int VN = 16 / sizeof(T);
   bool const full = vec_ok && ncols_valid == 32;
+  if (ep.add_d_before_act) {
+    if (full) {
+#pragma unroll
+      for (int j = 0; j < 32 / VN; ++j) {
+        Vec16<T> t = ld_vec(drow + j * VN);
+#pragma unroll
+        for (int i = 0; i < VN; ++i) v[j * VN + i] += to_f32(t.v[i]);
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < 32; ++i)
+        if (i < ncols_valid) v[i] += to_f32(drow[i]);
+    }
+  }
   if (ep.bias != nullptr) {
     T const *bp = reinterpret_cast<T const *>(ep.bias) + col0;
     if (full && ep.bias_vec_ok) {
@@ -780,10 +794,126 @@ int launch_simt(Problem const &p, Epilogue const &e, cudaStream_t stream) {
   return FFK_ERR_DTYPE;
 }
 
+// ------------------------------------------------------------------ split-bf16 fp32 path
+namespace {
+
+__global__ void __launch_bounds__(256)
+    split_bf16_kernel(float const *__restrict__ x, __nv_bfloat16 *__restrict__ hi,
+                      __nv_bfloat16 *__restrict__ lo, size_t n) {
+  size_t const nvec = n / 4, stride = size_t(gridDim.x) * blockDim.x;
+  size_t const tid = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  for (size_t i = tid; i < nvec; i += stride) {
+    Vec16<float> v = ld_stream(x + i * 4);
+    __nv_bfloat16 h[4], l[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      h[j] = __float2bfloat16_rn(v.v[j]);
+      l[j] = __float2bfloat16_rn(v.v[j] - __bfloat162float(h[j]));
+    }
+    *reinterpret_cast<uint2 *>(hi + i * 4) = *reinterpret_cast<uint2 *>(h);
+    *reinterpret_cast<uint2 *>(lo + i * 4) = *reinterpret_cast<uint2 *>(l);
+  }
+  for (size_t i = nvec * 4 + tid; i < n; i += stride) {
+    __nv_bfloat16 h = __float2bfloat16_rn(x[i]);
+    hi[i] = h;
+    lo[i] = __float2bfloat16_rn(x[i] - __bfloat162float(h));
+  }
+}
+
+struct Scratch {
+  void *ptr = nullptr;
+  size_t bytes = 0;
+};
+Scratch g_scratch;  // one process per GPU; registered by the owner of the device handle
+
+// Element count of a stored operand (rows x ld for every batch).
+size_t operand_elems(long long rows, long long ld, long long batch_stride, long long batch2_stride,
+                     int batch, int batch2) {
+  size_t one = size_t(rows) * size_t(ld);
+  int b2 = batch2 > 1 ? batch2 : 1, bo = batch / b2;
+  size_t span = one;
+  if (b2 > 1) span = std::max(span, size_t(b2 - 1) * size_t(batch2_stride) + one);
+  if (bo > 1) span = std::max(span, size_t(bo - 1) * size_t(batch_stride) + (b2 > 1 ? size_t(b2 - 1) * size_t(batch2_stride) : 0) + one);
+  return span;
+}
+
+}  // namespace
+
+void set_workspace(void *ptr, size_t bytes) {
+  g_scratch.ptr = ptr;
+  g_scratch.bytes = bytes;
+}
+
+size_t split_workspace_bytes(Problem const &p) {
+  size_t ea = operand_elems(p.a_mn_major ? p.K : p.M, p.lda, p.a_batch, p.a_batch2, p.batch, p.batch2);
+  size_t eb = operand_elems(p.b_mn_major ? p.K : p.N, p.ldb, p.b_batch, p.b_batch2, p.batch, p.batch2);
+  auto pad = [](size_t n) { return (n + 127) / 128 * 128; };
+  return (pad(ea) + pad(eb)) * 2 * sizeof(__nv_bfloat16);
+}
+
+int launch_split_bf16(Problem const &p, Epilogue const &e, cudaStream_t stream, void *workspace,
+                      size_t workspace_bytes) {
+  if (p.M <= 0 || p.N <= 0 || p.batch <= 0) return FFK_OK;
+  FFK_REQUIRE(p.in_dtype == FFK_FLOAT && p.out_dtype == FFK_FLOAT, "split-bf16 gemm: fp32 operands only");
+  FFK_REQUIRE(!(e.accumulate && (e.act != ACT_NONE || e.bias)), "split-bf16 gemm: accumulate with bias/activation");
+  size_t need = split_workspace_bytes(p);
+  if (!workspace || workspace_bytes < need || !aligned16(workspace)) {
+    set_error("split-bf16 gemm: needs %zu bytes of 16-byte aligned scratch, got %zu", need, workspace_bytes);
+    return FFK_ERR_UNSUPPORTED;
+  }
+  size_t ea = operand_elems(p.a_mn_major ? p.K : p.M, p.lda, p.a_batch, p.a_batch2, p.batch, p.batch2);
+  size_t eb = operand_elems(p.b_mn_major ? p.K : p.N, p.ldb, p.b_batch, p.b_batch2, p.batch, p.batch2);
+  auto pad = [](size_t n) { return (n + 127) / 128 * 128; };
+  __nv_bfloat16 *a_hi = static_cast<__nv_bfloat16 *>(workspace), *a_lo = a_hi + pad(ea);
+  __nv_bfloat16 *b_hi = a_lo + pad(ea), *b_lo = b_hi + pad(eb);
+  unsigned ga = stream_grid(ea / 4 + 1, 256, 8), gb = stream_grid(eb / 4 + 1, 256, 8);
+  split_bf16_kernel<<<ga, 256, 0, stream>>>(static_cast<float const *>(p.a), a_hi, a_lo, ea);
+  split_bf16_kernel<<<gb, 256, 0, stream>>>(static_cast<float const *>(p.b), b_hi, b_lo, eb);
+  FFK_LAUNCH_CHECK();
+  Problem q = p;
+  q.in_dtype = FFK_BFLOAT16;
+  if (!tc_eligible(q, e)) {
+    set_error("split-bf16 gemm: operands do not satisfy TMA alignment");
+    return FFK_ERR_UNSUPPORTED;
+  }
+  // pass 1: D (=|+=) A_hi B_hi ; pass 2: D += A_hi B_lo ; pass 3: D = epilogue(D + A_lo B_hi)
+  Epilogue plain = e;
+  plain.bias = nullptr;
+  plain.act = ACT_NONE;
+  plain.lambda = 0.f;
+  plain.r = nullptr;
+  int rc;
+  q.a = a_hi; q.b = b_hi;
+  if ((rc = launch_tc(q, plain, stream))) return rc;
+  plain.accumulate = 1;
+  q.b = b_lo;
+  if ((rc = launch_tc(q, plain, stream))) return rc;
+  Epilogue last = e;
+  last.accumulate = 0;
+  last.add_d_before_act = 1;
+  q.a = a_lo; q.b = b_hi;
+  return launch_tc(q, last, stream);
+}
+
+int launch_split_bf16_registered(Problem const &p, Epilogue const &e, cudaStream_t stream) {
+  return launch_split_bf16(p, e, stream, g_scratch.ptr, g_scratch.bytes);
+}
+
 int launch(Problem const &p, Epilogue const &e, cudaStream_t stream) {
   if (p.M <= 0 || p.N <= 0 || p.batch <= 0) return FFK_OK;
   bool sixteen = p.in_dtype == FFK_BFLOAT16 || p.in_dtype == FFK_HALF;
   if (sixteen && p.K > 0 && tc_eligible(p, e)) return launch_tc(p, e, stream);
+  // large fp32 products: tensor cores through the bf16 split when scratch has been registered
+  if (p.in_dtype == FFK_FLOAT && p.out_dtype == FFK_FLOAT && p.K >= 64 && g_scratch.ptr &&
+      double(p.M) * p.N * p.K * p.batch >= double(1 << 27) && e.alpha == 1.f &&
+      !(e.accumulate && (e.act != ACT_NONE || e.bias))) {
+    Problem q = p;
+    q.in_dtype = FFK_BFLOAT16;
+    size_t os = sizeof(float);
+    bool d_ok = aligned16(e.d) && (e.ldd * os) % 16 == 0;
+    if (tc_eligible(q, e) && d_ok && split_workspace_bytes(p) <= g_scratch.bytes)
+      return launch_split_bf16(p, e, stream, g_scratch.ptr, g_scratch.bytes);
+  }
   return launch_simt(p, e, stream);
 }
 

@@ -32,6 +32,7 @@ struct Epilogue {
   void const *r;         // R, same layout/dtype as D (may be null)
   int bias_vec_ok = 0;   // set by the launcher: bias readable as 16-byte packets
   long long d_batch2 = 0;  // elements between inner batches of D (see Problem::batch2)
+  int add_d_before_act = 0;  // 1: v = alpha*acc + D, THEN bias / activation (split-precision passes)
 };
 
 // Problem in "logical" terms. a/b pointers are the stored matrices:
@@ -62,7 +63,21 @@ bool tc_eligible(Problem const &p, Epilogue const &e);
 // is the fp32-exact path used for FLOAT tensors and the ragged fallback.
 int launch_simt(Problem const &p, Epilogue const &e, cudaStream_t stream);
 
-// Picks the tensor path for 16-bit inputs when eligible, else SIMT.
+// fp32 operands on the tensor cores at fp32-class accuracy: each operand is split into two
+// bf16 terms (x = hi + lo, |x - hi - lo| <= 2^-18 |x|) and the product is formed as
+// A_hi B_hi + A_hi B_lo + A_lo B_hi with fp32 accumulation in TMEM (relative error ~1e-5;
+// the dropped A_lo B_lo term is 2^-18). Needs split_workspace_bytes(p) of scratch.
+size_t split_workspace_bytes(Problem const &p);
+int launch_split_bf16(Problem const &p, Epilogue const &e, cudaStream_t stream, void *workspace,
+                      size_t workspace_bytes);
+
+// Scratch registered by the caller for GEMM-based entry points (the analogue of
+// cublasSetWorkspace); used by AUTO to run large fp32 products through launch_split_bf16.
+void set_workspace(void *ptr, size_t bytes);
+int launch_split_bf16_registered(Problem const &p, Epilogue const &e, cudaStream_t stream);
+
+// Picks the tensor path for 16-bit inputs when eligible; large fp32 products take the
+// split-bf16 tensor path when scratch is registered; everything else runs SIMT.
 int launch(Problem const &p, Epilogue const &e, cudaStream_t stream);
 
 __device__ __forceinline__ float tanh_fast(float x) {

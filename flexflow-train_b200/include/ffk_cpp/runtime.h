@@ -107,21 +107,34 @@ private:
 };
 
 // managed_per_device_ff_handle.h:8-27 (1 MiB workspace, tensor-op conversion allowed).
+// `gemm_scratch_bytes` > 0 additionally reserves scratch BEHIND the op workspace and registers
+// it with ffk_set_gemm_workspace, which lets fp32 Linear / BatchMatmul / MultiHeadAttention /
+// Conv2D run on the tensor cores (bf16 split, fp32-class accuracy). It is kept apart from
+// `workSpace` because an op's own scratch (e.g. Conv2D's im2col panel) can be a GEMM operand.
 struct ManagedPerDeviceFFHandle {
-  explicit ManagedPerDeviceFFHandle(size_t workspace_bytes = 1024 * 1024) : handle(new PerDeviceFFHandle) {
+  explicit ManagedPerDeviceFFHandle(size_t workspace_bytes = 1024 * 1024, size_t gemm_scratch_bytes = 0)
+      : handle(new PerDeviceFFHandle) {
     ffk_handle_t h;
-    FFK_CHECK(ffk_handle_create(&h, workspace_bytes, 1));
-    *handle = PerDeviceFFHandle{nullptr, nullptr, h.workSpace, h.workSpaceSize, true, nullptr};
+    size_t ws = (workspace_bytes + 255) / 256 * 256;
+    FFK_CHECK(ffk_handle_create(&h, ws + gemm_scratch_bytes, 1));
+    *handle = PerDeviceFFHandle{nullptr, nullptr, h.workSpace, ws, true, nullptr};
+    if (gemm_scratch_bytes) {
+      FFK_CHECK(ffk_set_gemm_workspace(static_cast<char *>(h.workSpace) + ws, gemm_scratch_bytes));
+      owns_gemm_scratch = true;
+    }
   }
   ManagedPerDeviceFFHandle(ManagedPerDeviceFFHandle const &) = delete;
   ManagedPerDeviceFFHandle &operator=(ManagedPerDeviceFFHandle const &) = delete;
-  ManagedPerDeviceFFHandle(ManagedPerDeviceFFHandle &&o) noexcept : handle(std::exchange(o.handle, nullptr)) {}
+  ManagedPerDeviceFFHandle(ManagedPerDeviceFFHandle &&o) noexcept
+      : handle(std::exchange(o.handle, nullptr)), owns_gemm_scratch(std::exchange(o.owns_gemm_scratch, false)) {}
   ManagedPerDeviceFFHandle &operator=(ManagedPerDeviceFFHandle &&o) noexcept {
     std::swap(handle, o.handle);
+    std::swap(owns_gemm_scratch, o.owns_gemm_scratch);
     return *this;
   }
   ~ManagedPerDeviceFFHandle() {
     if (handle) {
+      if (owns_gemm_scratch) ffk_set_gemm_workspace(nullptr, 0);
       ffk_handle_t h{nullptr, nullptr, handle->workSpace, handle->workSpaceSize, 1, nullptr};
       ffk_handle_destroy(&h);
       delete handle;
@@ -131,6 +144,7 @@ struct ManagedPerDeviceFFHandle {
 
 private:
   PerDeviceFFHandle *handle;
+  bool owns_gemm_scratch = false;
 };
 
 // The stream every profiled call runs on. The reference's get_legion_stream creates a new

@@ -28,7 +28,7 @@ _DT = {
 }
 
 ACT_NONE, ACT_RELU, ACT_SIGMOID, ACT_TANH, ACT_GELU = -1, 0, 1, 2, 3
-GEMM_AUTO, GEMM_TENSOR, GEMM_SIMT = 0, 1, 2
+GEMM_AUTO, GEMM_TENSOR, GEMM_SIMT, GEMM_SPLIT_BF16 = 0, 1, 2, 3
 
 
 class OperatorType:
@@ -69,6 +69,25 @@ def _call(name, *args):
 
 
 # ------------------------------------------------------------------ dense
+_gemm_ws = None
+
+
+def set_gemm_workspace(nbytes_or_tensor):
+    """Registers scratch for the GEMM-based entry points (ffk_set_gemm_workspace): lets fp32
+    products run on the tensor cores through the bf16 split. Pass None to unregister."""
+    global _gemm_ws
+    if nbytes_or_tensor is None:
+        _gemm_ws = None
+        _call("ffk_set_gemm_workspace", None, 0)
+        return None
+    t = nbytes_or_tensor
+    if not isinstance(t, torch.Tensor):
+        t = torch.empty(int(t), dtype=torch.uint8, device="cuda")
+    _gemm_ws = t  # keep it alive
+    _call("ffk_set_gemm_workspace", t.data_ptr(), t.numel() * t.element_size())
+    return t
+
+
 class Gemm:
     @staticmethod
     def run(a, b, d, M, N, K, batch=1, a_mn=False, b_mn=False, alpha=1.0, accumulate=False,

@@ -10,7 +10,17 @@ extern "C" {
 /* Which contraction engine a call uses. AUTO = tcgen05/TMEM/TMA tiles for 16-bit inputs
  * whose pitches are 16-byte aligned, CUDA-core fp32 (exact fp32 products, fp32
  * accumulation) otherwise. TENSOR on FLOAT inputs runs them as TF32 (10-bit mantissa). */
-typedef enum { FFK_GEMM_AUTO = 0, FFK_GEMM_TENSOR = 1, FFK_GEMM_SIMT = 2 } ffk_gemm_path_t;
+typedef enum { FFK_GEMM_AUTO = 0, FFK_GEMM_TENSOR = 1, FFK_GEMM_SIMT = 2, FFK_GEMM_SPLIT_BF16 = 3 } ffk_gemm_path_t;
+
+/* Registers device scratch for the GEMM-based entry points of this process (Linear,
+ * BatchMatmul, MultiHeadAttention, Conv2D, ffk_gemm) — the role cublasSetWorkspace /
+ * PerDeviceFFHandle::workSpace (include/kernels/ff_handle.h:17-18) play for the reference's
+ * cuBLAS calls. With scratch registered, AUTO runs large fp32 products on the tensor cores
+ * by splitting each fp32 operand into two bf16 terms and summing three tcgen05 products in
+ * fp32 (relative error ~1e-5, inside the fp32 tolerance of 1e-4) instead of the CUDA-core
+ * kernel; FFK_GEMM_SPLIT_BF16 forces that path. Needs 2 bytes x 2 x (elements of A + B) per
+ * call. Calls that share the scratch must be ordered on one stream. NULL unregisters. */
+int ffk_set_gemm_workspace(void *workspace, size_t workspace_bytes);
 
 /* General strided-batched product, the building block under Linear / BatchMatmul / MHA:
  *   D[b][m][n] = alpha * sum_k A(b,m,k) * B(b,n,k)  (+ bias[n]) (act)  (+ D if accumulate)

@@ -132,3 +132,34 @@ def test_batch_matmul_seq_length_truncation(K, oracle):
         K.BatchMatmul.forward_kernel(None, o, a, b, m, n, k, batch, ad, bd, sl)
         oracle.batch_matmul_forward(oref, an, bn, m, n, k, batch, ad, bd, sl)
         assert_close(o, oref, what=f"bmm truncation {ad},{bd},{sl}")
+
+
+def test_fp32_on_tensor_cores_through_the_bf16_split(K, oracle):
+    """fp32 operands, tcgen05 arithmetic: x = hi + lo in bf16, three products, fp32 accumulation.
+    Must meet the fp32 tolerance (rtol 1e-4) against the fp64-accumulating oracle."""
+    K.set_gemm_workspace(64 << 20)
+    try:
+        _linear_case(K, oracle, torch.float32, 512, 1024, 768, "relu", True, l2=1e-4, path=K.GEMM_SPLIT_BF16)
+        _linear_case(K, oracle, torch.float32, 384, 520, 264, "none", True, path=K.GEMM_SPLIT_BF16)
+        # AUTO picks the split path for large fp32 products once scratch is registered
+        _linear_case(K, oracle, torch.float32, 1024, 1024, 512, "gelu", True, path=K.GEMM_AUTO)
+        m, n, k, batch = 256, 192, 128, 6
+        a, an = to_dev(uniform((batch, n, k), SEED_ACT))
+        b, bn = to_dev(uniform((batch, k, m), SEED_W) / np.sqrt(k))
+        o = torch.zeros(batch, n, m, device="cuda")
+        K.BatchMatmul.forward_kernel(None, o, a, b, m, n, k, batch, path=K.GEMM_SPLIT_BF16)
+        oref = np.zeros((batch, n, m), np.float32)
+        oracle.batch_matmul_forward(oref, an, bn, m, n, k, batch, -1, -1, -1)
+        assert_close(o, oref, what="bmm split-bf16")
+    finally:
+        K.set_gemm_workspace(None)
+
+
+def test_split_path_without_scratch_is_refused(K, ffk):
+    K.set_gemm_workspace(None)
+    x = torch.zeros(256, 256, device="cuda")
+    y = torch.zeros(256, 256, device="cuda")
+    m = K.Linear.init_kernel(path=K.GEMM_SPLIT_BF16)
+    with pytest.raises(ffk.FFKError) as e:
+        K.Linear.forward_kernel(None, m, x, y, x, None, 256, 256, 256)
+    assert e.value.code == -3

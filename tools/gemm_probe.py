@@ -76,6 +76,24 @@ def bench(M, N, K, a_mn, b_mn, dt=torch.bfloat16, iters=20):
     print(f"   cuBLAS same shape: {ms*1e3:.1f} us  {2*M*N*K/ms/1e9:.1f} TFLOP/s", flush=True)
 
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "fp32":
+        ws = torch.empty(512 << 20, dtype=torch.uint8, device="cuda")
+        L.call("ffk_set_gemm_workspace", ws.data_ptr(), ws.numel())
+        M = N = Kd = 4096
+        A = torch.rand(1, M, Kd, device="cuda") - 0.5
+        B = torch.rand(1, N, Kd, device="cuda") - 0.5
+        d = torch.zeros(1, M, N, device="cuda")
+        e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+        for path, name in ((3, "split-bf16 tensor"), (2, "CUDA-core fp32"), (1, "tf32 tensor")):
+            for _ in range(2): gemm(A, B, M, N, Kd, 1, False, False, torch.float32, path, d=d)
+            torch.cuda.synchronize(); e0.record()
+            for _ in range(5): gemm(A, B, M, N, Kd, 1, False, False, torch.float32, path, d=d)
+            e1.record(); torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / 5
+            ref = torch.matmul(A[0].double(), B[0].double().t())
+            err = ((d[0].double() - ref).abs().max() / ref.abs().max()).item()
+            print(f"fp32 4096^3 {name:18s}: {ms*1e3:8.1f} us  {2*M*N*Kd/ms/1e9:7.1f} TFLOP/s  max err/scale {err:.2e}", flush=True)
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "bench":
         bench(8192, 4096, 4096, False, False, iters=5)
         sys.exit(0)
