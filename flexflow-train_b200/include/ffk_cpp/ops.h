@@ -744,4 +744,41 @@ inline void adam_ps_update_task_gpu(ffStream_t stream, float alpha_t, float beta
                             num_replicas, adam_m_ptr, adam_v_ptr, weight_ptr, FFK_FLOAT, nullptr));
 }
 
+// the *_nccl variants: all-reduce (SUM, no division) on handle.ncclComm, then the same update
+inline void sgd_nccl_update_task_gpu(ffStream_t stream, float lr, float momentum, bool nesterov,
+                                     float weight_decay, PerDeviceFFHandle const &handle,
+                                     float const *weight_grad_ptr, size_t size, float *weight_ptr,
+                                     float *sgd_v_ptr) {
+  FFK_CHECK(ffk_sgd_nccl_update(stream, handle.ncclComm, lr, momentum, nesterov, weight_decay,
+                                const_cast<float *>(weight_grad_ptr), size, weight_ptr, sgd_v_ptr,
+                                FFK_FLOAT, nullptr));
+}
+inline void adam_nccl_update_task_gpu(ffStream_t stream, float alpha_t, float beta1, float beta2,
+                                      float weight_decay, float epsilon, PerDeviceFFHandle const &handle,
+                                      float const *weight_grad_ptr, size_t size, float *adam_m_ptr,
+                                      float *adam_v_ptr, float *weight_ptr) {
+  FFK_CHECK(ffk_adam_nccl_update(stream, handle.ncclComm, alpha_t, beta1, beta2, weight_decay, epsilon,
+                                 const_cast<float *>(weight_grad_ptr), size, adam_m_ptr, adam_v_ptr,
+                                 weight_ptr, FFK_FLOAT, nullptr));
+}
+
+// ------------------------------------------------------------------ nccl.h
+struct ncclUniqueIdBytes {
+  char internal[FFK_NCCL_UNIQUE_ID_BYTES];
+};
+namespace Kernels {
+namespace NCCL {
+inline ncclUniqueIdBytes generate_unique_id() {
+  ncclUniqueIdBytes id;
+  FFK_CHECK(ffk_nccl_get_unique_id(id.internal));
+  return id;
+}
+inline void *create_comm(ncclUniqueIdBytes const &id, int num_ranks, int my_rank) {
+  void *comm = nullptr;
+  FFK_CHECK(ffk_nccl_comm_create(&comm, id.internal, num_ranks, my_rank));
+  return comm;
+}
+}  // namespace NCCL
+}  // namespace Kernels
+
 }  // namespace FlexFlow

@@ -1,9 +1,47 @@
+/* ffk_parallel.h — NCCL entry points of the kernel API: communicator bootstrap and the
+ * gradient-synchronising optimizer updates. Included by ffk.h.
+ * NCCL is resolved at run time (dlopen of libnccl.so.2): libffk.so itself does not link it, and
+ * a process that already carries NCCL (e.g. through torch) shares that copy. The single-device
+ * forms of Replicate / Reduction / Repartition / Combine are in ffk_elementwise.h; their
+ * multi-GPU forms are composed from these collectives by the host layer
+ * (flexflow-train_b200/parallel_ops.py). */
 #ifndef FFK_PARALLEL_H_
 #define FFK_PARALLEL_H_
 #include "ffk.h"
 #ifdef __cplusplus
 extern "C" {
 #endif
+
+#define FFK_NCCL_UNIQUE_ID_BYTES 128
+
+/* Kernels::NCCL::generate_unique_id — include/kernels/nccl.h:30, src/cuda/nccl.cc:8-15
+ * (ncclGetUniqueId). Writes FFK_NCCL_UNIQUE_ID_BYTES to host memory; rank 0 calls it and ships
+ * the bytes to the other ranks by any means. */
+int ffk_nccl_get_unique_id(void *id_out_host);
+
+/* Kernels::NCCL::create_comm — include/kernels/nccl.h:31, src/cuda/nccl.cc:17-29
+ * (ncclCommInitRank on the current device). The result is what PerDeviceFFHandle::ncclComm holds. */
+int ffk_nccl_comm_create(void **comm_out, void const *id_host, int num_ranks, int my_rank);
+int ffk_nccl_comm_destroy(void *comm);
+
+/* In-place sum over ranks (ncclAllReduce, ncclSum) of `count` elements: the exchange step of
+ * Replicate-backward / Reduction-forward and of the *_nccl_update tasks. FLOAT, HALF, BFLOAT16,
+ * DOUBLE, INT32, INT64. */
+int ffk_all_reduce_sum(void *stream, void *comm, void *buffer, size_t count, int dtype);
+
+/* sgd_nccl_update_task_gpu — include/kernels/optimizer_kernels.h:19 (its missing comma fixed),
+ * src/cuda/optimizer_kernel.cu:73-104: ncclAllReduce(weight_grad, SUM — no division by the
+ * replica count) on `comm`, then the SGD update of ffk_sgd_update. */
+int ffk_sgd_nccl_update(void *stream, void *comm, float lr, float momentum, int nesterov,
+                        float weight_decay, void *weight_grad, size_t size, void *weight,
+                        float *sgd_v, int dtype, float *master_weight);
+
+/* adam_nccl_update_task_gpu — include/kernels/optimizer_kernels.h:41,
+ * src/cuda/optimizer_kernel.cu:181-214. */
+int ffk_adam_nccl_update(void *stream, void *comm, float alpha_t, float beta1, float beta2,
+                         float weight_decay, float epsilon, void *weight_grad, size_t size,
+                         float *adam_m, float *adam_v, void *weight, int dtype,
+                         float *master_weight);
 
 #ifdef __cplusplus
 }

@@ -193,3 +193,22 @@ def test_dropout_value_rule_of_cudnn(G):
     assert ((dx != 0) == kept).all()
     near(dx[kept], dy[kept] / (1 - p))
     assert abs(kept.mean() - (1 - p)) < 0.02
+
+
+# ---------------------------------------------------------------------------------------------
+def _copy_like_cases():
+    return json.loads((GOLD / "copy_like.json").read_text())["cases"]
+
+
+@pytest.mark.parametrize("case", _copy_like_cases(), ids=lambda c: c["name"])
+def test_oracle_against_the_reference_tests_exact_vectors(oracle, case):
+    n = case["n"]
+    src = np.full(n * case.get("reps", 1), case["src_fill"], np.float32)
+    dst = np.full(n, case.get("dst_fill", 0.0), np.float32)
+    if case["op"] == "copy":
+        oracle.copy(dst, src, n * 4)
+    elif case["op"] == "accumulate":
+        oracle.accumulate(dst, src, n)
+    else:
+        oracle.sum_replicas(dst, src, n, case["reps"], case["accumulate"])
+    assert (dst == np.float32(case["expect_fill"])).all()

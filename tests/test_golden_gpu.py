@@ -93,3 +93,21 @@ def test_pool2d(K, G, name, ptype):
     dx = dev(G["pool_dx0"])
     K.Pool2D.backward_kernel(None, m, x, dx, y, dev(G["pool_dy"]))
     near(dx, G[name + "_dx"], atol=1e-5)
+
+
+import json
+
+
+@pytest.mark.parametrize("case", json.loads((GOLD / "copy_like.json").read_text())["cases"], ids=lambda c: c["name"])
+def test_reference_exact_vectors(K, case):
+    """The vectors the reference's own kernel tests assert with == (tests/golden/copy_like.json)."""
+    n = case["n"]
+    src = torch.full((n * case.get("reps", 1),), case["src_fill"], device="cuda")
+    dst = torch.full((n,), case.get("dst_fill", 0.0), device="cuda")
+    if case["op"] == "copy":
+        K.copy(None, dst, src)
+    elif case["op"] == "accumulate":
+        K.accumulate(None, dst, src)
+    else:
+        K._call("ffk_sum_replicas", None, dst.data_ptr(), src.data_ptr(), n, case["reps"], case["accumulate"], K.FLOAT)
+    assert torch.equal(dst, torch.full((n,), case["expect_fill"], device="cuda"))

@@ -70,3 +70,54 @@ def test_parallel_ops_two_gpus_nccl():
     for rank, ok in results.items():
         bad = [k for k, v in ok.items() if not v]
         assert not bad, f"rank {rank}: {bad}"
+
+
+def _nccl_abi_worker(rank, world, id_path, results):
+    """The NCCL entry points of the C ABI themselves (no torch.distributed): rank 0 creates the
+    unique id and publishes it through a file, every rank builds a communicator and runs the
+    nccl-SGD update; the result must equal the single-process update on the summed gradient."""
+    import ctypes
+    import time as _t
+
+    torch.cuda.set_device(rank)
+    sys.path.insert(0, str(ROOT))
+    import ffk_import
+
+    ffk = ffk_import.load()
+    L = ffk.lib()
+    idbuf = (ctypes.c_char * 128)()
+    if rank == 0:
+        L.call("ffk_nccl_get_unique_id", ctypes.cast(idbuf, ctypes.c_void_p))
+        Path(id_path + ".tmp").write_bytes(bytes(idbuf))
+        os.replace(id_path + ".tmp", id_path)
+    else:
+        while not os.path.exists(id_path):
+            _t.sleep(0.05)
+        ctypes.memmove(idbuf, Path(id_path).read_bytes(), 128)
+    comm = ctypes.c_void_p()
+    L.call("ffk_nccl_comm_create", ctypes.byref(comm), ctypes.cast(idbuf, ctypes.c_void_p), world, rank)
+    n = 100_003
+    g = torch.Generator(device="cuda").manual_seed(7)
+    w0 = torch.rand(n, device="cuda", generator=g)
+    base = torch.rand(n, device="cuda", generator=g)
+    grad = base * (rank + 1)
+    w = w0.clone()
+    v = torch.zeros(n, device="cuda")
+    stream = torch.cuda.current_stream().cuda_stream
+    L.call("ffk_sgd_nccl_update", stream, comm, 0.1, 0.9, 0, 1e-4, grad.data_ptr(), n, w.data_ptr(),
+           v.data_ptr(), 4, None)
+    torch.cuda.synchronize()
+    gsum = base * sum(r + 1 for r in range(world))       # SUM over ranks, not the mean
+    gt = gsum + 1e-4 * w0
+    expect = w0 - 0.1 * gt                                  # first step: V = g
+    results[rank] = bool(torch.allclose(w, expect, rtol=1e-5, atol=1e-6) and torch.allclose(grad, gsum, rtol=1e-6))
+    L.call("ffk_nccl_comm_destroy", comm)
+
+
+def test_nccl_c_abi_two_gpus(tmp_path):
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (run with gpurun --gpus 2)")
+    mgr = mp.Manager()
+    results = mgr.dict()
+    mp.spawn(_nccl_abi_worker, args=(2, str(tmp_path / "nccl_id"), results), nprocs=2, join=True)
+    assert dict(results) == {0: True, 1: True}
