@@ -698,48 +698,80 @@ int launch_tc(Problem const &p, Epilogue const &e, cudaStream_t stream) {
 // ------------------------------------------------------------------ SIMT GEMM
 namespace {
 
+// 64 x 64 output tile per CTA, 4 x 4 outputs per thread, fp32 FMA. Short problems (a handful of
+// tiles, long K — the small-batch Linear shapes of BASELINE configs[0]) would leave most SMs idle
+// and serialise the whole K loop in a few CTAs, so K is split across the CTAs of a thread-block
+// cluster (cluster dim z = `splits`, 1..8): every CTA accumulates its K range, parks the partial
+// tile in its own shared memory, and after a cluster barrier CTA r reduces rows [r*64/splits, ...)
+// of all partial tiles through distributed shared memory in rank order (deterministic — no
+// atomics, no global scratch) and runs the epilogue for them.
+template <typename TIn, typename TOut>
+__device__ __forceinline__ void simt_epilogue_store(Epilogue const &ep, TOut *d, TOut const *r,
+                                                    TOut const *bias, int gm, int gn, float acc) {
+  float v = acc * ep.alpha;
+  if (bias) v += to_f32(bias[gn]);
+  v = apply_act(v, ep.act);
+  long long off = gm * ep.ldd + gn;
+  if (r) v += ep.lambda * to_f32(r[off]);
+  if (ep.accumulate) v += to_f32(d[off]);
+  d[off] = from_f32<TOut>(v);
+}
+
 template <typename TIn, typename TOut>
 __global__ void __launch_bounds__(256)
     gemm_simt_kernel(TIn const *__restrict__ a, TIn const *__restrict__ b, Epilogue ep, int M,
                      int N, int K, long long sa_m, long long sa_k, long long sb_n, long long sb_k,
                      long long a_batch, long long b_batch, int batch2, long long a_batch2,
-                     long long b_batch2) {
+                     long long b_batch2, int splits) {
   constexpr int TM = 64, TN = 64, TK = 16;
-  __shared__ float As[TK][TM + 4];
-  __shared__ float Bs[TK][TN + 4];
-  int const bo = blockIdx.z / batch2, bi = blockIdx.z % batch2;
+  __shared__ __align__(16) float As[TK][TM + 4];
+  __shared__ __align__(16) float Bs[TK][TN + 4];
+  __shared__ __align__(16) float Cs[TM][TN];  // partial tile, read by the cluster peers
+  int const rank = blockIdx.z % splits, bz = blockIdx.z / splits;
+  int const bo = bz / batch2, bi = bz % batch2;
   a += bo * a_batch + bi * a_batch2;
   b += bo * b_batch + bi * b_batch2;
   int const m0 = blockIdx.y * TM, n0 = blockIdx.x * TN;
   int const tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+  int const k_per = ((K + splits - 1) / splits + TK - 1) / TK * TK;
+  int const k_begin = rank * k_per, k_end = min(K, k_begin + k_per);
   float acc[4][4] = {};
   bool const a_kmajor = (sa_k == 1), b_kmajor = (sb_k == 1);
-  for (int k0 = 0; k0 < K; k0 += TK) {
+  float ra[4], rb[4];
+  auto fetch = [&](int k0) {  // global -> registers for the k-block at k0
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       int idx = threadIdx.x + i * 256;
       int mm, kk;
       if (a_kmajor) { mm = idx >> 4; kk = idx & 15; } else { kk = idx >> 6; mm = idx & 63; }
       int gm = m0 + mm, gk = k0 + kk;
-      As[kk][mm] = (gm < M && gk < K) ? to_f32(a[gm * sa_m + gk * sa_k]) : 0.f;
+      ra[i] = (gm < M && gk < k_end) ? to_f32(a[gm * sa_m + gk * sa_k]) : 0.f;
       int nn;
       if (b_kmajor) { nn = idx >> 4; kk = idx & 15; } else { kk = idx >> 6; nn = idx & 63; }
       int gn = n0 + nn;
       gk = k0 + kk;
-      Bs[kk][nn] = (gn < N && gk < K) ? to_f32(b[gn * sb_n + gk * sb_k]) : 0.f;
+      rb[i] = (gn < N && gk < k_end) ? to_f32(b[gn * sb_n + gk * sb_k]) : 0.f;
+    }
+  };
+  if (k_begin < k_end) fetch(k_begin);
+  for (int k0 = k_begin; k0 < k_end; k0 += TK) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      int idx = threadIdx.x + i * 256;
+      if (a_kmajor) As[idx & 15][idx >> 4] = ra[i]; else As[idx >> 6][idx & 63] = ra[i];
+      if (b_kmajor) Bs[idx & 15][idx >> 4] = rb[i]; else Bs[idx >> 6][idx & 63] = rb[i];
     }
     __syncthreads();
+    if (k0 + TK < k_end) fetch(k0 + TK);  // next block's loads fly under this block's FMAs
 #pragma unroll
     for (int kk = 0; kk < TK; ++kk) {
-      float av[4], bv[4];
-#pragma unroll
-      for (int i = 0; i < 4; ++i) av[i] = As[kk][ty * 4 + i];
-#pragma unroll
-      for (int j = 0; j < 4; ++j) bv[j] = Bs[kk][tx * 4 + j];
+      float4 const av = *reinterpret_cast<float4 const *>(&As[kk][ty * 4]);
+      float4 const bv = *reinterpret_cast<float4 const *>(&Bs[kk][tx * 4]);
+      float const avv[4] = {av.x, av.y, av.z, av.w}, bvv[4] = {bv.x, bv.y, bv.z, bv.w};
 #pragma unroll
       for (int i = 0; i < 4; ++i)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(avv[i], bvv[j], acc[i][j]);
     }
     __syncthreads();
   }
@@ -747,34 +779,67 @@ __global__ void __launch_bounds__(256)
   TOut *d = reinterpret_cast<TOut *>(ep.d) + d_off;
   TOut const *r = ep.r ? reinterpret_cast<TOut const *>(ep.r) + d_off : nullptr;
   TOut const *bias = reinterpret_cast<TOut const *>(ep.bias);
+  if (splits == 1) {
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    int gm = m0 + ty * 4 + i;
-    if (gm >= M) continue;
+    for (int i = 0; i < 4; ++i) {
+      int gm = m0 + ty * 4 + i;
+      if (gm >= M) continue;
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      int gn = n0 + tx * 4 + j;
-      if (gn >= N) continue;
-      float v = acc[i][j] * ep.alpha;
-      if (bias) v += to_f32(bias[gn]);
-      v = apply_act(v, ep.act);
-      long long off = gm * ep.ldd + gn;
-      if (r) v += ep.lambda * to_f32(r[off]);
-      if (ep.accumulate) v += to_f32(d[off]);
-      d[off] = from_f32<TOut>(v);
+      for (int j = 0; j < 4; ++j) {
+        int gn = n0 + tx * 4 + j;
+        if (gn < N) simt_epilogue_store<TIn, TOut>(ep, d, r, bias, gm, gn, acc[i][j]);
+      }
     }
+    return;
   }
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+    *reinterpret_cast<float4 *>(&Cs[ty * 4 + i][tx * 4]) =
+        make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+  ptx::cluster_sync();  // every partial tile is parked
+  int const rows_per = TM / splits;
+  uint32_t const cs_base = ptx::smem_u32(&Cs[0][0]);
+  for (int e = threadIdx.x; e < rows_per * TN; e += 256) {
+    int row = rank * rows_per + e / TN, col = e % TN;
+    int gm = m0 + row, gn = n0 + col;
+    if (gm >= M || gn >= N) continue;
+    float sum = 0.f;
+    for (int s2 = 0; s2 < splits; ++s2)
+      sum += ptx::ld_dsmem_f32(ptx::map_to_cta(cs_base + uint32_t(row * TN + col) * 4u, uint32_t(s2)));
+    simt_epilogue_store<TIn, TOut>(ep, d, r, bias, gm, gn, sum);
+  }
+  ptx::cluster_sync();  // nobody leaves while a peer still reads its tile
+}
+
+// K splits for the cluster: fill the machine (two 256-thread CTAs per SM is plenty for a
+// latency-bound problem) while every split keeps at least 64 of K.
+int simt_splits(Problem const &p, long long tiles) {
+  int s = 1;
+  while (s < 8 && tiles * s * 2 <= 2LL * device_info().sm_count && p.K / (s * 2) >= 64) s *= 2;
+  return s;
 }
 
 template <typename TIn, typename TOut>
 int launch_simt_t(Problem const &p, Epilogue const &e, cudaStream_t stream) {
   long long sa_m = p.a_mn_major ? 1 : p.lda, sa_k = p.a_mn_major ? p.lda : 1;
   long long sb_n = p.b_mn_major ? 1 : p.ldb, sb_k = p.b_mn_major ? p.ldb : 1;
-  dim3 grid((p.N + 63) / 64, (p.M + 63) / 64, p.batch);
-  gemm_simt_kernel<TIn, TOut><<<grid, 256, 0, stream>>>(
-      reinterpret_cast<TIn const *>(p.a), reinterpret_cast<TIn const *>(p.b), e, p.M, p.N, p.K,
-      sa_m, sa_k, sb_n, sb_k, p.a_batch, p.b_batch, p.batch2 > 1 ? p.batch2 : 1, p.a_batch2,
-      p.b_batch2);
+  unsigned gx = (p.N + 63) / 64, gy = (p.M + 63) / 64;
+  int splits = simt_splits(p, 1LL * gx * gy * p.batch);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(gx, gy, unsigned(p.batch) * splits);
+  cfg.blockDim = dim3(256);
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 1;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = unsigned(splits);
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  FFK_CUDA(cudaLaunchKernelEx(
+      &cfg, gemm_simt_kernel<TIn, TOut>, reinterpret_cast<TIn const *>(p.a),
+      reinterpret_cast<TIn const *>(p.b), e, p.M, p.N, p.K, sa_m, sa_k, sb_n, sb_k, p.a_batch,
+      p.b_batch, p.batch2 > 1 ? p.batch2 : 1, p.a_batch2, p.b_batch2, splits));
   FFK_LAUNCH_CHECK();
   return FFK_OK;
 }

@@ -187,6 +187,11 @@ __device__ __forceinline__ uint32_t map_to_cta(uint32_t local, uint32_t rank) {
   asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local), "r"(rank));
   return r;
 }
+__device__ __forceinline__ float ld_dsmem_f32(uint32_t cluster_addr) {
+  float v;
+  asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(cluster_addr) : "memory");
+  return v;
+}
 // Arrive on a barrier that may live in the peer CTA. Deliberately NOT `.release.cluster`: that
 // form compiles to MEMBAR.ALL.GPU + ERRBAR in front of the arrive (seen in the round-1 ncu
 // source page, where it throttled the producer); the data these barriers guard travels through
