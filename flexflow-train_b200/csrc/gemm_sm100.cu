@@ -16,14 +16,18 @@ constexpr int SWIZZLE_BYTES = 128; // TMA / UMMA swizzle span
 constexpr int MMA_K_BYTES = 32;    // one tcgen05.mma consumes 32 bytes of K per row
 constexpr int K_STEPS = SWIZZLE_BYTES / MMA_K_BYTES;
 constexpr int GROUP_M = 8;         // tile rasterisation: 8 row-blocks share B columns in L2
-constexpr int NUM_THREADS = 192;   // warp0 TMA, warp1 MMA, warps 2..5 epilogue
+constexpr int NUM_THREADS = 320;   // warp0 TMA, warp1 MMA, warps 2..9 epilogue
+constexpr int EPI_WARPS = 8;       // two warps per TMEM lane quadrant, each drains half of the tile's columns
+constexpr int EPI_STAGE_PER_WARP = 32 * 64;  // 32 rows x 32 sixteen-bit outputs, transposed through smem
+constexpr int EPI_STAGING_BYTES = EPI_WARPS * EPI_STAGE_PER_WARP;
 
 template <int BLOCK_N, int STAGES> struct SmemPlan {
   static constexpr int A_BYTES = BLOCK_M * SWIZZLE_BYTES;
   static constexpr int B_BYTES = BLOCK_N * SWIZZLE_BYTES;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int BAR_OFFSET = STAGES * STAGE_BYTES;
-  static constexpr int TOTAL = BAR_OFFSET + 256 + 1024;  // barriers + alignment slack
+  static constexpr int STAGING_OFFSET = BAR_OFFSET + 256;  // after the barriers
+  static constexpr int TOTAL = STAGING_OFFSET + EPI_STAGING_BYTES + 1024;  // + alignment slack
 };
 
 struct TileCoord {
@@ -137,6 +141,133 @@ __device__ __forceinline__ void epilogue_row_chunk(uint32_t const (&acc)[32], Ep
   }
 }
 
+// 16-bit outputs, full 32-column chunk, 16-byte-aligned rows: the warp turns its 32 x 32 block
+// through 2 KB of shared memory so that global memory sees 64-byte row segments written (and,
+// for beta = 1 / the regulariser, read) by 4 adjacent lanes — 8 rows per instruction — instead
+// of 32 lanes touching 32 different rows with 16 bytes each. Row r keeps its four 16-byte
+// pieces at piece ^ ((r >> 1) & 3): conflict-free for both the row-per-thread and the
+// 8-rows-by-4-pieces access. Warp-collective: every lane calls it, `row_ok` masks dead rows.
+template <typename T>
+__device__ __forceinline__ void epilogue_chunk_staged(uint32_t const (&acc)[32], Epilogue const &ep,
+                                                      uint8_t *stage, long long block_off,
+                                                      int rows_valid, int col0, bool row_ok) {
+  static_assert(sizeof(T) == 2, "staged epilogue is for 16-bit outputs");
+  int const lane = threadIdx.x & 31;
+  float v[32];
+#pragma unroll
+  for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(acc[i]) * ep.alpha;
+  if (ep.bias != nullptr) {
+    T const *bp = reinterpret_cast<T const *>(ep.bias) + col0;
+    if (ep.bias_vec_ok) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        Vec16<T> t = ld_vec(bp + j * 8);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v[j * 8 + i] += to_f32(t.v[i]);
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] += to_f32(bp[i]);
+    }
+  }
+  if (ep.act == ACT_RELU) {
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = fmaxf(v[i], 0.f);
+  } else if (ep.act != ACT_NONE) {
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = apply_act_fast(v[i], ep.act);
+  }
+  // coalesced side: lane -> (row = it*8 + lane/4, piece = lane%4)
+  int const c_row = lane >> 2, c_piece = lane & 3;
+  int const my_sw = (lane >> 1) & 3;  // row-per-thread side: this thread's row is `lane`
+  auto add_from_global = [&](T const *src, float scale) {
+    uint4 t[4];
+#pragma unroll
+    for (int it = 0; it < 4; ++it) {
+      int const r = it * 8 + c_row;
+      t[it] = r < rows_valid
+                  ? *reinterpret_cast<uint4 const *>(src + block_off + r * ep.ldd + col0 + c_piece * 8)
+                  : make_uint4(0, 0, 0, 0);
+    }
+#pragma unroll
+    for (int it = 0; it < 4; ++it) {
+      int const r = it * 8 + c_row;
+      *reinterpret_cast<uint4 *>(stage + r * 64 + ((c_piece ^ ((r >> 1) & 3)) << 4)) = t[it];
+    }
+    __syncwarp();
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      Vec16<T> t2;
+      *reinterpret_cast<uint4 *>(&t2) =
+          *reinterpret_cast<uint4 const *>(stage + lane * 64 + ((j ^ my_sw) << 4));
+#pragma unroll
+      for (int i = 0; i < 8; ++i) v[j * 8 + i] += scale * to_f32(t2.v[i]);
+    }
+    __syncwarp();
+  };
+  if (ep.r != nullptr) add_from_global(reinterpret_cast<T const *>(ep.r), ep.lambda);
+  if (ep.accumulate) add_from_global(reinterpret_cast<T const *>(ep.d), 1.f);
+  (void)row_ok;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    Vec16<T> t;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) t.v[i] = from_f32<T>(v[j * 8 + i]);
+    *reinterpret_cast<uint4 *>(stage + lane * 64 + ((j ^ my_sw) << 4)) = *reinterpret_cast<uint4 *>(&t);
+  }
+  __syncwarp();
+  T *d = reinterpret_cast<T *>(ep.d);
+#pragma unroll
+  for (int it = 0; it < 4; ++it) {
+    int const r = it * 8 + c_row;
+    uint4 t = *reinterpret_cast<uint4 const *>(stage + r * 64 + ((c_piece ^ ((r >> 1) & 3)) << 4));
+    if (r < rows_valid) *reinterpret_cast<uint4 *>(d + block_off + r * ep.ldd + col0 + c_piece * 8) = t;
+  }
+  __syncwarp();
+}
+
+// One warp's share of a tile epilogue: NCHUNK chunks of 32 accumulator columns for the 32 rows
+// (TMEM lanes) of its quadrant. The TMEM load of chunk c+1 is in flight while chunk c is
+// converted and stored; `release` runs once the last load has landed (the accumulator buffer
+// may then be overwritten by the next tile's MMAs).
+template <int NCHUNK, typename Release>
+__device__ __forceinline__ void epilogue_columns(uint32_t taddr, Epilogue const &ep, long long block_off,
+                                                 int rows_valid, int N, int col_first, int out_dtype,
+                                                 int vec_ok, uint8_t *stage, Release release) {
+  int const lane = threadIdx.x & 31;
+  bool const row_ok = lane < rows_valid;
+  long long const row_off = block_off + static_cast<long long>(lane) * ep.ldd;
+  bool const staged_ok = vec_ok && out_dtype != FFK_FLOAT && !ep.add_d_before_act;
+  uint32_t r[2][32];
+  ptx::tmem_ld_32x32(taddr, r[0]);
+#pragma unroll
+  for (int c = 0; c < NCHUNK; ++c) {
+    ptx::tmem_ld_wait_for(r[c & 1]);
+    if (c + 1 < NCHUNK) {
+      ptx::tmem_ld_32x32(taddr + (c + 1) * 32, r[(c + 1) & 1]);
+    } else {
+      release();
+    }
+    int const col0 = col_first + c * 32;
+    int const valid = min(32, N - col0);
+    if (valid <= 0 || rows_valid <= 0) continue;
+    if (staged_ok && valid == 32) {  // warp-uniform
+      if (out_dtype == FFK_BFLOAT16)
+        epilogue_chunk_staged<__nv_bfloat16>(r[c & 1], ep, stage, block_off, rows_valid, col0, row_ok);
+      else
+        epilogue_chunk_staged<__half>(r[c & 1], ep, stage, block_off, rows_valid, col0, row_ok);
+    } else if (row_ok) {
+      switch (out_dtype) {
+        case FFK_FLOAT: epilogue_row_chunk<float>(r[c & 1], ep, row_off, col0, valid, vec_ok); break;
+        case FFK_BFLOAT16:
+          epilogue_row_chunk<__nv_bfloat16>(r[c & 1], ep, row_off, col0, valid, vec_ok);
+          break;
+        default: epilogue_row_chunk<__half>(r[c & 1], ep, row_off, col0, valid, vec_ok); break;
+      }
+    }
+  }
+}
+
 // ESIZE: bytes per input element (2: f16/bf16, 4: fp32 consumed as tf32).
 template <int ESIZE, bool A_MN, bool B_MN, int BLOCK_N, int STAGES>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
@@ -172,7 +303,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
     }
     for (int s = 0; s < 2; ++s) {
       ptx::mbar_init(&tmem_full[s], 1);
-      ptx::mbar_init(&tmem_empty[s], 4);  // one arrive per epilogue warp
+      ptx::mbar_init(&tmem_empty[s], EPI_WARPS);  // one arrive per epilogue warp
     }
     ptx::fence_mbar_init();
   }
@@ -270,40 +401,29 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
     }
   } else if (warp >= 2) {
     // ------------------------------------------------------------ epilogue
-    int const q = warp & 3;  // TMEM lane quadrant this warp may read
+    int const q = warp & 3;             // TMEM lane quadrant this warp may read
+    int const half = (warp - 2) >> 2;   // which half of the tile's columns it drains
+    constexpr int NCHUNK = BLOCK_N / 64;
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       TileCoord tc = decode_tile(tile, num_m, num_n, BLOCK_N);
       ptx::mbar_wait(&tmem_full[acc], acc_phase);
       ptx::tc_fence_after();
-      int const row = tc.m_idx + q * 32 + lane;
-      long long const row_off = static_cast<long long>(tc.b / batch2) * ep.d_batch +
-                                static_cast<long long>(tc.b % batch2) * ep.d_batch2 +
-                                static_cast<long long>(row) * ep.ldd;
-#pragma unroll 1
-      for (int c = 0; c < BLOCK_N / 32; ++c) {
-        uint32_t r[32];
-        ptx::tmem_ld_32x32(tmem_base + (uint32_t(q * 32) << 16) + acc * BLOCK_N + c * 32, r);
-        ptx::tmem_ld_wait();
-        if (c == BLOCK_N / 32 - 1) {
-          // accumulator fully in registers: hand the TMEM buffer back to the MMA warp
-          ptx::tc_fence_before();
-          __syncwarp();
-          if (lane == 0) ptx::mbar_arrive(&tmem_empty[acc]);
-        }
-        int const col0 = tc.n_idx + c * 32;
-        int const valid = min(32, N - col0);
-        if (row < M && valid > 0) {
-          switch (out_dtype) {
-            case FFK_FLOAT: epilogue_row_chunk<float>(r, ep, row_off, col0, valid, vec_ok); break;
-            case FFK_BFLOAT16:
-              epilogue_row_chunk<__nv_bfloat16>(r, ep, row_off, col0, valid, vec_ok);
-              break;
-            default: epilogue_row_chunk<__half>(r, ep, row_off, col0, valid, vec_ok); break;
-          }
-        }
-      }
+      int const row0 = tc.m_idx + q * 32;  // first row of this warp's 32-row block
+      long long const block_off = static_cast<long long>(tc.b / batch2) * ep.d_batch +
+                                  static_cast<long long>(tc.b % batch2) * ep.d_batch2 +
+                                  static_cast<long long>(row0) * ep.ldd;
+      int const col_off = half * (BLOCK_N / 2);
+      epilogue_columns<NCHUNK>(
+          tmem_base + (uint32_t(q * 32) << 16) + acc * BLOCK_N + col_off, ep, block_off,
+          min(32, M - row0), N, tc.n_idx + col_off, out_dtype, vec_ok,
+          smem + Plan::STAGING_OFFSET + (warp - 2) * EPI_STAGE_PER_WARP, [&] {
+            // accumulator fully in registers: hand the TMEM buffer back to the MMA warp
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(&tmem_empty[acc]);
+          });
       if (++acc == 2) {
         acc = 0;
         acc_phase ^= 1;
@@ -361,7 +481,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
     }
     for (int s = 0; s < 2; ++s) {
       ptx::mbar_init(&tmem_full[s], 1);
-      ptx::mbar_init(&tmem_empty[s], 8);  // 4 epilogue warps in each of the two CTAs
+      ptx::mbar_init(&tmem_empty[s], 2 * EPI_WARPS);  // the epilogue warps of both CTAs
     }
     ptx::fence_mbar_init();
   }
@@ -468,6 +588,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
   } else if (warp >= 2) {
     // ------------------------------------------------------------ epilogue (both CTAs)
     int const q = warp & 3;
+    int const half = (warp - 2) >> 2;
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int tile = tile0; tile < num_tiles; tile += tile_step) {
@@ -475,30 +596,20 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
       decode(tile, b, m_idx, n_idx);
       ptx::mbar_wait(&tmem_full[acc], acc_phase);
       ptx::tc_fence_after();
-      int const row = m_idx + rank * BLOCK_M + q * 32 + lane;
-      long long const row_off = static_cast<long long>(b / batch2) * ep.d_batch +
-                                static_cast<long long>(b % batch2) * ep.d_batch2 +
-                                static_cast<long long>(row) * ep.ldd;
-#pragma unroll 1
-      for (int c = 0; c < BLOCK_N / 32; ++c) {
-        uint32_t r[32];
-        ptx::tmem_ld_32x32(tmem_base + (uint32_t(q * 32) << 16) + acc * BLOCK_N + c * 32, r);
-        ptx::tmem_ld_wait();
-        if (c == BLOCK_N / 32 - 1) {
-          ptx::tc_fence_before();
-          __syncwarp();
-          if (lane == 0) ptx::mbar_arrive_cluster(ptx::map_to_cta(ptx::smem_u32(&tmem_empty[acc]), 0));
-        }
-        int const col0 = n_idx + c * 32;
-        int const valid = min(32, N - col0);
-        if (row < M && valid > 0) {
-          switch (out_dtype) {
-            case FFK_FLOAT: epilogue_row_chunk<float>(r, ep, row_off, col0, valid, vec_ok); break;
-            case FFK_BFLOAT16: epilogue_row_chunk<__nv_bfloat16>(r, ep, row_off, col0, valid, vec_ok); break;
-            default: epilogue_row_chunk<__half>(r, ep, row_off, col0, valid, vec_ok); break;
-          }
-        }
-      }
+      int const row0 = m_idx + rank * BLOCK_M + q * 32;
+      long long const block_off = static_cast<long long>(b / batch2) * ep.d_batch +
+                                  static_cast<long long>(b % batch2) * ep.d_batch2 +
+                                  static_cast<long long>(row0) * ep.ldd;
+      int const col_off = half * (BLOCK_N / 2);
+      epilogue_columns<BLOCK_N / 64>(
+          tmem_base + (uint32_t(q * 32) << 16) + acc * BLOCK_N + col_off, ep, block_off,
+          min(32, M - row0), N, n_idx + col_off, out_dtype, vec_ok,
+          smem + STAGES * STAGE_BYTES + 256 + (warp - 2) * EPI_STAGE_PER_WARP, [&] {
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0)
+              ptx::mbar_arrive_cluster(ptx::map_to_cta(ptx::smem_u32(&tmem_empty[acc]), 0));
+          });
       if (++acc == 2) {
         acc = 0;
         acc_phase ^= 1;
@@ -615,7 +726,8 @@ int launch_tc_layout(Problem const &p, Epilogue const &e, cudaStream_t s) {
 template <bool A_MN, bool B_MN>
 int launch_tc_pair_inst(Problem const &p, Epilogue const &e, cudaStream_t stream) {
   constexpr int STAGES = 6, BLOCK_K = 64, ATOM = 64, HALF_N = 128;
-  constexpr int SMEM = STAGES * (BLOCK_M * SWIZZLE_BYTES + HALF_N * SWIZZLE_BYTES) + 256 + 1024;
+  constexpr int SMEM = STAGES * (BLOCK_M * SWIZZLE_BYTES + HALF_N * SWIZZLE_BYTES) + 256 +
+                       EPI_STAGING_BYTES + 1024;
   CUtensorMap ma, mb;
   int rc;
   int const b2 = p.batch2 > 1 ? p.batch2 : 1, bo = p.batch / b2;

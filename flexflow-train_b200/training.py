@@ -122,13 +122,20 @@ class Dropout(Layer):
         self.x = x
         self.y = Tensor(x.shape, x.data.dtype, x.data.device)
         self.state = K.Dropout.init_kernel(rate, seed, x.data.numel(), device=x.data.device)
-        self.scratch = torch.zeros_like(x.data)
+        self.scratch = None
+        self.sole_reader = False  # set by Model once the whole graph is known
 
     def forward(self):
         K.Dropout.forward_kernel(None, self.state, self.x.data, self.y.data)
 
     def backward(self):
-        # the kernel overwrites (reference semantics); the driver accumulates into x.grad
+        # the kernel overwrites (reference semantics). When this layer is the only reader of x the
+        # result IS x's gradient; otherwise the driver accumulates it into x.grad.
+        if self.sole_reader:
+            K.Dropout.backward_kernel(None, self.state, self.y.grad, self.x.grad)
+            return
+        if self.scratch is None:
+            self.scratch = torch.zeros_like(self.x.data)
         K.Dropout.backward_kernel(None, self.state, self.y.grad, self.scratch)
         K.accumulate(None, self.x.grad, self.scratch)
 
@@ -192,10 +199,14 @@ class SGD:
         for p, g in zip(params, grads):
             v = None
             if self.momentum > 0:
-                v = self.velocity.setdefault(id(p), torch.zeros(p.numel(), dtype=torch.float32, device=p.device))
+                v = self.velocity.get(id(p))
+                if v is None:
+                    v = self.velocity[id(p)] = torch.zeros(p.numel(), dtype=torch.float32, device=p.device)
             m = None
             if p.dtype != torch.float32:
-                m = self.master.setdefault(id(p), p.detach().float().clone())
+                m = self.master.get(id(p))
+                if m is None:  # fp32 master copy, made once (setdefault would rebuild it every step)
+                    m = self.master[id(p)] = p.detach().float().clone()
             K.sgd_ps_update_task_gpu(None, self.lr, self.momentum, self.nesterov, self.weight_decay, g,
                                      p.numel(), num_replicas, p, v, m)
 
@@ -203,6 +214,19 @@ class SGD:
 class Model:
     def __init__(self, inp: Tensor, layers: List[Layer], out: Tensor):
         self.input, self.layers, self.output = inp, layers, out
+        # gradients that a backward kernel overwrites need no zero fill and no accumulate pass:
+        # a Dropout whose input nobody else reads writes its result straight into x.grad
+        readers: Dict[int, int] = {}
+        for l in layers:
+            for name in ("x", "a", "b"):
+                t = getattr(l, name, None)
+                if isinstance(t, Tensor):
+                    readers[id(t)] = readers.get(id(t), 0) + 1
+        self._overwritten = set()
+        for l in layers:
+            if isinstance(l, Dropout) and readers.get(id(l.x), 0) == 1 and l.x.grad is not None:
+                l.sole_reader = True
+                self._overwritten.add(id(l.x))
         self._flatten_gradients()
         self.params = [p for l in layers for p in l.params]
         self.grads = [g for l in layers for g in l.grads]
@@ -243,7 +267,7 @@ class Model:
         for b in self.grad_buckets:
             _fill0(b)
         for t in self.activations():
-            if t.grad is not None:
+            if t.grad is not None and id(t) not in self._overwritten:
                 _fill0(t.grad)
 
     def forward(self):

@@ -114,3 +114,33 @@ def test_mlp_step_is_cuda_graph_capturable(ffk):
     eager, graphed = run(False), run(True)
     for a, b in zip(eager, graphed):
         assert torch.equal(a, b)
+
+
+def test_direct_dropout_gradient_matches_the_accumulating_path(ffk):
+    """A Dropout that is the only reader of its input writes dX straight into x.grad (no zero
+    fill, no accumulate pass). Two steps must give bit-identical weights to the generic path."""
+    import importlib
+    T = importlib.import_module("flexflow_train_b200.training")
+
+    def run(direct):
+        model = T.build_transformer_encoder(num_layers=2, d_model=64, heads=4, seq=16, batch=4, dim_ff=128,
+                                            dropout=0.25, dtype=torch.bfloat16)
+        n_direct = sum(1 for l in model.layers if isinstance(l, T.Dropout) and l.sole_reader)
+        assert n_direct == 4
+        if not direct:
+            for l in model.layers:
+                if isinstance(l, T.Dropout):
+                    l.sole_reader = False
+            model._overwritten.clear()
+        opt = T.SGD(lr=0.05, weight_decay=0.0)
+        g = torch.Generator(device="cuda").manual_seed(1)
+        x = (torch.rand(4, 16, 64, device="cuda", generator=g) * 2 - 1).to(torch.bfloat16)
+        target = (torch.rand(4, 16, 64, device="cuda", generator=g) * 2 - 1).to(torch.bfloat16)
+        for _ in range(2):
+            model.input.data.copy_(x)
+            T.mse_step(model, target, opt)
+        torch.cuda.synchronize()
+        return [p.clone() for p in model.params]
+
+    for a, b in zip(run(True), run(False)):
+        assert torch.equal(a, b)

@@ -75,7 +75,46 @@ def bench(M, N, K, a_mn, b_mn, dt=torch.bfloat16, iters=20):
     ms = e0.elapsed_time(e1) / iters
     print(f"   cuBLAS same shape: {ms*1e3:.1f} us  {2*M*N*K/ms/1e9:.1f} TFLOP/s", flush=True)
 
+def timed(fn, iters=10):
+    for _ in range(3): fn()
+    e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize(); e0.record()
+    for _ in range(iters): fn()
+    e1.record(); torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / iters
+
+
+def bench_encoder_shapes(dt=torch.bfloat16):
+    """The GEMM shapes of one encoder layer (BASELINE configs[2]) with their epilogues."""
+    r = lambda *s: (torch.rand(*s, device="cuda") - 0.5).to(dt)
+    for (name, M, N, K, batch, a_mn, b_mn, kw) in (
+            ("proj  NT plain       ", 32768, 4096, 1024, 1, False, False, {}),
+            ("ffn1  NT bias+relu   ", 32768, 4096, 1024, 1, False, False, dict(bias=True, act=0)),
+            ("ffn2  NT bias        ", 32768, 1024, 4096, 1, False, False, dict(bias=True)),
+            ("dgrad NN accumulate  ", 32768, 4096, 1024, 1, False, True, dict(accumulate=True)),
+            ("dgrad NN accumulate k", 32768, 1024, 4096, 1, False, True, dict(accumulate=True)),
+            ("wgrad TN accumulate  ", 4096, 1024, 32768, 1, True, True, dict(accumulate=True)),
+            ("S=QK^T batched NT    ", 512, 512, 256, 1024, False, False, {}),
+            ("O=PV   batched NN    ", 512, 256, 512, 1024, False, True, {}),
+            ("dV=P^T dO batched TN ", 512, 256, 512, 1024, True, True, {})):
+        A = r(batch, K if a_mn else M, M if a_mn else K)
+        B = r(batch, K if b_mn else N, N if b_mn else K)
+        d = torch.zeros(batch, M, N, dtype=dt, device="cuda")
+        kw = dict(kw)
+        if kw.get("bias"):
+            kw["bias"] = r(N)
+        ms = timed(lambda: gemm(A, B, M, N, K, batch, a_mn, b_mn, dt, 1, d=d, **kw))
+        At = A.transpose(1, 2) if a_mn else A
+        Bt = B if b_mn else B.transpose(1, 2)
+        ms_ref = timed(lambda: torch.bmm(At, Bt))
+        fl = 2.0 * M * N * K * batch
+        print(f"{name}: {ms*1e3:7.1f} us {fl/ms/1e9:7.1f} TF/s | cuBLAS plain {ms_ref*1e3:7.1f} us {fl/ms_ref/1e9:7.1f} TF/s", flush=True)
+
+
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "enc":
+        bench_encoder_shapes()
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "fp32":
         ws = torch.empty(512 << 20, dtype=torch.uint8, device="cuda")
         L.call("ffk_set_gemm_workspace", ws.data_ptr(), ws.numel())
