@@ -131,7 +131,13 @@ __global__ void __launch_bounds__(256)
   db[c] = from_f32<T>(to_f32(db[c]) + t);
 }
 
-constexpr int kBiasGradSplits = 32;
+// Row splits of the bias-gradient reduction: enough (column block x split) CTAs to cover the
+// machine about four times, whatever the width; 32 for wide layers, up to 256 for narrow ones.
+inline int bias_grad_max_splits(int out_dim) {
+  int col_blocks = (out_dim + 255) / 256;  // 32 lanes x 8 sixteen-bit columns per CTA
+  int want = (4 * device_info().sm_count + col_blocks - 1) / col_blocks;
+  return std::max(32, std::min(256, want));
+}
 
 }  // namespace
 }  // namespace ffk
@@ -214,7 +220,7 @@ int ffk_linear_backward(void *stream, void const *input, void *input_grad, void 
   if (bias_grad) {
     FFK_DISPATCH_FLOAT(dtype, T, {
       constexpr int VN = Vec16<T>::N;
-      int splits = workspace ? int(std::min<size_t>(kBiasGradSplits,
+      int splits = workspace ? int(std::min<size_t>(bias_grad_max_splits(out_dim),
                                                     workspace_bytes / (size_t(out_dim) * 4)))
                              : 0;
       splits = std::min(splits, (batch_size + 63) / 64);
@@ -246,7 +252,7 @@ int ffk_linear_backward(void *stream, void const *input, void *input_grad, void 
 }
 
 size_t ffk_linear_backward_workspace_bytes(int out_dim) {
-  return out_dim > 0 ? size_t(kBiasGradSplits) * size_t(out_dim) * sizeof(float) : 0;
+  return out_dim > 0 ? size_t(bias_grad_max_splits(out_dim)) * size_t(out_dim) * sizeof(float) : 0;
 }
 
 int ffk_batch_matmul_forward(void *stream, void *output, void const *a_input, void const *b_input,

@@ -203,6 +203,70 @@ __global__ void __launch_bounds__(kThreads)
   block_commit(p, perf);
 }
 
+// Wide rows (>= 64 classes): one WARP per sample so that the row is read with coalesced
+// loads; per-lane partial results are combined with shuffles. Same definitions as the
+// thread-per-sample kernels above (first maximum wins, last label above 0.9 is the truth).
+__device__ __forceinline__ void warp_argmax(float &mx, int &arg) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    float om = __shfl_xor_sync(0xffffffffu, mx, o);
+    int oa = __shfl_xor_sync(0xffffffffu, arg, o);
+    bool take = oa >= 0 && (arg < 0 || om > mx || (om == mx && oa < arg));
+    if (take) { mx = om; arg = oa; }
+  }
+}
+
+template <bool SPARSE>
+__global__ void __launch_bounds__(kThreads)
+    metrics_wide_kernel(float const *__restrict__ logits, void const *__restrict__ labels_,
+                        ffk_perf_metrics_t *perf, int metrics, int samples, int classes) {
+  Partial p{};
+  int const lane = threadIdx.x & 31;
+  int const warps = gridDim.x * (kThreads / 32);
+  for (int b = blockIdx.x * (kThreads / 32) + (threadIdx.x >> 5); b < samples; b += warps) {
+    float const *row = logits + size_t(b) * classes;
+    float const *lab = SPARSE ? nullptr : reinterpret_cast<float const *>(labels_) + size_t(b) * classes;
+    int const label = SPARSE ? reinterpret_cast<int const *>(labels_)[b] : -1;
+    float mx = SPARSE ? -1.0f : 0.f, cce = 0.f, mse = 0.f, mae = 0.f;
+    int arg = -1, truth = -1;
+    for (int i = lane; i < classes; i += 32) {
+      float const v = row[i];
+      float const t = SPARSE ? (label == i ? 1.0f : 0.0f) : lab[i];
+      if (SPARSE ? (v > mx) : (arg == -1 || v > mx)) { mx = v; arg = i; }
+      if (!SPARSE && t > 0.9f) truth = i;
+      if (!SPARSE && t > 0.f) cce += t * -logf(fmaxf(v, kLogMin));
+      float const d = v - t;
+      mse += d * d;
+      mae += fabsf(d);
+    }
+    warp_argmax(mx, arg);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) truth = max(truth, __shfl_xor_sync(0xffffffffu, truth, o));
+    cce = warp_sum(cce);
+    mse = warp_sum(mse);
+    mae = warp_sum(mae);
+    if (lane == 0) {
+      if (SPARSE) {
+        if (metrics & FFK_METRIC_ACCURACY) {
+          p.all += 1;
+          if (label == arg) p.correct += 1;
+        }
+        if (metrics & FFK_METRIC_SPARSE_CCE) p.scce += -logf(fmaxf(row[label], kLogMin));
+      } else {
+        p.all += 1;
+        if ((metrics & FFK_METRIC_ACCURACY) && truth == arg) p.correct += 1;
+        if (metrics & FFK_METRIC_CCE) p.cce += cce;
+      }
+      if (metrics & FFK_METRIC_MSE) p.mse += mse;
+      if (metrics & FFK_METRIC_RMSE) p.rmse += sqrtf(mse);
+      if (metrics & FFK_METRIC_MAE) p.mae += mae;
+    }
+  }
+  block_commit(p, perf);
+}
+
+constexpr int kWideMetricsClasses = 64;
+
 int diff_scale(void *stream, void *g, void const *p, void const *y, size_t n, float s, int dtype) {
   if (n == 0) return FFK_OK;
   FFK_REQUIRE(g && p && y, "loss backward: null tensor");
@@ -305,6 +369,13 @@ int ffk_update_metrics_sparse_label(void *stream, int metrics, float const *logi
   FFK_REQUIRE(num_samples >= 0 && num_classes > 0, "metrics: bad extents");
   if (num_samples == 0) return FFK_OK;
   FFK_REQUIRE(logit && label && perf, "metrics: null pointer");
+  if (num_classes >= kWideMetricsClasses) {
+    unsigned grid = stream_grid(size_t(num_samples) * 32, kThreads, 8);
+    metrics_wide_kernel<true><<<grid, kThreads, 0, as_stream(stream)>>>(logit, label, perf, metrics,
+                                                                        num_samples, num_classes);
+    FFK_LAUNCH_CHECK();
+    return FFK_OK;
+  }
   unsigned grid = stream_grid(num_samples, kThreads, 4);
   metrics_sparse_kernel<<<grid, kThreads, 0, as_stream(stream)>>>(logit, label, perf, metrics,
                                                                   num_samples, num_classes);
@@ -317,6 +388,13 @@ int ffk_update_metrics_label(void *stream, int metrics, float const *logit, floa
   FFK_REQUIRE(num_samples >= 0 && num_classes > 0, "metrics: bad extents");
   if (num_samples == 0) return FFK_OK;
   FFK_REQUIRE(logit && label && perf, "metrics: null pointer");
+  if (num_classes >= kWideMetricsClasses) {
+    unsigned grid = stream_grid(size_t(num_samples) * 32, kThreads, 8);
+    metrics_wide_kernel<false><<<grid, kThreads, 0, as_stream(stream)>>>(logit, label, perf, metrics,
+                                                                         num_samples, num_classes);
+    FFK_LAUNCH_CHECK();
+    return FFK_OK;
+  }
   unsigned grid = stream_grid(num_samples, kThreads, 4);
   metrics_label_kernel<<<grid, kThreads, 0, as_stream(stream)>>>(logit, label, perf, metrics,
                                                                  num_samples, num_classes);

@@ -99,7 +99,7 @@ int ffk_sum_replicas(void *stream, void *dst, void const *src, size_t n, int num
                      int accumulate, int dtype);
 
 /* Kernels::Dropout — include/kernels/dropout_kernels.h:37-57, src/cuda/ops/dropout_kernels.cu:24-105.
- * y = x * keep / (1 - rate), keep ~ Bernoulli(1 - rate) from a Philox4x32-10 stream keyed by
+ * y = x * keep / (1 - rate), keep ~ Bernoulli(1 - rate) from a Philox4x32-10 stream (16 bits per element) keyed by
  * (seed, offset); the keep decisions are written as one bit per element to `mask`
  * (ceil(n/32) uint32 words — the analogue of cuDNN's reserve space) and reused by backward,
  * which OVERWRITES input_grad like the reference does. */
