@@ -2,7 +2,9 @@
 // 16-byte packets (up to 8 packets per thread), reduced with warp shuffles and written
 // back; rows that do not fit or are not 16-byte aligned take a generic looped kernel.
 #include "common.cuh"
+#include "ptx_sm100.cuh"
 
+#include <cstdlib>
 #include <mutex>
 
 namespace ffk {
@@ -56,6 +58,8 @@ __global__ void __launch_bounds__(kThreads)
     T *yr = y + r * (long long)nvec * VN;
     float v[P][VN];
     float mx = -INFINITY;
+    // (64 resident warps per SM hide the latency here; issuing a thread's loads all at once
+    //  measured slower for these long rows, unlike in the one-warp-per-row kernels below)
 #pragma unroll
     for (int p = 0; p < P; ++p) {
       int i = threadIdx.x + p * kThreads;
@@ -111,14 +115,20 @@ __global__ void __launch_bounds__(kThreads)
     T *yr = y + r * (long long)nvec * VN;
     float v[PW][VN];
     float mx = -INFINITY;
+    Vec16<T> t[PW];
+#pragma unroll
+    for (int p = 0; p < PW; ++p) {
+      int i = lane + p * 32;
+      int ii = i < nvec ? i : 0;
+      t[p] = inplace ? ld_vec(xr + ii * VN) : ld_stream(xr + ii * VN);
+    }
 #pragma unroll
     for (int p = 0; p < PW; ++p) {
       int i = lane + p * 32;
       if (i < nvec) {
-        Vec16<T> t = inplace ? ld_vec(xr + i * VN) : ld_stream(xr + i * VN);
 #pragma unroll
         for (int j = 0; j < VN; ++j) {
-          v[p][j] = to_f32(t.v[j]);
+          v[p][j] = to_f32(t[p].v[j]);
           mx = fmaxf(mx, v[p][j]);
         }
       }
@@ -164,15 +174,22 @@ __global__ void __launch_bounds__(kThreads)
     long long const base = r * (long long)nvec * VN;
     float g[PW][VN], p_[PW][VN];
     float dot = 0.f;
+    Vec16<T> a[PW], b[PW];
+#pragma unroll
+    for (int p = 0; p < PW; ++p) {
+      int i = lane + p * 32;
+      int ii = i < nvec ? i : 0;
+      a[p] = ld_vec(dy + base + ii * VN);
+      b[p] = ld_stream(y + base + ii * VN);
+    }
 #pragma unroll
     for (int p = 0; p < PW; ++p) {
       int i = lane + p * 32;
       if (i < nvec) {
-        Vec16<T> a = ld_vec(dy + base + i * VN), b = ld_stream(y + base + i * VN);
 #pragma unroll
         for (int j = 0; j < VN; ++j) {
-          g[p][j] = to_f32(a.v[j]);
-          p_[p][j] = to_f32(b.v[j]);
+          g[p][j] = to_f32(a[p].v[j]);
+          p_[p][j] = to_f32(b[p].v[j]);
           dot += g[p][j] * p_[p][j];
         }
       }
@@ -315,10 +332,10 @@ __global__ void __launch_bounds__(kThreads)
         if (beta) b = ld_vec(beta + i * VN);
 #pragma unroll
         for (int j = 0; j < VN; ++j) {
-          float t = (v[p][j] - mu) * rs;
-          if (gamma) t *= to_f32(g.v[j]);
-          if (beta) t += to_f32(b.v[j]);
-          o.v[j] = from_f32<T>(t);
+          float u = (v[p][j] - mu) * rs;
+          if (gamma) u *= to_f32(g.v[j]);
+          if (beta) u += to_f32(b.v[j]);
+          o.v[j] = from_f32<T>(u);
         }
         st_stream(yr + i * VN, o);
       }
@@ -594,7 +611,7 @@ __global__ void __launch_bounds__(kThreads)
 
 // Short rows: one warp per row for LayerNorm as well (a d_model = 1024 bf16 row is 128 packets).
 template <typename T, int PW>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, (PW <= 4 ? 3 : 1))
     layer_norm_fwd_warp_rows_kernel(T const *__restrict__ x, T *__restrict__ y,
                                     T const *__restrict__ gamma, T const *__restrict__ beta,
                                     float *__restrict__ mean, float *__restrict__ rstd,
@@ -607,18 +624,23 @@ __global__ void __launch_bounds__(kThreads)
   for (long long r = warp0; r < rows; r += wstride) {
     T const *xr = x + r * (long long)nvec * VN;
     T *yr = y + r * (long long)nvec * VN;
-    float v[PW][VN];
-    float s1 = 0.f, s2 = 0.f;
+    // the row stays PACKED in registers (widened where used): 4 registers per packet instead of
+    // VN, which is what keeps three 256-thread CTAs resident per SM at 32 columns per lane
+    Vec16<T> t[PW];
 #pragma unroll
     for (int p = 0; p < PW; ++p) {
       int i = lane + p * 32;
-      if (i < nvec) {
-        Vec16<T> t = ld_stream(xr + i * VN);
+      t[p] = ld_stream(xr + (i < nvec ? i : 0) * VN);
+    }
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int p = 0; p < PW; ++p) {
+      if (lane + p * 32 < nvec) {
 #pragma unroll
         for (int j = 0; j < VN; ++j) {
-          v[p][j] = to_f32(t.v[j]);
-          s1 += v[p][j];
-          s2 += v[p][j] * v[p][j];
+          float const v = to_f32(t[p].v[j]);
+          s1 += v;
+          s2 += v * v;
         }
       }
     }
@@ -640,12 +662,149 @@ __global__ void __launch_bounds__(kThreads)
         if (beta) b = ld_vec(beta + i * VN);
 #pragma unroll
         for (int j = 0; j < VN; ++j) {
-          float t = (v[p][j] - mu) * rs;
-          if (gamma) t *= to_f32(g.v[j]);
-          if (beta) t += to_f32(b.v[j]);
-          o.v[j] = from_f32<T>(t);
+          float u = (to_f32(t[p].v[j]) - mu) * rs;
+          if (gamma) u *= to_f32(g.v[j]);
+          if (beta) u += to_f32(b.v[j]);
+          o.v[j] = from_f32<T>(u);
         }
         st_stream(yr + i * VN, o);
+      }
+    }
+  }
+}
+
+// Backward for rows of up to 32 columns per lane (N <= 1024 for 16-bit, fp32 alike), one warp per
+// row, fed through shared memory: lane 0 of every warp keeps `STAGES` rows of dY, X and the old
+// dX in flight with 1-D bulk copies (cp.async.bulk, completion counted on an mbarrier per stage),
+// so memory latency is hidden by the ring and not by occupancy — which is what lets each lane keep
+// its 64 fp32 dgamma / dbeta accumulators in registers. Each WARP writes its own partial slab.
+template <typename T, int PW>
+__global__ void __launch_bounds__(128)
+    layer_norm_bwd_ring_kernel(T const *__restrict__ dy, T const *__restrict__ x,
+                               T *__restrict__ dx, T const *__restrict__ gamma,
+                               float const *__restrict__ mean, float const *__restrict__ rstd,
+                               float *__restrict__ part, long long rows, int nvec,
+                               long long num_warps, int stages) {
+  constexpr int VN = Vec16<T>::N;
+  extern __shared__ __align__(128) uint8_t ring_smem[];
+  int const lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  long long const N = (long long)nvec * VN;
+  uint32_t const row_bytes = uint32_t(N * sizeof(T));
+  int const tensors = dx ? 3 : 2;
+  long long const gw = (long long)blockIdx.x * 4 + warp;
+  // layout: [4 warps][stages][tensors][row_bytes] then [4 warps][stages] barriers
+  uint8_t *my_ring = ring_smem + size_t(warp) * stages * tensors * row_bytes;
+  uint64_t *bars = reinterpret_cast<uint64_t *>(ring_smem + size_t(4) * stages * tensors * row_bytes) +
+                   warp * stages;
+  if (lane == 0) {
+    for (int s2 = 0; s2 < stages; ++s2) ptx::mbar_init(&bars[s2], 1);
+    ptx::fence_mbar_init();
+  }
+  __syncwarp();
+  if (gw >= num_warps) return;
+  auto issue = [&](long long r, int st) {  // lane 0 only
+    uint8_t *dst = my_ring + size_t(st) * tensors * row_bytes;
+    ptx::mbar_arrive_expect_tx(&bars[st], tensors * row_bytes);
+    ptx::bulk_load(dst, dy + r * N, row_bytes, &bars[st]);
+    ptx::bulk_load(dst + row_bytes, x + r * N, row_bytes, &bars[st]);
+    if (dx) ptx::bulk_load(dst + 2 * row_bytes, dx + r * N, row_bytes, &bars[st]);
+  };
+  if (lane == 0) {
+    for (int s2 = 0; s2 < stages; ++s2) {
+      long long r = gw + (long long)s2 * num_warps;
+      if (r < rows) issue(r, s2);
+    }
+  }
+  float const invn = 1.f / float(N);
+  Vec16<T> gk[PW];
+  float pg[PW][VN], pb[PW][VN];
+#pragma unroll
+  for (int p = 0; p < PW; ++p) {
+    int i = lane + p * 32;
+#pragma unroll
+    for (int j = 0; j < VN; ++j) {
+      gk[p].v[j] = from_f32<T>(1.f);
+      pg[p][j] = 0.f;
+      pb[p][j] = 0.f;
+    }
+    if (gamma && i < nvec) gk[p] = ld_vec(gamma + i * VN);
+  }
+  int st = 0;
+  uint32_t phase = 0;
+  for (long long r = gw; r < rows; r += num_warps) {
+    ptx::mbar_wait(&bars[st], phase);
+    uint8_t const *src = my_ring + size_t(st) * tensors * row_bytes;
+    Vec16<T> a[PW], b[PW], o[PW];
+#pragma unroll
+    for (int p = 0; p < PW; ++p) {
+      int i = lane + p * 32;
+      if (i < nvec) {
+        a[p] = *reinterpret_cast<Vec16<T> const *>(src + size_t(i) * 16);
+        b[p] = *reinterpret_cast<Vec16<T> const *>(src + row_bytes + size_t(i) * 16);
+        if (dx) o[p] = *reinterpret_cast<Vec16<T> const *>(src + 2 * row_bytes + size_t(i) * 16);
+      }
+    }
+    // the row is in registers: hand the stage back and refill it
+    __syncwarp();
+    if (lane == 0) {
+      long long rn = r + (long long)stages * num_warps;
+      if (rn < rows) {
+        ptx::fence_proxy_async();
+        issue(rn, st);
+      }
+    }
+    float const mu = mean[r], rs = rstd[r];
+    float ds = 0.f, db = 0.f;
+#pragma unroll
+    for (int p = 0; p < PW; ++p) {
+      if (lane + p * 32 < nvec) {
+#pragma unroll
+        for (int j = 0; j < VN; ++j) {
+          float const dg = to_f32(a[p].v[j]) * to_f32(gk[p].v[j]);
+          ds += dg * to_f32(b[p].v[j]);
+          db += dg;
+        }
+      }
+    }
+    ds = warp_sum(ds);
+    db = warp_sum(db);
+    float const c1 = (db * mu - ds) * rs * rs * rs * invn;
+    float const c2 = -(c1 * mu + db * rs * invn);
+    T *dxr = dx ? dx + r * N : nullptr;
+#pragma unroll
+    for (int p = 0; p < PW; ++p) {
+      int i = lane + p * 32;
+      if (i < nvec) {
+#pragma unroll
+        for (int j = 0; j < VN; ++j) {
+          float const d = to_f32(a[p].v[j]), xx = to_f32(b[p].v[j]);
+          if (dx)
+            o[p].v[j] = from_f32<T>(to_f32(o[p].v[j]) + rs * d * to_f32(gk[p].v[j]) + c1 * xx + c2);
+          pg[p][j] += d * (xx - mu) * rs;
+          pb[p][j] += d;
+        }
+        if (dx) st_vec(dxr + i * VN, o[p]);
+      }
+    }
+    if (++st == stages) {
+      st = 0;
+      phase ^= 1;
+    }
+  }
+  if (part) {
+    float *pgr = part + (size_t(gw) * 2 + 0) * N;
+    float *pbr = part + (size_t(gw) * 2 + 1) * N;
+#pragma unroll
+    for (int p = 0; p < PW; ++p) {
+      int i = lane + p * 32;
+      if (i < nvec) {
+#pragma unroll
+        for (int q = 0; q < VN / 4; ++q) {
+          *reinterpret_cast<float4 *>(pgr + i * VN + q * 4) =
+              make_float4(pg[p][q * 4], pg[p][q * 4 + 1], pg[p][q * 4 + 2], pg[p][q * 4 + 3]);
+          *reinterpret_cast<float4 *>(pbr + i * VN + q * 4) =
+              make_float4(pb[p][q * 4], pb[p][q * 4 + 1], pb[p][q * 4 + 2], pb[p][q * 4 + 3]);
+        }
       }
     }
   }
@@ -688,11 +847,19 @@ __global__ void __launch_bounds__(kThreads)
     T const *xr = x + r * N;
     float dv[PW][VN], xv[PW][VN];
     float ds = 0.f, db = 0.f;
+    Vec16<T> ak[PW], bk[PW], ok[PW];  // all loads of the row (old dX included) go out together
+#pragma unroll
+    for (int p = 0; p < PW; ++p) {
+      int i = lane + p * 32, ii = i < nvec ? i : 0;
+      ak[p] = ld_stream(dyr + ii * VN);
+      bk[p] = ld_stream(xr + ii * VN);
+      if (dx) ok[p] = ld_vec(dx + r * N + ii * VN);
+    }
 #pragma unroll
     for (int p = 0; p < PW; ++p) {
       int i = lane + p * 32;
       if (i < nvec) {
-        Vec16<T> a = ld_stream(dyr + i * VN), b = ld_stream(xr + i * VN);
+        Vec16<T> const &a = ak[p], &b = bk[p];
 #pragma unroll
         for (int j = 0; j < VN; ++j) {
           dv[p][j] = to_f32(a.v[j]);
@@ -713,7 +880,7 @@ __global__ void __launch_bounds__(kThreads)
       if (i < nvec) {
         if (dx) {
           T *dxr = dx + r * N;
-          Vec16<T> o = ld_vec(dxr + i * VN);
+          Vec16<T> o = ok[p];
 #pragma unroll
           for (int j = 0; j < VN; ++j)
             o.v[j] = from_f32<T>(to_f32(o.v[j]) + rs * dv[p][j] * g[p][j] + c1 * xv[p][j] + c2);
@@ -986,7 +1153,51 @@ int ffk_layer_norm_backward(void *stream, void const *output_grad, void const *i
     size_t parts_fit = (workspace && want_params) ? workspace_bytes / per_part : 0;
     bool fused = vec && want_params && parts_fit >= 1;
     bool short_rows = vec && pick_pw(N / VN) != 0 && pick_pw(N / VN) <= 2;
-    if (short_rows && (input_grad || fused)) {
+    static bool const no_ring = std::getenv("FFK_LN_NO_RING") != nullptr;
+    int const ring_pw = vec ? pick_pw(N / VN) : 0;
+    // measured: the ring wins from 256-byte rows up for 16-bit types and from 1 KB rows for fp32
+    bool ring_rows = !no_ring && ring_pw != 0 && ring_pw * VN <= 32 &&
+                     (N * sizeof(T)) >= (sizeof(T) == 2 ? 256u : 1024u);
+    if (ring_rows && (input_grad || fused)) {
+      int nvec = int(N / VN);
+      size_t row_bytes = size_t(N) * sizeof(T);
+      int tensors = input_grad ? 3 : 2;
+      int stages = (int)std::max<size_t>(2, std::min<size_t>(6, (24 * 1024) / (tensors * row_bytes)));
+      size_t smem = size_t(4) * stages * tensors * row_bytes + size_t(4) * stages * 8;
+      float *wpart = fused ? reinterpret_cast<float *>(workspace) : nullptr;
+      long long warps = 0;
+      auto launch = [&](auto kern) -> int {
+        FFK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        int per_sm = 0;  // registers (up to 240 a thread at 32 columns per lane) or the ring decide
+        FFK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 128, smem));
+        warps = (long long)device_info().sm_count * std::max(1, std::min(per_sm, 4)) * 4;
+        warps = std::min<long long>(warps, M);
+        if (fused) warps = std::min<long long>(warps, (long long)parts_fit);
+        kern<<<unsigned((warps + 3) / 4), 128, smem, s>>>(
+            reinterpret_cast<T const *>(output_grad), reinterpret_cast<T const *>(input),
+            reinterpret_cast<T *>(input_grad), reinterpret_cast<T const *>(gamma), mean, rstd, wpart, M,
+            nvec, warps, stages);
+        return FFK_OK;
+      };
+      int rc = FFK_OK;
+      switch (ring_pw) {
+        case 1: rc = launch(layer_norm_bwd_ring_kernel<T, 1>); break;
+        case 2: rc = launch(layer_norm_bwd_ring_kernel<T, 2>); break;
+        case 4: rc = launch(layer_norm_bwd_ring_kernel<T, 4>); break;
+        default:
+          if constexpr (sizeof(T) == 4) rc = launch(layer_norm_bwd_ring_kernel<T, 8>);
+          break;
+      }
+      if (rc) return rc;
+      FFK_LAUNCH_CHECK();
+      if (fused) {
+        layer_norm_param_reduce_kernel<T><<<unsigned((N + 31) / 32), 1024, 0, s>>>(
+            reinterpret_cast<float const *>(workspace), int(warps), N,
+            reinterpret_cast<T *>(gamma_grad), reinterpret_cast<T *>(beta_grad),
+            accumulate_param_grads != 0);
+        FFK_LAUNCH_CHECK();
+      }
+    } else if (short_rows && (input_grad || fused)) {
       int nvec = int(N / VN), p = pick_pw(nvec);
       size_t smem = size_t(2) * size_t(N) * sizeof(float);
       unsigned grid = rows_grid((M + 7) / 8, 3);

@@ -55,6 +55,15 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
 }
 
 // ---------------------------------------------------------------- TMA
+// 1-D bulk copy global -> this CTA's shared memory, completion counted in bytes on `bar`.
+// Address and size must be multiples of 16.
+__device__ __forceinline__ void bulk_load(void *smem_dst, void const *gsrc, uint32_t bytes,
+                                          uint64_t *bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+      :: "r"(smem_u32(smem_dst)), "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+      : "memory");
+}
 __device__ __forceinline__ void prefetch_tensormap(CUtensorMap const *m) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(m) : "memory");
 }

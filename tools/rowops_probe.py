@@ -31,6 +31,19 @@ B = M * N * 2
 if which in ("all", "ln"):
     report("layer_norm fwd 32768x1024", timed(lambda: K.LayerNorm.forward_kernel(None, ln, x, y, gamma, beta)), 2 * B)
     report("layer_norm bwd 32768x1024", timed(lambda: K.LayerNorm.backward_kernel(None, ln, dy, x, dx, gamma, dgamma, dbeta, True)), 4 * B)
+if which == "lnsweep":
+    for dtt in (torch.bfloat16, torch.float32):
+        for NN in (128, 256, 512, 768, 1024):
+            MM = (32 << 20) // NN
+            xs = (torch.rand(MM, NN, device="cuda") - 0.5).to(dtt)
+            dys, dxs, ys = xs.clone(), xs.clone(), xs.clone()
+            gm = torch.ones(NN, device="cuda", dtype=dtt)
+            dg, dbb = torch.zeros_like(gm), torch.zeros_like(gm)
+            st = K.LayerNorm.init_kernel(True, MM, NN, 1e-5)
+            eb = MM * NN * xs.element_size()
+            report(f"ln fwd {str(dtt)[6:]} {MM}x{NN}", timed(lambda: K.LayerNorm.forward_kernel(None, st, xs, ys, gm, gm)), 2 * eb)
+            report(f"ln bwd {str(dtt)[6:]} {MM}x{NN}", timed(lambda: K.LayerNorm.backward_kernel(None, st, dys, xs, dxs, gm, dg, dbb, True)), 4 * eb)
+    sys.exit(0)
 if which in ("all", "softmax"):
     R, C = 64 * 16 * 512, 512
     p, q, g = r(R, C), r(R, C), r(R, C)
