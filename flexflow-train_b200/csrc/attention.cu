@@ -125,11 +125,27 @@ int ffk_mha_forward(void *stream, ffk_mha_config_t const *cfg_host, void const *
   if ((rc = mm(c, query, g.qS, false, c.at(weight, g.wq), g.HQ, true, qp, g.HQ, g.Rq, g.HQ, g.qS, false))) return rc;
   if ((rc = mm(c, key, g.kS, false, c.at(weight, g.wk), g.HK, true, kp, g.HK, g.Rk, g.HK, g.kS, false))) return rc;
   if ((rc = mm(c, value, g.vS, false, c.at(weight, g.wv), g.HV, true, vp, g.HV, g.Rk, g.HV, g.vS, false))) return rc;
-  // scores S[n][h] = Qh Kh^T (scale 1.0), batched over (sample, head)
-  if ((rc = mm(c, qp, g.HQ, false, kp, g.HK, false, pp, g.Sk, g.Sq, g.Sk, g.qP, false, g.N * g.H, g.H,
-               g.Sq * g.HQ, g.qP, g.Sk * g.HK, g.kP, g.H * g.Sq * g.Sk, g.Sq * g.Sk)))
-    return rc;
-  if ((rc = ffk_softmax_forward(stream, pp, pp, g.N * g.H * g.Sq, g.Sk, 1, dtype))) return rc;
+  // scores S[n][h] = Qh Kh^T (scale 1.0), batched over (sample, head), then P = softmax rows.
+  // 512-key rows of 16-bit tensors are normalised inside the score GEMM (in TMEM); anything
+  // else is the GEMM followed by the in-place row softmax.
+  {
+    gemm::Problem p{qp, kp, g.HQ, g.HK, g.Sq * g.HQ, g.Sk * g.HK, (int)g.Sq, (int)g.Sk, (int)g.qP,
+                    (int)(g.N * g.H), dtype, dtype, false, false};
+    p.batch2 = (int)g.H;
+    p.a_batch2 = g.qP;
+    p.b_batch2 = g.kP;
+    gemm::Epilogue e{pp, g.Sk, g.H * g.Sq * g.Sk, nullptr, gemm::ACT_NONE, 0, 1.f, 0.f, nullptr};
+    e.d_batch2 = g.Sq * g.Sk;
+    bool const tensor_path = path == FFK_GEMM_AUTO || path == FFK_GEMM_TENSOR;
+    if (tensor_path && gemm::softmax_gemm_eligible(p, e)) {
+      if ((rc = gemm::launch_softmax_gemm(p, e, c.s))) return rc;
+    } else {
+      if ((rc = mm(c, qp, g.HQ, false, kp, g.HK, false, pp, g.Sk, g.Sq, g.Sk, g.qP, false, g.N * g.H,
+                   g.H, g.Sq * g.HQ, g.qP, g.Sk * g.HK, g.kP, g.H * g.Sq * g.Sk, g.Sq * g.Sk)))
+        return rc;
+      if ((rc = ffk_softmax_forward(stream, pp, pp, g.N * g.H * g.Sq, g.Sk, 1, dtype))) return rc;
+    }
+  }
   // head outputs O[n][:, h, :] = P[n][h] Vh, written straight into the concatenated layout
   if ((rc = mm(c, pp, g.Sk, false, vp, g.HV, true, oc, g.HV, g.Sq, g.vP, g.Sk, false, g.N * g.H, g.H,
                g.H * g.Sq * g.Sk, g.Sq * g.Sk, g.Sk * g.HV, g.vP, g.Sq * g.HV, g.vP)))

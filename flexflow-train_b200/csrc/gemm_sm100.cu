@@ -625,6 +625,220 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
   }
 }
 
+// ------------------------------------------------------------------ scores + row softmax
+// P = softmax_rows(A B^T) for rows of exactly 512 columns (the attention scores of a 512-token
+// sequence), both operands K-major. A CTA pair owns 256 rows x all 512 columns: the fp32 score
+// tile fills the whole of TMEM (no double buffer), and the eight epilogue warps of each CTA
+// normalise it there — row maximum, exp written back to TMEM with tcgen05.st while the row
+// sum accumulates, then scale, convert and store — so the scores never travel to HBM in
+// fp32 or unnormalised form. Same barrier protocol as gemm_tc_pair_kernel.
+template <int STAGES>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
+    gemm_softmax_pair_kernel(const __grid_constant__ CUtensorMap map_a,
+                             const __grid_constant__ CUtensorMap map_b, Epilogue ep, int M, int K,
+                             int batch, int batch2, uint32_t idesc, int out_dtype) {
+  constexpr int N = 512, HALF_N = 128, PAIR_M = 256, ESIZE = 2;
+  constexpr int BLOCK_K = SWIZZLE_BYTES / ESIZE;
+  constexpr int A_BYTES = BLOCK_M * SWIZZLE_BYTES, B_BYTES = HALF_N * SWIZZLE_BYTES;
+  constexpr int STAGE_BYTES = A_BYTES + 2 * B_BYTES;  // this CTA's quarter of each 256-column half
+  constexpr uint32_t TMEM_COLS = N;
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t *smem = reinterpret_cast<uint8_t *>(
+      (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+  uint64_t *full_bar = reinterpret_cast<uint64_t *>(smem + STAGES * STAGE_BYTES);
+  uint64_t *empty_bar = full_bar + STAGES;
+  uint64_t *tmem_full = empty_bar + STAGES;
+  uint64_t *tmem_empty = tmem_full + 1;
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tmem_empty + 1);
+  float *exch = reinterpret_cast<float *>(smem + STAGES * STAGE_BYTES + 128);  // [2 halves][128 rows]
+  uint8_t *staging = smem + STAGES * STAGE_BYTES + 128 + 1024;
+
+  int const warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  uint32_t const rank = ptx::cluster_ctarank();
+  bool const leader = rank == 0;
+
+  if (threadIdx.x == 0) {
+    ptx::prefetch_tensormap(&map_a);
+    ptx::prefetch_tensormap(&map_b);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      ptx::mbar_init(&full_bar[s], 1);
+      ptx::mbar_init(&empty_bar[s], 1);
+    }
+    ptx::mbar_init(tmem_full, 1);
+    ptx::mbar_init(tmem_empty, 2 * EPI_WARPS);
+    ptx::fence_mbar_init();
+  }
+  if (warp == 2) {
+    ptx::tmem_alloc_2cta(tmem_slot, TMEM_COLS);
+    ptx::tmem_relinquish_2cta();
+  }
+  ptx::tc_fence_before();
+  ptx::cluster_sync();
+  ptx::tc_fence_after();
+  uint32_t const tmem_base = *tmem_slot;
+
+  int const num_m = (M + PAIR_M - 1) / PAIR_M;
+  int const num_tiles = num_m * batch;
+  int const num_k = (K + BLOCK_K - 1) / BLOCK_K;
+  int const tile0 = ptx::cluster_id_x(), tile_step = ptx::num_clusters_x();
+
+  if (warp == 0 && lane == 0) {
+    // ------------------------------------------------------------ TMA producer (both CTAs)
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int tile = tile0; tile < num_tiles; tile += tile_step) {
+      int const b = tile / num_m, m_idx = (tile - b * num_m) * PAIR_M;
+      int const my_m = m_idx + rank * BLOCK_M;
+      int const b_in = b % batch2, b_out = b / batch2;
+      for (int kb = 0; kb < num_k; ++kb) {
+        ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+        uint8_t *sa = smem + stage * STAGE_BYTES;
+        uint8_t *sb = sa + A_BYTES;
+        uint32_t const lead_full = ptx::map_to_cta(ptx::smem_u32(&full_bar[stage]), 0);
+        if (leader) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * STAGE_BYTES);
+        int const k_idx = kb * BLOCK_K;
+        ptx::tma_load_4d_2cta(sa, &map_a, lead_full, k_idx, my_m, b_in, b_out);
+        ptx::tma_load_4d_2cta(sb, &map_b, lead_full, k_idx, int(rank) * HALF_N, b_in, b_out);
+        ptx::tma_load_4d_2cta(sb + B_BYTES, &map_b, lead_full, k_idx, 256 + int(rank) * HALF_N, b_in,
+                              b_out);
+        if (++stage == STAGES) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+    }
+  } else if (warp == 1 && lane == 0 && leader) {
+    // ------------------------------------------------------------ MMA issuer (leader only)
+    int stage = 0;
+    uint32_t phase = 0, acc_phase = 0;
+    for (int tile = tile0; tile < num_tiles; tile += tile_step) {
+      ptx::mbar_wait(tmem_empty, acc_phase ^ 1);
+      ptx::tc_fence_after();
+      for (int kb = 0; kb < num_k; ++kb) {
+        ptx::mbar_wait(&full_bar[stage], phase);
+        ptx::tc_fence_after();
+        uint32_t const sa = ptx::smem_u32(smem + stage * STAGE_BYTES);
+        uint32_t const sb = sa + A_BYTES;
+#pragma unroll
+        for (int nh = 0; nh < 2; ++nh) {
+#pragma unroll
+          for (int k = 0; k < K_STEPS; ++k) {
+            uint64_t da = ptx::make_smem_desc_sw128(sa + k * MMA_K_BYTES, 0, 1024);
+            uint64_t db = ptx::make_smem_desc_sw128(sb + nh * B_BYTES + k * MMA_K_BYTES, 0, 1024);
+            ptx::mma_f16_ss_2cta(tmem_base + nh * 256, da, db, idesc, (kb | k) != 0);
+          }
+        }
+        ptx::mma_commit_2cta(&empty_bar[stage], 0b11);
+        if (kb == num_k - 1) ptx::mma_commit_2cta(tmem_full, 0b11);
+        if (++stage == STAGES) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+      acc_phase ^= 1;
+    }
+  } else if (warp >= 2) {
+    // ------------------------------------------------------------ softmax epilogue (both CTAs)
+    int const q = warp & 3, half = (warp - 2) >> 2;
+    int const row_in_cta = q * 32 + lane;
+    uint32_t const taddr = tmem_base + (uint32_t(q * 32) << 16) + half * 256;
+    uint8_t *stage_buf = staging + (warp - 2) * EPI_STAGE_PER_WARP;
+    constexpr float kLog2e = 1.4426950408889634f;
+    uint32_t acc_phase = 0;
+    for (int tile = tile0; tile < num_tiles; tile += tile_step) {
+      int const b = tile / num_m, m_idx = (tile - b * num_m) * PAIR_M;
+      ptx::mbar_wait(tmem_full, acc_phase);
+      ptx::tc_fence_after();
+      // pass 1: row maximum over this warp's 256 columns, then over both halves. The loops over
+      // chunks are NOT unrolled: the three passes must stay inside the instruction cache (a fully
+      // unrolled version spent most of its time on instruction fetch and ran 1.5x slower).
+      float mx = -INFINITY;
+#pragma unroll 1
+      for (int c = 0; c < 8; c += 2) {
+        uint32_t r0[32], r1[32];
+        ptx::tmem_ld_32x32(taddr + c * 32, r0);
+        ptx::tmem_ld_32x32(taddr + c * 32 + 32, r1);
+        ptx::tmem_ld_wait_for(r0);
+        float m0 = -INFINITY, m1 = -INFINITY;
+#pragma unroll
+        for (int i = 0; i < 32; i += 2) {
+          m0 = fmaxf(m0, __uint_as_float(r0[i]));
+          m1 = fmaxf(m1, __uint_as_float(r0[i + 1]));
+        }
+        ptx::tmem_ld_wait_for(r1);
+#pragma unroll
+        for (int i = 0; i < 32; i += 2) {
+          m0 = fmaxf(m0, __uint_as_float(r1[i]));
+          m1 = fmaxf(m1, __uint_as_float(r1[i + 1]));
+        }
+        mx = fmaxf(mx, fmaxf(m0, m1));
+      }
+      exch[half * 128 + row_in_cta] = mx;
+      ptx::named_barrier(1, EPI_WARPS * 32);
+      mx = fmaxf(mx, exch[(half ^ 1) * 128 + row_in_cta]);
+      ptx::named_barrier(1, EPI_WARPS * 32);  // both values read before the slots are reused
+      // pass 2: p = exp(s - max) back into TMEM, row sum on the side. Even columns go through
+      // the special-function unit, odd columns through the FMA-pipe polynomial (ptx::ex2_poly).
+      float const shift = -mx * kLog2e;
+      float sum = 0.f;
+#pragma unroll 1
+      for (int c = 0; c < 8; ++c) {
+        uint32_t r[32];
+        ptx::tmem_ld_32x32(taddr + c * 32, r);
+        ptx::tmem_ld_wait_for(r);
+        float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+        for (int i = 0; i < 32; i += 2) {
+          float const p0 = ptx::ex2_approx(fmaf(__uint_as_float(r[i]), kLog2e, shift));
+          float const p1 = ptx::ex2_poly(fmaf(__uint_as_float(r[i + 1]), kLog2e, shift));
+          s0 += p0;
+          s1 += p1;
+          r[i] = __float_as_uint(p0);
+          r[i + 1] = __float_as_uint(p1);
+        }
+        sum += s0 + s1;
+        ptx::tmem_st_32x32(taddr + c * 32, r);
+      }
+      ptx::tmem_st_wait();
+      exch[half * 128 + row_in_cta] = sum;
+      ptx::named_barrier(1, EPI_WARPS * 32);
+      sum += exch[(half ^ 1) * 128 + row_in_cta];
+      ptx::named_barrier(1, EPI_WARPS * 32);
+      // pass 3: scale by 1 / sum, convert, coalesced store
+      Epilogue row_ep = ep;
+      row_ep.alpha = 1.f / sum;
+      int const row0 = m_idx + int(rank) * BLOCK_M + q * 32;
+      long long const block_off = static_cast<long long>(b / batch2) * ep.d_batch +
+                                  static_cast<long long>(b % batch2) * ep.d_batch2 +
+                                  static_cast<long long>(row0) * ep.ldd;
+#pragma unroll 1
+      for (int cc = 0; cc < 4; ++cc) {
+        epilogue_columns<2>(taddr + cc * 64, row_ep, block_off, min(32, M - row0), N,
+                            half * 256 + cc * 64, out_dtype, 1, stage_buf, [&] {
+                              if (cc == 3) {
+                                ptx::tc_fence_before();
+                                __syncwarp();
+                                if (lane == 0)
+                                  ptx::mbar_arrive_cluster(
+                                      ptx::map_to_cta(ptx::smem_u32(tmem_empty), 0));
+                              }
+                            });
+      }
+      acc_phase ^= 1;
+    }
+  }
+
+  ptx::tc_fence_before();
+  ptx::cluster_sync();
+  if (warp == 2) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc_2cta(tmem_base, TMEM_COLS);
+  }
+}
+
 // ------------------------------------------------------------------ host side
 PFN_cuTensorMapEncodeTiled_v12000 encode_fn() {
   static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
@@ -765,6 +979,28 @@ int launch_tc_pair(Problem const &p, Epilogue const &e, cudaStream_t s) {
   return launch_tc_pair_inst<true, true>(p, e, s);
 }
 
+int launch_softmax_pair(Problem const &p, Epilogue const &e, cudaStream_t stream) {
+  constexpr int STAGES = 3, BLOCK_K = 64, HALF_N = 128;
+  constexpr int SMEM = STAGES * (BLOCK_M * SWIZZLE_BYTES + 2 * HALF_N * SWIZZLE_BYTES) + 128 + 1024 +
+                       EPI_STAGING_BYTES + 1024;
+  CUtensorMap ma, mb;
+  int const b2 = p.batch2 > 1 ? p.batch2 : 1, bo = p.batch / b2;
+  int rc = make_map(&ma, p.a, p.in_dtype, p.K, p.M, bo, b2, p.lda, p.a_batch, p.a_batch2, BLOCK_K, BLOCK_M);
+  if (rc) return rc;
+  rc = make_map(&mb, p.b, p.in_dtype, p.K, p.N, bo, b2, p.ldb, p.b_batch, p.b_batch2, BLOCK_K, HALF_N);
+  if (rc) return rc;
+  auto kern = gemm_softmax_pair_kernel<STAGES>;
+  FFK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+  uint32_t fmt = p.in_dtype == FFK_BFLOAT16 ? ptx::kFmtBF16 : ptx::kFmtF16;
+  uint32_t idesc = ptx::make_idesc(fmt, false, false, 256, 256);
+  long long tiles = 1LL * ((p.M + 255) / 256) * p.batch;
+  int clusters = (int)std::min<long long>(tiles, device_info().sm_count / 2);
+  kern<<<clusters * 2, NUM_THREADS, SMEM, stream>>>(ma, mb, e, p.M, p.K, p.batch, b2, idesc,
+                                                    p.out_dtype);
+  FFK_LAUNCH_CHECK();
+  return FFK_OK;
+}
+
 }  // namespace
 
 bool tc_eligible(Problem const &p, Epilogue const &e) {
@@ -805,6 +1041,24 @@ int launch_tc(Problem const &p, Epilogue const &e, cudaStream_t stream) {
   if (!no_pair && !narrow && p.M > 128) return launch_tc_pair(p, e, stream);
   return narrow ? launch_tc_layout<2, 128, 6>(p, e, stream)
                 : launch_tc_layout<2, 256, 4>(p, e, stream);
+}
+
+bool softmax_gemm_eligible(Problem const &p, Epilogue const &e) {
+  static bool const off = std::getenv("FFK_NO_FUSED_SOFTMAX") != nullptr;
+  size_t os = dtype_size(p.out_dtype);
+  return !off && tc_eligible(p, e) && p.N == 512 && !p.a_mn_major && !p.b_mn_major &&
+         (p.in_dtype == FFK_BFLOAT16 || p.in_dtype == FFK_HALF) && p.out_dtype == p.in_dtype &&
+         e.bias == nullptr && e.act == ACT_NONE && !e.accumulate && e.r == nullptr &&
+         e.alpha == 1.f && aligned16(e.d) && (e.ldd * os) % 16 == 0 && (e.d_batch * os) % 16 == 0 &&
+         (e.d_batch2 * os) % 16 == 0;
+}
+
+int launch_softmax_gemm(Problem const &p, Epilogue const &e, cudaStream_t stream) {
+  if (!softmax_gemm_eligible(p, e)) {
+    set_error("gemm+softmax: needs 512-column K-major 16-bit operands with aligned rows");
+    return FFK_ERR_UNSUPPORTED;
+  }
+  return launch_softmax_pair(p, e, stream);
 }
 
 // ------------------------------------------------------------------ SIMT GEMM

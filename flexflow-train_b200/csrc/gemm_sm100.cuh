@@ -58,6 +58,10 @@ struct Problem {
 // operands break a TMA constraint (16-byte aligned base and row pitch).
 int launch_tc(Problem const &p, Epilogue const &e, cudaStream_t stream);
 bool tc_eligible(Problem const &p, Epilogue const &e);
+// D = softmax over each row of (A B^T): 512-column rows, K-major 16-bit operands (the attention
+// scores of a 512-token sequence), normalised in TMEM before they are stored.
+bool softmax_gemm_eligible(Problem const &p, Epilogue const &e);
+int launch_softmax_gemm(Problem const &p, Epilogue const &e, cudaStream_t stream);
 
 // CUDA-core path: any pitch, fp32 accumulate in strict k order per tile. This
 // is the fp32-exact path used for FLOAT tensors and the ragged fallback.

@@ -81,3 +81,29 @@ def test_mha_null_key_value_grads_and_bad_config(K, ffk):
     assert dk is None and dv is None and torch.isfinite(dq).all()
     with pytest.raises(ffk.FFKError):
         K.MultiHeadAttention.init_kernel(2, 2, 16, 16, 16, 8, 4, 8, 16, 4, 4)  # qProj != kProj
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("dims", [[2, 2, 64, 64, 64, 32, 32, 32, 64, 512, 512],
+                                  [1, 3, 64, 64, 64, 64, 64, 64, 64, 300, 512],   # ragged query block
+                                  [3, 2, 32, 32, 32, 256, 256, 256, 32, 256, 512]])  # the encoder's head dim
+def test_mha_512_keys_scores_normalised_in_tmem(K, oracle, dims, dtype):
+    """512-key rows of 16-bit tensors take the fused score+softmax kernel (probabilities are
+    normalised in TMEM and stored once). Checked against the oracle and against the unfused
+    CUDA-core path of the same entry point."""
+    N, H, qS, kS, vS, qP, kP, vP, oP, Sq, Sk = dims
+    q, qn = to_dev(uniform((N, Sq, qS), 1234), dtype)
+    k, kn = to_dev(uniform((N, Sk, kS), 1235), dtype)
+    v, vn = to_dev(uniform((N, Sk, vS), 1236), dtype)
+    nw = qS * H * qP + kS * H * kP + vS * H * vP + H * vP * oP
+    w, wn = to_dev(uniform((nw,), 4321) * (2.0 / np.sqrt(qS)), dtype)
+    dout, doutn = to_dev(uniform((N, Sq, oP), 1237), dtype)
+    out, dq, dk, dv, dw = run_mha(K, dims, q, k, v, w, dout, dtype, 0)
+    ref = np.zeros((N, Sq, oP), np.float32)
+    oracle.mha_forward(dims, qn, kn, vn, wn, ref)
+    rdq, rdk, rdv, rdw = np.zeros_like(qn), np.zeros_like(kn), np.zeros_like(vn), np.ones_like(wn)
+    oracle.mha_backward(dims, qn, rdq, kn, rdk, vn, rdv, wn, rdw, doutn)
+    for got, want, name in ((out, ref, "out"), (dq, rdq, "dq"), (dk, rdk, "dk"), (dv, rdv, "dv"), (dw, rdw, "dw")):
+        assert_close_l2(got, want, what="mha512 " + name)
+    out2, _, _, _, _ = run_mha(K, dims, q, k, v, w, dout, dtype, K.GEMM_SIMT)
+    assert_close_l2(out, out2.float().cpu().numpy(), rel=2e-2, what="fused vs unfused out")
