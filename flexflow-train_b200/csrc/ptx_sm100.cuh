@@ -189,19 +189,6 @@ __device__ __forceinline__ float ex2_approx(float x) {
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
-// 2^x for x <= 0 on the FMA pipe: round-to-nearest split x = n + f, f in [-0.5, 0.5], cubic
-// minimax polynomial for 2^f (relative error 7.5e-5: below bf16 / half output rounding), then n
-// is added to the exponent field. The special-function unit retires 16 ex2 per clock per SM
-// against 128 FMAs, so a softmax that alternates this with ex2.approx is no longer bound by it.
-__device__ __forceinline__ float ex2_poly(float x) {
-  x = fmaxf(x, -125.f);
-  float const t = x + 12582912.f;           // 1.5 * 2^23: n lands in the low mantissa bits
-  float const f = x - (t - 12582912.f);
-  float p = fmaf(f, 0.05517164f, 0.24261113f);  // minimax on [-0.5, 0.5]
-  p = fmaf(p, f, 0.69326097f);
-  p = fmaf(p, f, 0.99992806f);
-  return __int_as_float(__float_as_int(p) + (__float_as_int(t) << 23));
-}
 // Named barrier among `nthreads` threads of the CTA (id 1..15; 0 is __syncthreads).
 __device__ __forceinline__ void named_barrier(uint32_t id, uint32_t nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
