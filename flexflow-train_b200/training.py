@@ -159,7 +159,9 @@ class SelfAttention(Layer):
         self.w = ((torch.rand(nw, device=dev, generator=g) * 2 - 1) * (1.0 / E ** 0.5)).to(dt)
         self.dw = torch.zeros_like(self.w)
         self.y = Tensor(x.shape, dt, dev)
-        self.dq, self.dk, self.dv = (torch.zeros_like(x.data) for _ in range(3))
+        # dq | dk | dv stacked like the replicas of a Replicate op: their sum is one kernel
+        self.dqkv = torch.zeros((3,) + tuple(x.data.shape), dtype=dt, device=dev)
+        self.dq, self.dk, self.dv = self.dqkv[0], self.dqkv[1], self.dqkv[2]
         self.params, self.grads = [self.w], [self.dw]
 
     def forward(self):
@@ -168,8 +170,7 @@ class SelfAttention(Layer):
     def backward(self):
         K.MultiHeadAttention.backward_kernel(None, self.state, self.x.data, self.dq, self.x.data, self.dk,
                                              self.x.data, self.dv, self.w, self.dw, self.y.grad)
-        for g in (self.dq, self.dk, self.dv):
-            K.accumulate(None, self.x.grad, g)
+        K.Replicate.backward_kernel(None, self.x.grad, self.dqkv, 3)  # x.grad += dq + dk + dv
 
 
 class Softmax(Layer):
