@@ -1,0 +1,321 @@
+// Sum over ranks through NVLink peer memory: every rank maps the other ranks' gradient regions
+// (CUDA IPC) and the reduction is done by plain loads from peer memory inside one kernel — no
+// NCCL call, no staging copies. Small buffers take one shot (every rank reads all peers and sums
+// in rank order); large ones take two (rank r reduces chunk r from all peers, then the reduced
+// chunks are gathered), so that each byte crosses the switch twice per GPU instead of world times.
+//
+// Cross-rank ordering uses flags that live in each rank's region and only ever grow: a launch
+// takes its epoch from a counter in device memory that its last block increments, so the same
+// launch can be replayed (CUDA graph) and no host state has to agree between ranks beyond
+// "everybody calls the collectives in the same order". Waits are bounded (a peer that never
+// arrives turns into FFK_ERR_CUDA on the next status query instead of a hung GPU).
+#include "common.cuh"
+
+#include <cstring>
+
+namespace ffk {
+namespace {
+
+constexpr int kMaxRanks = 16;
+constexpr size_t kFlagBytes = 4096;         // head of every region
+constexpr int kPhases = 3;                  // input ready / chunk reduced / done reading
+constexpr size_t kOneShotLimit = 512 << 10;  // bytes
+constexpr long long kSpinLimit = 4000000000LL;  // ~2 s of SM clocks
+
+struct Control {                 // lives at the head of each rank's region (device memory)
+  unsigned flags[kPhases][kMaxRanks];
+  unsigned epoch;                // completed launches
+  unsigned blocks_done;          // grid-wide arrival counters of the current launch
+  unsigned blocks_mid;
+  unsigned timed_out;            // sticky: a bounded wait expired
+};
+static_assert(sizeof(Control) <= kFlagBytes, "control block must fit the reserved head");
+
+struct PeerTable {
+  unsigned char *base[kMaxRanks];  // region base of every rank as mapped in THIS process
+};
+
+struct Group {
+  int rank = 0, world = 1, device = 0;
+  size_t data_bytes = 0;
+  unsigned char *local = nullptr;     // cudaMalloc'd region: [Control | data]
+  void *peer_mapped[kMaxRanks] = {};  // cudaIpcOpenMemHandle results (own slot unused)
+  PeerTable table{};
+  bool connected = false;
+};
+
+__device__ __forceinline__ void st_release_sys(unsigned *p, unsigned v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned ld_acquire_sys(unsigned const *p) {
+  unsigned v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint4 ld_peer16(void const *p) {
+  // peer memory must not be served from a stale L1 line of an earlier launch
+  uint4 v;
+  asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "l"(p)
+               : "memory");
+  return v;
+}
+
+// Tell every peer that this rank reached `phase` of launch `epoch`.
+__device__ void signal_peers(PeerTable const &t, int rank, int world, int phase, unsigned epoch) {
+  if (threadIdx.x < world) {
+    Control *c = reinterpret_cast<Control *>(t.base[threadIdx.x]);
+    st_release_sys(&c->flags[phase][rank], epoch);
+  }
+}
+// Wait (bounded) until every rank has signalled `phase` of launch `epoch` in OUR control block.
+__device__ void wait_peers(Control *mine, int world, int phase, unsigned epoch) {
+  if (threadIdx.x < world) {
+    long long const t0 = clock64();
+    while (ld_acquire_sys(&mine->flags[phase][threadIdx.x]) < epoch) {
+      if (clock64() - t0 > kSpinLimit) {
+        mine->timed_out = 1;
+        break;
+      }
+    }
+  }
+  __syncthreads();
+}
+
+template <typename T> struct Acc16 {
+  static constexpr int N = 16 / sizeof(T);
+  float v[N];
+  __device__ void zero() {
+#pragma unroll
+    for (int i = 0; i < N; ++i) v[i] = 0.f;
+  }
+  __device__ void add(uint4 raw) {
+    Vec16<T> p;
+    *reinterpret_cast<uint4 *>(&p) = raw;
+#pragma unroll
+    for (int i = 0; i < N; ++i) v[i] += to_f32(p.v[i]);
+  }
+  __device__ uint4 pack() const {
+    Vec16<T> p;
+#pragma unroll
+    for (int i = 0; i < N; ++i) p.v[i] = from_f32<T>(v[i]);
+    return *reinterpret_cast<uint4 const *>(&p);
+  }
+};
+
+// in_off / out_off: byte offsets of the summed range and of the result inside every region's data
+// part; npk = number of 16-byte packets. two_shot: packets are split into `world` chunks.
+template <typename T>
+__global__ void __launch_bounds__(512)
+    p2p_all_reduce_kernel(PeerTable t, int rank, int world, size_t in_off, size_t out_off,
+                          size_t npk, int two_shot) {
+  Control *mine = reinterpret_cast<Control *>(t.base[rank]);
+  unsigned const epoch = mine->epoch + 1;  // every block reads it before the last block bumps it
+  size_t const tid = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  size_t const nthreads = size_t(gridDim.x) * blockDim.x;
+
+  // ---- entry: every rank's input is complete (stream order on its side) once its kernel runs
+  if (blockIdx.x == 0) signal_peers(t, rank, world, 0, epoch);
+  wait_peers(mine, world, 0, epoch);
+
+  unsigned char *out_local = t.base[rank] + kFlagBytes + out_off;
+  if (!two_shot) {
+    for (size_t i = tid; i < npk; i += nthreads) {
+      Acc16<T> acc;
+      acc.zero();
+      for (int p = 0; p < world; ++p) acc.add(ld_peer16(t.base[p] + kFlagBytes + in_off + i * 16));
+      *reinterpret_cast<uint4 *>(out_local + i * 16) = acc.pack();
+    }
+  } else {
+    size_t const per = (npk + world - 1) / world;
+    size_t const lo = size_t(rank) * per, hi = min(npk, lo + per);
+    // 4 packets per thread and trip: enough loads in flight to cover the switch latency
+    for (size_t i0 = lo + tid * 4; i0 < hi; i0 += nthreads * 4) {
+      Acc16<T> acc[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) acc[u].zero();
+      for (int p = 0; p < world; ++p) {
+        uint4 raw[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+          raw[u] = (i0 + u < hi) ? ld_peer16(t.base[p] + kFlagBytes + in_off + (i0 + u) * 16)
+                                 : make_uint4(0, 0, 0, 0);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) acc[u].add(raw[u]);
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (i0 + u < hi) *reinterpret_cast<uint4 *>(out_local + (i0 + u) * 16) = acc[u].pack();
+    }
+    // ---- middle: my chunk is reduced and visible before any peer gathers it
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence_system();
+      unsigned arrived = atomicAdd(&mine->blocks_mid, 1u) + 1;
+      if (arrived == gridDim.x) {
+        mine->blocks_mid = 0;
+        __threadfence_system();
+        st_release_sys(&mine->flags[1][rank], epoch);  // own slot, for the local waiters below
+      }
+    }
+    // the block that completed the count tells the peers; everybody waits on local flags
+    if (threadIdx.x == 0) {
+      long long const t0 = clock64();
+      while (ld_acquire_sys(&mine->flags[1][rank]) < epoch) {
+        if (clock64() - t0 > kSpinLimit) { mine->timed_out = 1; break; }
+      }
+    }
+    __syncthreads();
+    if (blockIdx.x == 0) signal_peers(t, rank, world, 1, epoch);
+    wait_peers(mine, world, 1, epoch);
+    // ---- gather the other ranks' reduced chunks
+    for (int q = 1; q < world; ++q) {
+      int const p = (rank + q) % world;  // spread the ranks over different peers at any moment
+      size_t const plo = size_t(p) * per, phi = min(npk, plo + per);
+      unsigned char const *src = t.base[p] + kFlagBytes + out_off;
+      for (size_t i0 = plo + tid * 4; i0 < phi; i0 += nthreads * 4) {
+        uint4 raw[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+          raw[u] = (i0 + u < phi) ? ld_peer16(src + (i0 + u) * 16) : make_uint4(0, 0, 0, 0);
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+          if (i0 + u < phi) *reinterpret_cast<uint4 *>(out_local + (i0 + u) * 16) = raw[u];
+      }
+    }
+  }
+
+  // ---- exit: nobody may overwrite what a peer is still reading; the last block of this rank
+  // signals "done reading", bumps the epoch, and every block leaves only when all peers are done
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence_system();
+    unsigned arrived = atomicAdd(&mine->blocks_done, 1u) + 1;
+    if (arrived == gridDim.x) {
+      mine->blocks_done = 0;
+      for (int p = 0; p < world; ++p)
+        st_release_sys(&reinterpret_cast<Control *>(t.base[p])->flags[2][rank], epoch);
+      long long const t0 = clock64();
+      for (int p = 0; p < world; ++p)
+        while (ld_acquire_sys(&mine->flags[2][p]) < epoch) {
+          if (clock64() - t0 > kSpinLimit) { mine->timed_out = 1; break; }
+        }
+      __threadfence_system();
+      mine->epoch = epoch;  // the next launch on this stream starts after this kernel has ended
+    }
+  }
+}
+
+
+}  // namespace
+}  // namespace ffk
+
+using namespace ffk;
+
+extern "C" {
+
+int ffk_p2p_create(void **group_out, int rank, int world, size_t data_bytes,
+                   unsigned char *handle_out) {
+  FFK_REQUIRE(group_out && handle_out, "p2p: null argument");
+  FFK_REQUIRE(world >= 1 && world <= kMaxRanks && rank >= 0 && rank < world,
+              "p2p: rank %d of %d (at most %d ranks)", rank, world, kMaxRanks);
+  FFK_REQUIRE(data_bytes % 16 == 0, "p2p: region size must be a multiple of 16 bytes");
+  Group *g = new Group();
+  g->rank = rank;
+  g->world = world;
+  g->data_bytes = data_bytes;
+  FFK_CUDA(cudaGetDevice(&g->device));
+  FFK_CUDA(cudaMalloc(reinterpret_cast<void **>(&g->local), kFlagBytes + data_bytes));
+  FFK_CUDA(cudaMemset(g->local, 0, kFlagBytes));
+  cudaIpcMemHandle_t h;
+  FFK_CUDA(cudaIpcGetMemHandle(&h, g->local));
+  static_assert(sizeof(h) == FFK_P2P_HANDLE_BYTES, "IPC handle size");
+  std::memcpy(handle_out, &h, sizeof(h));
+  g->table.base[rank] = g->local;
+  *group_out = g;
+  return FFK_OK;
+}
+
+int ffk_p2p_connect(void *group, unsigned char const *handles_all) {
+  Group *g = reinterpret_cast<Group *>(group);
+  FFK_REQUIRE(g && handles_all, "p2p: null argument");
+  FFK_REQUIRE(!g->connected, "p2p: group already connected");
+  for (int p = 0; p < g->world; ++p) {
+    if (p == g->rank) continue;
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, handles_all + size_t(p) * FFK_P2P_HANDLE_BYTES, sizeof(h));
+    FFK_CUDA(cudaIpcOpenMemHandle(&g->peer_mapped[p], h, cudaIpcMemLazyEnablePeerAccess));
+    g->table.base[p] = reinterpret_cast<unsigned char *>(g->peer_mapped[p]);
+  }
+  g->connected = true;
+  return FFK_OK;
+}
+
+int ffk_p2p_local_buffer(void *group, void **data_out, size_t *bytes_out) {
+  Group *g = reinterpret_cast<Group *>(group);
+  FFK_REQUIRE(g && data_out, "p2p: null argument");
+  *data_out = g->local + kFlagBytes;
+  if (bytes_out) *bytes_out = g->data_bytes;
+  return FFK_OK;
+}
+
+int ffk_p2p_all_reduce_sum(void *stream, void *group, size_t in_offset, size_t out_offset,
+                           size_t count, int dtype) {
+  Group *g = reinterpret_cast<Group *>(group);
+  FFK_REQUIRE(g, "p2p: null group");
+  FFK_REQUIRE(g->connected || g->world == 1, "p2p: ffk_p2p_connect has not been called");
+  size_t es = dtype_size(dtype);
+  FFK_REQUIRE(dtype == FFK_FLOAT || dtype == FFK_HALF || dtype == FFK_BFLOAT16,
+              "p2p all-reduce: dtype %d not supported (FLOAT, HALF, BFLOAT16)", dtype);
+  size_t bytes = count * es;
+  if (count == 0) return FFK_OK;
+  FFK_REQUIRE(bytes % 16 == 0 && in_offset % 16 == 0 && out_offset % 16 == 0,
+              "p2p all-reduce: offsets and size must be multiples of 16 bytes");
+  FFK_REQUIRE(in_offset + bytes <= g->data_bytes && out_offset + bytes <= g->data_bytes,
+              "p2p all-reduce: range exceeds the region");
+  FFK_REQUIRE(in_offset + bytes <= out_offset || out_offset + bytes <= in_offset,
+              "p2p all-reduce: input and output ranges overlap");
+  size_t npk = bytes / 16;
+  int two_shot = bytes > kOneShotLimit && g->world > 1;
+  // few, fat blocks: the kernel shares the GPU with whatever the step is computing meanwhile
+  unsigned blocks = two_shot ? 48u : unsigned(std::min<size_t>(16, (npk + 511) / 512));
+  cudaStream_t s = as_stream(stream);
+  switch (dtype) {
+    case FFK_FLOAT:
+      p2p_all_reduce_kernel<float><<<blocks, 512, 0, s>>>(g->table, g->rank, g->world, in_offset, out_offset, npk, two_shot);
+      break;
+    case FFK_HALF:
+      p2p_all_reduce_kernel<__half><<<blocks, 512, 0, s>>>(g->table, g->rank, g->world, in_offset, out_offset, npk, two_shot);
+      break;
+    default:
+      p2p_all_reduce_kernel<__nv_bfloat16><<<blocks, 512, 0, s>>>(g->table, g->rank, g->world, in_offset, out_offset, npk, two_shot);
+      break;
+  }
+  FFK_LAUNCH_CHECK();
+  return FFK_OK;
+}
+
+int ffk_p2p_status(void *group) {
+  Group *g = reinterpret_cast<Group *>(group);
+  FFK_REQUIRE(g, "p2p: null group");
+  Control c;
+  FFK_CUDA(cudaMemcpy(&c, g->local, sizeof(c), cudaMemcpyDeviceToHost));
+  if (c.timed_out) {
+    set_error("p2p: a wait for a peer rank expired (a rank did not reach the collective)");
+    return FFK_ERR_CUDA;
+  }
+  return FFK_OK;
+}
+
+int ffk_p2p_destroy(void *group) {
+  Group *g = reinterpret_cast<Group *>(group);
+  if (!g) return FFK_OK;
+  for (int p = 0; p < g->world; ++p)
+    if (g->peer_mapped[p]) cudaIpcCloseMemHandle(g->peer_mapped[p]);
+  if (g->local) cudaFree(g->local);
+  delete g;
+  return FFK_OK;
+}
+
+}  // extern "C"

@@ -133,3 +133,64 @@ class ParallelOps:
         SUM over ranks, no division; one collective per flat bucket."""
         for b in flat_buffers:
             dist.all_reduce(b, op=dist.ReduceOp.SUM, group=self.group)
+
+
+class _DeviceBytes:
+    """Raw device memory presented through __cuda_array_interface__ (so torch can view it)."""
+
+    def __init__(self, ptr: int, nbytes: int, owner):
+        self.owner = owner
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False),
+                                         "version": 3}
+
+
+class PeerMemoryGroup:
+    """Gradient sums over NVLink peer memory (ffk_p2p_* in include/ffk_parallel.h): every rank of
+    one node maps the other ranks' regions through CUDA IPC and one kernel per collective reads
+    them directly. Tensors that take part are views into the region (`tensor`). The handle
+    exchange rides on torch.distributed (any backend); the data never touches NCCL."""
+
+    def __init__(self, nbytes: int, group: Optional[dist.ProcessGroup] = None):
+        import ctypes
+
+        from . import kernels as K
+
+        self.K, self.ctypes = K, ctypes
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        nbytes = (int(nbytes) + 255) // 256 * 256
+        self.handle = ctypes.c_void_p()
+        mine = (ctypes.c_ubyte * 64)()
+        K._call("ffk_p2p_create", ctypes.byref(self.handle), self.rank, self.world, nbytes, mine)
+        if self.world > 1:
+            all_handles: List[Optional[bytes]] = [None] * self.world
+            dist.all_gather_object(all_handles, bytes(mine), group=group)
+            blob = (ctypes.c_ubyte * (64 * self.world)).from_buffer_copy(b"".join(all_handles))
+            K._call("ffk_p2p_connect", self.handle, blob)
+        base, size = ctypes.c_void_p(), ctypes.c_size_t()
+        K._call("ffk_p2p_local_buffer", self.handle, ctypes.byref(base), ctypes.byref(size))
+        self.nbytes = size.value
+        self.bytes = torch.as_tensor(_DeviceBytes(base.value, self.nbytes, self), device="cuda")
+        if self.world > 1:
+            dist.barrier(group=group)  # nobody starts a collective before every rank has mapped its peers
+
+    def tensor(self, offset_bytes: int, shape, dtype) -> torch.Tensor:
+        n = 1
+        for s in shape:
+            n *= s
+        nb = n * torch.empty(0, dtype=dtype).element_size()
+        assert offset_bytes % 16 == 0 and offset_bytes + nb <= self.nbytes
+        return self.bytes[offset_bytes:offset_bytes + nb].view(dtype).view(tuple(shape))
+
+    def all_reduce_sum(self, in_offset: int, out_offset: int, count: int, dtype, stream=None) -> None:
+        K = self.K
+        K._call("ffk_p2p_all_reduce_sum", K._stream(stream), self.handle, in_offset, out_offset, count,
+                K._DT[dtype])
+
+    def check(self) -> None:
+        self.K._call("ffk_p2p_status", self.handle)
+
+    def close(self) -> None:
+        if self.handle:
+            self.K._call("ffk_p2p_destroy", self.handle)
+            self.handle = None

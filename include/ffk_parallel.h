@@ -43,6 +43,30 @@ int ffk_adam_nccl_update(void *stream, void *comm, float alpha_t, float beta1, f
                          float *adam_m, float *adam_v, void *weight, int dtype,
                          float *master_weight);
 
+/* ---- Sum over ranks through NVLink peer memory (no counterpart in the reference, which only
+ * has the NCCL call above). One process per GPU on one node. Each rank creates a region of
+ * `data_bytes` (device memory, cudaMalloc) and gets a 64-byte handle; the handles of all ranks,
+ * concatenated in rank order and shipped by any means, connect the group (cudaIpcOpenMemHandle).
+ * Tensors that take part in the collective live inside the region (ffk_p2p_local_buffer). */
+#define FFK_P2P_HANDLE_BYTES 64
+int ffk_p2p_create(void **group_out, int rank, int world, size_t data_bytes,
+                   unsigned char *handle_out /* FFK_P2P_HANDLE_BYTES */);
+int ffk_p2p_connect(void *group, unsigned char const *handles_all /* world * FFK_P2P_HANDLE_BYTES */);
+int ffk_p2p_local_buffer(void *group, void **data_out, size_t *bytes_out);
+
+/* out[i] = sum over ranks of in[i] for `count` elements (FLOAT, HALF, BFLOAT16; fp32
+ * accumulation in rank order, so every rank ends with bit-identical results). `in_offset` and
+ * `out_offset` are byte offsets into the region, the same on every rank; the two ranges must not
+ * overlap; offsets and size are multiples of 16 bytes. Up to 512 KB every rank reads all peers
+ * (one shot); above, rank r reduces chunk r and the chunks are gathered (two shots). Every rank
+ * must issue the group's collectives in the same order. The input may be overwritten and the
+ * output read as soon as the kernel has finished on the caller's stream. Waits for peers are
+ * bounded (~2 s): a rank that never arrives shows up in ffk_p2p_status, not as a hung GPU. */
+int ffk_p2p_all_reduce_sum(void *stream, void *group, size_t in_offset, size_t out_offset,
+                           size_t count, int dtype);
+int ffk_p2p_status(void *group);
+int ffk_p2p_destroy(void *group);
+
 #ifdef __cplusplus
 }
 #endif
