@@ -211,18 +211,53 @@ def run_gpu(args):
     lib = ffk_import.load().lib()
 
     pops = None
+    peer = None          # gradient sums over NVLink peer memory (default for N > 1)
+    grad_sync = "none"
+    db_result = wl.db
     if world > 1:
-        pops = importlib.import_module("flexflow_train_b200.parallel_ops").ParallelOps()
+        P = importlib.import_module("flexflow_train_b200.parallel_ops")
+        pops = P.ParallelOps()
+        if os.environ.get("FFK_BENCH_GRAD_SYNC", "peer") == "peer":
+            # both gradient buckets and their sums live in one IPC-mapped region per rank
+            b16 = (wl.flat16.numel() * 2 + 255) // 256 * 256
+            b32 = (wl.flat32.numel() * 4 + 255) // 256 * 256
+            peer = P.PeerMemoryGroup(2 * b16 + 2 * b32)
+            off = {"g16": 0, "s16": b16, "g32": 2 * b16, "s32": 2 * b16 + b32}
+            wl.flat16 = peer.tensor(off["g16"], (wl.flat16.numel(),), torch.bfloat16).zero_()
+            wl.dw = wl.flat16[: N * KDIM].view(N, KDIM)
+            wl.db = wl.flat16[N * KDIM:]
+            wl.flat32 = peer.tensor(off["g32"], (wl.flat32.numel(),), torch.float32).zero_()
+            wl.dgamma, wl.dbeta = wl.flat32[:COLS], wl.flat32[COLS:]
+            db_result = peer.tensor(off["s16"], (N * KDIM + N,), torch.bfloat16)[N * KDIM:]
+            grad_sync = ("peer-memory all-reduce (ffk_p2p_all_reduce_sum, sum over ranks, no division): "
+                         "dW|db bf16 32 MiB two-shot on a side stream under the rest of the step, "
+                         "dgamma|dbeta fp32 one-shot")
+        else:
+            grad_sync = ("NCCL all-reduce (sum) of two flat gradient buckets per step: dW|db bf16 32 MiB "
+                         "(async), dgamma|dbeta fp32")
+    side = torch.cuda.Stream(device=device) if peer is not None else None
+    lin_done, side_done = torch.cuda.Event(), torch.cuda.Event()
 
     pending = []
 
     def start_weight_sync():
         # Replicate-backward / *_nccl_update gradient sync (SUM over ranks, no division) of the
-        # 32 MiB dW|db bucket, asynchronous on NCCL's stream
-        pending.append(dist.all_reduce(wl.flat16, op=dist.ReduceOp.SUM, async_op=True))
+        # 32 MiB dW|db bucket, under the memory-bound rest of the step
+        if peer is not None:
+            lin_done.record()
+            side.wait_event(lin_done)
+            peer.all_reduce_sum(off["g16"], off["s16"], wl.flat16.numel(), torch.bfloat16, stream=side)
+            side_done.record(side)
+        else:
+            pending.append(dist.all_reduce(wl.flat16, op=dist.ReduceOp.SUM, async_op=True))
 
     def sync_grads():
-        if pops is not None:
+        if peer is not None:
+            # same order of collectives on every rank: the small bucket follows the large one
+            side.wait_stream(torch.cuda.current_stream())
+            peer.all_reduce_sum(off["g32"], off["s32"], wl.flat32.numel(), torch.float32, stream=side)
+            torch.cuda.current_stream().wait_stream(side)
+        elif pops is not None:
             pops.allreduce_gradients([wl.flat32])
             for w in pending:
                 w.wait()
@@ -306,7 +341,7 @@ def run_gpu(args):
             wl.x, wl.idx = xbuf[b], ibuf[b]
             full_step()
             consumed[b].record(main)
-            hres[b].copy_(wl.db, non_blocking=True)
+            hres[b].copy_(db_result, non_blocking=True)
             if trace is not None:
                 ev = torch.cuda.Event(enable_timing=True)
                 ev.record(main)
@@ -336,8 +371,13 @@ def run_gpu(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms_total, ms_e2e = t.tolist()
 
+    if peer is not None:
+        peer.check()  # raises if any bounded wait for a peer rank expired
     if rank != 0:
         if world > 1:
+            dist.barrier()
+            if peer is not None:
+                peer.close()
             dist.destroy_process_group()
         return
 
@@ -374,7 +414,7 @@ def run_gpu(args):
             "samples_per_step": SAMPLES_PER_STEP,
             "l2": "inputs larger than L2 (step touches >2 GB; L2 is 126 MB), no explicit flush",
             "parallelism": f"dp{n_gpus}" if n_gpus > 1 else "single",
-            "grad_sync": "NCCL all-reduce (sum) of two flat gradient buckets per step: dW|db bf16 32 MiB, dgamma|dbeta fp32" if n_gpus > 1 else "none",
+            "grad_sync": grad_sync,
         },
         "roofline": {
             "kernel": "gemm_tc_pair_kernel (tcgen05 cta_group::2, Linear forward 8192x4096x4096 bf16, fused bias+ReLU)",
@@ -397,7 +437,7 @@ def run_gpu(args):
             "warmup_steps": e2e_warmup,
             "host_staging": numa,
         },
-        "gpu_launches": args.steps * sum(LAUNCHES_PER_STEP.values()),
+        "gpu_launches": args.steps * (sum(LAUNCHES_PER_STEP.values()) + (2 if peer is not None else 0)),
         "abi_calls_timed": abi_calls,
         "clocks": clock_info,
     }
@@ -405,6 +445,9 @@ def run_gpu(args):
         out["cpu_baseline"] = cpu_baseline(threads=os.cpu_count() or 1, budget_s=20.0, kind_note="port")
     print(json.dumps(out), flush=True)
     if world > 1:
+        dist.barrier()
+        if peer is not None:
+            peer.close()
         dist.destroy_process_group()
 
 

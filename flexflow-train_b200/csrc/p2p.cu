@@ -11,6 +11,7 @@
 // arrives turns into FFK_ERR_CUDA on the next status query instead of a hung GPU).
 #include "common.cuh"
 
+#include <cstdlib>
 #include <cstring>
 
 namespace ffk {
@@ -53,9 +54,11 @@ __device__ __forceinline__ unsigned ld_acquire_sys(unsigned const *p) {
   return v;
 }
 __device__ __forceinline__ uint4 ld_peer16(void const *p) {
-  // peer memory must not be served from a stale L1 line of an earlier launch
+  // peer memory must not be served from a stale L1 line of an earlier launch: .cg skips L1
+  // (peer lines are never held in the local L2). Not .volatile — strong system-scope loads ran
+  // at 140 GB/s whatever the grid size.
   uint4 v;
-  asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];"
+  asm volatile("ld.global.cg.v4.u32 {%0,%1,%2,%3}, [%4];"
                : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
                : "l"(p)
                : "memory");
@@ -131,7 +134,9 @@ __global__ void __launch_bounds__(512)
     size_t const per = (npk + world - 1) / world;
     size_t const lo = size_t(rank) * per, hi = min(npk, lo + per);
     // 4 packets per thread and trip: enough loads in flight to cover the switch latency
-    for (size_t i0 = lo + tid * 4; i0 < hi; i0 += nthreads * 4) {
+    // (a warp's load covers 512 contiguous bytes; the 4 packets of a thread are a block apart)
+    size_t const bstride = size_t(blockDim.x);
+    for (size_t i0 = lo + size_t(blockIdx.x) * bstride * 4 + threadIdx.x; i0 < hi; i0 += nthreads * 4) {
       Acc16<T> acc[4];
 #pragma unroll
       for (int u = 0; u < 4; ++u) acc[u].zero();
@@ -139,14 +144,16 @@ __global__ void __launch_bounds__(512)
         uint4 raw[4];
 #pragma unroll
         for (int u = 0; u < 4; ++u)
-          raw[u] = (i0 + u < hi) ? ld_peer16(t.base[p] + kFlagBytes + in_off + (i0 + u) * 16)
-                                 : make_uint4(0, 0, 0, 0);
+          raw[u] = (i0 + u * bstride < hi)
+                       ? ld_peer16(t.base[p] + kFlagBytes + in_off + (i0 + u * bstride) * 16)
+                       : make_uint4(0, 0, 0, 0);
 #pragma unroll
         for (int u = 0; u < 4; ++u) acc[u].add(raw[u]);
       }
 #pragma unroll
       for (int u = 0; u < 4; ++u)
-        if (i0 + u < hi) *reinterpret_cast<uint4 *>(out_local + (i0 + u) * 16) = acc[u].pack();
+        if (i0 + u * bstride < hi)
+          *reinterpret_cast<uint4 *>(out_local + (i0 + u * bstride) * 16) = acc[u].pack();
     }
     // ---- middle: my chunk is reduced and visible before any peer gathers it
     __syncthreads();
@@ -174,14 +181,17 @@ __global__ void __launch_bounds__(512)
       int const p = (rank + q) % world;  // spread the ranks over different peers at any moment
       size_t const plo = size_t(p) * per, phi = min(npk, plo + per);
       unsigned char const *src = t.base[p] + kFlagBytes + out_off;
-      for (size_t i0 = plo + tid * 4; i0 < phi; i0 += nthreads * 4) {
+      for (size_t i0 = plo + size_t(blockIdx.x) * bstride * 4 + threadIdx.x; i0 < phi;
+           i0 += nthreads * 4) {
         uint4 raw[4];
 #pragma unroll
         for (int u = 0; u < 4; ++u)
-          raw[u] = (i0 + u < phi) ? ld_peer16(src + (i0 + u) * 16) : make_uint4(0, 0, 0, 0);
+          raw[u] = (i0 + u * bstride < phi) ? ld_peer16(src + (i0 + u * bstride) * 16)
+                                            : make_uint4(0, 0, 0, 0);
 #pragma unroll
         for (int u = 0; u < 4; ++u)
-          if (i0 + u < phi) *reinterpret_cast<uint4 *>(out_local + (i0 + u) * 16) = raw[u];
+          if (i0 + u * bstride < phi)
+            *reinterpret_cast<uint4 *>(out_local + (i0 + u * bstride) * 16) = raw[u];
       }
     }
   }
@@ -279,7 +289,12 @@ int ffk_p2p_all_reduce_sum(void *stream, void *group, size_t in_offset, size_t o
   size_t npk = bytes / 16;
   int two_shot = bytes > kOneShotLimit && g->world > 1;
   // few, fat blocks: the kernel shares the GPU with whatever the step is computing meanwhile
-  unsigned blocks = two_shot ? 48u : unsigned(std::min<size_t>(16, (npk + 511) / 512));
+  // measured inside bench.py at 2 GPUs (32 MiB bucket under the memory-bound tail of the step):
+  // 24 blocks 1.221 ms/step, 48 1.182, 96 1.156, 148 1.165, NCCL 1.168. FFK_P2P_BLOCKS overrides.
+  unsigned blocks = two_shot ? 96u : unsigned(std::min<size_t>(16, (npk + 511) / 512));
+  if (two_shot) {
+    if (char const *e = std::getenv("FFK_P2P_BLOCKS")) blocks = unsigned(std::max(1, atoi(e)));
+  }
   cudaStream_t s = as_stream(stream);
   switch (dtype) {
     case FFK_FLOAT:
