@@ -18,9 +18,13 @@ namespace ffk {
 namespace {
 
 constexpr int kMaxRanks = 16;
-constexpr size_t kFlagBytes = 4096;         // head of every region
-constexpr int kPhases = 3;                  // input ready / chunk reduced / done reading
-constexpr size_t kOneShotLimit = 512 << 10;  // bytes
+constexpr size_t kControlBytes = 4096;       // Control block at the head of every region
+constexpr int kPhases = 5;                  // input ready / chunk reduced / done reading / pushed (x2 parities)
+constexpr size_t kPushLimit = 64 << 10;     // bytes: below, every rank PUSHES its input to all peers
+constexpr size_t kOneShotLimit = 512 << 10;  // bytes: below, every rank reads all peers
+// receive slots of the push protocol: [parity][source rank][kPushLimit], after the Control block
+constexpr size_t kSlotBytes = 2 * size_t(kMaxRanks) * kPushLimit;
+constexpr size_t kFlagBytes = kControlBytes + kSlotBytes;  // data part starts here
 constexpr long long kSpinLimit = 4000000000LL;  // ~2 s of SM clocks
 
 struct Control {                 // lives at the head of each rank's region (device memory)
@@ -30,7 +34,7 @@ struct Control {                 // lives at the head of each rank's region (dev
   unsigned blocks_mid;
   unsigned timed_out;            // sticky: a bounded wait expired
 };
-static_assert(sizeof(Control) <= kFlagBytes, "control block must fit the reserved head");
+static_assert(sizeof(Control) <= kControlBytes, "control block must fit the reserved head");
 
 struct PeerTable {
   unsigned char *base[kMaxRanks];  // region base of every rank as mapped in THIS process
@@ -127,33 +131,49 @@ __global__ void __launch_bounds__(512)
     for (size_t i = tid; i < npk; i += nthreads) {
       Acc16<T> acc;
       acc.zero();
-      for (int p = 0; p < world; ++p) acc.add(ld_peer16(t.base[p] + kFlagBytes + in_off + i * 16));
+      for (int p0 = 0; p0 < world; p0 += 8) {  // all peers' loads go out before the first add
+        uint4 raw[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (p0 + j < world) raw[j] = ld_peer16(t.base[p0 + j] + kFlagBytes + in_off + i * 16);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (p0 + j < world) acc.add(raw[j]);
+      }
       *reinterpret_cast<uint4 *>(out_local + i * 16) = acc.pack();
     }
   } else {
     size_t const per = (npk + world - 1) / world;
     size_t const lo = size_t(rank) * per, hi = min(npk, lo + per);
-    // 4 packets per thread and trip: enough loads in flight to cover the switch latency
-    // (a warp's load covers 512 contiguous bytes; the 4 packets of a thread are a block apart)
+    // Two packets per thread and trip from EVERY peer are requested before the first is added
+    // (16 loads in flight per thread at 8 ranks); the additions then run in rank order.
+    // (A warp's load covers 512 contiguous bytes; a thread's packets are a block apart.)
     size_t const bstride = size_t(blockDim.x);
-    for (size_t i0 = lo + size_t(blockIdx.x) * bstride * 4 + threadIdx.x; i0 < hi; i0 += nthreads * 4) {
-      Acc16<T> acc[4];
+    for (size_t i0 = lo + size_t(blockIdx.x) * bstride * 2 + threadIdx.x; i0 < hi; i0 += nthreads * 2) {
+      Acc16<T> acc[2];
+      acc[0].zero();
+      acc[1].zero();
+      bool const ok1 = i0 + bstride < hi;
+      for (int p0 = 0; p0 < world; p0 += 8) {
+        uint4 raw[8][2];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) acc[u].zero();
-      for (int p = 0; p < world; ++p) {
-        uint4 raw[4];
+        for (int j = 0; j < 8; ++j) {
+          if (p0 + j < world) {
+            unsigned char const *src = t.base[p0 + j] + kFlagBytes + in_off;
+            raw[j][0] = ld_peer16(src + i0 * 16);
+            raw[j][1] = ok1 ? ld_peer16(src + (i0 + bstride) * 16) : make_uint4(0, 0, 0, 0);
+          }
+        }
 #pragma unroll
-        for (int u = 0; u < 4; ++u)
-          raw[u] = (i0 + u * bstride < hi)
-                       ? ld_peer16(t.base[p] + kFlagBytes + in_off + (i0 + u * bstride) * 16)
-                       : make_uint4(0, 0, 0, 0);
-#pragma unroll
-        for (int u = 0; u < 4; ++u) acc[u].add(raw[u]);
+        for (int j = 0; j < 8; ++j) {
+          if (p0 + j < world) {
+            acc[0].add(raw[j][0]);
+            acc[1].add(raw[j][1]);
+          }
+        }
       }
-#pragma unroll
-      for (int u = 0; u < 4; ++u)
-        if (i0 + u * bstride < hi)
-          *reinterpret_cast<uint4 *>(out_local + (i0 + u * bstride) * 16) = acc[u].pack();
+      *reinterpret_cast<uint4 *>(out_local + i0 * 16) = acc[0].pack();
+      if (ok1) *reinterpret_cast<uint4 *>(out_local + (i0 + bstride) * 16) = acc[1].pack();
     }
     // ---- middle: my chunk is reduced and visible before any peer gathers it
     __syncthreads();
@@ -181,15 +201,15 @@ __global__ void __launch_bounds__(512)
       int const p = (rank + q) % world;  // spread the ranks over different peers at any moment
       size_t const plo = size_t(p) * per, phi = min(npk, plo + per);
       unsigned char const *src = t.base[p] + kFlagBytes + out_off;
-      for (size_t i0 = plo + size_t(blockIdx.x) * bstride * 4 + threadIdx.x; i0 < phi;
-           i0 += nthreads * 4) {
-        uint4 raw[4];
+      for (size_t i0 = plo + size_t(blockIdx.x) * bstride * 8 + threadIdx.x; i0 < phi;
+           i0 += nthreads * 8) {
+        uint4 raw[8];
 #pragma unroll
-        for (int u = 0; u < 4; ++u)
+        for (int u = 0; u < 8; ++u)
           raw[u] = (i0 + u * bstride < phi) ? ld_peer16(src + (i0 + u * bstride) * 16)
                                             : make_uint4(0, 0, 0, 0);
 #pragma unroll
-        for (int u = 0; u < 4; ++u)
+        for (int u = 0; u < 8; ++u)
           if (i0 + u * bstride < phi)
             *reinterpret_cast<uint4 *>(out_local + (i0 + u * bstride) * 16) = raw[u];
       }
@@ -218,6 +238,52 @@ __global__ void __launch_bounds__(512)
 }
 
 
+// Small buffers: one-way protocol. Block b stores this rank's input into rank b's receive slot
+// (remote stores are fire-and-forget) and raises a flag behind it; then every block sums a
+// slice of the `world` slots that have arrived HERE, in rank order. One switch traversal instead
+// of the two round trips of the read-based kernel. Slots alternate with the epoch's parity: a
+// peer can only overwrite a slot two launches later, which it cannot start before this rank has
+// begun the launch in between, i.e. finished this one.
+template <typename T>
+__global__ void __launch_bounds__(512)
+    p2p_push_all_reduce_kernel(PeerTable t, int rank, int world, size_t in_off, size_t out_off,
+                               size_t npk) {
+  Control *mine = reinterpret_cast<Control *>(t.base[rank]);
+  unsigned const epoch = mine->epoch + 1;
+  int const parity = int(epoch & 1u);
+  unsigned char const *in_local = t.base[rank] + kFlagBytes + in_off;
+  for (int p = blockIdx.x; p < world; p += gridDim.x) {
+    unsigned char *slot = t.base[p] + kControlBytes + (size_t(parity) * kMaxRanks + rank) * kPushLimit;
+    for (size_t i = threadIdx.x; i < npk; i += blockDim.x)
+      *reinterpret_cast<uint4 *>(slot + i * 16) = *reinterpret_cast<uint4 const *>(in_local + i * 16);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence_system();
+      st_release_sys(&reinterpret_cast<Control *>(t.base[p])->flags[3 + parity][rank], epoch);
+    }
+  }
+  wait_peers(mine, world, 3 + parity, epoch);
+  unsigned char const *slots = t.base[rank] + kControlBytes + size_t(parity) * kMaxRanks * kPushLimit;
+  unsigned char *out_local = t.base[rank] + kFlagBytes + out_off;
+  size_t const tid = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  for (size_t i = tid; i < npk; i += size_t(gridDim.x) * blockDim.x) {
+    Acc16<T> acc;
+    acc.zero();
+    for (int p = 0; p < world; ++p) acc.add(ld_peer16(slots + size_t(p) * kPushLimit + i * 16));
+    *reinterpret_cast<uint4 *>(out_local + i * 16) = acc.pack();
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    unsigned arrived = atomicAdd(&mine->blocks_done, 1u) + 1;
+    if (arrived == gridDim.x) {
+      mine->blocks_done = 0;
+      __threadfence();
+      mine->epoch = epoch;
+    }
+  }
+}
+
 }  // namespace
 }  // namespace ffk
 
@@ -237,7 +303,7 @@ int ffk_p2p_create(void **group_out, int rank, int world, size_t data_bytes,
   g->data_bytes = data_bytes;
   FFK_CUDA(cudaGetDevice(&g->device));
   FFK_CUDA(cudaMalloc(reinterpret_cast<void **>(&g->local), kFlagBytes + data_bytes));
-  FFK_CUDA(cudaMemset(g->local, 0, kFlagBytes));
+  FFK_CUDA(cudaMemset(g->local, 0, kControlBytes));
   cudaIpcMemHandle_t h;
   FFK_CUDA(cudaIpcGetMemHandle(&h, g->local));
   static_assert(sizeof(h) == FFK_P2P_HANDLE_BYTES, "IPC handle size");
@@ -287,15 +353,30 @@ int ffk_p2p_all_reduce_sum(void *stream, void *group, size_t in_offset, size_t o
   FFK_REQUIRE(in_offset + bytes <= out_offset || out_offset + bytes <= in_offset,
               "p2p all-reduce: input and output ranges overlap");
   size_t npk = bytes / 16;
+  cudaStream_t s = as_stream(stream);
+  if (bytes <= kPushLimit) {
+    unsigned blocks = unsigned(g->world);
+    switch (dtype) {
+      case FFK_FLOAT:
+        p2p_push_all_reduce_kernel<float><<<blocks, 512, 0, s>>>(g->table, g->rank, g->world, in_offset, out_offset, npk);
+        break;
+      case FFK_HALF:
+        p2p_push_all_reduce_kernel<__half><<<blocks, 512, 0, s>>>(g->table, g->rank, g->world, in_offset, out_offset, npk);
+        break;
+      default:
+        p2p_push_all_reduce_kernel<__nv_bfloat16><<<blocks, 512, 0, s>>>(g->table, g->rank, g->world, in_offset, out_offset, npk);
+        break;
+    }
+    FFK_LAUNCH_CHECK();
+    return FFK_OK;
+  }
   int two_shot = bytes > kOneShotLimit && g->world > 1;
-  // few, fat blocks: the kernel shares the GPU with whatever the step is computing meanwhile
   // measured inside bench.py at 2 GPUs (32 MiB bucket under the memory-bound tail of the step):
   // 24 blocks 1.221 ms/step, 48 1.182, 96 1.156, 148 1.165, NCCL 1.168. FFK_P2P_BLOCKS overrides.
   unsigned blocks = two_shot ? 96u : unsigned(std::min<size_t>(16, (npk + 511) / 512));
   if (two_shot) {
     if (char const *e = std::getenv("FFK_P2P_BLOCKS")) blocks = unsigned(std::max(1, atoi(e)));
   }
-  cudaStream_t s = as_stream(stream);
   switch (dtype) {
     case FFK_FLOAT:
       p2p_all_reduce_kernel<float><<<blocks, 512, 0, s>>>(g->table, g->rank, g->world, in_offset, out_offset, npk, two_shot);

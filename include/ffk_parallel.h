@@ -57,8 +57,10 @@ int ffk_p2p_local_buffer(void *group, void **data_out, size_t *bytes_out);
 /* out[i] = sum over ranks of in[i] for `count` elements (FLOAT, HALF, BFLOAT16; fp32
  * accumulation in rank order, so every rank ends with bit-identical results). `in_offset` and
  * `out_offset` are byte offsets into the region, the same on every rank; the two ranges must not
- * overlap; offsets and size are multiples of 16 bytes. Up to 512 KB every rank reads all peers
- * (one shot); above, rank r reduces chunk r and the chunks are gathered (two shots). Every rank
+ * overlap; offsets and size are multiples of 16 bytes. Up to 64 KB every rank pushes its input
+ * into receive slots of all peers and sums what arrived (one switch traversal); up to 512 KB
+ * every rank reads all peers (one shot); above, rank r reduces chunk r and the chunks are
+ * gathered (two shots). Every rank
  * must issue the group's collectives in the same order. The input may be overwritten and the
  * output read as soon as the kernel has finished on the caller's stream. Waits for peers are
  * bounded (~2 s): a rank that never arrives shows up in ffk_p2p_status, not as a hung GPU. */

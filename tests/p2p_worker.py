@@ -23,7 +23,8 @@ def main():
     region = 2 * (big * 4) + (1 << 20)
     g = P.PeerMemoryGroup(region)
     ok = True
-    for dtype, count in ((torch.float32, 1000 * 4), (torch.bfloat16, 24 * 8), (torch.float32, big),
+    # push protocol (<= 64 KB), one-shot reads (<= 512 KB), two-shot above
+    for dtype, count in ((torch.float32, 1000 * 4), (torch.bfloat16, 24 * 8), (torch.float32, 30000 * 4), (torch.float32, big),
                          (torch.bfloat16, big), (torch.float16, 70000 * 8)):
         es = torch.empty(0, dtype=dtype).element_size()
         nb = count * es
