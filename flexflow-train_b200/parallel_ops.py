@@ -161,12 +161,31 @@ class PeerMemoryGroup:
         nbytes = (int(nbytes) + 255) // 256 * 256
         self.handle = ctypes.c_void_p()
         mine = (ctypes.c_ubyte * 64)()
-        K._call("ffk_p2p_create", ctypes.byref(self.handle), self.rank, self.world, nbytes, mine)
+        # Every rank runs every exchange below even when its own step failed, so that a failure
+        # anywhere becomes the same exception on all ranks instead of a rank waiting forever.
+        err = None
+        try:
+            K._call("ffk_p2p_create", ctypes.byref(self.handle), self.rank, self.world, nbytes, mine)
+        except Exception as e:  # noqa: BLE001 - reported to every rank below
+            err, self.handle = f"rank {self.rank}: {e}", None
         if self.world > 1:
-            all_handles: List[Optional[bytes]] = [None] * self.world
-            dist.all_gather_object(all_handles, bytes(mine), group=group)
-            blob = (ctypes.c_ubyte * (64 * self.world)).from_buffer_copy(b"".join(all_handles))
-            K._call("ffk_p2p_connect", self.handle, blob)
+            gathered: List[Optional[tuple]] = [None] * self.world
+            dist.all_gather_object(gathered, (err, bytes(mine)), group=group)
+            errors = [g[0] for g in gathered if g[0]]
+            if not errors:
+                try:
+                    blob = (ctypes.c_ubyte * (64 * self.world)).from_buffer_copy(b"".join(g[1] for g in gathered))
+                    K._call("ffk_p2p_connect", self.handle, blob)
+                except Exception as e:  # noqa: BLE001
+                    err = f"rank {self.rank}: {e}"
+            second: List[Optional[str]] = [None] * self.world
+            dist.all_gather_object(second, err, group=group)
+            errors += [e for e in second if e and e not in errors]
+            if errors:
+                self.close()
+                raise RuntimeError("peer-memory group could not be set up: " + "; ".join(errors))
+        elif err:
+            raise RuntimeError("peer-memory group could not be set up: " + err)
         base, size = ctypes.c_void_p(), ctypes.c_size_t()
         K._call("ffk_p2p_local_buffer", self.handle, ctypes.byref(base), ctypes.byref(size))
         self.nbytes = size.value
