@@ -1,8 +1,10 @@
 // Sum over ranks through NVLink peer memory: every rank maps the other ranks' gradient regions
 // (CUDA IPC) and the reduction is done by plain loads from peer memory inside one kernel — no
-// NCCL call, no staging copies. Small buffers take one shot (every rank reads all peers and sums
-// in rank order); large ones take two (rank r reduces chunk r from all peers, then the reduced
-// chunks are gathered), so that each byte crosses the switch twice per GPU instead of world times.
+// NCCL call, no staging copies. Up to 64 KB every rank pushes its input into receive slots of all
+// peers and sums what has arrived (one switch traversal); up to 512 KB every rank reads all
+// peers and sums in rank order (one shot); larger buffers take two shots (rank r reduces chunk r
+// from all peers, then the reduced chunks are gathered), so that each byte crosses the switch
+// twice per GPU instead of world times.
 //
 // Cross-rank ordering uses flags that live in each rank's region and only ever grow: a launch
 // takes its epoch from a counter in device memory that its last block increments, so the same
