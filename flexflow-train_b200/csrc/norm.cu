@@ -810,6 +810,133 @@ __global__ void __launch_bounds__(128)
   }
 }
 
+// The same ring for LONG rows (up to 16 columns per thread of a 256-thread CTA: N <= 4096): one
+// CTA per row at a time, two rows of dY, X and the old dX in flight per CTA as bulk copies, gamma
+// in shared memory, the running dgamma / dbeta sums of each thread's columns in registers
+// (the older kernel kept them in shared memory and had to rely on occupancy to hide its loads).
+template <typename T, int P>
+__global__ void __launch_bounds__(256, 2)
+    layer_norm_bwd_cta_ring_kernel(T const *__restrict__ dy, T const *__restrict__ x,
+                                   T *__restrict__ dx, T const *__restrict__ gamma,
+                                   float const *__restrict__ mean, float const *__restrict__ rstd,
+                                   float *__restrict__ part, long long rows, int nvec) {
+  constexpr int VN = Vec16<T>::N, STAGES = 2;
+  extern __shared__ __align__(128) uint8_t ring_smem[];
+  __shared__ float red[64];
+  __shared__ __align__(8) uint64_t bars[STAGES];
+  long long const N = (long long)nvec * VN;
+  uint32_t const row_bytes = uint32_t(N * sizeof(T));
+  int const tensors = dx ? 3 : 2;
+  T *sgamma = reinterpret_cast<T *>(ring_smem + size_t(STAGES) * tensors * row_bytes);
+  if (threadIdx.x == 0) {
+    for (int s2 = 0; s2 < STAGES; ++s2) ptx::mbar_init(&bars[s2], 1);
+    ptx::fence_mbar_init();
+  }
+  for (int i = threadIdx.x; i < nvec; i += 256) {
+    Vec16<T> g;
+#pragma unroll
+    for (int j = 0; j < VN; ++j) g.v[j] = from_f32<T>(1.f);
+    if (gamma) g = ld_vec(gamma + i * VN);
+    *reinterpret_cast<Vec16<T> *>(sgamma + i * VN) = g;
+  }
+  __syncthreads();
+  auto issue = [&](long long r, int st) {  // thread 0 only
+    uint8_t *dst = ring_smem + size_t(st) * tensors * row_bytes;
+    ptx::mbar_arrive_expect_tx(&bars[st], tensors * row_bytes);
+    ptx::bulk_load(dst, dy + r * N, row_bytes, &bars[st]);
+    ptx::bulk_load(dst + row_bytes, x + r * N, row_bytes, &bars[st]);
+    if (dx) ptx::bulk_load(dst + 2 * row_bytes, dx + r * N, row_bytes, &bars[st]);
+  };
+  if (threadIdx.x == 0) {
+    for (int s2 = 0; s2 < STAGES; ++s2) {
+      long long r = blockIdx.x + (long long)s2 * gridDim.x;
+      if (r < rows) issue(r, s2);
+    }
+  }
+  float const invn = 1.f / float(N);
+  float pg[P][VN], pb[P][VN];
+#pragma unroll
+  for (int p = 0; p < P; ++p)
+#pragma unroll
+    for (int j = 0; j < VN; ++j) {
+      pg[p][j] = 0.f;
+      pb[p][j] = 0.f;
+    }
+  int st = 0;
+  uint32_t phase = 0;
+  for (long long r = blockIdx.x; r < rows; r += gridDim.x) {
+    ptx::mbar_wait(&bars[st], phase);
+    uint8_t const *src = ring_smem + size_t(st) * tensors * row_bytes;
+    Vec16<T> a[P], b[P], o[P];
+    float ds = 0.f, db = 0.f;
+#pragma unroll
+    for (int p = 0; p < P; ++p) {
+      int i = threadIdx.x + p * 256;
+      if (i < nvec) {
+        a[p] = *reinterpret_cast<Vec16<T> const *>(src + size_t(i) * 16);
+        b[p] = *reinterpret_cast<Vec16<T> const *>(src + row_bytes + size_t(i) * 16);
+        if (dx) o[p] = *reinterpret_cast<Vec16<T> const *>(src + 2 * row_bytes + size_t(i) * 16);
+        Vec16<T> g = *reinterpret_cast<Vec16<T> const *>(sgamma + i * VN);
+#pragma unroll
+        for (int j = 0; j < VN; ++j) {
+          float const dg = to_f32(a[p].v[j]) * to_f32(g.v[j]);
+          ds += dg * to_f32(b[p].v[j]);
+          db += dg;
+        }
+      }
+    }
+    block_sum2(ds, db, red);  // its barriers also mean: every thread has the row in registers
+    if (threadIdx.x == 0) {
+      long long rn = r + (long long)STAGES * gridDim.x;
+      if (rn < rows) {
+        ptx::fence_proxy_async();
+        issue(rn, st);
+      }
+    }
+    float const mu = mean[r], rs = rstd[r];
+    float const c1 = (db * mu - ds) * rs * rs * rs * invn;
+    float const c2 = -(c1 * mu + db * rs * invn);
+    T *dxr = dx ? dx + r * N : nullptr;
+#pragma unroll
+    for (int p = 0; p < P; ++p) {
+      int i = threadIdx.x + p * 256;
+      if (i < nvec) {
+        Vec16<T> g = *reinterpret_cast<Vec16<T> const *>(sgamma + i * VN);
+#pragma unroll
+        for (int j = 0; j < VN; ++j) {
+          float const d = to_f32(a[p].v[j]), xx = to_f32(b[p].v[j]);
+          if (dx)
+            o[p].v[j] = from_f32<T>(to_f32(o[p].v[j]) + rs * d * to_f32(g.v[j]) + c1 * xx + c2);
+          pg[p][j] += d * (xx - mu) * rs;
+          pb[p][j] += d;
+        }
+        if (dx) st_vec(dxr + i * VN, o[p]);
+      }
+    }
+    if (++st == STAGES) {
+      st = 0;
+      phase ^= 1;
+    }
+  }
+  if (part) {
+    float *pgr = part + (size_t(blockIdx.x) * 2 + 0) * N;
+    float *pbr = part + (size_t(blockIdx.x) * 2 + 1) * N;
+#pragma unroll
+    for (int p = 0; p < P; ++p) {
+      int i = threadIdx.x + p * 256;
+      if (i < nvec) {
+#pragma unroll
+        for (int q = 0; q < VN / 4; ++q) {
+          *reinterpret_cast<float4 *>(pgr + i * VN + q * 4) =
+              make_float4(pg[p][q * 4], pg[p][q * 4 + 1], pg[p][q * 4 + 2], pg[p][q * 4 + 3]);
+          *reinterpret_cast<float4 *>(pbr + i * VN + q * 4) =
+              make_float4(pb[p][q * 4], pb[p][q * 4 + 1], pb[p][q * 4 + 2], pb[p][q * 4 + 3]);
+        }
+      }
+    }
+  }
+}
+
 // Fused backward for short rows, one warp per row. Each lane owns fixed columns, keeps gamma
 // and its running dgamma / dbeta sums in registers over all the rows its warp visits; the 8
 // warps of a CTA are combined through shared memory into this CTA's partial slab.
@@ -1193,6 +1320,43 @@ int ffk_layer_norm_backward(void *stream, void const *output_grad, void const *i
       if (fused) {
         layer_norm_param_reduce_kernel<T><<<unsigned((N + 31) / 32), 1024, 0, s>>>(
             reinterpret_cast<float const *>(workspace), int(warps), N,
+            reinterpret_cast<T *>(gamma_grad), reinterpret_cast<T *>(beta_grad),
+            accumulate_param_grads != 0);
+        FFK_LAUNCH_CHECK();
+      }
+    } else if (!no_ring && vec && pick_p(N / VN) != 0 && pick_p(N / VN) * VN <= 16 &&
+               N * sizeof(T) >= 4096 && (input_grad || fused)) {
+      // long rows: CTA-level ring (N <= 4096 at 16 columns per thread)
+      int nvec = int(N / VN), pp = pick_p(nvec);
+      size_t row_bytes = size_t(N) * sizeof(T);
+      int tensors = input_grad ? 3 : 2;
+      size_t smem = size_t(2) * tensors * row_bytes + row_bytes;
+      float *wpart = fused ? reinterpret_cast<float *>(workspace) : nullptr;
+      unsigned grid = 0;
+      auto launch = [&](auto kern) -> int {
+        FFK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        int per_sm = 0;
+        FFK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 256, smem));
+        grid = rows_grid(M, std::max(1, per_sm));
+        if (fused) grid = (unsigned)std::min<size_t>(grid, parts_fit);
+        kern<<<grid, 256, smem, s>>>(
+            reinterpret_cast<T const *>(output_grad), reinterpret_cast<T const *>(input),
+            reinterpret_cast<T *>(input_grad), reinterpret_cast<T const *>(gamma), mean, rstd, wpart, M, nvec);
+        return FFK_OK;
+      };
+      int rc = FFK_OK;
+      switch (pp) {
+        case 1: rc = launch(layer_norm_bwd_cta_ring_kernel<T, 1>); break;
+        case 2: rc = launch(layer_norm_bwd_cta_ring_kernel<T, 2>); break;
+        default:
+          if constexpr (sizeof(T) == 4) rc = launch(layer_norm_bwd_cta_ring_kernel<T, 4>);
+          break;
+      }
+      if (rc) return rc;
+      FFK_LAUNCH_CHECK();
+      if (fused) {
+        layer_norm_param_reduce_kernel<T><<<unsigned((N + 31) / 32), 1024, 0, s>>>(
+            reinterpret_cast<float const *>(workspace), int(grid), N,
             reinterpret_cast<T *>(gamma_grad), reinterpret_cast<T *>(beta_grad),
             accumulate_param_grads != 0);
         FFK_LAUNCH_CHECK();
