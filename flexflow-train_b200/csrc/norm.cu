@@ -673,6 +673,87 @@ __global__ void __launch_bounds__(kThreads, (PW <= 4 ? 3 : 1))
   }
 }
 
+// Forward for long rows through a bulk-copy ring: three rows in flight per CTA, the row is read
+// from shared memory twice (statistics, then normalisation), so nothing of it lives in registers
+// and four CTAs stay resident per SM at 16 KB rows.
+template <typename T>
+__global__ void __launch_bounds__(256)
+    layer_norm_fwd_cta_ring_kernel(T const *__restrict__ x, T *__restrict__ y,
+                                   T const *__restrict__ gamma, T const *__restrict__ beta,
+                                   float *__restrict__ mean, float *__restrict__ rstd,
+                                   long long rows, int nvec, float eps) {
+  constexpr int VN = Vec16<T>::N, STAGES = 3;
+  extern __shared__ __align__(128) uint8_t ring_smem[];
+  __shared__ float red[64];
+  __shared__ __align__(8) uint64_t bars[STAGES];
+  long long const N = (long long)nvec * VN;
+  uint32_t const row_bytes = uint32_t(N * sizeof(T));
+  if (threadIdx.x == 0) {
+    for (int s2 = 0; s2 < STAGES; ++s2) ptx::mbar_init(&bars[s2], 1);
+    ptx::fence_mbar_init();
+    for (int s2 = 0; s2 < STAGES; ++s2) {
+      long long r = blockIdx.x + (long long)s2 * gridDim.x;
+      if (r < rows) {
+        ptx::mbar_arrive_expect_tx(&bars[s2], row_bytes);
+        ptx::bulk_load(ring_smem + size_t(s2) * row_bytes, x + r * N, row_bytes, &bars[s2]);
+      }
+    }
+  }
+  __syncthreads();
+  float const invn = 1.f / float(N);
+  int st = 0;
+  uint32_t phase = 0;
+  for (long long r = blockIdx.x; r < rows; r += gridDim.x) {
+    ptx::mbar_wait(&bars[st], phase);
+    uint8_t const *src = ring_smem + size_t(st) * row_bytes;
+    float s1 = 0.f, s2 = 0.f;
+    for (int i = threadIdx.x; i < nvec; i += 256) {
+      Vec16<T> t = *reinterpret_cast<Vec16<T> const *>(src + size_t(i) * 16);
+#pragma unroll
+      for (int j = 0; j < VN; ++j) {
+        float const v = to_f32(t.v[j]);
+        s1 += v;
+        s2 += v * v;
+      }
+    }
+    block_sum2(s1, s2, red);
+    float const mu = s1 * invn;
+    float const var = fmaxf(s2 * invn - mu * mu, 0.f);
+    float const rs = rsqrtf(var + eps);
+    if (threadIdx.x == 0) {
+      mean[r] = mu;
+      rstd[r] = rs;
+    }
+    T *yr = y + r * N;
+    for (int i = threadIdx.x; i < nvec; i += 256) {
+      Vec16<T> t = *reinterpret_cast<Vec16<T> const *>(src + size_t(i) * 16), o, g, b;
+      if (gamma) g = ld_vec(gamma + i * VN);
+      if (beta) b = ld_vec(beta + i * VN);
+#pragma unroll
+      for (int j = 0; j < VN; ++j) {
+        float u = (to_f32(t.v[j]) - mu) * rs;
+        if (gamma) u *= to_f32(g.v[j]);
+        if (beta) u += to_f32(b.v[j]);
+        o.v[j] = from_f32<T>(u);
+      }
+      st_stream(yr + i * VN, o);
+    }
+    __syncthreads();  // the stage has been read for the last time
+    if (threadIdx.x == 0) {
+      long long rn = r + (long long)STAGES * gridDim.x;
+      if (rn < rows) {
+        ptx::fence_proxy_async();
+        ptx::mbar_arrive_expect_tx(&bars[st], row_bytes);
+        ptx::bulk_load(ring_smem + size_t(st) * row_bytes, x + rn * N, row_bytes, &bars[st]);
+      }
+    }
+    if (++st == STAGES) {
+      st = 0;
+      phase ^= 1;
+    }
+  }
+}
+
 // Backward for rows of up to 32 columns per lane (N <= 1024 for 16-bit, fp32 alike), one warp per
 // row, fed through shared memory: lane 0 of every warp keeps `STAGES` rows of dY, X and the old
 // dX in flight with 1-D bulk copies (cp.async.bulk, completion counted on an mbarrier per stage),
@@ -1236,6 +1317,17 @@ int ffk_layer_norm_forward(void *stream, void const *input, void *output, void c
             reinterpret_cast<T const *>(gamma), reinterpret_cast<T const *>(beta), mean, rstd, M,
             nvec, eps);
       });
+    } else if (vec && std::getenv("FFK_LN_NO_RING") == nullptr && N * sizeof(T) >= 8192 &&
+               N * sizeof(T) <= 32768) {
+      int nvec = int(N / VN);
+      size_t smem = size_t(3) * size_t(N) * sizeof(T);
+      auto kern = layer_norm_fwd_cta_ring_kernel<T>;
+      FFK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      int per_sm = 0;
+      FFK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 256, smem));
+      kern<<<rows_grid(M, std::max(1, per_sm)), 256, smem, s>>>(
+          reinterpret_cast<T const *>(input), reinterpret_cast<T *>(output),
+          reinterpret_cast<T const *>(gamma), reinterpret_cast<T const *>(beta), mean, rstd, M, nvec, eps);
     } else if (vec) {
       int nvec = int(N / VN), p = pick_p(nvec);
       FFK_DISPATCH_P(p, P, {
