@@ -1331,10 +1331,78 @@ int launch_split_bf16_registered(Problem const &p, Epilogue const &e, cudaStream
   return launch_split_bf16(p, e, stream, g_scratch.ptr, g_scratch.bytes);
 }
 
+namespace {
+
+// 16-bit operand whose base, row pitch or batch strides break TMA's 16-byte rule (a vocabulary of
+// 30522 columns, say): copy it once into registered scratch with the pitch rounded up to 8
+// elements so that the product still runs on the tensor cores; the copy costs two passes over the
+// operand, the CUDA-core fallback it replaces runs at 2 % of the tensor-core rate.
+__global__ void __launch_bounds__(256)
+    repack_rows_kernel(uint16_t const *__restrict__ src, uint16_t *__restrict__ dst, long long rows,
+                       long long cols, long long ld_src, long long ld_dst, long long batch_outer,
+                       long long batch2, long long stride_outer, long long stride_inner) {
+  long long const per = rows * ld_dst, total = per * batch_outer * batch2;
+  long long const step = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += step) {
+    long long const b = i / per, in = i - b * per;
+    long long const r = in / ld_dst, c = in - r * ld_dst;
+    long long const bo = b / batch2, bi = b - bo * batch2;
+    dst[i] = c < cols ? src[bo * stride_outer + bi * stride_inner + r * ld_src + c] : uint16_t(0);
+  }
+}
+
+bool operand_ok(void const *ptr, long long ld, long long bs, long long bs2, int batch, int batch2) {
+  if (!aligned16(ptr) || (ld * 2) % 16) return false;
+  if (batch > 1 && (bs * 2) % 16) return false;
+  if (batch2 > 1 && (bs2 * 2) % 16) return false;
+  return true;
+}
+
+// Returns FFK_OK and fills `q` when the operands that needed it were repacked into the scratch.
+int repack_for_tensor_cores(Problem const &p, Problem &q, cudaStream_t stream) {
+  int const b2 = p.batch2 > 1 ? p.batch2 : 1, bo = p.batch / b2;
+  if (p.batch % b2 != 0) return FFK_ERR_UNSUPPORTED;
+  char *cursor = static_cast<char *>(g_scratch.ptr);
+  size_t left = g_scratch.bytes;
+  q = p;
+  q.scratch_busy = true;
+  auto fix = [&](void const *&ptr, long long &ld, long long &bs, long long &bs2, long long rows,
+                 long long cols) -> int {
+    if (operand_ok(ptr, ld, bs, bs2, p.batch, b2)) return FFK_OK;
+    long long const ld_new = (cols + 7) / 8 * 8;
+    size_t const bytes = (size_t(rows) * ld_new * p.batch * 2 + 255) / 256 * 256;
+    if (bytes > left) return FFK_ERR_UNSUPPORTED;
+    unsigned grid = stream_grid(size_t(rows) * ld_new * p.batch, 256, 8);
+    repack_rows_kernel<<<grid, 256, 0, stream>>>(
+        static_cast<uint16_t const *>(ptr), reinterpret_cast<uint16_t *>(cursor), rows, cols, ld,
+        ld_new, bo, b2, bs, bs2);
+    ptr = cursor;
+    ld = ld_new;
+    bs2 = rows * ld_new;
+    bs = bs2 * b2;
+    cursor += bytes;
+    left -= bytes;
+    return FFK_OK;
+  };
+  int rc = fix(q.a, q.lda, q.a_batch, q.a_batch2, p.a_mn_major ? p.K : p.M, p.a_mn_major ? p.M : p.K);
+  if (rc) return rc;
+  rc = fix(q.b, q.ldb, q.b_batch, q.b_batch2, p.b_mn_major ? p.K : p.N, p.b_mn_major ? p.N : p.K);
+  if (rc) return rc;
+  if (cudaGetLastError() != cudaSuccess) return FFK_ERR_CUDA;
+  return FFK_OK;
+}
+
+}  // namespace
+
 int launch(Problem const &p, Epilogue const &e, cudaStream_t stream) {
   if (p.M <= 0 || p.N <= 0 || p.batch <= 0) return FFK_OK;
   bool sixteen = p.in_dtype == FFK_BFLOAT16 || p.in_dtype == FFK_HALF;
   if (sixteen && p.K > 0 && tc_eligible(p, e)) return launch_tc(p, e, stream);
+  if (sixteen && p.K >= 64 && g_scratch.ptr && !p.scratch_busy && aligned16(g_scratch.ptr) &&
+      double(p.M) * p.N * p.K * p.batch >= double(1 << 27)) {
+    Problem q;
+    if (repack_for_tensor_cores(p, q, stream) == FFK_OK && tc_eligible(q, e)) return launch_tc(q, e, stream);
+  }
   // large fp32 products: tensor cores through the bf16 split when scratch has been registered
   if (p.in_dtype == FFK_FLOAT && p.out_dtype == FFK_FLOAT && p.K >= 64 && g_scratch.ptr &&
       double(p.M) * p.N * p.K * p.batch >= double(1 << 27) && e.alpha == 1.f &&

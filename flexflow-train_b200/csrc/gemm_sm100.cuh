@@ -52,6 +52,9 @@ struct Problem {
   // [sample][seq][head][dim] tensor is batched over (sample, head).
   int batch2 = 1;
   long long a_batch2 = 0, b_batch2 = 0;
+  // set when the operands already live in the registered scratch (ffk_set_gemm_workspace), so
+  // that the launch does not repack anything into it
+  bool scratch_busy = false;
 };
 
 // Tensor-core path. Returns FFK_ERR_UNSUPPORTED (without launching) when the

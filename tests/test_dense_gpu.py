@@ -187,3 +187,17 @@ def test_cuda_core_gemm_cluster_split_k(K, a_mn, b_mn):
             outs.append(d)
         assert torch.equal(outs[0], outs[1])
         assert_close(outs[0], ref.cpu().numpy(), rtol=1e-5, what=f"split-k gemm {M}x{N}x{Kd}x{batch} {a_mn}{b_mn}")
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_unaligned_pitch_is_repacked_onto_the_tensor_cores(K, oracle, dtype):
+    """A 16-bit Linear whose out_dim is not a multiple of 8 (BERT's 30522-word vocabulary) breaks
+    TMA's 16-byte pitch rule for dY in both backward products. With scratch registered the operand
+    is repacked once and the products stay on the tensor cores; results must match the oracle like
+    any other 16-bit Linear, and the CUDA-core answer of the same call without scratch."""
+    K.set_gemm_workspace(96 << 20)
+    try:
+        _linear_case(K, oracle, dtype, 1024, 256, 1003, "gelu", True)
+        _linear_case(K, oracle, dtype, 520, 264, 250, "none", False, l2=1e-3)
+    finally:
+        K.set_gemm_workspace(None)
