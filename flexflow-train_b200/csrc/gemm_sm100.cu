@@ -226,6 +226,55 @@ __device__ __forceinline__ void epilogue_chunk_staged(uint32_t const (&acc)[32],
   __syncwarp();
 }
 
+// 16-bit outputs whose rows are NOT 16-byte aligned (a 30522-column vocabulary): same transposition,
+// but global memory is written element by element with the 32 lanes on 32 consecutive columns of
+// one row (64 contiguous bytes per instruction) instead of every lane walking its own row.
+// Plain epilogues only (alpha, bias, activation); ragged right edge and bottom handled.
+template <typename T>
+__device__ __forceinline__ void epilogue_chunk_staged_unaligned(uint32_t const (&acc)[32],
+                                                                Epilogue const &ep, uint8_t *stage,
+                                                                long long block_off, int rows_valid,
+                                                                int col0, int valid) {
+  int const lane = threadIdx.x & 31;
+  float v[32];
+#pragma unroll
+  for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(acc[i]) * ep.alpha;
+  if (ep.bias != nullptr) {
+    T const *bp = reinterpret_cast<T const *>(ep.bias) + col0;
+#pragma unroll
+    for (int i = 0; i < 32; ++i)
+      if (i < valid) v[i] += to_f32(bp[i]);
+  }
+  if (ep.act == ACT_RELU) {
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = fmaxf(v[i], 0.f);
+  } else if (ep.act != ACT_NONE) {
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = apply_act_fast(v[i], ep.act);
+  }
+  int const my_sw = (lane >> 1) & 3;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    Vec16<T> t;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) t.v[i] = from_f32<T>(v[j * 8 + i]);
+    *reinterpret_cast<uint4 *>(stage + lane * 64 + ((j ^ my_sw) << 4)) = *reinterpret_cast<uint4 *>(&t);
+  }
+  __syncwarp();
+  T *d = reinterpret_cast<T *>(ep.d) + block_off + col0 + lane;
+  int const piece = lane >> 3, within = lane & 7;
+  if (lane < valid) {
+#pragma unroll 8
+    for (int r = 0; r < 32; ++r) {
+      if (r < rows_valid) {
+        T const x = *reinterpret_cast<T const *>(stage + r * 64 + ((piece ^ ((r >> 1) & 3)) << 4) + within * 2);
+        d[static_cast<long long>(r) * ep.ldd] = x;
+      }
+    }
+  }
+  __syncwarp();
+}
+
 // One warp's share of a tile epilogue: NCHUNK chunks of 32 accumulator columns for the 32 rows
 // (TMEM lanes) of its quadrant. The TMEM load of chunk c+1 is in flight while chunk c is
 // converted and stored; `release` runs once the last load has landed (the accumulator buffer
@@ -238,6 +287,8 @@ __device__ __forceinline__ void epilogue_columns(uint32_t taddr, Epilogue const 
   bool const row_ok = lane < rows_valid;
   long long const row_off = block_off + static_cast<long long>(lane) * ep.ldd;
   bool const staged_ok = vec_ok && out_dtype != FFK_FLOAT && !ep.add_d_before_act;
+  bool const unaligned_ok = !vec_ok && out_dtype != FFK_FLOAT && !ep.add_d_before_act &&
+                            !ep.accumulate && ep.r == nullptr;
   uint32_t r[2][32];
   ptx::tmem_ld_32x32(taddr, r[0]);
 #pragma unroll
@@ -251,7 +302,12 @@ __device__ __forceinline__ void epilogue_columns(uint32_t taddr, Epilogue const 
     int const col0 = col_first + c * 32;
     int const valid = min(32, N - col0);
     if (valid <= 0 || rows_valid <= 0) continue;
-    if (staged_ok && valid == 32) {  // warp-uniform
+    if (unaligned_ok) {  // warp-uniform
+      if (out_dtype == FFK_BFLOAT16)
+        epilogue_chunk_staged_unaligned<__nv_bfloat16>(r[c & 1], ep, stage, block_off, rows_valid, col0, valid);
+      else
+        epilogue_chunk_staged_unaligned<__half>(r[c & 1], ep, stage, block_off, rows_valid, col0, valid);
+    } else if (staged_ok && valid == 32) {  // warp-uniform
       if (out_dtype == FFK_BFLOAT16)
         epilogue_chunk_staged<__nv_bfloat16>(r[c & 1], ep, stage, block_off, rows_valid, col0, row_ok);
       else
