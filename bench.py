@@ -484,22 +484,33 @@ def run_encoder(args):
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=device)
         pops = importlib.import_module("flexflow_train_b200.parallel_ops").ParallelOps()
-    B, S, D, H, FF, L = args.batch, 512, 1024, 16, 4096, args.layers
+    bert = args.workload == "bert"
+    B, S, L = args.batch, 512, args.layers
+    D, H, FF, V = (768, 12, 3072, 30522) if bert else (1024, 16, 4096, 0)
     hd = args.head_dim if args.head_dim > 0 else FF // H
-    model = T.build_transformer_encoder(L, D, H, S, B, FF, hd, dropout=0.1, dtype=torch.bfloat16, device=device)
-    opt = T.SGD(lr=1e-3, weight_decay=1e-4)
     g = torch.Generator(device=device).manual_seed(1234 + rank)
+    if bert:
+        # the vocabulary head's gradients go through repacked operands: that needs scratch
+        Kmod.set_gemm_workspace(int(B * S * ((V + 7) // 8 * 8) * 2 * 1.05))
+        model = T.build_bert(L, D, H, FF, S, B, V, dropout=0.1, dtype=torch.bfloat16, device=device)
+        labels = torch.randint(0, V, (B * S,), generator=g, device=device, dtype=torch.int32)
+    else:
+        model = T.build_transformer_encoder(L, D, H, S, B, FF, hd, dropout=0.1, dtype=torch.bfloat16, device=device)
+    opt = T.SGD(lr=1e-3, weight_decay=1e-4)
     hx = (torch.rand(B, S, D, generator=g, device=device) * 2 - 1).to(torch.bfloat16).cpu().pin_memory()
-    target = (torch.rand(B, S, D, generator=g, device=device) * 2 - 1).to(torch.bfloat16)
+    target = None if bert else (torch.rand(B, S, D, generator=g, device=device) * 2 - 1).to(torch.bfloat16)
     model.input.data.copy_(hx)
     lib = ffk_import.load().lib()
     perf = Kmod.PerfMetrics(device=device)
-    out32 = torch.empty(B * S, D, device=device)
-    tgt32 = target.float().view(B * S, D).contiguous()
+    out32 = None if bert else torch.empty(B * S, D, device=device)
+    tgt32 = None if bert else target.float().view(B * S, D).contiguous()
     hres = torch.empty(7, dtype=torch.int32).pin_memory()
 
     def step():
-        T.mse_step(model, target, opt, pops)
+        if bert:
+            T.sparse_cce_step(model, labels, opt, pops, global_batch=B * S * world)
+        else:
+            T.mse_step(model, target, opt, pops)
 
     def barrier():
         if world > 1:
@@ -527,9 +538,10 @@ def run_encoder(args):
     def e2e_step():
         model.input.data.copy_(hx, non_blocking=True)          # the batch arrives from the host
         step()
-        Kmod.Cast.forward_kernel(None, model.output.data.view(B * S, D), out32)
         Kmod._call("ffk_fill", Kmod._stream(None), perf.buf.data_ptr(), 7, 0.0, Kmod.INT32)
-        Kmod.update_metrics_label_kernel(None, Kmod.METRIC_MSE, out32, tgt32, B * S, D, perf)
+        if not bert:  # the metrics kernels take fp32 (reference signature); BERT reads back train_all only
+            Kmod.Cast.forward_kernel(None, model.output.data.view(B * S, D), out32)
+            Kmod.update_metrics_label_kernel(None, Kmod.METRIC_MSE, out32, tgt32, B * S, D, perf)
         hres.copy_(perf.buf, non_blocking=True)                # the step's metric goes back
         torch.cuda.current_stream().synchronize()
 
@@ -555,17 +567,21 @@ def run_encoder(args):
     params = sum(p.numel() for p in model.params)
     # fwd+bwd FLOPs per sample: 3 x (projections + scores + FFN), SURVEY §8d
     per_tok = 2 * (3 * D * H * hd + H * hd * D + 2 * S * H * hd + 2 * D * FF)
-    flops_per_sample = 3 * per_tok * S * L
+    flops_per_sample = 3 * per_tok * S * L + 3 * 2 * D * V * S
     tf_peak, _, peak_src = load_peaks()
     achieved = flops_per_sample * B / (ms_per_step * 1e-3) / 1e12
     out = {
-        "metric": "training samples/sec (transformer encoder, fwd+bwd+SGD)",
+        "metric": "training samples/sec (BERT-base graph of lib/models, fwd+bwd+SGD)" if bert else
+                  "training samples/sec (transformer encoder, fwd+bwd+SGD)",
         "value": B * world / (ms_per_step * 1e-3), "unit": "samples/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
         "data": "synthetic",
-        "config": {"workload": f"BASELINE configs[2]: transformer encoder {L} layers, d {D}, {H} heads, head dim {hd}, "
-                               f"dim_ff {FF}, seq {S}, batch {B} per GPU, MSE + SGD",
+        "config": {"workload": (f"BASELINE configs[3], data-parallel form: BERT-base graph, {L} layers, hidden {D}, "
+                                f"{H} heads, head dim {hd}, dim_ff {FF} GELU, vocabulary head {V} + softmax, seq {S}, "
+                                f"batch {B} per GPU, sparse CCE + SGD") if bert else
+                               (f"BASELINE configs[2]: transformer encoder {L} layers, d {D}, {H} heads, head dim {hd}, "
+                                f"dim_ff {FF}, seq {S}, batch {B} per GPU, MSE + SGD"),
                    "global_batch": B * world, "seq_len": S, "parameters": params,
                    "parallelism": f"dp{world}" if world > 1 else "single",
                    "l2": "activations of one layer exceed L2 (>= 0.5 GB)"},
@@ -752,7 +768,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--workload", default="microbench", choices=["microbench", "encoder", "mlp"])
+    ap.add_argument("--workload", default="microbench", choices=["microbench", "encoder", "bert", "mlp"])
     ap.add_argument("--layers", type=int, default=12)
     ap.add_argument("--batch", type=int, default=64)
     ap.add_argument("--head-dim", type=int, default=0, help="0 = the reference's dim_ff/heads (256)")
@@ -761,7 +777,7 @@ def main():
         args.warmup = 3  # timing rule: at least 3 warm-up steps
     if args.impl == "reference":
         run_reference(args)
-    elif args.workload == "encoder":
+    elif args.workload in ("encoder", "bert"):
         run_encoder(args)
     elif args.workload == "mlp":
         run_mlp(args)

@@ -1397,13 +1397,20 @@ __global__ void __launch_bounds__(256)
     repack_rows_kernel(uint16_t const *__restrict__ src, uint16_t *__restrict__ dst, long long rows,
                        long long cols, long long ld_src, long long ld_dst, long long batch_outer,
                        long long batch2, long long stride_outer, long long stride_inner) {
-  long long const per = rows * ld_dst, total = per * batch_outer * batch2;
-  long long const step = (long long)gridDim.x * blockDim.x;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += step) {
-    long long const b = i / per, in = i - b * per;
-    long long const r = in / ld_dst, c = in - r * ld_dst;
+  // one CTA per row at a time; a thread moves 8 columns: element loads (the source row is only
+  // 2-byte aligned), one 16-byte store (the padded pitch is a multiple of 8 elements)
+  long long const total_rows = rows * batch_outer * batch2;
+  for (long long row = blockIdx.x; row < total_rows; row += gridDim.x) {
+    long long const b = row / rows, r = row - b * rows;
     long long const bo = b / batch2, bi = b - bo * batch2;
-    dst[i] = c < cols ? src[bo * stride_outer + bi * stride_inner + r * ld_src + c] : uint16_t(0);
+    uint16_t const *s = src + bo * stride_outer + bi * stride_inner + r * ld_src;
+    uint16_t *d = dst + row * ld_dst;
+    for (long long c0 = (long long)threadIdx.x * 8; c0 < ld_dst; c0 += 256 * 8) {
+      alignas(16) uint16_t v[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] = (c0 + j < cols) ? s[c0 + j] : uint16_t(0);
+      *reinterpret_cast<uint4 *>(d + c0) = *reinterpret_cast<uint4 *>(v);
+    }
   }
 }
 
@@ -1428,7 +1435,7 @@ int repack_for_tensor_cores(Problem const &p, Problem &q, cudaStream_t stream) {
     long long const ld_new = (cols + 7) / 8 * 8;
     size_t const bytes = (size_t(rows) * ld_new * p.batch * 2 + 255) / 256 * 256;
     if (bytes > left) return FFK_ERR_UNSUPPORTED;
-    unsigned grid = stream_grid(size_t(rows) * ld_new * p.batch, 256, 8);
+    unsigned grid = (unsigned)std::min<long long>(rows * p.batch, (long long)device_info().sm_count * 16);
     repack_rows_kernel<<<grid, 256, 0, stream>>>(
         static_cast<uint16_t const *>(ptr), reinterpret_cast<uint16_t *>(cursor), rows, cols, ld,
         ld_new, bo, b2, bs, bs2);

@@ -217,6 +217,35 @@ inline int pick_pw(long long nvec) {
   return 0;
 }
 
+// Contiguous rows that cannot be read in 16-byte packets (30522 columns of bf16: the rows are only
+// 4-byte aligned) but fit shared memory: one CTA per row, the row is brought in once element by
+// element (coalesced), reduced twice from shared memory, and written once.
+template <typename T>
+__global__ void __launch_bounds__(kThreads)
+    softmax_rows_smem_kernel(T const *x, T *y, long long rows, long long dim) {
+  extern __shared__ __align__(16) uint8_t sm_row_raw[];
+  T *row = reinterpret_cast<T *>(sm_row_raw);
+  __shared__ float red[32];
+  for (long long r = blockIdx.x; r < rows; r += gridDim.x) {
+    T const *xr = x + r * dim;
+    T *yr = y + r * dim;
+    float mx = -INFINITY;
+    for (long long i = threadIdx.x; i < dim; i += kThreads) {
+      T const t = xr[i];
+      row[i] = t;
+      mx = fmaxf(mx, to_f32(t));
+    }
+    mx = block_max(mx, red);
+    float sum = 0.f;
+    for (long long i = threadIdx.x; i < dim; i += kThreads) sum += __expf(to_f32(row[i]) - mx);
+    sum = block_sum(sum, red);
+    float const inv = 1.f / sum;
+    for (long long i = threadIdx.x; i < dim; i += kThreads)
+      yr[i] = from_f32<T>(__expf(to_f32(row[i]) - mx) * inv);
+    __syncthreads();  // the row buffer is reused by the next row
+  }
+}
+
 // Generic: one warp per (outer, inner) line, element stride `inner`.
 template <typename T>
 __global__ void __launch_bounds__(kThreads)
@@ -1250,6 +1279,14 @@ int ffk_softmax_forward(void *stream, void const *input, void *output, long long
         softmax_rows_kernel<T, P><<<rows_grid(outer, 8), kThreads, 0, s>>>(
             reinterpret_cast<T const *>(input), reinterpret_cast<T *>(output), outer, nvec);
       });
+    } else if (inner == 1 && dim >= 1024 && size_t(dim) * sizeof(T) <= (96u << 10)) {
+      size_t smem = (size_t(dim) * sizeof(T) + 15) / 16 * 16;
+      auto kern = softmax_rows_smem_kernel<T>;
+      FFK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      int per_sm = 0;
+      FFK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kThreads, smem));
+      kern<<<rows_grid(outer, std::max(1, per_sm)), kThreads, smem, s>>>(
+          reinterpret_cast<T const *>(input), reinterpret_cast<T *>(output), outer, dim);
     } else if (inner >= 32) {
       unsigned grid = stream_grid(size_t(outer * inner), kThreads, 8);
       softmax_strided_kernel<T><<<grid, kThreads, 0, s>>>(

@@ -6,12 +6,36 @@ namespace {
 
 constexpr int kThreads = 256;
 
+// g = (p - onehot(label)) * s over the flat [rows][classes] tensor in 16-byte packets (a packet may
+// straddle rows: one division per packet finds the first element's row, the rest is stepped).
 template <typename T>
 __global__ void __launch_bounds__(kThreads)
     sparse_cce_bwd_kernel(T *__restrict__ g, T const *__restrict__ p, int const *__restrict__ label,
-                          long long rows, int classes, int k, float s) {
+                          long long rows, int classes, int k, float s, bool vec_ok) {
+  constexpr int VN = Vec16<T>::N;
   long long const n = rows * classes, stride = (long long)gridDim.x * blockDim.x;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+  long long const tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  long long const nvec = vec_ok ? n / VN : 0;
+  for (long long i = tid; i < nvec; i += stride) {
+    long long const e0 = i * VN;
+    long long r = e0 / classes;
+    int c = int(e0 - r * classes);
+    int lab = label[r / k];
+    Vec16<T> a = ld_stream(p + e0), o;
+#pragma unroll
+    for (int j = 0; j < VN; ++j) {
+      float v = to_f32(a.v[j]);
+      if (c == lab) v -= 1.0f;
+      o.v[j] = from_f32<T>(v * s);
+      if (++c == classes) {
+        c = 0;
+        ++r;
+        if (r < rows) lab = label[r / k];
+      }
+    }
+    st_stream(g + e0, o);
+  }
+  for (long long i = nvec * VN + tid; i < n; i += stride) {
     long long r = i / classes;
     int c = int(i - r * classes);
     float v = to_f32(p[i]);
@@ -295,10 +319,11 @@ int ffk_sparse_categorical_crossentropy_loss_backward(void *stream, void *logit_
   if (num_samples == 0) return FFK_OK;
   FFK_REQUIRE(logit_grad && logit && label, "sparse cce: null tensor");
   FFK_DISPATCH_FLOAT(dtype, T, {
-    unsigned grid = stream_grid(size_t(num_samples) * num_classes, kThreads, 8);
+    bool vec_ok = aligned16(logit_grad) && aligned16(logit);
+    unsigned grid = stream_grid(size_t(num_samples) * num_classes / Vec16<T>::N + 1, kThreads, 8);
     sparse_cce_bwd_kernel<T><<<grid, kThreads, 0, as_stream(stream)>>>(
         (T *)logit_grad, (T const *)logit, label, num_samples, num_classes, k,
-        scale_factor * float(k));
+        scale_factor * float(k), vec_ok);
   });
   FFK_LAUNCH_CHECK();
   return FFK_OK;

@@ -351,3 +351,33 @@ def build_transformer_encoder(num_layers=12, d_model=1024, heads=16, seq=512, ba
         layers += [att, add1, ln1, ff1, dp1, ff2, dp2, add2, ln2]
         cur = ln2.y
     return Model(x, layers, cur)
+
+
+def build_bert(num_layers=12, hidden=768, heads=12, dim_ff=3072, seq=512, batch=64, vocab=30522,
+               dropout=0.1, layer_norm_eps=1e-12, dtype=torch.bfloat16, device="cuda", seed=0):
+    """BASELINE configs[3] (data-parallel form): the graph lib/models builds for BERT
+    (lib/models/src/models/bert/bert.cc:52-155) — the input is the already embedded sequence
+    [batch, seq, hidden]; each layer is MHA(x,x,x) with kdim = vdim = dim_ff / heads -> add ->
+    LayerNorm -> dense(dim_ff, GELU) -> dropout -> dense(hidden) -> dropout -> add -> LayerNorm;
+    the head is dense(vocab, GELU) -> softmax. The reference passes attention dropout and bias flags
+    that its MHA kernel ignores (attention_kernels.cu:94,109); so does this."""
+    hd = dim_ff // heads
+    x = Tensor((batch, seq, hidden), dtype, device)
+    layers: List[Layer] = []
+    cur = x
+    for i in range(num_layers):
+        att = SelfAttention(cur, heads, hd, hd, seed=seed + i)
+        add1 = Add(att.y, cur)
+        ln1 = LayerNorm(add1.y, eps=layer_norm_eps)
+        ff1 = Linear(ln1.y, dim_ff, K.ACT_GELU, True, seed=100 + i)
+        dp1 = Dropout(ff1.y, dropout, 22345 + 2 * i)
+        ff2 = Linear(dp1.y, hidden, K.ACT_NONE, True, seed=200 + i)
+        dp2 = Dropout(ff2.y, dropout, 22346 + 2 * i)
+        add2 = Add(ln1.y, dp2.y)
+        ln2 = LayerNorm(add2.y, eps=layer_norm_eps)
+        layers += [att, add1, ln1, ff1, dp1, ff2, dp2, add2, ln2]
+        cur = ln2.y
+    head = Linear(cur, vocab, K.ACT_GELU, True, seed=300)
+    sm = Softmax(head.y)
+    layers += [head, sm]
+    return Model(x, layers, sm.y)

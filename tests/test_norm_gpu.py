@@ -10,7 +10,7 @@ pytestmark = pytest.mark.gpu
 
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 @pytest.mark.parametrize("outer,dim,inner", [(1, 100, 1), (64, 10, 1), (33, 4096, 1), (7, 1000, 1),
-                                             (2, 5, 12), (4, 32, 100), (3, 8200, 1)])
+                                             (2, 5, 12), (4, 32, 100), (3, 8200, 1), (5, 3001, 1), (9, 30522, 1)])
 def test_softmax_forward(K, oracle, dtype, outer, dim, inner):
     x, xn = to_dev(uniform((outer, dim, inner), SEED_ACT) * 4, dtype)
     y = torch.empty_like(x)

@@ -144,3 +144,29 @@ def test_direct_dropout_gradient_matches_the_accumulating_path(ffk):
 
     for a, b in zip(run(True), run(False)):
         assert torch.equal(a, b)
+
+
+def test_small_bert_trains(ffk):
+    """lib/models' BERT graph at toy size (GELU feed-forward, LayerNorm eps 1e-12, a vocabulary
+    that is not a multiple of 8 so that the head's gradients take the repacked-operand path)."""
+    import importlib
+    T = importlib.import_module("flexflow_train_b200.training")
+    K = importlib.import_module("flexflow_train_b200.kernels")
+    K.set_gemm_workspace(32 << 20)
+    try:
+        model = T.build_bert(num_layers=2, hidden=64, heads=4, dim_ff=128, seq=16, batch=4, vocab=203,
+                             dropout=0.0)
+        opt = T.SGD(lr=0.2, weight_decay=0.0)
+        g = torch.Generator(device="cuda").manual_seed(1)
+        x = (torch.rand(4, 16, 64, device="cuda", generator=g) * 2 - 1).to(torch.bfloat16)
+        labels = torch.randint(0, 203, (4 * 16,), device="cuda", generator=g, dtype=torch.int32)
+        losses = []
+        for _ in range(10):
+            model.input.data.copy_(x)
+            T.sparse_cce_step(model, labels, opt)
+            p = model.output.data.float().view(64, 203)
+            losses.append(float(-torch.log(p[torch.arange(64), labels.long()].clamp_min(1e-8)).mean()))
+        assert all(np.isfinite(losses)), losses
+        assert losses[-1] < losses[0], losses
+    finally:
+        K.set_gemm_workspace(None)
