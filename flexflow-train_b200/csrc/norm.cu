@@ -226,10 +226,42 @@ __global__ void __launch_bounds__(kThreads)
   extern __shared__ __align__(16) uint8_t sm_row_raw[];
   T *row = reinterpret_cast<T *>(sm_row_raw);
   __shared__ float red[32];
+  // 16-bit rows of even length whose base is 4-byte aligned move two elements per access
+  bool const pairs = sizeof(T) == 2 && dim % 2 == 0 &&
+                     (reinterpret_cast<uintptr_t>(x) & 3) == 0 && (reinterpret_cast<uintptr_t>(y) & 3) == 0;
   for (long long r = blockIdx.x; r < rows; r += gridDim.x) {
     T const *xr = x + r * dim;
     T *yr = y + r * dim;
     float mx = -INFINITY;
+    if (pairs) {
+      struct alignas(4) Pair { T a, b; };
+      Pair const *xp = reinterpret_cast<Pair const *>(xr);
+      Pair *yp = reinterpret_cast<Pair *>(yr);
+      Pair *rp = reinterpret_cast<Pair *>(row);
+      long long const np = dim / 2;
+      for (long long i = threadIdx.x; i < np; i += kThreads) {
+        Pair const t = xp[i];
+        rp[i] = t;
+        mx = fmaxf(mx, fmaxf(to_f32(t.a), to_f32(t.b)));
+      }
+      mx = block_max(mx, red);
+      float sum = 0.f;
+      for (long long i = threadIdx.x; i < np; i += kThreads) {
+        Pair const t = rp[i];
+        sum += __expf(to_f32(t.a) - mx) + __expf(to_f32(t.b) - mx);
+      }
+      sum = block_sum(sum, red);
+      float const inv = 1.f / sum;
+      for (long long i = threadIdx.x; i < np; i += kThreads) {
+        Pair const t = rp[i];
+        Pair o;
+        o.a = from_f32<T>(__expf(to_f32(t.a) - mx) * inv);
+        o.b = from_f32<T>(__expf(to_f32(t.b) - mx) * inv);
+        yp[i] = o;
+      }
+      __syncthreads();
+      continue;
+    }
     for (long long i = threadIdx.x; i < dim; i += kThreads) {
       T const t = xr[i];
       row[i] = t;

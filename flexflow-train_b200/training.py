@@ -228,6 +228,12 @@ class Model:
             if isinstance(l, Dropout) and readers.get(id(l.x), 0) == 1 and l.x.grad is not None:
                 l.sole_reader = True
                 self._overwritten.add(id(l.x))
+            # the reference's softmax backward is a copy: it overwrites its input gradient
+            if isinstance(l, Softmax) and readers.get(id(l.x), 0) == 1 and l.x.grad is not None:
+                self._overwritten.add(id(l.x))
+        # every loss kernel writes the whole gradient of the model output
+        if out.grad is not None and readers.get(id(out), 0) == 0:
+            self._overwritten.add(id(out))
         self._flatten_gradients()
         self.params = [p for l in layers for p in l.params]
         self.grads = [g for l in layers for g in l.grads]
