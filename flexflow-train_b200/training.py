@@ -16,6 +16,7 @@ from dataclasses import dataclass, field
 from typing import Dict, List, Optional
 
 import torch
+import torch.distributed as dist
 
 from . import kernels as K
 
@@ -48,15 +49,27 @@ class Layer:
 
 
 class Linear(Layer):
-    def __init__(self, x: Tensor, out_dim: int, activation=K.ACT_NONE, bias=True, seed=0):
+    def __init__(self, x: Tensor, out_dim: int, activation=K.ACT_NONE, bias=True, seed=0,
+                 shard_out=None, shard_in=None):
+        """shard_out = (index, count): this rank holds rows [index*out_dim, ...) of a weight with
+        count*out_dim outputs (column-parallel layer); shard_in = (index, count): it holds the
+        matching slice of the input features (row-parallel layer, partial sums out). The full
+        weight is drawn from the seed and sliced, so that a sharded model equals the unsharded one."""
         self.x = x
         dt, dev = x.data.dtype, x.data.device
         self.in_dim = x.shape[-1]
         self.batch = x.data.numel() // self.in_dim
         self.out_dim = out_dim
         g = torch.Generator(device=dev).manual_seed(4321 + seed)
-        bound = (6.0 / (self.in_dim + out_dim)) ** 0.5  # glorot uniform, the reference's default initializer
-        self.w = ((torch.rand(out_dim, self.in_dim, device=dev, generator=g) * 2 - 1) * bound).to(dt)
+        full_out = out_dim * (shard_out[1] if shard_out else 1)
+        full_in = self.in_dim * (shard_in[1] if shard_in else 1)
+        bound = (6.0 / (full_in + full_out)) ** 0.5  # glorot uniform, the reference's default initializer
+        full = (torch.rand(full_out, full_in, device=dev, generator=g) * 2 - 1) * bound
+        if shard_out:
+            full = full[shard_out[0] * out_dim:(shard_out[0] + 1) * out_dim]
+        if shard_in:
+            full = full[:, shard_in[0] * self.in_dim:(shard_in[0] + 1) * self.in_dim]
+        self.w = full.to(dt).contiguous()
         self.b = torch.zeros(out_dim, dtype=dt, device=dev) if bias else None
         self.dw = torch.zeros_like(self.w)
         self.db = torch.zeros_like(self.b) if bias else None
@@ -147,7 +160,9 @@ class SelfAttention(Layer):
 
     _shared_ws: Dict = {}  # backward scratch is dead between layers: one buffer per (device, size)
 
-    def __init__(self, x: Tensor, heads: int, kdim: int, vdim: int, seed=0):
+    def __init__(self, x: Tensor, heads: int, kdim: int, vdim: int, seed=0, shard=None):
+        """shard = (index, count): this rank computes `heads` of the count*heads heads (its slice of
+        the packed weight Wq[E][H][kdim] | Wk | Wv | Wo[H][vdim][E]); its output is a partial sum."""
         self.x = x
         dt, dev = x.data.dtype, x.data.device
         N, S, E = x.shape
@@ -156,7 +171,16 @@ class SelfAttention(Layer):
         self.state.workSpace = SelfAttention._shared_ws.setdefault(key, self.state.workSpace)
         nw = self.state.weightSize // x.data.element_size()
         g = torch.Generator(device=dev).manual_seed(977 + seed)
-        self.w = ((torch.rand(nw, device=dev, generator=g) * 2 - 1) * (1.0 / E ** 0.5)).to(dt)
+        idx, cnt = shard if shard else (0, 1)
+        full = (torch.rand(nw * cnt, device=dev, generator=g) * 2 - 1) * (1.0 / E ** 0.5)
+        if cnt > 1:
+            H = heads * cnt
+            sizes = [E * H * kdim, E * H * kdim, E * H * vdim, H * vdim * E]
+            wq, wk, wv, wo = torch.split(full, sizes)
+            h0, h1 = idx * heads, (idx + 1) * heads
+            full = torch.cat([wq.view(E, H, kdim)[:, h0:h1].reshape(-1), wk.view(E, H, kdim)[:, h0:h1].reshape(-1),
+                              wv.view(E, H, vdim)[:, h0:h1].reshape(-1), wo.view(H, vdim, E)[h0:h1].reshape(-1)])
+        self.w = full.to(dt).contiguous()
         self.dw = torch.zeros_like(self.w)
         self.y = Tensor(x.shape, dt, dev)
         # dq | dk | dv stacked like the replicas of a Replicate op: their sum is one kernel
@@ -171,6 +195,39 @@ class SelfAttention(Layer):
         K.MultiHeadAttention.backward_kernel(None, self.state, self.x.data, self.dq, self.x.data, self.dk,
                                              self.x.data, self.dv, self.w, self.dw, self.y.grad)
         K.Replicate.backward_kernel(None, self.x.grad, self.dqkv, 3)  # x.grad += dq + dk + dv
+
+
+class ReduceSum(Layer):
+    """Reduction over the tensor-parallel group (lib/op-attrs .../ops/reduction.cc): forward sums
+    the ranks' partial tensors (all-reduce), backward hands the gradient through unchanged."""
+
+    def __init__(self, x: Tensor, group=None):
+        self.x, self.group = x, group
+        self.y = Tensor(x.shape, x.data.dtype, x.data.device)
+
+    def forward(self):
+        K.copy(None, self.y.data, self.x.data)
+        dist.all_reduce(self.y.data, op=dist.ReduceOp.SUM, group=self.group)
+
+    def backward(self):
+        K.accumulate(None, self.x.grad, self.y.grad)
+
+
+class ReplicateIn(Layer):
+    """Replicate towards the tensor-parallel group (.../ops/replicate.cc): forward is the identity
+    (every rank already holds x), backward sums the ranks' gradients of their replicas."""
+
+    def __init__(self, x: Tensor, group=None):
+        self.x, self.group = x, group
+        self.y = Tensor(x.shape, x.data.dtype, x.data.device)
+        self.y.data = x.data  # same storage: no copy in the forward pass
+
+    def forward(self):
+        pass
+
+    def backward(self):
+        dist.all_reduce(self.y.grad, op=dist.ReduceOp.SUM, group=self.group)
+        K.accumulate(None, self.x.grad, self.y.grad)
 
 
 class Softmax(Layer):
@@ -360,7 +417,8 @@ def build_transformer_encoder(num_layers=12, d_model=1024, heads=16, seq=512, ba
 
 
 def build_bert(num_layers=12, hidden=768, heads=12, dim_ff=3072, seq=512, batch=64, vocab=30522,
-               dropout=0.1, layer_norm_eps=1e-12, dtype=torch.bfloat16, device="cuda", seed=0):
+               dropout=0.1, layer_norm_eps=1e-12, dtype=torch.bfloat16, device="cuda", seed=0,
+               tp_rank=0, tp_world=1, tp_group=None):
     """BASELINE configs[3] (data-parallel form): the graph lib/models builds for BERT
     (lib/models/src/models/bert/bert.cc:52-155) — the input is the already embedded sequence
     [batch, seq, hidden]; each layer is MHA(x,x,x) with kdim = vdim = dim_ff / heads -> add ->
@@ -371,17 +429,28 @@ def build_bert(num_layers=12, hidden=768, heads=12, dim_ff=3072, seq=512, batch=
     x = Tensor((batch, seq, hidden), dtype, device)
     layers: List[Layer] = []
     cur = x
+    tp = tp_world > 1
+    if tp:
+        assert heads % tp_world == 0 and dim_ff % tp_world == 0
+    sh = (tp_rank, tp_world) if tp else None
     for i in range(num_layers):
-        att = SelfAttention(cur, heads, hd, hd, seed=seed + i)
-        add1 = Add(att.y, cur)
+        # tensor-parallel form (the placement a searched strategy gives BERT): heads and the
+        # feed-forward width are split over the group; Replicate in front of each split block,
+        # Reduction behind it; LayerNorm, residuals and the head stay replicated
+        a_in = ReplicateIn(cur, tp_group) if tp else None
+        att = SelfAttention(a_in.y if tp else cur, heads // tp_world, hd, hd, seed=seed + i, shard=sh)
+        a_out = ReduceSum(att.y, tp_group) if tp else None
+        add1 = Add(a_out.y if tp else att.y, cur)
         ln1 = LayerNorm(add1.y, eps=layer_norm_eps)
-        ff1 = Linear(ln1.y, dim_ff, K.ACT_GELU, True, seed=100 + i)
-        dp1 = Dropout(ff1.y, dropout, 22345 + 2 * i)
-        ff2 = Linear(dp1.y, hidden, K.ACT_NONE, True, seed=200 + i)
-        dp2 = Dropout(ff2.y, dropout, 22346 + 2 * i)
+        f_in = ReplicateIn(ln1.y, tp_group) if tp else None
+        ff1 = Linear(f_in.y if tp else ln1.y, dim_ff // tp_world, K.ACT_GELU, True, seed=100 + i, shard_out=sh)
+        dp1 = Dropout(ff1.y, dropout, 22345 + 2 * i + 7919 * tp_rank)
+        ff2 = Linear(dp1.y, hidden, K.ACT_NONE, tp_rank == 0, seed=200 + i, shard_in=sh)
+        f_out = ReduceSum(ff2.y, tp_group) if tp else None
+        dp2 = Dropout(f_out.y if tp else ff2.y, dropout, 22346 + 2 * i)
         add2 = Add(ln1.y, dp2.y)
         ln2 = LayerNorm(add2.y, eps=layer_norm_eps)
-        layers += [att, add1, ln1, ff1, dp1, ff2, dp2, add2, ln2]
+        layers += [l for l in (a_in, att, a_out, add1, ln1, f_in, ff1, dp1, ff2, f_out, dp2, add2, ln2) if l is not None]
         cur = ln2.y
     head = Linear(cur, vocab, K.ACT_GELU, True, seed=300)
     sm = Softmax(head.y)
