@@ -480,19 +480,45 @@ def run_encoder(args):
     torch.cuda.set_device(local_rank)
     device = torch.device("cuda", local_rank)
     pops = None
+    bert = args.workload == "bert"
+    tp = 1
+    if args.strategy:
+        # "imported search strategy": the one placement decision this driver understands is the
+        # tensor-parallel degree of the split blocks ({"tensor_parallel": T}); the rest is data parallel
+        tp = int(json.loads(Path(args.strategy).read_text()).get("tensor_parallel", 1))
+    if args.tp:
+        tp = args.tp
+    if not bert or world % tp != 0:
+        tp = 1
+    dp = world // tp
+    tp_group, tp_rank = None, 0
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=device)
-        pops = importlib.import_module("flexflow_train_b200.parallel_ops").ParallelOps()
-    bert = args.workload == "bert"
+        dp_group = None
+        if tp > 1:
+            # consecutive ranks form a tensor-parallel group; ranks with the same index in their
+            # group form a data-parallel group (every rank must create every group)
+            for b in range(dp):
+                grp = dist.new_group(list(range(b * tp, (b + 1) * tp)))
+                if rank // tp == b:
+                    tp_group = grp
+            for i in range(tp):
+                grp = dist.new_group(list(range(i, world, tp)))
+                if rank % tp == i:
+                    dp_group = grp
+            tp_rank = rank % tp
+        if dp > 1:
+            pops = importlib.import_module("flexflow_train_b200.parallel_ops").ParallelOps(group=dp_group)
     B, S, L = args.batch, 512, args.layers
     D, H, FF, V = (768, 12, 3072, 30522) if bert else (1024, 16, 4096, 0)
     hd = args.head_dim if args.head_dim > 0 else FF // H
-    g = torch.Generator(device=device).manual_seed(1234 + rank)
+    g = torch.Generator(device=device).manual_seed(1234 + rank // tp)  # one batch per data-parallel replica
     if bert:
         # the vocabulary head's gradients go through repacked operands: that needs scratch
         Kmod.set_gemm_workspace(int(B * S * ((V + 7) // 8 * 8) * 2 * 1.05))
-        model = T.build_bert(L, D, H, FF, S, B, V, dropout=0.1, dtype=torch.bfloat16, device=device)
+        model = T.build_bert(L, D, H, FF, S, B, V, dropout=0.1, dtype=torch.bfloat16, device=device,
+                             tp_rank=tp_rank, tp_world=tp, tp_group=tp_group)
         labels = torch.randint(0, V, (B * S,), generator=g, device=device, dtype=torch.int32)
     else:
         model = T.build_transformer_encoder(L, D, H, S, B, FF, hd, dropout=0.1, dtype=torch.bfloat16, device=device)
@@ -508,7 +534,7 @@ def run_encoder(args):
 
     def step():
         if bert:
-            T.sparse_cce_step(model, labels, opt, pops, global_batch=B * S * world)
+            T.sparse_cce_step(model, labels, opt, pops, global_batch=B * S * dp)
         else:
             T.mse_step(model, target, opt, pops)
 
@@ -569,11 +595,11 @@ def run_encoder(args):
     per_tok = 2 * (3 * D * H * hd + H * hd * D + 2 * S * H * hd + 2 * D * FF)
     flops_per_sample = 3 * per_tok * S * L + 3 * 2 * D * V * S
     tf_peak, _, peak_src = load_peaks()
-    achieved = flops_per_sample * B / (ms_per_step * 1e-3) / 1e12
+    achieved = flops_per_sample * B / tp / (ms_per_step * 1e-3) / 1e12  # per GPU
     out = {
         "metric": "training samples/sec (BERT-base graph of lib/models, fwd+bwd+SGD)" if bert else
                   "training samples/sec (transformer encoder, fwd+bwd+SGD)",
-        "value": B * world / (ms_per_step * 1e-3), "unit": "samples/s", "n_gpus": world,
+        "value": B * dp / (ms_per_step * 1e-3), "unit": "samples/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
         "data": "synthetic",
@@ -582,13 +608,13 @@ def run_encoder(args):
                                 f"batch {B} per GPU, sparse CCE + SGD") if bert else
                                (f"BASELINE configs[2]: transformer encoder {L} layers, d {D}, {H} heads, head dim {hd}, "
                                 f"dim_ff {FF}, seq {S}, batch {B} per GPU, MSE + SGD"),
-                   "global_batch": B * world, "seq_len": S, "parameters": params,
-                   "parallelism": f"dp{world}" if world > 1 else "single",
+                   "global_batch": B * dp, "seq_len": S, "parameters": params,
+                   "parallelism": (f"dp{dp}" + (f" x tp{tp}" if tp > 1 else "")) if world > 1 else "single",
                    "l2": "activations of one layer exceed L2 (>= 0.5 GB)"},
         "roofline": {"kernel": "whole step (model FLOPs, all kernels)", "bound": "tensor", "achieved": achieved,
                      "peak": tf_peak, "peak_source": f"{peak_src} bf16_tflops (burst)", "unit": "TFLOP/s",
                      "frac": achieved / tf_peak, "traffic": None},
-        "e2e": {"value": B * world / (ms_e2e / args.steps * 1e-3), "unit": "samples/s",
+        "e2e": {"value": B * dp / (ms_e2e / args.steps * 1e-3), "unit": "samples/s",
                 "h2d_bytes_per_step": hx.numel() * 2, "d2h_bytes_per_step": 28,
                 "ms_per_step": ms_e2e / args.steps},
         "gpu_launches": None, "abi_calls_timed": abi_calls, "clocks": clock_info,
@@ -772,6 +798,8 @@ def main():
     ap.add_argument("--layers", type=int, default=12)
     ap.add_argument("--batch", type=int, default=64)
     ap.add_argument("--head-dim", type=int, default=0, help="0 = the reference's dim_ff/heads (256)")
+    ap.add_argument("--tp", type=int, default=0, help="bert: tensor-parallel degree (divides --gpus)")
+    ap.add_argument("--strategy", default="", help='bert: JSON file with {"tensor_parallel": T}')
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3  # timing rule: at least 3 warm-up steps
