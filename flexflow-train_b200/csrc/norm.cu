@@ -11,7 +11,6 @@ namespace ffk {
 namespace {
 
 constexpr int kThreads = 256;
-constexpr int kMaxP = 8;  // packets per thread held in registers
 
 __device__ __forceinline__ void block_sum2(float &a, float &b, float *red /* >= 64 floats */) {
   int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -1079,6 +1078,17 @@ __global__ void __launch_bounds__(256, 2)
   }
 }
 
+// 32 columns per lane are 8 packets of fp32 but only 4 of a 16-bit type.
+template <typename T> auto widest_ring_kernel() {
+  if constexpr (sizeof(T) == 4) return layer_norm_bwd_ring_kernel<T, 8>;
+  else return layer_norm_bwd_ring_kernel<T, 4>;
+}
+
+template <typename T> auto widest_cta_ring_kernel() {
+  if constexpr (sizeof(T) == 4) return layer_norm_bwd_cta_ring_kernel<T, 4>;
+  else return layer_norm_bwd_cta_ring_kernel<T, 2>;
+}
+
 // Fused backward for short rows, one warp per row. Each lane owns fixed columns, keeps gamma
 // and its running dgamma / dbeta sums in registers over all the rows its warp visits; the 8
 // warps of a CTA are combined through shared memory into this CTA's partial slab.
@@ -1472,9 +1482,7 @@ int ffk_layer_norm_backward(void *stream, void const *output_grad, void const *i
         case 1: rc = launch(layer_norm_bwd_ring_kernel<T, 1>); break;
         case 2: rc = launch(layer_norm_bwd_ring_kernel<T, 2>); break;
         case 4: rc = launch(layer_norm_bwd_ring_kernel<T, 4>); break;
-        default:
-          if constexpr (sizeof(T) == 4) rc = launch(layer_norm_bwd_ring_kernel<T, 8>);
-          break;
+        default: rc = launch(widest_ring_kernel<T>()); break;  // reached by fp32 only (8 x 4 columns)
       }
       if (rc) return rc;
       FFK_LAUNCH_CHECK();
@@ -1509,9 +1517,7 @@ int ffk_layer_norm_backward(void *stream, void const *output_grad, void const *i
       switch (pp) {
         case 1: rc = launch(layer_norm_bwd_cta_ring_kernel<T, 1>); break;
         case 2: rc = launch(layer_norm_bwd_cta_ring_kernel<T, 2>); break;
-        default:
-          if constexpr (sizeof(T) == 4) rc = launch(layer_norm_bwd_cta_ring_kernel<T, 4>);
-          break;
+        default: rc = launch(widest_cta_ring_kernel<T>()); break;  // reached by fp32 only
       }
       if (rc) return rc;
       FFK_LAUNCH_CHECK();
