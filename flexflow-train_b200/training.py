@@ -456,3 +456,135 @@ def build_bert(num_layers=12, hidden=768, heads=12, dim_ff=3072, seq=512, batch=
     sm = Softmax(head.y)
     layers += [head, sm]
     return Model(x, layers, sm.y)
+
+
+# ------------------------------------------------------------------ DLRM (BASELINE configs[4])
+class Concat(Layer):
+    """concat along the last dimension of 2-D activations (DLRM's "cat" interaction)."""
+
+    def __init__(self, inputs: List[Tensor]):
+        self.inputs = inputs
+        rows = inputs[0].shape[0]
+        width = sum(t.shape[1] for t in inputs)
+        self.y = Tensor((rows, width), inputs[0].data.dtype, inputs[0].data.device)
+
+    def forward(self):
+        K.Concat.forward_kernel(None, self.y.data, [t.data for t in self.inputs], 1)
+
+    def backward(self):
+        K.Concat.backward_kernel(None, self.y.grad, [t.grad for t in self.inputs], 1)
+
+
+class ShardedEmbeddings(Layer):
+    """The embedding tables of a DLRM, table-sharded over the ranks (model parallel), feeding
+    data-parallel MLPs: rank r owns tables [r*tl, (r+1)*tl), looks up the WHOLE global batch in
+    them and the results are repartitioned along the batch dimension with one all-to-all, so that
+    every rank ends with all tables' vectors for its own `batch` rows; backward runs the same
+    exchange in reverse and scatters into the local tables. With one rank it is plain lookups.
+    Tables and their gradients stay out of the data-parallel gradient buckets."""
+
+    def __init__(self, indices: torch.Tensor, entries: int, dim: int, batch: int, tables: int, rank=0,
+                 world=1, group=None, seed=0, device="cuda"):
+        assert tables % world == 0
+        self.tl, self.T, self.B, self.W, self.rank, self.group = tables // world, tables, batch, world, rank, group
+        self.dim, self.bag = dim, indices.shape[-1]
+        assert tuple(indices.shape[:2]) == (self.tl, world * batch)
+        self.idx = indices.contiguous()
+        self.tables, self.dtables = [], []
+        for j in range(self.tl):
+            g = torch.Generator(device=device).manual_seed(5000 + seed + rank * self.tl + j)
+            bound = (1.0 / entries) ** 0.5
+            self.tables.append((torch.rand(entries, dim, device=device, generator=g) * 2 - 1) * bound)
+            self.dtables.append(torch.zeros(entries, dim, device=device))
+        self.y = Tensor((tables, batch, dim), torch.float32, device)          # [table][row][dim] for MY rows
+        self.send = torch.zeros(world, self.tl, batch, dim, device=device)    # [dest rank][local table][row][dim]
+        self.gsend = torch.zeros_like(self.send) if world > 1 else None
+        self.params, self.grads = [], []
+
+    def views(self) -> List[Tensor]:
+        """One activation per table (rows of this rank), sharing storage with y."""
+        out = []
+        for t in range(self.T):
+            v = Tensor.__new__(Tensor)
+            v.data, v.grad = self.y.data[t], self.y.grad[t]
+            out.append(v)
+        return out
+
+    def forward(self):
+        dst = self.send if self.W > 1 else self.y.data.view(1, self.tl, self.B, self.dim)
+        for j in range(self.tl):
+            for q in range(self.W):
+                K.Embedding.forward_kernel(None, self.idx[j, q * self.B:(q + 1) * self.B], dst[q, j],
+                                           self.tables[j], K.AGGR_SUM, self.bag, self.dim, self.B)
+        if self.W > 1:
+            dist.all_to_all_single(self.y.data.view(-1), self.send.view(-1), group=self.group)
+
+    def backward(self):
+        if self.W > 1:
+            dist.all_to_all_single(self.gsend.view(-1), self.y.grad.view(-1), group=self.group)
+            src = self.gsend
+        else:
+            src = self.y.grad.view(1, self.tl, self.B, self.dim)
+        for j in range(self.tl):
+            _fill0(self.dtables[j])
+            for q in range(self.W):
+                K.Embedding.backward_kernel(None, self.idx[j, q * self.B:(q + 1) * self.B], src[q, j],
+                                            self.dtables[j], K.AGGR_SUM, self.bag, self.dim, self.B)
+
+    def update(self, opt: "SGD"):
+        for w, g in zip(self.tables, self.dtables):
+            K.sgd_ps_update_task_gpu(None, opt.lr, 0.0, False, opt.weight_decay, g, w.numel(), 1, w, None, None)
+
+
+class DLRM:
+    """examples/cpp/DLRM/dlrm.cc:139-166: dense features -> bottom MLP; one embedding lookup per
+    sparse feature; "cat" interaction; top MLP (sigmoid on its last layer); MSE loss.
+    Defaults are the example's: 4 tables of 1 M x 64, bag size 1, bottom 4-64-64, top 64-64-2."""
+
+    def __init__(self, batch=8192, embedding_size=(1000000,) * 4, sparse_feature_size=64, bag=1,
+                 mlp_bot=(4, 64, 64), mlp_top=(64, 64, 2), rank=0, world=1, group=None, device="cuda",
+                 seed=0):
+        self.batch, self.world, self.rank = batch, world, rank
+        T = len(embedding_size)
+        assert len(set(embedding_size)) == 1, "one table size (the example's default)"
+        tl = T // world
+        # synthetic indices for the GLOBAL batch, the same on every rank (common seed); a rank
+        # keeps the rows of its own tables only
+        g = torch.Generator(device=device).manual_seed(99 + seed)
+        all_idx = torch.randint(0, embedding_size[0], (T, world * batch, bag), device=device, generator=g,
+                                dtype=torch.int64)
+        self.dense = Tensor((batch, mlp_bot[0]), torch.float32, device)
+        layers: List[Layer] = []
+        cur = self.dense
+        for i, d in enumerate(mlp_bot[1:]):
+            lin = Linear(cur, d, K.ACT_RELU, True, seed=400 + i)
+            layers.append(lin)
+            cur = lin.y
+        self.emb = ShardedEmbeddings(all_idx[rank * tl:(rank + 1) * tl], embedding_size[0], sparse_feature_size,
+                                     batch, T, rank, world, group, seed, device)
+        layers.append(self.emb)
+        cat = Concat([cur] + self.emb.views())
+        layers.append(cat)
+        cur = cat.y
+        for i, d in enumerate(mlp_top):
+            last = i == len(mlp_top) - 1
+            lin = Linear(cur, d, K.ACT_SIGMOID if last else K.ACT_RELU, True, seed=500 + i)
+            layers.append(lin)
+            cur = lin.y
+        self.model = Model(self.dense, layers, cur)
+
+
+def dlrm_step(net: DLRM, target: torch.Tensor, opt: SGD, pops=None):
+    """zero grads, forward (with the table exchange), MSE gradient, backward, data-parallel sum
+    of the MLP gradients, SGD on the MLPs and on this rank's tables."""
+    m = net.model
+    m.zero_gradients()
+    m.forward()
+    out = m.output
+    scale = 2.0 / float(out.data.numel() * net.world)
+    K.mean_squared_error_avg_loss_backward_kernel(None, out.grad, out.data, target, scale)
+    m.backward()
+    if pops is not None:
+        pops.allreduce_gradients(m.grad_buckets)
+    opt.step(m.params, m.grads)
+    net.emb.update(opt)

@@ -170,3 +170,26 @@ def test_small_bert_trains(ffk):
         assert losses[-1] < losses[0], losses
     finally:
         K.set_gemm_workspace(None)
+
+
+def test_small_dlrm_trains(ffk):
+    """examples/cpp/DLRM's graph at toy size on one GPU: loss must fall and only looked-up table
+    rows may change."""
+    import importlib
+    T = importlib.import_module("flexflow_train_b200.training")
+    net = T.DLRM(batch=256, embedding_size=(1000,) * 4, sparse_feature_size=16, bag=2, mlp_bot=(4, 32, 16),
+                 mlp_top=(32, 16, 2))
+    opt = T.SGD(lr=0.5, weight_decay=0.0)
+    g = torch.Generator(device="cuda").manual_seed(2)
+    net.dense.data.copy_(torch.rand(256, 4, device="cuda", generator=g))
+    target = (torch.rand(256, 2, device="cuda", generator=g) > 0.5).float()
+    before = [t.clone() for t in net.emb.tables]
+    losses = []
+    for _ in range(30):
+        T.dlrm_step(net, target, opt)
+        losses.append(float(((net.model.output.data - target) ** 2).mean()))
+    assert all(np.isfinite(losses)) and losses[-1] < losses[0], losses
+    for j, (b, a) in enumerate(zip(before, net.emb.tables)):
+        touched = torch.zeros(1000, dtype=torch.bool, device="cuda")
+        touched[net.emb.idx[j].reshape(-1)] = True
+        assert torch.equal(a[~touched], b[~touched]) and not torch.equal(a[touched], b[touched])
