@@ -624,6 +624,113 @@ def run_encoder(args):
         dist.destroy_process_group()
 
 
+# ----------------------------------------------------------------------------- DLRM workload
+def run_dlrm(args):
+    """BASELINE configs[4]: the DLRM of examples/cpp/DLRM (8 tables of 1 M x 64 fp32 here, so that
+    8 GPUs own one each; bag size 1; bottom MLP 4-64-64, "cat" interaction, top MLP 64-64-2, MSE +
+    SGD), tables sharded over the ranks, lookups repartitioned with an all-to-all, MLPs data parallel.
+    `--workload dlrm [--batch B]` (B per GPU, default 8192)."""
+    import importlib
+
+    import torch
+    import torch.distributed as dist
+
+    import ffk_import
+
+    ffk_import.load()
+    T = importlib.import_module("flexflow_train_b200.training")
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    pops = None
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=device)
+        pops = importlib.import_module("flexflow_train_b200.parallel_ops").ParallelOps()
+    B = args.batch if args.batch != 64 else 8192
+    tables = 8
+    net = T.DLRM(batch=B, embedding_size=(1000000,) * tables, rank=rank, world=world, device=device)
+    opt = T.SGD(lr=0.01, weight_decay=0.0)
+    g = torch.Generator(device=device).manual_seed(77 + rank)
+    hdense = torch.rand(B, 4, generator=g, device=device).cpu().pin_memory()
+    target = (torch.rand(B, 2, generator=g, device=device) > 0.5).float()
+    hout = torch.empty(B, 2).pin_memory()
+    net.dense.data.copy_(hdense)
+    lib = ffk_import.load().lib()
+
+    def step():
+        T.dlrm_step(net, target, opt, pops)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, n):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(n):
+            fn()
+        e1.record()
+        barrier()
+        return e0.elapsed_time(e1)
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    clocks = ClockSampler(local_rank)
+    if rank == 0:
+        clocks.start()
+    calls0 = lib.launches
+    ms_total = timed(step, args.steps)
+    abi_calls = lib.launches - calls0
+    clock_info = clocks.stop() if rank == 0 else None
+
+    def e2e_step():
+        net.dense.data.copy_(hdense, non_blocking=True)
+        step()
+        hout.copy_(net.model.output.data, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+
+    for _ in range(3):
+        e2e_step()
+    ms_e2e = timed(e2e_step, args.steps)
+    if world > 1:
+        t = torch.tensor([ms_total, ms_e2e], device=device, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_total, ms_e2e = t.tolist()
+    if rank == 0:
+        ms = ms_total / args.steps
+        # bytes one step must move per GPU: for each local table, gather + scatter of the global
+        # batch's rows, zero fill and SGD pass over table and gradient
+        tl = tables // world
+        row = 64 * 4
+        lookups = tl * B * world
+        table_bytes = tl * 1000000 * row
+        algo = lookups * (8 + 2 * row) + lookups * (8 + 3 * row) + table_bytes * (1 + 3)
+        _, hbm_peak, peak_src = load_peaks()
+        print(json.dumps({
+            "metric": "training samples/sec (DLRM, fwd+bwd+SGD)", "value": B * world / (ms * 1e-3),
+            "unit": "samples/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "fp32", "data": "synthetic",
+            "config": {"workload": f"BASELINE configs[4]: DLRM, {tables} tables of 1M x 64 fp32 sharded over {world} "
+                                   f"rank(s), bag 1, bottom 4-64-64, cat, top 64-64-2, batch {B} per GPU, MSE + SGD",
+                       "global_batch": B * world, "parallelism": f"tables/{world} x dp{world}" if world > 1 else "single",
+                       "l2": "tables exceed L2 (256 MB each)"},
+            "roofline": {"kernel": "whole step (embedding traffic + dense table passes)", "bound": "hbm",
+                         "achieved": algo / (ms * 1e-3) / 1e9, "peak": hbm_peak, "peak_source": peak_src,
+                         "unit": "GB/s", "frac": algo / (ms * 1e-3) / 1e9 / hbm_peak, "traffic": None},
+            "e2e": {"value": B * world / (ms_e2e / args.steps * 1e-3), "unit": "samples/s",
+                    "h2d_bytes_per_step": B * 4 * 4, "d2h_bytes_per_step": B * 2 * 4,
+                    "ms_per_step": ms_e2e / args.steps},
+            "gpu_launches": None, "abi_calls_timed": abi_calls, "clocks": clock_info}), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
 # ----------------------------------------------------------------------------- MLP workload
 def run_mlp(args):
     """BASELINE configs[0]: the reference's own CPU-runnable case — MLP 784-512-512-10, batch 64,
@@ -794,7 +901,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--workload", default="microbench", choices=["microbench", "encoder", "bert", "mlp"])
+    ap.add_argument("--workload", default="microbench", choices=["microbench", "encoder", "bert", "dlrm", "mlp"])
     ap.add_argument("--layers", type=int, default=12)
     ap.add_argument("--batch", type=int, default=64)
     ap.add_argument("--head-dim", type=int, default=0, help="0 = the reference's dim_ff/heads (256)")
@@ -809,6 +916,8 @@ def main():
         run_encoder(args)
     elif args.workload == "mlp":
         run_mlp(args)
+    elif args.workload == "dlrm":
+        run_dlrm(args)
     else:
         run_gpu(args)
 
