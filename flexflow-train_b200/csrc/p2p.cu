@@ -303,11 +303,16 @@ int ffk_p2p_create(void **group_out, int rank, int world, size_t data_bytes,
   g->rank = rank;
   g->world = world;
   g->data_bytes = data_bytes;
-  FFK_CUDA(cudaGetDevice(&g->device));
-  FFK_CUDA(cudaMalloc(reinterpret_cast<void **>(&g->local), kFlagBytes + data_bytes));
-  FFK_CUDA(cudaMemset(g->local, 0, kControlBytes));
   cudaIpcMemHandle_t h;
-  FFK_CUDA(cudaIpcGetMemHandle(&h, g->local));
+  cudaError_t err = cudaGetDevice(&g->device);
+  if (err == cudaSuccess) err = cudaMalloc(reinterpret_cast<void **>(&g->local), kFlagBytes + data_bytes);
+  if (err == cudaSuccess) err = cudaMemset(g->local, 0, kControlBytes);
+  if (err == cudaSuccess) err = cudaIpcGetMemHandle(&h, g->local);
+  if (err != cudaSuccess) {  // nothing of a half-built group survives
+    if (g->local) cudaFree(g->local);
+    delete g;
+    FFK_CUDA(err);
+  }
   static_assert(sizeof(h) == FFK_P2P_HANDLE_BYTES, "IPC handle size");
   std::memcpy(handle_out, &h, sizeof(h));
   g->table.base[rank] = g->local;

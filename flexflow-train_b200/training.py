@@ -219,8 +219,9 @@ class ReplicateIn(Layer):
 
     def __init__(self, x: Tensor, group=None):
         self.x, self.group = x, group
-        self.y = Tensor(x.shape, x.data.dtype, x.data.device)
+        self.y = Tensor.__new__(Tensor)
         self.y.data = x.data  # same storage: no copy in the forward pass
+        self.y.grad = torch.zeros_like(x.data)
 
     def forward(self):
         pass
