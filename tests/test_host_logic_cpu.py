@@ -1,0 +1,27 @@
+"""Host-side helpers that need no GPU: pinned-staging NUMA parsing, the strategy file the BERT
+workload imports, and the headers' new entry points being exported by the library."""
+import importlib
+import json
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parents[1]
+
+
+def test_cpulist_parsing(ffk):
+    h = importlib.import_module("flexflow_train_b200.hostmem")
+    assert h._parse_cpulist("0-3,8,10-11\n") == [0, 1, 2, 3, 8, 10, 11]
+    assert h._parse_cpulist("") == []
+    info = h.bind_host_thread_to_gpu_node(0)   # no GPU here: must report, not raise
+    assert info["bound"] in (False, True) and "gpu_numa_node" in info
+
+
+def test_strategy_file_names_a_tensor_parallel_degree():
+    s = json.loads((ROOT / "strategies" / "bert_tp2.json").read_text())
+    assert int(s["tensor_parallel"]) == 2
+
+
+def test_peer_memory_and_static_entry_points_are_exported(ffk):
+    lib = ffk.lib()
+    for name in ("ffk_p2p_create", "ffk_p2p_connect", "ffk_p2p_local_buffer", "ffk_p2p_all_reduce_sum",
+                 "ffk_p2p_status", "ffk_p2p_destroy", "ffk_layer_norm_backward_static"):
+        assert name in lib.protos and hasattr(lib.cdll, name)
