@@ -12,8 +12,12 @@ the per-operator hot path over one batch of 8192 samples:
 
 all through the C ABI of libffk.so (include/*.h). metric = training samples/sec =
 8192 * n_gpus / step time. With --gpus N > 1 every rank runs the step on its own batch (weak
-scaling) and the weight gradients (Linear dW/db, LayerNorm dgamma/dbeta) are summed over ranks
-with one NCCL all-reduce per step — the Replicate-backward exchange of data parallelism.
+scaling) and the weight gradients (Linear dW/db, LayerNorm dgamma/dbeta) are summed over ranks —
+the Replicate-backward exchange of data parallelism — by the peer-memory all-reduce kernels of
+libffk.so (ffk_p2p_*; FFK_BENCH_GRAD_SYNC=nccl selects NCCL all-reduces instead).
+
+Other workloads (not the headline line): --workload mlp (configs[0], one CUDA-graph replay per
+step), encoder (configs[2]), bert [--tp T | --strategy file.json] (configs[3]), dlrm (configs[4]).
 
 The JSON line also carries: roofline (the tcgen05 GEMM of Linear forward against the measured
 bf16 peak), cpu_baseline (the CPU oracle on a bounded sample of the same step, rank 0, N=1),
