@@ -100,15 +100,23 @@ class LocalCostEstimator:
 # ---- tensor movement (the reference returns 0.0): NVLink 5 through NVSwitch
 NVLINK_PEER_GBS = 770.0        # measured peer copy, per direction per GPU (B200_PROFILING.md)
 NVLINK_ALLREDUCE_BUS_GBS = 725.0  # measured 8-rank all-reduce bus bandwidth at 1 GiB
-LAUNCH_LATENCY_MS = 0.02       # one collective launch
+HALF_RATE_BYTES = 17e6         # message size at which a collective reaches half of that rate
+LAUNCH_LATENCY_MS = 0.015      # one collective: launch + one switch round trip
+ONE_SHOT_BYTES = 512 << 10     # up to here every rank talks to all peers directly
+ONE_SHOT_GBS = 100.0           # per-rank rate of those small exchanges
 
 
 def estimate_movement_ms(num_bytes: int, kind: str = "copy", ranks: int = 2) -> float:
     """Milliseconds to move one tensor between GPUs of one NVSwitch domain.
-    kind: copy (point to point), all_reduce, all_gather, reduce_scatter, all_to_all."""
+    kind: copy (point to point), all_reduce, all_gather, reduce_scatter, all_to_all.
+    Calibrated on this repository's own collectives (profiles/r01_summary.md): 32 KB all-reduce
+    at 8 ranks 14.9 us, 33.6 MB 139 us at 8 ranks and 78 us at 2."""
     if num_bytes <= 0 or ranks <= 1:
         return 0.0
     if kind == "copy":
         return LAUNCH_LATENCY_MS + num_bytes / (NVLINK_PEER_GBS * 1e6)
     factor = 2.0 * (ranks - 1) / ranks if kind == "all_reduce" else (ranks - 1) / ranks
-    return LAUNCH_LATENCY_MS + factor * num_bytes / (NVLINK_ALLREDUCE_BUS_GBS * 1e6)
+    if num_bytes <= ONE_SHOT_BYTES:  # latency-bound protocols (push / one-shot reads)
+        return LAUNCH_LATENCY_MS + factor * num_bytes / (ONE_SHOT_GBS * 1e6)
+    rate = NVLINK_ALLREDUCE_BUS_GBS * num_bytes / (num_bytes + HALF_RATE_BYTES)  # GB/s at this size
+    return LAUNCH_LATENCY_MS + factor * num_bytes / (rate * 1e6)

@@ -25,3 +25,15 @@ def test_peer_memory_and_static_entry_points_are_exported(ffk):
     for name in ("ffk_p2p_create", "ffk_p2p_connect", "ffk_p2p_local_buffer", "ffk_p2p_all_reduce_sum",
                  "ffk_p2p_status", "ffk_p2p_destroy", "ffk_layer_norm_backward_static"):
         assert name in lib.protos and hasattr(lib.cdll, name)
+
+
+def test_movement_model_reproduces_measured_collectives(ffk):
+    """The NVLink model of the cost estimator against the all-reduce times measured on B200
+    (profiles/r01_summary.md), within 25 %."""
+    ce = importlib.import_module("flexflow_train_b200.cost_estimator")
+    for nbytes, ranks, measured_ms in ((32768, 8, 0.0149), (33.563e6, 8, 0.1387), (33.563e6, 2, 0.0778)):
+        got = ce.estimate_movement_ms(int(nbytes), "all_reduce", ranks)
+        assert abs(got - measured_ms) <= 0.25 * measured_ms, (nbytes, ranks, got, measured_ms)
+    assert ce.estimate_movement_ms(0, "all_reduce", 8) == 0.0
+    assert ce.estimate_movement_ms(1 << 20, "all_reduce", 1) == 0.0
+    assert ce.estimate_movement_ms(1 << 30, "copy", 2) > ce.estimate_movement_ms(1 << 20, "copy", 2)
