@@ -487,9 +487,10 @@ def run_encoder(args):
     bert = args.workload == "bert"
     tp = 1
     if args.strategy:
-        # "imported search strategy": the one placement decision this driver understands is the
-        # tensor-parallel degree of the split blocks ({"tensor_parallel": T}); the rest is data parallel
-        tp = int(json.loads(Path(args.strategy).read_text()).get("tensor_parallel", 1))
+        # "imported search strategy": {"tensor_parallel": T}, or a parallel computation graph in the
+        # reference's v1 JSON layout, from whose Replicate / Reduction nodes the degree is read
+        # (flexflow-train_b200/strategy.py); the rest of the world size is data parallel
+        tp = importlib.import_module("flexflow_train_b200.strategy").load_strategy(args.strategy).tensor_parallel
     if args.tp:
         tp = args.tp
     if not bert or world % tp != 0:

@@ -37,3 +37,27 @@ def test_movement_model_reproduces_measured_collectives(ffk):
     assert ce.estimate_movement_ms(0, "all_reduce", 8) == 0.0
     assert ce.estimate_movement_ms(1 << 20, "all_reduce", 1) == 0.0
     assert ce.estimate_movement_ms(1 << 30, "copy", 2) > ce.estimate_movement_ms(1 << 20, "copy", 2)
+
+
+def test_strategy_reader_understands_both_forms(ffk, tmp_path):
+    S = importlib.import_module("flexflow_train_b200.strategy")
+    assert S.load_strategy(ROOT / "strategies" / "bert_tp2.json").tensor_parallel == 2
+    # a parallel computation graph in the reference's v1 layout: input -> Repartition(sample dim, 4)
+    # -> Replicate(2) -> Linear -> Reduction(2) -> Combine(sample dim, 4)
+    def layer(kind, value):
+        return {"op_attrs": {"type": kind, "value": value}, "name": None}
+    pcg = {"raw_graph": {
+        "node_labels": {"0": layer("InputAttrs", {}),
+                        "1": layer("RepartitionAttrs", {"repartition_dim": {"value": 0}, "repartition_degree": 4}),
+                        "2": layer("ReplicateAttrs", {"replicate_degree": 2}),
+                        "3": layer("LinearAttrs", {"out_channels": 3072, "use_bias": True}),
+                        "4": layer("ReductionAttrs", {"reduction_degree": 2}),
+                        "5": layer("CombineAttrs", {"combine_dim": 0, "combine_degree": 4})},
+        "output_labels": {},
+        "graph": {"nodes": [0, 1, 2, 3, 4, 5],
+                  "edges": [{"srcNode": i, "srcIdx": 0, "dstNode": i + 1, "dstIdx": 0} for i in range(5)]}}}
+    p = tmp_path / "pcg.json"
+    p.write_text(json.dumps(pcg))
+    s = S.load_strategy(p)
+    assert s.tensor_parallel == 2 and s.data_parallel == 4
+    assert sorted(f["op"] for f in s.parallel_ops) == ["combine", "reduction", "repartition", "replicate"]
