@@ -9,8 +9,12 @@
 // Cross-rank ordering uses flags that live in each rank's region and only ever grow: a launch
 // takes its epoch from a counter in device memory that its last block increments, so the same
 // launch can be replayed (CUDA graph) and no host state has to agree between ranks beyond
-// "everybody calls the collectives in the same order". Waits are bounded (a peer that never
-// arrives turns into FFK_ERR_CUDA on the next status query instead of a hung GPU).
+// "everybody calls the collectives in the same order". Waits are bounded (FFK_P2P_TIMEOUT_MS,
+// 30 s by default). A wait that expires never publishes a sum: the rank raises a sticky failure
+// flag in EVERY rank's control block, overwrites its own output range with NaN bit patterns and
+// leaves without the done / epoch hand-off; every rank that sees the flag (inside a wait or at
+// the entry of a later launch) does the same, so a late or missing rank turns into NaN
+// gradients and FFK_ERR_CUDA from ffk_p2p_status on all ranks instead of silently wrong sums.
 #include "common.cuh"
 
 #include <cstdlib>
@@ -27,14 +31,14 @@ constexpr size_t kOneShotLimit = 512 << 10;  // bytes: below, every rank reads a
 // receive slots of the push protocol: [parity][source rank][kPushLimit], after the Control block
 constexpr size_t kSlotBytes = 2 * size_t(kMaxRanks) * kPushLimit;
 constexpr size_t kFlagBytes = kControlBytes + kSlotBytes;  // data part starts here
-constexpr long long kSpinLimit = 4000000000LL;  // ~2 s of SM clocks
+constexpr unsigned long long kDefaultTimeoutNs = 30ull * 1000000000ull;  // FFK_P2P_TIMEOUT_MS overrides
 
 struct Control {                 // lives at the head of each rank's region (device memory)
   unsigned flags[kPhases][kMaxRanks];
   unsigned epoch;                // completed launches
   unsigned blocks_done;          // grid-wide arrival counters of the current launch
   unsigned blocks_mid;
-  unsigned timed_out;            // sticky: a bounded wait expired
+  unsigned timed_out;            // sticky: a bounded wait expired on this or on another rank
 };
 static_assert(sizeof(Control) <= kControlBytes, "control block must fit the reserved head");
 
@@ -49,6 +53,7 @@ struct Group {
   void *peer_mapped[kMaxRanks] = {};  // cudaIpcOpenMemHandle results (own slot unused)
   PeerTable table{};
   bool connected = false;
+  unsigned long long timeout_ns = kDefaultTimeoutNs;
 };
 
 __device__ __forceinline__ void st_release_sys(unsigned *p, unsigned v) {
@@ -71,6 +76,12 @@ __device__ __forceinline__ uint4 ld_peer16(void const *p) {
   return v;
 }
 
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
 // Tell every peer that this rank reached `phase` of launch `epoch`.
 __device__ void signal_peers(PeerTable const &t, int rank, int world, int phase, unsigned epoch) {
   if (threadIdx.x < world) {
@@ -78,18 +89,43 @@ __device__ void signal_peers(PeerTable const &t, int rank, int world, int phase,
     st_release_sys(&c->flags[phase][rank], epoch);
   }
 }
-// Wait (bounded) until every rank has signalled `phase` of launch `epoch` in OUR control block.
-__device__ void wait_peers(Control *mine, int world, int phase, unsigned epoch) {
-  if (threadIdx.x < world) {
-    long long const t0 = clock64();
-    while (ld_acquire_sys(&mine->flags[phase][threadIdx.x]) < epoch) {
-      if (clock64() - t0 > kSpinLimit) {
-        mine->timed_out = 1;
-        break;
+// A bounded wait expired: raise the sticky failure flag on every rank (own block included).
+__device__ void poison_all(PeerTable const &t, int world) {
+  for (int p = 0; p < world; ++p)
+    st_release_sys(&reinterpret_cast<Control *>(t.base[p])->timed_out, 1u);
+  __threadfence_system();
+}
+// One thread spins until *flag >= epoch. false = the wait expired here (all ranks are then
+// poisoned) or another rank has poisoned this one.
+__device__ bool spin_until(PeerTable const &t, Control *mine, int world, unsigned const *flag,
+                           unsigned epoch, unsigned long long timeout_ns) {
+  unsigned long long const t0 = global_ns();
+  unsigned polls = 0;
+  while (ld_acquire_sys(flag) < epoch) {
+    if ((++polls & 255u) == 0) {
+      if (ld_acquire_sys(&mine->timed_out)) return false;
+      if (global_ns() - t0 > timeout_ns) {
+        poison_all(t, world);
+        return false;
       }
     }
   }
-  __syncthreads();
+  return true;
+}
+// Wait (bounded) until every rank has signalled `phase` of launch `epoch` in OUR control block.
+// Returns the same verdict to every thread of the block.
+__device__ bool wait_peers(PeerTable const &t, Control *mine, int world, int phase, unsigned epoch,
+                           unsigned long long timeout_ns) {
+  int ok = 1;
+  if (threadIdx.x < world)
+    ok = spin_until(t, mine, world, &mine->flags[phase][threadIdx.x], epoch, timeout_ns) ? 1 : 0;
+  return __syncthreads_and(ok) != 0;
+}
+// The failed launch's result: all-ones packets (NaN in fp32, half and bf16) over the output.
+__device__ void nan_fill(unsigned char *out_local, size_t npk) {
+  uint4 const q = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);
+  for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < npk; i += size_t(gridDim.x) * blockDim.x)
+    *reinterpret_cast<uint4 *>(out_local + i * 16) = q;
 }
 
 template <typename T> struct Acc16 {
@@ -118,17 +154,25 @@ template <typename T> struct Acc16 {
 template <typename T>
 __global__ void __launch_bounds__(512)
     p2p_all_reduce_kernel(PeerTable t, int rank, int world, size_t in_off, size_t out_off,
-                          size_t npk, int two_shot) {
+                          size_t npk, int two_shot, unsigned long long timeout_ns) {
   Control *mine = reinterpret_cast<Control *>(t.base[rank]);
   unsigned const epoch = mine->epoch + 1;  // every block reads it before the last block bumps it
   size_t const tid = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
   size_t const nthreads = size_t(gridDim.x) * blockDim.x;
+  unsigned char *out_local = t.base[rank] + kFlagBytes + out_off;
 
+  // a group that has failed once fails fast from then on
+  if (__syncthreads_or(threadIdx.x == 0 ? int(ld_acquire_sys(&mine->timed_out)) : 0)) {
+    nan_fill(out_local, npk);
+    return;
+  }
   // ---- entry: every rank's input is complete (stream order on its side) once its kernel runs
   if (blockIdx.x == 0) signal_peers(t, rank, world, 0, epoch);
-  wait_peers(mine, world, 0, epoch);
+  if (!wait_peers(t, mine, world, 0, epoch, timeout_ns)) {
+    nan_fill(out_local, npk);
+    return;
+  }
 
-  unsigned char *out_local = t.base[rank] + kFlagBytes + out_off;
   if (!two_shot) {
     for (size_t i = tid; i < npk; i += nthreads) {
       Acc16<T> acc;
@@ -189,15 +233,18 @@ __global__ void __launch_bounds__(512)
       }
     }
     // the block that completed the count tells the peers; everybody waits on local flags
-    if (threadIdx.x == 0) {
-      long long const t0 = clock64();
-      while (ld_acquire_sys(&mine->flags[1][rank]) < epoch) {
-        if (clock64() - t0 > kSpinLimit) { mine->timed_out = 1; break; }
-      }
+    int mid_ok = 1;
+    if (threadIdx.x == 0)
+      mid_ok = spin_until(t, mine, world, &mine->flags[1][rank], epoch, timeout_ns) ? 1 : 0;
+    if (!__syncthreads_and(mid_ok)) {
+      nan_fill(out_local, npk);
+      return;
     }
-    __syncthreads();
     if (blockIdx.x == 0) signal_peers(t, rank, world, 1, epoch);
-    wait_peers(mine, world, 1, epoch);
+    if (!wait_peers(t, mine, world, 1, epoch, timeout_ns)) {
+      nan_fill(out_local, npk);
+      return;
+    }
     // ---- gather the other ranks' reduced chunks
     for (int q = 1; q < world; ++q) {
       int const p = (rank + q) % world;  // spread the ranks over different peers at any moment
@@ -228,13 +275,12 @@ __global__ void __launch_bounds__(512)
       mine->blocks_done = 0;
       for (int p = 0; p < world; ++p)
         st_release_sys(&reinterpret_cast<Control *>(t.base[p])->flags[2][rank], epoch);
-      long long const t0 = clock64();
-      for (int p = 0; p < world; ++p)
-        while (ld_acquire_sys(&mine->flags[2][p]) < epoch) {
-          if (clock64() - t0 > kSpinLimit) { mine->timed_out = 1; break; }
-        }
+      bool ok = true;
+      for (int p = 0; p < world && ok; ++p)
+        ok = spin_until(t, mine, world, &mine->flags[2][p], epoch, timeout_ns);
       __threadfence_system();
-      mine->epoch = epoch;  // the next launch on this stream starts after this kernel has ended
+      // no hand-off after a failure: the epoch stays, later launches leave at their entry check
+      if (ok) mine->epoch = epoch;  // the next launch on this stream starts after this kernel has ended
     }
   }
 }
@@ -249,11 +295,16 @@ __global__ void __launch_bounds__(512)
 template <typename T>
 __global__ void __launch_bounds__(512)
     p2p_push_all_reduce_kernel(PeerTable t, int rank, int world, size_t in_off, size_t out_off,
-                               size_t npk) {
+                               size_t npk, unsigned long long timeout_ns) {
   Control *mine = reinterpret_cast<Control *>(t.base[rank]);
   unsigned const epoch = mine->epoch + 1;
   int const parity = int(epoch & 1u);
   unsigned char const *in_local = t.base[rank] + kFlagBytes + in_off;
+  unsigned char *out_local = t.base[rank] + kFlagBytes + out_off;
+  if (__syncthreads_or(threadIdx.x == 0 ? int(ld_acquire_sys(&mine->timed_out)) : 0)) {
+    nan_fill(out_local, npk);
+    return;
+  }
   for (int p = blockIdx.x; p < world; p += gridDim.x) {
     unsigned char *slot = t.base[p] + kControlBytes + (size_t(parity) * kMaxRanks + rank) * kPushLimit;
     for (size_t i = threadIdx.x; i < npk; i += blockDim.x)
@@ -264,9 +315,11 @@ __global__ void __launch_bounds__(512)
       st_release_sys(&reinterpret_cast<Control *>(t.base[p])->flags[3 + parity][rank], epoch);
     }
   }
-  wait_peers(mine, world, 3 + parity, epoch);
+  if (!wait_peers(t, mine, world, 3 + parity, epoch, timeout_ns)) {
+    nan_fill(out_local, npk);
+    return;
+  }
   unsigned char const *slots = t.base[rank] + kControlBytes + size_t(parity) * kMaxRanks * kPushLimit;
-  unsigned char *out_local = t.base[rank] + kFlagBytes + out_off;
   size_t const tid = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
   for (size_t i = tid; i < npk; i += size_t(gridDim.x) * blockDim.x) {
     Acc16<T> acc;
@@ -303,6 +356,10 @@ int ffk_p2p_create(void **group_out, int rank, int world, size_t data_bytes,
   g->rank = rank;
   g->world = world;
   g->data_bytes = data_bytes;
+  if (char const *e = std::getenv("FFK_P2P_TIMEOUT_MS")) {
+    long long ms = atoll(e);
+    if (ms > 0) g->timeout_ns = (unsigned long long)ms * 1000000ull;
+  }
   cudaIpcMemHandle_t h;
   cudaError_t err = cudaGetDevice(&g->device);
   if (err == cudaSuccess) err = cudaMalloc(reinterpret_cast<void **>(&g->local), kFlagBytes + data_bytes);
@@ -365,13 +422,13 @@ int ffk_p2p_all_reduce_sum(void *stream, void *group, size_t in_offset, size_t o
     unsigned blocks = unsigned(g->world);
     switch (dtype) {
       case FFK_FLOAT:
-        p2p_push_all_reduce_kernel<float><<<blocks, 512, 0, s>>>(g->table, g->rank, g->world, in_offset, out_offset, npk);
+        p2p_push_all_reduce_kernel<float><<<blocks, 512, 0, s>>>(g->table, g->rank, g->world, in_offset, out_offset, npk, g->timeout_ns);
         break;
       case FFK_HALF:
-        p2p_push_all_reduce_kernel<__half><<<blocks, 512, 0, s>>>(g->table, g->rank, g->world, in_offset, out_offset, npk);
+        p2p_push_all_reduce_kernel<__half><<<blocks, 512, 0, s>>>(g->table, g->rank, g->world, in_offset, out_offset, npk, g->timeout_ns);
         break;
       default:
-        p2p_push_all_reduce_kernel<__nv_bfloat16><<<blocks, 512, 0, s>>>(g->table, g->rank, g->world, in_offset, out_offset, npk);
+        p2p_push_all_reduce_kernel<__nv_bfloat16><<<blocks, 512, 0, s>>>(g->table, g->rank, g->world, in_offset, out_offset, npk, g->timeout_ns);
         break;
     }
     FFK_LAUNCH_CHECK();
@@ -386,13 +443,13 @@ int ffk_p2p_all_reduce_sum(void *stream, void *group, size_t in_offset, size_t o
   }
   switch (dtype) {
     case FFK_FLOAT:
-      p2p_all_reduce_kernel<float><<<blocks, 512, 0, s>>>(g->table, g->rank, g->world, in_offset, out_offset, npk, two_shot);
+      p2p_all_reduce_kernel<float><<<blocks, 512, 0, s>>>(g->table, g->rank, g->world, in_offset, out_offset, npk, two_shot, g->timeout_ns);
       break;
     case FFK_HALF:
-      p2p_all_reduce_kernel<__half><<<blocks, 512, 0, s>>>(g->table, g->rank, g->world, in_offset, out_offset, npk, two_shot);
+      p2p_all_reduce_kernel<__half><<<blocks, 512, 0, s>>>(g->table, g->rank, g->world, in_offset, out_offset, npk, two_shot, g->timeout_ns);
       break;
     default:
-      p2p_all_reduce_kernel<__nv_bfloat16><<<blocks, 512, 0, s>>>(g->table, g->rank, g->world, in_offset, out_offset, npk, two_shot);
+      p2p_all_reduce_kernel<__nv_bfloat16><<<blocks, 512, 0, s>>>(g->table, g->rank, g->world, in_offset, out_offset, npk, two_shot, g->timeout_ns);
       break;
   }
   FFK_LAUNCH_CHECK();
@@ -405,7 +462,8 @@ int ffk_p2p_status(void *group) {
   Control c;
   FFK_CUDA(cudaMemcpy(&c, g->local, sizeof(c), cudaMemcpyDeviceToHost));
   if (c.timed_out) {
-    set_error("p2p: a wait for a peer rank expired (a rank did not reach the collective)");
+    set_error("p2p: a wait for a peer rank expired on some rank of the group (a rank did not reach a "
+              "collective in time); results since then are NaN and the group must be recreated");
     return FFK_ERR_CUDA;
   }
   return FFK_OK;

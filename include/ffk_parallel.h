@@ -63,7 +63,10 @@ int ffk_p2p_local_buffer(void *group, void **data_out, size_t *bytes_out);
  * gathered (two shots). Every rank
  * must issue the group's collectives in the same order. The input may be overwritten and the
  * output read as soon as the kernel has finished on the caller's stream. Waits for peers are
- * bounded (~2 s): a rank that never arrives shows up in ffk_p2p_status, not as a hung GPU. */
+ * bounded (30 s; FFK_P2P_TIMEOUT_MS, read by ffk_p2p_create, overrides). A wait that expires
+ * never publishes a sum: the failure flag is raised on EVERY rank of the group, each rank's
+ * output range of the failed launch and of every later launch is filled with NaN bit patterns,
+ * and ffk_p2p_status returns FFK_ERR_CUDA on all ranks until the group is destroyed. */
 int ffk_p2p_all_reduce_sum(void *stream, void *group, size_t in_offset, size_t out_offset,
                            size_t count, int dtype);
 int ffk_p2p_status(void *group);
