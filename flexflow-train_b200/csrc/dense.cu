@@ -148,9 +148,10 @@ extern "C" {
 
 int ffk_set_gemm_workspace(void *workspace, size_t workspace_bytes) {
   FFK_REQUIRE(workspace == nullptr || aligned16(workspace), "gemm workspace must be 16-byte aligned");
-  gemm::set_workspace(workspace, workspace ? workspace_bytes : 0);
-  return FFK_OK;
+  return gemm::set_workspace(workspace, workspace ? workspace_bytes : 0);
 }
+
+int ffk_set_gemm_fp32_tensor_math(int allow) { return gemm::set_fp32_tensor_math(allow); }
 
 int ffk_gemm(void *stream, void const *a, void const *b, void *d, int M, int N, int K, int batch,
              long long lda, long long ldb, long long ldd, long long a_batch_stride,

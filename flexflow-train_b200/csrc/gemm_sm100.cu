@@ -1308,11 +1308,65 @@ __global__ void __launch_bounds__(256)
   }
 }
 
+// Scratch registered with ffk_set_gemm_workspace: one slot per DEVICE (the registration and
+// every use look the slot up by the current device, so a process that drives several GPUs keeps
+// them apart). Uses on different streams of one device are serialised with an event recorded
+// behind the last consumer; a use inside a stream capture cannot be ordered against another
+// stream and is refused there.
 struct Scratch {
   void *ptr = nullptr;
   size_t bytes = 0;
+  int fp32_tensor_math = 0;      // ffk_set_gemm_fp32_tensor_math: AUTO may split fp32 into bf16 terms
+  cudaStream_t last_stream = nullptr;
+  bool used = false;             // last_stream is meaningful
+  bool last_captured = false;    // the last use was recorded into a CUDA graph
+  cudaEvent_t last_use = nullptr;
 };
-Scratch g_scratch;  // one process per GPU; registered by the owner of the device handle
+constexpr int kMaxDevices = 64;
+Scratch g_scratch_table[kMaxDevices];
+std::mutex g_scratch_mu;
+
+Scratch *scratch_slot() {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) return nullptr;
+  return &g_scratch_table[dev];
+}
+
+bool stream_capturing(cudaStream_t s) {
+  cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(s, &st) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return st != cudaStreamCaptureStatusNone;
+}
+
+// Order `stream` behind the scratch's previous consumer. Returns FFK_ERR_UNSUPPORTED when that
+// is impossible (the caller then takes the path that needs no scratch).
+int scratch_acquire(Scratch &sc, cudaStream_t stream) {
+  if (!sc.used || sc.last_stream == stream) return FFK_OK;
+  if (sc.last_captured || stream_capturing(stream)) {
+    set_error("gemm scratch: last used on another stream inside / outside a stream capture");
+    return FFK_ERR_UNSUPPORTED;
+  }
+  if (sc.last_use && cudaStreamWaitEvent(stream, sc.last_use, 0) != cudaSuccess) {
+    cudaGetLastError();
+    return FFK_ERR_CUDA;
+  }
+  return FFK_OK;
+}
+void scratch_release(Scratch &sc, cudaStream_t stream) {
+  sc.used = true;
+  sc.last_stream = stream;
+  sc.last_captured = stream_capturing(stream);
+  if (sc.last_captured) return;
+  if (!sc.last_use && cudaEventCreateWithFlags(&sc.last_use, cudaEventDisableTiming) != cudaSuccess) {
+    cudaGetLastError();
+    sc.last_use = nullptr;
+    return;
+  }
+  cudaEventRecord(sc.last_use, stream);
+}
 
 // Element count of a stored operand (rows x ld for every batch).
 size_t operand_elems(long long rows, long long ld, long long batch_stride, long long batch2_stride,
@@ -1327,9 +1381,40 @@ size_t operand_elems(long long rows, long long ld, long long batch_stride, long 
 
 }  // namespace
 
-void set_workspace(void *ptr, size_t bytes) {
-  g_scratch.ptr = ptr;
-  g_scratch.bytes = bytes;
+int set_workspace(void *ptr, size_t bytes) {
+  std::lock_guard<std::mutex> lock(g_scratch_mu);
+  Scratch *sc = scratch_slot();
+  if (!sc) {
+    set_error("gemm workspace: no current CUDA device");
+    return FFK_ERR_CUDA;
+  }
+  if (ptr) {
+    cudaPointerAttributes attr{};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (cudaPointerGetAttributes(&attr, ptr) != cudaSuccess || attr.type != cudaMemoryTypeDevice ||
+        attr.device != dev) {
+      cudaGetLastError();
+      set_error("gemm workspace: the pointer is not device memory of the current device %d", dev);
+      return FFK_ERR_INVALID;
+    }
+  }
+  sc->ptr = ptr;
+  sc->bytes = ptr ? bytes : 0;
+  sc->used = false;
+  sc->last_captured = false;
+  return FFK_OK;
+}
+
+int set_fp32_tensor_math(int allow) {
+  std::lock_guard<std::mutex> lock(g_scratch_mu);
+  Scratch *sc = scratch_slot();
+  if (!sc) {
+    set_error("gemm fp32 policy: no current CUDA device");
+    return FFK_ERR_CUDA;
+  }
+  sc->fp32_tensor_math = allow ? 1 : 0;
+  return FFK_OK;
 }
 
 size_t split_workspace_bytes(Problem const &p) {
@@ -1384,7 +1469,17 @@ int launch_split_bf16(Problem const &p, Epilogue const &e, cudaStream_t stream, 
 }
 
 int launch_split_bf16_registered(Problem const &p, Epilogue const &e, cudaStream_t stream) {
-  return launch_split_bf16(p, e, stream, g_scratch.ptr, g_scratch.bytes);
+  std::lock_guard<std::mutex> lock(g_scratch_mu);
+  Scratch *sc = scratch_slot();
+  if (!sc || !sc->ptr) {
+    set_error("split-bf16 gemm: no scratch registered for the current device (ffk_set_gemm_workspace)");
+    return FFK_ERR_UNSUPPORTED;
+  }
+  int rc = scratch_acquire(*sc, stream);
+  if (rc) return rc;
+  rc = launch_split_bf16(p, e, stream, sc->ptr, sc->bytes);
+  scratch_release(*sc, stream);
+  return rc;
 }
 
 namespace {
@@ -1422,11 +1517,11 @@ bool operand_ok(void const *ptr, long long ld, long long bs, long long bs2, int 
 }
 
 // Returns FFK_OK and fills `q` when the operands that needed it were repacked into the scratch.
-int repack_for_tensor_cores(Problem const &p, Problem &q, cudaStream_t stream) {
+int repack_for_tensor_cores(Problem const &p, Problem &q, cudaStream_t stream, Scratch const &sc) {
   int const b2 = p.batch2 > 1 ? p.batch2 : 1, bo = p.batch / b2;
   if (p.batch % b2 != 0) return FFK_ERR_UNSUPPORTED;
-  char *cursor = static_cast<char *>(g_scratch.ptr);
-  size_t left = g_scratch.bytes;
+  char *cursor = static_cast<char *>(sc.ptr);
+  size_t left = sc.bytes;
   q = p;
   q.scratch_busy = true;
   auto fix = [&](void const *&ptr, long long &ld, long long &bs, long long &bs2, long long rows,
@@ -1461,21 +1556,36 @@ int launch(Problem const &p, Epilogue const &e, cudaStream_t stream) {
   if (p.M <= 0 || p.N <= 0 || p.batch <= 0) return FFK_OK;
   bool sixteen = p.in_dtype == FFK_BFLOAT16 || p.in_dtype == FFK_HALF;
   if (sixteen && p.K > 0 && tc_eligible(p, e)) return launch_tc(p, e, stream);
-  if (sixteen && p.K >= 64 && g_scratch.ptr && !p.scratch_busy && aligned16(g_scratch.ptr) &&
-      double(p.M) * p.N * p.K * p.batch >= double(1 << 27)) {
-    Problem q;
-    if (repack_for_tensor_cores(p, q, stream) == FFK_OK && tc_eligible(q, e)) return launch_tc(q, e, stream);
-  }
-  // large fp32 products: tensor cores through the bf16 split when scratch has been registered
-  if (p.in_dtype == FFK_FLOAT && p.out_dtype == FFK_FLOAT && p.K >= 64 && g_scratch.ptr &&
-      double(p.M) * p.N * p.K * p.batch >= double(1 << 27) && e.alpha == 1.f &&
-      !(e.accumulate && (e.act != ACT_NONE || e.bias))) {
-    Problem q = p;
-    q.in_dtype = FFK_BFLOAT16;
-    size_t os = sizeof(float);
-    bool d_ok = aligned16(e.d) && (e.ldd * os) % 16 == 0;
-    if (tc_eligible(q, e) && d_ok && split_workspace_bytes(p) <= g_scratch.bytes)
-      return launch_split_bf16(p, e, stream, g_scratch.ptr, g_scratch.bytes);
+  bool const big = p.K >= 64 && double(p.M) * p.N * p.K * p.batch >= double(1 << 27);
+  if (big && (sixteen || p.in_dtype == FFK_FLOAT)) {
+    std::lock_guard<std::mutex> lock(g_scratch_mu);
+    Scratch *sc = scratch_slot();
+    if (sc && sc->ptr && aligned16(sc->ptr)) {
+      // 16-bit operands that break TMA's pitch rule: repacked into the scratch
+      if (sixteen && !p.scratch_busy && scratch_acquire(*sc, stream) == FFK_OK) {
+        Problem q;
+        if (repack_for_tensor_cores(p, q, stream, *sc) == FFK_OK && tc_eligible(q, e)) {
+          int rc = launch_tc(q, e, stream);
+          scratch_release(*sc, stream);
+          return rc;
+        }
+        scratch_release(*sc, stream);  // a repack kernel may have been queued
+      }
+      // large fp32 products: tensor cores through the bf16 split, when the owner of the device
+      // handle allows it (PerDeviceFFHandle::allowTensorOpMathConversion)
+      if (p.in_dtype == FFK_FLOAT && p.out_dtype == FFK_FLOAT && sc->fp32_tensor_math &&
+          e.alpha == 1.f && !(e.accumulate && (e.act != ACT_NONE || e.bias))) {
+        Problem q = p;
+        q.in_dtype = FFK_BFLOAT16;
+        bool d_ok = aligned16(e.d) && (e.ldd * sizeof(float)) % 16 == 0;
+        if (tc_eligible(q, e) && d_ok && split_workspace_bytes(p) <= sc->bytes &&
+            scratch_acquire(*sc, stream) == FFK_OK) {
+          int rc = launch_split_bf16(p, e, stream, sc->ptr, sc->bytes);
+          scratch_release(*sc, stream);
+          return rc;
+        }
+      }
+    }
   }
   return launch_simt(p, e, stream);
 }

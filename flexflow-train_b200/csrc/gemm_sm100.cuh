@@ -80,7 +80,10 @@ int launch_split_bf16(Problem const &p, Epilogue const &e, cudaStream_t stream, 
 
 // Scratch registered by the caller for GEMM-based entry points (the analogue of
 // cublasSetWorkspace); used by AUTO to run large fp32 products through launch_split_bf16.
-void set_workspace(void *ptr, size_t bytes);
+// One slot per device (the current one); uses on different streams are event-ordered.
+int set_workspace(void *ptr, size_t bytes);
+// AUTO may run large fp32 products through the bf16 split (current device's slot).
+int set_fp32_tensor_math(int allow);
 int launch_split_bf16_registered(Problem const &p, Epilogue const &e, cudaStream_t stream);
 
 // Picks the tensor path for 16-bit inputs when eligible; large fp32 products take the

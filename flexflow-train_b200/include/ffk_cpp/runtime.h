@@ -107,12 +107,18 @@ private:
 };
 
 // managed_per_device_ff_handle.h:8-27 (1 MiB workspace, tensor-op conversion allowed).
-// `gemm_scratch_bytes` > 0 additionally reserves scratch BEHIND the op workspace and registers
-// it with ffk_set_gemm_workspace, which lets fp32 Linear / BatchMatmul / MultiHeadAttention /
-// Conv2D run on the tensor cores (bf16 split, fp32-class accuracy). It is kept apart from
-// `workSpace` because an op's own scratch (e.g. Conv2D's im2col panel) can be a GEMM operand.
+// Behind the op workspace the handle also reserves GEMM scratch (256 MiB by default: 0.14 % of
+// the GPU's memory) and registers it for this device with ffk_set_gemm_workspace; and because
+// the reference's handle says allowTensorOpMathConversion = true (managed_per_device_ff_handle.cc:9)
+// it switches ffk_set_gemm_fp32_tensor_math on. An UNCHANGED fp32 caller of Linear / BatchMatmul /
+// MultiHeadAttention / Conv2D therefore runs its large products on the tensor cores (bf16 split,
+// fp32-class accuracy). The scratch is kept apart from `workSpace` because an op's own scratch
+// (e.g. Conv2D's im2col panel) can be a GEMM operand. gemm_scratch_bytes = 0 leaves fp32 products
+// on the exact CUDA-core kernel.
 struct ManagedPerDeviceFFHandle {
-  explicit ManagedPerDeviceFFHandle(size_t workspace_bytes = 1024 * 1024, size_t gemm_scratch_bytes = 0)
+  static constexpr size_t kDefaultGemmScratch = size_t(256) << 20;
+  explicit ManagedPerDeviceFFHandle(size_t workspace_bytes = 1024 * 1024,
+                                    size_t gemm_scratch_bytes = kDefaultGemmScratch)
       : handle(new PerDeviceFFHandle) {
     ffk_handle_t h;
     size_t ws = (workspace_bytes + 255) / 256 * 256;
@@ -120,6 +126,7 @@ struct ManagedPerDeviceFFHandle {
     *handle = PerDeviceFFHandle{nullptr, nullptr, h.workSpace, ws, true, nullptr};
     if (gemm_scratch_bytes) {
       FFK_CHECK(ffk_set_gemm_workspace(static_cast<char *>(h.workSpace) + ws, gemm_scratch_bytes));
+      FFK_CHECK(ffk_set_gemm_fp32_tensor_math(handle->allowTensorOpMathConversion ? 1 : 0));
       owns_gemm_scratch = true;
     }
   }
@@ -134,7 +141,10 @@ struct ManagedPerDeviceFFHandle {
   }
   ~ManagedPerDeviceFFHandle() {
     if (handle) {
-      if (owns_gemm_scratch) ffk_set_gemm_workspace(nullptr, 0);
+      if (owns_gemm_scratch) {
+        ffk_set_gemm_workspace(nullptr, 0);
+        ffk_set_gemm_fp32_tensor_math(0);
+      }
       ffk_handle_t h{nullptr, nullptr, handle->workSpace, handle->workSpaceSize, 1, nullptr};
       ffk_handle_destroy(&h);
       delete handle;

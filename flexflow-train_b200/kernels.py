@@ -69,22 +69,27 @@ def _call(name, *args):
 
 
 # ------------------------------------------------------------------ dense
-_gemm_ws = None
+_gemm_ws = {}  # device index -> registered scratch tensor
 
 
-def set_gemm_workspace(nbytes_or_tensor):
-    """Registers scratch for the GEMM-based entry points (ffk_set_gemm_workspace): lets fp32
-    products run on the tensor cores through the bf16 split. Pass None to unregister."""
-    global _gemm_ws
+def set_gemm_workspace(nbytes_or_tensor, fp32_tensor_math=False):
+    """Registers scratch for the GEMM-based entry points on the CURRENT device
+    (ffk_set_gemm_workspace): unaligned 16-bit operands are repacked into it. fp32_tensor_math
+    (ffk_set_gemm_fp32_tensor_math, the reference handle's allowTensorOpMathConversion) lets
+    GEMM_AUTO run large fp32 products on the tensor cores through the bf16 split.
+    Pass None to unregister (and switch the fp32 policy off)."""
+    dev = torch.cuda.current_device()
     if nbytes_or_tensor is None:
-        _gemm_ws = None
+        _gemm_ws.pop(dev, None)
         _call("ffk_set_gemm_workspace", None, 0)
+        _call("ffk_set_gemm_fp32_tensor_math", 0)
         return None
     t = nbytes_or_tensor
     if not isinstance(t, torch.Tensor):
         t = torch.empty(int(t), dtype=torch.uint8, device="cuda")
-    _gemm_ws = t  # keep it alive
+    _gemm_ws[dev] = t  # keep it alive
     _call("ffk_set_gemm_workspace", t.data_ptr(), t.numel() * t.element_size())
+    _call("ffk_set_gemm_fp32_tensor_math", 1 if fp32_tensor_math else 0)
     return t
 
 

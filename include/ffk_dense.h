@@ -12,15 +12,25 @@ extern "C" {
  * accumulation) otherwise. TENSOR on FLOAT inputs runs them as TF32 (10-bit mantissa). */
 typedef enum { FFK_GEMM_AUTO = 0, FFK_GEMM_TENSOR = 1, FFK_GEMM_SIMT = 2, FFK_GEMM_SPLIT_BF16 = 3 } ffk_gemm_path_t;
 
-/* Registers device scratch for the GEMM-based entry points of this process (Linear,
- * BatchMatmul, MultiHeadAttention, Conv2D, ffk_gemm) — the role cublasSetWorkspace /
+/* Registers device scratch for the GEMM-based entry points (Linear, BatchMatmul,
+ * MultiHeadAttention, Conv2D, ffk_gemm) ON THE CURRENT DEVICE — the role cublasSetWorkspace /
  * PerDeviceFFHandle::workSpace (include/kernels/ff_handle.h:17-18) play for the reference's
- * cuBLAS calls. With scratch registered, AUTO runs large fp32 products on the tensor cores
- * by splitting each fp32 operand into two bf16 terms and summing three tcgen05 products in
- * fp32 (relative error ~1e-5, inside the fp32 tolerance of 1e-4) instead of the CUDA-core
- * kernel; FFK_GEMM_SPLIT_BF16 forces that path. Needs 2 bytes x 2 x (elements of A + B) per
- * call. Calls that share the scratch must be ordered on one stream. NULL unregisters. */
+ * cuBLAS calls. One slot per device: a process that drives several GPUs registers one buffer
+ * per device, with that device current; the pointer must be memory of that device. With
+ * scratch registered, 16-bit operands that break TMA's 16-byte pitch rule are repacked into it
+ * and stay on the tensor cores. Calls on different streams of one device that need the scratch
+ * are ordered behind each other with an event (inside a stream capture that is impossible and
+ * the call takes the path without scratch). NULL unregisters. */
 int ffk_set_gemm_workspace(void *workspace, size_t workspace_bytes);
+
+/* PerDeviceFFHandle::allowTensorOpMathConversion (include/kernels/ff_handle.h:19; the reference's
+ * handle sets it to true, src/managed_per_device_ff_handle.cc:9). allow != 0: FFK_GEMM_AUTO runs
+ * large fp32 products of the current device on the tensor cores by splitting each fp32 operand
+ * into two bf16 terms and summing three tcgen05 products in fp32 (relative error ~1e-5, inside
+ * the fp32 tolerance of 1e-4) — needs registered scratch of 2 bytes x 2 x (elements of A + B) per
+ * call. allow == 0 (the default): fp32 products stay exact on the CUDA cores whatever is
+ * registered. FFK_GEMM_SPLIT_BF16 as an explicit path needs only the scratch. */
+int ffk_set_gemm_fp32_tensor_math(int allow);
 
 /* General strided-batched product, the building block under Linear / BatchMatmul / MHA:
  *   D[b][m][n] = alpha * sum_k A(b,m,k) * B(b,n,k)  (+ bias[n]) (act)  (+ D if accumulate)

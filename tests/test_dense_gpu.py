@@ -137,11 +137,11 @@ def test_batch_matmul_seq_length_truncation(K, oracle):
 def test_fp32_on_tensor_cores_through_the_bf16_split(K, oracle):
     """fp32 operands, tcgen05 arithmetic: x = hi + lo in bf16, three products, fp32 accumulation.
     Must meet the fp32 tolerance (rtol 1e-4) against the fp64-accumulating oracle."""
-    K.set_gemm_workspace(64 << 20)
+    K.set_gemm_workspace(64 << 20, fp32_tensor_math=True)
     try:
         _linear_case(K, oracle, torch.float32, 512, 1024, 768, "relu", True, l2=1e-4, path=K.GEMM_SPLIT_BF16)
         _linear_case(K, oracle, torch.float32, 384, 520, 264, "none", True, path=K.GEMM_SPLIT_BF16)
-        # AUTO picks the split path for large fp32 products once scratch is registered
+        # AUTO picks the split path for large fp32 products once the fp32 policy allows it
         _linear_case(K, oracle, torch.float32, 1024, 1024, 512, "gelu", True, path=K.GEMM_AUTO)
         m, n, k, batch = 256, 192, 128, 6
         a, an = to_dev(uniform((batch, n, k), SEED_ACT))
@@ -151,6 +151,40 @@ def test_fp32_on_tensor_cores_through_the_bf16_split(K, oracle):
         oref = np.zeros((batch, n, m), np.float32)
         oracle.batch_matmul_forward(oref, an, bn, m, n, k, batch, -1, -1, -1)
         assert_close(o, oref, what="bmm split-bf16")
+    finally:
+        K.set_gemm_workspace(None)
+
+
+def test_registration_alone_keeps_fp32_exact(K):
+    """Registering scratch must not change fp32 numerics: without the explicit policy
+    (ffk_set_gemm_fp32_tensor_math) AUTO stays on the exact CUDA-core kernel, bit-identical to the
+    result without scratch; with the policy the split path answers within 1e-4 and, on different
+    streams of one device, calls that share the scratch are ordered (same result as serial calls)."""
+    g = torch.Generator(device="cuda").manual_seed(5)
+    x = torch.rand(1024, 512, device="cuda", generator=g) * 2 - 1
+    w = (torch.rand(1024, 512, device="cuda", generator=g) * 2 - 1) / 16
+    m = K.Linear.init_kernel(path=K.GEMM_AUTO)
+
+    def run(stream=None):
+        y = torch.zeros(1024, 1024, device="cuda")
+        K.Linear.forward_kernel(stream, m, x, y, w, None, 512, 1024, 1024)
+        return y
+
+    K.set_gemm_workspace(None)
+    exact = run()
+    K.set_gemm_workspace(64 << 20)
+    try:
+        assert torch.equal(run(), exact)
+        K.set_gemm_workspace(64 << 20, fp32_tensor_math=True)
+        split = run()
+        assert not torch.equal(split, exact)
+        assert_close(split, exact.cpu().numpy(), what="fp32 split vs exact")
+        torch.cuda.synchronize()
+        s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
+        outs = [run(s1 if i % 2 else s2) for i in range(6)]
+        torch.cuda.synchronize()
+        for o in outs:
+            assert torch.equal(o, split)
     finally:
         K.set_gemm_workspace(None)
 
