@@ -61,3 +61,76 @@ def test_strategy_reader_understands_both_forms(ffk, tmp_path):
     s = S.load_strategy(p)
     assert s.tensor_parallel == 2 and s.data_parallel == 4
     assert sorted(f["op"] for f in s.parallel_ops) == ["combine", "reduction", "repartition", "replicate"]
+
+
+def _v1(labels, edges):
+    """A V1ParallelComputationGraph document the way nlohmann writes it: the int-keyed maps as
+    [key, value] pairs, variants as {"type": key, "value": record}."""
+    return {"raw_graph": {
+        "node_labels": [[i, {"op_attrs": {"type": k, "value": v}, "name": None}] for i, (k, v) in enumerate(labels)],
+        "output_labels": [],
+        "graph": {"nodes": list(range(len(labels))),
+                  "edges": [{"srcNode": a, "srcIdx": 0, "dstNode": b, "dstIdx": i} for a, b, i in edges]}}}
+
+
+def test_weight_replication_is_not_tensor_parallelism(ffk):
+    """What ParallelComputationGraphBuilder really emits for a data-parallel Linear of degree 8
+    (parallel_computation_graph_builder.cc:588-634, generate_weight_transform): the input is
+    repartitioned along the batch, and EVERY weight gets a Replicate{8} behind its Weight node.
+    That graph is data parallel 8, tensor parallel 1."""
+    S = importlib.import_module("flexflow_train_b200.strategy")
+    labels = [("input", {}),
+              ("partition_distributed", {"repartition_dim": {"value": 0}, "repartition_degree": 8}),
+              ("weight", {"tensor_shape": {}}), ("replicate_distributed", {"replicate_degree": 8}),
+              ("weight", {"tensor_shape": {}}), ("replicate_distributed", {"replicate_degree": 8}),
+              ("linear", {"out_channels": 3072, "use_bias": True}),
+              ("combine_distributed", {"combine_dim": {"value": 0}, "combine_degree": 8})]
+    edges = [(0, 1, 0), (2, 3, 0), (4, 5, 0), (1, 6, 0), (3, 6, 1), (5, 6, 2), (6, 7, 0)]
+    s = S.parse_strategy(_v1(labels, edges), world_size=8)
+    assert (s.tensor_parallel, s.data_parallel, s.weight_replication) == (1, 8, 8)
+    lin = [p for p in s.placements if p.kind == "linear"][0]
+    assert [o.op for o in lin.inputs[0]] == ["repartition"] and lin.inputs[0][0].dim == 0
+    assert [[o.op for o in w] for w in lin.weights] == [["replicate"], ["replicate"]]
+    assert [o.op for o in lin.output] == ["combine"]
+    # weight replication alone (no activation op written) still reads as data parallelism
+    s2 = S.parse_strategy(_v1(labels[:1] + labels[2:7], [(1, 2, 0), (3, 4, 0), (0, 5, 0), (2, 5, 1), (4, 5, 2)]))
+    assert (s2.tensor_parallel, s2.data_parallel) == (1, 8)
+
+
+def test_tensor_parallel_block_is_placed_per_layer(ffk):
+    """Megatron-style feed-forward block in the reference's parallel ops: Replicate(2) in front of a
+    column-parallel Linear (weight sharded along out-channels), a row-parallel Linear (weight
+    sharded along in-channels) and the Reduction(2) behind it, inside a batch split of 4; the
+    weights also carry the data-parallel Replicate(4)."""
+    import pytest
+    S = importlib.import_module("flexflow_train_b200.strategy")
+    labels = [("input", {}),                                                                   # 0
+              ("partition_distributed", {"repartition_dim": {"value": 0}, "repartition_degree": 4}),  # 1
+              ("replicate_distributed", {"replicate_degree": 2}),                                  # 2
+              ("weight", {}), ("partition_distributed", {"repartition_dim": 0, "repartition_degree": 2}),  # 3 4
+              ("replicate_distributed", {"replicate_degree": 4}),                                  # 5
+              ("linear", {"out_channels": 3072, "use_bias": False}),                               # 6
+              ("weight", {}), ("partition_distributed", {"repartition_dim": 1, "repartition_degree": 2}),  # 7 8
+              ("replicate_distributed", {"replicate_degree": 4}),                                  # 9
+              ("linear", {"out_channels": 768, "use_bias": False}),                                # 10
+              ("reduce_distributed", {"reduction_degree": 2}),                                     # 11
+              ("layer_norm", {"elementwise_affine": True})]                                        # 12
+    edges = [(0, 1, 0), (1, 2, 0), (3, 4, 0), (4, 5, 0), (2, 6, 0), (5, 6, 1),
+             (7, 8, 0), (8, 9, 0), (6, 10, 0), (9, 10, 1), (10, 11, 0), (11, 12, 0)]
+    doc = _v1(labels, edges)
+    s = S.parse_strategy(doc, world_size=8)
+    assert (s.tensor_parallel, s.data_parallel) == (2, 4)
+    kinds = [p.kind for p in s.placements]
+    assert kinds == ["input", "linear", "linear", "layer_norm"]
+    col, row = s.placements[1], s.placements[2]
+    assert [(o.op, o.degree) for o in col.inputs[0]] == [("repartition", 4), ("replicate", 2)]
+    assert [(o.op, o.dim, o.degree) for o in col.weights[0]] == [("repartition", 0, 2), ("replicate", 0, 4)]
+    assert [(o.op, o.dim) for o in row.weights[0]][0] == ("repartition", 1)
+    assert [(o.op, o.degree) for o in row.output] == [("reduction", 2)]
+    assert row.producers == [col.node]
+    with pytest.raises(ValueError):
+        S.parse_strategy(doc, world_size=6)       # tp 2 x dp 4 != 6
+    # the variant may also be written by index
+    doc["raw_graph"]["node_labels"][11][1]["op_attrs"] = {"index": S.PCG_OPERATOR_KEYS.index("reduce_distributed"),
+                                                         "value": {"reduction_degree": 2}}
+    assert S.parse_strategy(doc).tensor_parallel == 2
