@@ -1,31 +1,34 @@
 #!/usr/bin/env python
 """bench.py — the measurement contract of this repository.
 
-Workload (BASELINE.json configs[1], "per-op microbench on 1 B200"): one STEP is one pass of
-the per-operator hot path over one batch of 8192 samples:
+Default workload = BASELINE.json configs[2], the configuration the metric "training samples/sec at
+1/2/4/8 B200" is quoted on: lib/models' transformer encoder (12 layers, d 1024, 16 heads, seq 512,
+batch 64 per GPU, bf16), one STEP = zero grads, forward, MSE gradient, backward, data-parallel
+gradient sum, SGD — every arithmetic step a C-ABI call into libffk.so (include/*.h). With
+--gpus N > 1 each rank trains on its own batch (weak scaling) and the weight gradients are summed
+over the ranks (Replicate backward; SUM, no division) by the peer-memory all-reduce kernels of
+libffk.so, issued bucket by bucket under the backward pass (FFK_BENCH_GRAD_SYNC=nccl selects NCCL
+all-reduces after backward instead). Before anything is timed at N > 1 one step's summed gradients
+are checked: bit-identical on all ranks and within 1 bf16 ulp of an NCCL all-reduce of the same
+buckets ("grad_sync_check").
 
-    Linear 8192x4096x4096 bf16 (+bias, ReLU)  forward + backward (act-grad, wgrad, bias-grad, dgrad)
-    Softmax 8192x4096 fp32                     forward
-    LayerNorm 8192x4096 fp32                   forward + backward (dX, dgamma, dbeta)
-    ElementBinary add 8192x4096 fp32           forward + backward
-    Embedding 1,000,000 x 256 fp32, 65536 i64  forward + backward
+The JSON line carries, besides the contract's keys:
+  roofline   the dominant kernel (the tcgen05 GEMM of a feed-forward layer, 275 GFLOP per launch)
+             event-timed live inside the timed steps, against the SUSTAINED measured bf16 peak,
+             plus the whole step's model FLOPs;
+  per_op     (N = 1) BASELINE configs[1], the per-op microbench: every op event-timed on rotating
+             buffer sets larger than 2x L2, with SURVEY §8(d)'s algorithmic bytes / FLOP and the
+             fraction of the HBM / tensor roofline — measured outside the timed region;
+  e2e        the same step fed from pinned HOST memory every step, the step's metric read back;
+  cpu_baseline (N = 1) the CPU oracle on a bounded sample of the same workload;
+  gpu_launches  kernel nodes of one step captured into a CUDA graph, times the timed steps.
 
-all through the C ABI of libffk.so (include/*.h). metric = training samples/sec =
-8192 * n_gpus / step time. With --gpus N > 1 every rank runs the step on its own batch (weak
-scaling) and the weight gradients (Linear dW/db, LayerNorm dgamma/dbeta) are summed over ranks —
-the Replicate-backward exchange of data parallelism — by the peer-memory all-reduce kernels of
-libffk.so (ffk_p2p_*; FFK_BENCH_GRAD_SYNC=nccl selects NCCL all-reduces instead).
+Other workloads: --workload microbench (configs[1] as one step), mlp (configs[0]), bert
+[--tp T | --strategy file.json] (configs[3]), dlrm (configs[4]).
 
-Other workloads (not the headline line): --workload mlp (configs[0], one CUDA-graph replay per
-step), encoder (configs[2]), bert [--tp T | --strategy file.json] (configs[3]), dlrm (configs[4]).
-
-The JSON line also carries: roofline (the tcgen05 GEMM of Linear forward against the measured
-bf16 peak), cpu_baseline (the CPU oracle on a bounded sample of the same step, rank 0, N=1),
-e2e (the same step fed from pinned HOST memory each step, result read back), clocks.
-
-`--impl reference` times the reference arm: the CPU restatement of the reference kernels
-(oracle/, the reference itself has no CPU path and cannot be built — DESIGN.md) on all host
-threads, on a bounded sample of the same step.
+`--impl reference` times the reference arm: the CPU restatement of the reference kernels (oracle/,
+the reference itself has no CPU path and cannot be built — DESIGN.md) on all host threads, on a
+bounded sample of the same workload.
 """
 from __future__ import annotations
 
@@ -62,6 +65,51 @@ def load_peaks():
         d = json.loads(p.read_text())
         return d.get("bf16_tflops", 1590.0), d.get("hbm_gbs", 6650.0), "measured"
     return 1590.0, 6650.0, "fallback"
+
+
+def load_peaks_full():
+    """(burst bf16 TF/s, sustained bf16 TF/s, HBM GB/s, source) — MEASURED_PEAKS.json, else the
+    fallback B200_PROFILING.md states."""
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        d = json.loads(p.read_text())
+        burst = d.get("bf16_tflops", 1590.0)
+        return burst, d.get("bf16_tflops_sustained", burst), d.get("hbm_gbs", 6650.0), "measured (MEASURED_PEAKS.json)"
+    return 1590.0, 1590.0, 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def count_step_kernels(torch, step_fn):
+    """Kernel launches of one step, counted: the step is captured into a CUDA graph on a side
+    stream (nothing executes) and the graph's kernel nodes are counted. Returns
+    (kernel nodes, other nodes) or None when the step cannot be captured."""
+    try:
+        from cuda.bindings import runtime as rt
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        g = torch.cuda.CUDAGraph(keep_graph=True)
+        with torch.cuda.stream(side):
+            with torch.cuda.graph(g, stream=side, capture_error_mode="thread_local"):
+                step_fn()
+        torch.cuda.current_stream().wait_stream(side)
+        raw = g.raw_cuda_graph()
+        err, _, n = rt.cudaGraphGetNodes(raw, 0)
+        err, nodes, n = rt.cudaGraphGetNodes(raw, n)
+        kernels = other = 0
+        for nd in nodes[:n]:
+            err, ty = rt.cudaGraphNodeGetType(nd)
+            if ty == rt.cudaGraphNodeType.cudaGraphNodeTypeKernel:
+                kernels += 1
+            else:
+                other += 1
+        del g
+        return kernels, other
+    except Exception as e:  # noqa: BLE001 - reported in the JSON line
+        print(f"bench: kernel count by graph capture failed: {e}", file=sys.stderr)
+        try:
+            torch.cuda.synchronize()
+        except Exception:
+            pass
+        return None
 
 
 # ----------------------------------------------------------------------------- clocks
@@ -287,6 +335,29 @@ def run_gpu(args):
         full_step()
     barrier()
 
+    check = None
+    if world > 1:
+        # the summed gradients of one step: bit-identical on all ranks, within 1 ulp of NCCL's sums
+        full_step()
+        torch.cuda.synchronize()
+        for flat, name, key in ((wl.flat16, "dW|db", "s16"), (wl.flat32, "dgamma|dbeta", "s32")):
+            want = flat.clone()
+            dist.all_reduce(want, op=dist.ReduceOp.SUM)
+            got = peer.tensor(off[key], (flat.numel(),), flat.dtype) if peer is not None else want
+            if peer is None:
+                continue   # NCCL path: the bucket itself was all-reduced in place by the step
+            ref0 = got.clone()
+            dist.broadcast(ref0, src=0)
+            if not torch.equal(ref0, got):
+                raise SystemExit(f"grad_sync_check: {name}: rank {rank} holds a different sum than rank 0")
+            a, b = got.float(), want.float()
+            ulp = torch.maximum(a.abs(), b.abs()) * (2.0 ** -7 if flat.dtype == torch.bfloat16 else 2.0 ** -22)
+            bad = ((a - b).abs() > ulp + 1e-30).sum().item()
+            if bad or not torch.isfinite(a).all():
+                raise SystemExit(f"grad_sync_check: {name}: {bad} elements differ from NCCL by more than 1 ulp")
+        check = "ok"
+        barrier()
+
     clocks = ClockSampler(local_rank)
     if rank == 0:
         clocks.start()
@@ -452,6 +523,8 @@ def run_gpu(args):
         "abi_calls_timed": abi_calls,
         "clocks": clock_info,
     }
+    if check is not None:
+        out["grad_sync_check"] = check
     if n_gpus == 1 and not args.no_cpu_baseline:
         out["cpu_baseline"] = cpu_baseline(threads=os.cpu_count() or 1, budget_s=20.0, kind_note="port")
     print(json.dumps(out), flush=True)
@@ -462,12 +535,174 @@ def run_gpu(args):
         dist.destroy_process_group()
 
 
+# ----------------------------------------------------------------------------- per-op table
+L2_BYTES = 126 * 1024 * 1024
+
+
+def per_op_table(torch, Kmod, device, iters=10):
+    """BASELINE configs[1] op by op: event-timed over `iters` launches that rotate through buffer
+    sets whose total size exceeds 2x L2 (so no launch finds its operands in the 126 MB L2), with
+    SURVEY §8(d)'s algorithmic bytes / FLOP per launch. HBM-bound ops are judged against the
+    measured copy bandwidth, GEMMs against the measured burst bf16 peak (each op is timed alone)."""
+    K = Kmod
+    burst, _, hbm, src = load_peaks_full()
+    bf, f32 = torch.bfloat16, torch.float32
+    g = torch.Generator(device=device).manual_seed(4321)
+    r = lambda *shape: torch.rand(*shape, device=device, generator=g) * 2 - 1
+    rows = []
+
+    def timed(name, bound, work, set_bytes, make, run, note=None):
+        nsets = max(2, -(-2 * L2_BYTES // max(set_bytes, 1)) + 1)
+        sets = [make() for _ in range(nsets)]
+        for i in range(3):
+            run(sets[i % nsets])
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(iters):
+            run(sets[i % nsets])
+        e1.record()
+        torch.cuda.synchronize()
+        us = e0.elapsed_time(e1) * 1e3 / iters
+        if bound == "tensor":
+            ach, peak, unit = work / (us * 1e-6) / 1e12, burst, "TFLOP/s"
+        else:
+            ach, peak, unit = work / (us * 1e-6) / 1e9, hbm, "GB/s"
+        row = {"op": name, "us": round(us, 2), "bound": bound, "algorithmic": work, "achieved": round(ach, 1),
+               "peak": peak, "unit": unit, "frac": round(ach / peak, 3), "buffer_sets": nsets}
+        if note:
+            row["note"] = note
+        rows.append(row)
+        del sets
+        torch.cuda.empty_cache()
+
+    # ---- Linear 8192 x 4096 x 4096 bf16
+    flop = 2.0 * M * N * KDIM
+    lin = K.Linear.init_kernel(K.ACT_RELU, 0.0, True, K.GEMM_TENSOR, out_dim=N, device=device)
+    w = (r(N, KDIM) / 64).to(bf)
+    b = r(N).to(bf)
+    mk_fwd = lambda: (r(M, KDIM).to(bf), torch.empty(M, N, dtype=bf, device=device))
+    timed("Linear fwd 8192x4096x4096 bf16 (+bias+ReLU)", "tensor", flop, 2 * M * KDIM * 2,
+          mk_fwd, lambda s: K.Linear.forward_kernel(None, lin, s[0], s[1], w, b, KDIM, N, M))
+    mk_d = lambda: (r(M, N).to(bf), torch.zeros(M, KDIM, dtype=bf, device=device))
+    timed("Linear dgrad (NN, beta=1)", "tensor", flop, 2 * M * N * 2, mk_d,
+          lambda s: K.Gemm.run(s[0], w, s[1], M, KDIM, N, b_mn=True, accumulate=True, path=K.GEMM_TENSOR))
+    mk_w = lambda: (r(M, N).to(bf), r(M, KDIM).to(bf), torch.zeros(N, KDIM, dtype=bf, device=device))
+    timed("Linear wgrad (TN, beta=1)", "tensor", flop, 2 * M * N * 2 + N * KDIM * 2, mk_w,
+          lambda s: K.Gemm.run(s[0], s[1], s[2], N, KDIM, M, a_mn=True, b_mn=True, accumulate=True,
+                               path=K.GEMM_TENSOR))
+    mk_b = lambda: (r(M, KDIM).to(bf), torch.zeros(M, KDIM, dtype=bf, device=device), r(M, N).relu().to(bf),
+                    r(M, N).to(bf), torch.zeros(N, KDIM, dtype=bf, device=device), torch.zeros(N, dtype=bf, device=device))
+    timed("Linear bwd (ReLU grad + wgrad + bias grad + dgrad)", "tensor", 2 * flop, 4 * M * N * 2 + N * KDIM * 2, mk_b,
+          lambda s: K.Linear.backward_kernel(None, lin, s[0], s[1], s[2], s[3], w, s[4], s[5], KDIM, N, M),
+          note="4 launches + 2 reduction launches; the elementwise and column-sum passes are HBM-bound")
+    del w, b
+
+    # ---- row ops on 8192 x 4096 fp32
+    es = 4
+    t = ROWS * COLS * es
+    mk2 = lambda: (r(ROWS, COLS), torch.empty(ROWS, COLS, device=device))
+    timed("Softmax fwd 8192x4096 fp32", "hbm", 2 * t, 2 * t, mk2,
+          lambda s: K.Softmax.forward_kernel(None, s[0], s[1], ROWS, COLS, 1))
+    gamma, beta = r(COLS) + 1, r(COLS)
+    ln = K.LayerNorm.init_kernel(True, ROWS, COLS, 1e-5, device=device)
+    timed("LayerNorm fwd 8192x4096 fp32", "hbm", 2 * t + 2 * COLS * 4 + 2 * ROWS * 4, 2 * t, mk2,
+          lambda s: K.LayerNorm.forward_kernel(None, ln, s[0], s[1], gamma, beta))
+    dg, db = torch.zeros(COLS, device=device), torch.zeros(COLS, device=device)
+    x_ln = r(ROWS, COLS)
+    K.LayerNorm.forward_kernel(None, ln, x_ln, torch.empty_like(x_ln), gamma, beta)  # mean / rstd of x_ln
+    mk_lb = lambda: (r(ROWS, COLS), x_ln.clone(), torch.zeros(ROWS, COLS, device=device))
+    timed("LayerNorm bwd (dX, dgamma, dbeta) 8192x4096 fp32", "hbm", 3 * t, 3 * t, mk_lb,
+          lambda s: K.LayerNorm.backward_kernel(None, ln, s[0], s[1], s[2], gamma, dg, db),
+          note="algorithmic = read dY, X + write dX (SURVEY a9); the kernel accumulates into dX (reads it), 4 passes in fact")
+    mk3 = lambda: (r(ROWS, COLS), r(ROWS, COLS), torch.empty(ROWS, COLS, device=device))
+    timed("ElementBinary add fwd 8192x4096 fp32", "hbm", 3 * t, 3 * t, mk3,
+          lambda s: K.ElementBinary.forward_kernel(None, K.OperatorType.EW_ADD, s[0], s[1], s[2]))
+    mk5 = lambda: (r(ROWS, COLS), r(ROWS, COLS), r(ROWS, COLS), torch.zeros(ROWS, COLS, device=device),
+                   torch.zeros(ROWS, COLS, device=device))
+    timed("ElementBinary add bwd 8192x4096 fp32", "hbm", 5 * t, 5 * t, mk5,
+          lambda s: K.ElementBinary.backward_kernel(None, K.OperatorType.EW_ADD, s[0], s[1], s[2], s[3], s[4]))
+    del x_ln
+
+    # ---- Embedding 1M x 256 fp32, 65536 int64 indices: the table itself is 1 GB, the gathered
+    # rows are scattered over it, so only index / output sets rotate
+    table = r(ENTRIES, EDIM)
+    mk_e = lambda: (torch.randint(0, ENTRIES, (EBATCH,), device=device, generator=g, dtype=torch.int64),
+                    torch.empty(EBATCH, EDIM, device=device))
+    timed("Embedding fwd 1Mx256 fp32, 65536 i64 indices", "hbm", EBATCH * (8 + 2 * EDIM * 4),
+          EBATCH * (8 + 2 * EDIM * 4), mk_e,
+          lambda s: K.Embedding.forward_kernel(None, s[0], s[1], table, K.AGGR_NONE, 1, EDIM, EBATCH))
+    dtable = table.zero_()
+    mk_eb = lambda: (torch.randint(0, ENTRIES, (EBATCH,), device=device, generator=g, dtype=torch.int64),
+                     r(EBATCH, EDIM))
+    timed("Embedding bwd 1Mx256 fp32 (scatter-add)", "hbm", EBATCH * (8 + 3 * EDIM * 4),
+          EBATCH * (8 + 3 * EDIM * 4), mk_eb,
+          lambda s: K.Embedding.backward_kernel(None, s[0], s[1], dtable, K.AGGR_NONE, 1, EDIM, EBATCH),
+          note="red.global.add does not return the old value: dW is written, not read back over HBM")
+    del table, dtable
+
+    # ---- the encoder's own shapes (configs[2]): bf16 rows of 1024 and the attention block
+    TOK, D = 64 * 512, 1024
+    mk2b = lambda: (r(TOK, D).to(bf), torch.empty(TOK, D, dtype=bf, device=device))
+    gb, bb = (r(D) + 1).to(bf), r(D).to(bf)
+    lnb = K.LayerNorm.init_kernel(True, TOK, D, 1e-5, device=device)
+    timed("LayerNorm fwd 32768x1024 bf16", "hbm", 2 * TOK * D * 2, 2 * TOK * D * 2, mk2b,
+          lambda s: K.LayerNorm.forward_kernel(None, lnb, s[0], s[1], gb, bb))
+    dpo = K.Dropout.init_kernel(0.1, 12345, TOK * 4096, device=device)
+    mk_dp = lambda: (r(TOK, 4096).to(bf), torch.empty(TOK, 4096, dtype=bf, device=device))
+    timed("Dropout fwd 32768x4096 bf16", "hbm", 2 * TOK * 4096 * 2 + TOK * 4096 // 8, 2 * TOK * 4096 * 2, mk_dp,
+          lambda s: K.Dropout.forward_kernel(None, dpo, s[0], s[1]))
+    torch.cuda.synchronize()
+    return {"peaks": {"bf16_tflops_burst": burst, "hbm_gbs": hbm, "source": src},
+            "l2": "each op rotates through buffer sets of more than 2 x 126 MB in total", "iters": iters, "rows": rows}
+
+
 # ----------------------------------------------------------------------------- encoder workload
+def grad_sync_check(torch, dist, model, sync, dp_group, rank):
+    """N > 1, before timing: one step's gradients summed by the product's own path must be
+    bit-identical on every rank and agree with an NCCL all-reduce of the same buckets to 1 bf16
+    (fp32 for fp32 buckets) ulp. Returns "ok" or raises."""
+    flats = model.grad_buckets
+    for b in flats:   # rank-dependent, reproducible contents
+        gen = torch.Generator(device=b.device).manual_seed(4242 + rank)
+        b.copy_(((torch.rand(b.numel(), device=b.device, generator=gen) - 0.5) * 2e-2).to(b.dtype))
+    want = [b.clone() for b in flats]
+    for w in want:
+        dist.all_reduce(w, op=dist.ReduceOp.SUM, group=dp_group)
+    if hasattr(sync, "after_layer"):
+        for l in reversed(model.layers):
+            if l.grads:
+                sync.after_layer(l)
+        sync.finish()
+        got = sync.sums
+    else:
+        sync.allreduce_gradients(flats)
+        got = flats
+    torch.cuda.synchronize()
+    for gsum, w in zip(got, want):
+        if not torch.isfinite(gsum.float()).all():
+            raise SystemExit("grad_sync_check: non-finite values in the summed gradients")
+        ref0 = gsum.clone()
+        dist.broadcast(ref0, src=dist.get_global_rank(dp_group, 0) if dp_group is not None else 0, group=dp_group)
+        if not torch.equal(ref0, gsum):
+            raise SystemExit(f"grad_sync_check: rank {rank} holds a different sum than rank 0")
+        # 1 ulp of the storage type around the NCCL result
+        a, b = gsum.float(), w.float()
+        ulp = torch.maximum(a.abs(), b.abs()) * (2.0 ** -7 if gsum.dtype == torch.bfloat16 else
+                                                2.0 ** -10 if gsum.dtype == torch.float16 else 2.0 ** -22)
+        bad = ((a - b).abs() > ulp + 1e-30).sum().item()
+        if bad:
+            raise SystemExit(f"grad_sync_check: {bad} elements differ from the NCCL all-reduce by more than 1 ulp")
+    if hasattr(sync, "check"):
+        sync.check()
+    return "ok"
+
+
 def run_encoder(args):
-    """BASELINE configs[2]: lib/models' transformer encoder (12 layers, d 1024, 16 heads, seq 512,
-    batch 64 per GPU, bf16, dim_ff 4096 assumed) trained with MSE + SGD through the step driver
-    (flexflow-train_b200/training.py), data-parallel over --gpus ranks. Selected with
-    `--workload encoder`; the default workload stays configs[1]."""
+    """BASELINE configs[2] (default) / configs[3] (--workload bert): lib/models' transformer encoder
+    (12 layers, d 1024, 16 heads, seq 512, batch 64 per GPU, bf16, dim_ff 4096 assumed) trained with
+    MSE + SGD — or the BERT-base graph with sparse CCE — through the step driver
+    (flexflow-train_b200/training.py), data-parallel over --gpus ranks."""
     import importlib
 
     import torch
@@ -481,26 +716,33 @@ def run_encoder(args):
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
     torch.cuda.set_device(local_rank)
     device = torch.device("cuda", local_rank)
     pops = None
     bert = args.workload == "bert"
     tp = 1
+    strategy_note = None
     if args.strategy:
         # "imported search strategy": {"tensor_parallel": T}, or a parallel computation graph in the
-        # reference's v1 JSON layout, from whose Replicate / Reduction nodes the degree is read
-        # (flexflow-train_b200/strategy.py); the rest of the world size is data parallel
-        tp = importlib.import_module("flexflow_train_b200.strategy").load_strategy(args.strategy).tensor_parallel
+        # reference's v1 JSON layout (flexflow-train_b200/strategy.py reads its edges and places the
+        # parallel ops per layer); the rest of the world size is data parallel
+        st = importlib.import_module("flexflow_train_b200.strategy").load_strategy(args.strategy, world)
+        tp = st.tensor_parallel
+        strategy_note = {"file": os.path.basename(args.strategy), "tensor_parallel": st.tensor_parallel,
+                         "data_parallel": st.data_parallel or world // st.tensor_parallel,
+                         "placed_layers": len(st.placements)}
     if args.tp:
         tp = args.tp
     if not bert or world % tp != 0:
         tp = 1
     dp = world // tp
-    tp_group, tp_rank = None, 0
+    tp_group, tp_rank, dp_group = None, 0, None
+    grad_sync = "none"
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=device)
-        dp_group = None
         if tp > 1:
             # consecutive ranks form a tensor-parallel group; ranks with the same index in their
             # group form a data-parallel group (every rank must create every group)
@@ -513,8 +755,6 @@ def run_encoder(args):
                 if rank % tp == i:
                     dp_group = grp
             tp_rank = rank % tp
-        if dp > 1:
-            pops = importlib.import_module("flexflow_train_b200.parallel_ops").ParallelOps(group=dp_group)
     B, S, L = args.batch, 512, args.layers
     D, H, FF, V = (768, 12, 3072, 30522) if bert else (1024, 16, 4096, 0)
     hd = args.head_dim if args.head_dim > 0 else FF // H
@@ -527,6 +767,24 @@ def run_encoder(args):
         labels = torch.randint(0, V, (B * S,), generator=g, device=device, dtype=torch.int32)
     else:
         model = T.build_transformer_encoder(L, D, H, S, B, FF, hd, dropout=0.1, dtype=torch.bfloat16, device=device)
+    sync_launches_per_step = 0
+    if dp > 1:
+        P = importlib.import_module("flexflow_train_b200.parallel_ops")
+        if os.environ.get("FFK_BENCH_GRAD_SYNC", "peer") == "peer":
+            try:
+                pops = P.PeerGradSync(model, group=dp_group)   # raises the same error on every rank
+                grad_sync = ("peer-memory all-reduce (ffk_p2p_all_reduce_sum_background: SUM over ranks, no "
+                             "division), one launch per >= 48 MiB of finished gradients on a high-priority side "
+                             "stream under the backward pass; SGD reads the summed buckets")
+            except RuntimeError as e:
+                grad_sync = "NCCL all-reduce [peer-memory path unavailable on this box: " + str(e)[:200] + "]"
+        if pops is None:
+            pops = P.ParallelOps(group=dp_group)
+            if grad_sync == "none":
+                grad_sync = "NCCL all-reduce (SUM) of the flat gradient buckets after backward"
+    check = None
+    if dp > 1:
+        check = grad_sync_check(torch, dist, model, pops, dp_group, rank)
     opt = T.SGD(lr=1e-3, weight_decay=1e-4)
     hx = (torch.rand(B, S, D, generator=g, device=device) * 2 - 1).to(torch.bfloat16).cpu().pin_memory()
     target = None if bert else (torch.rand(B, S, D, generator=g, device=device) * 2 - 1).to(torch.bfloat16)
@@ -537,24 +795,49 @@ def run_encoder(args):
     tgt32 = None if bert else target.float().view(B * S, D).contiguous()
     hres = torch.empty(7, dtype=torch.int32).pin_memory()
 
-    def step():
+    def step(sync=pops):
         if bert:
-            T.sparse_cce_step(model, labels, opt, pops, global_batch=B * S * dp)
+            T.sparse_cce_step(model, labels, opt, sync, global_batch=B * S * dp)
         else:
-            T.mse_step(model, target, opt, pops)
+            T.mse_step(model, target, opt, sync, replicas=dp)
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
+    # the dominant kernel, timed live: the first feed-forward Linear (one tcgen05 GEMM launch with
+    # the bias + activation epilogue) of every timed step
+    ff1 = next(l for l in model.layers if isinstance(l, T.Linear))
+    gemm_flop = 2.0 * ff1.batch * ff1.in_dim * ff1.out_dim
+    gemm_events = []
+    plain_forward = ff1.forward
+
+    def timed_forward():
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        plain_forward()
+        b.record()
+        gemm_events.append((a, b))
+
     for _ in range(args.warmup):
         step()
     barrier()
+    counted = None
+    if tp == 1:
+        counted = count_step_kernels(torch, lambda: step(None))   # the compute part of one step
+        if hasattr(pops, "launches"):
+            l0 = pops.launches
+            step()
+            sync_launches_per_step = pops.launches - l0
+        elif pops is not None:
+            sync_launches_per_step = len(model.grad_buckets)
+        barrier()
     clocks = ClockSampler(local_rank)
     if rank == 0:
         clocks.start()
     calls0 = lib.launches
+    ff1.forward = timed_forward
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     e0.record()
@@ -562,9 +845,11 @@ def run_encoder(args):
         step()
     e1.record()
     barrier()
+    ff1.forward = plain_forward
     ms_total = e0.elapsed_time(e1)
     abi_calls = lib.launches - calls0
     clock_info = clocks.stop() if rank == 0 else None
+    gemm_ms = [a.elapsed_time(b) for a, b in gemm_events]
 
     def e2e_step():
         model.input.data.copy_(hx, non_blocking=True)          # the batch arrives from the host
@@ -576,7 +861,7 @@ def run_encoder(args):
         hres.copy_(perf.buf, non_blocking=True)                # the step's metric goes back
         torch.cuda.current_stream().synchronize()
 
-    for _ in range(2):
+    for _ in range(3):
         e2e_step()
     barrier()
     e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -590,8 +875,13 @@ def run_encoder(args):
         t = torch.tensor([ms_total, ms_e2e], device=device, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms_total, ms_e2e = t.tolist()
+    if hasattr(pops, "check"):
+        pops.check()  # raises if a bounded wait for a peer rank expired
     if rank != 0:
         if world > 1:
+            dist.barrier()
+            if hasattr(pops, "close"):
+                pops.close()
             dist.destroy_process_group()
         return
     ms_per_step = ms_total / args.steps
@@ -599,8 +889,20 @@ def run_encoder(args):
     # fwd+bwd FLOPs per sample: 3 x (projections + scores + FFN), SURVEY §8d
     per_tok = 2 * (3 * D * H * hd + H * hd * D + 2 * S * H * hd + 2 * D * FF)
     flops_per_sample = 3 * per_tok * S * L + 3 * 2 * D * V * S
-    tf_peak, _, peak_src = load_peaks()
-    achieved = flops_per_sample * B / tp / (ms_per_step * 1e-3) / 1e12  # per GPU
+    burst, sustained, _, peak_src = load_peaks_full()
+    step_tflops = flops_per_sample * B / tp / (ms_per_step * 1e-3) / 1e12  # per GPU
+    gemm_avg_ms = sum(gemm_ms) / len(gemm_ms)
+    achieved = gemm_flop / (gemm_avg_ms * 1e-3) / 1e12
+    traffic = None
+    tr = ROOT / "profiles" / "gemm_traffic_bytes.json"
+    if tr.exists():
+        try:
+            traffic = json.loads(tr.read_text()).get(f"{ff1.batch}x{ff1.out_dim}x{ff1.in_dim}")
+        except Exception:
+            traffic = None
+    launches = None
+    if counted is not None:
+        launches = args.steps * (counted[0] + sync_launches_per_step)
     out = {
         "metric": "training samples/sec (BERT-base graph of lib/models, fwd+bwd+SGD)" if bert else
                   "training samples/sec (transformer encoder, fwd+bwd+SGD)",
@@ -612,20 +914,45 @@ def run_encoder(args):
                                 f"{H} heads, head dim {hd}, dim_ff {FF} GELU, vocabulary head {V} + softmax, seq {S}, "
                                 f"batch {B} per GPU, sparse CCE + SGD") if bert else
                                (f"BASELINE configs[2]: transformer encoder {L} layers, d {D}, {H} heads, head dim {hd}, "
-                                f"dim_ff {FF}, seq {S}, batch {B} per GPU, MSE + SGD"),
+                                f"dim_ff {FF}, seq {S}, batch {B} per GPU, dropout 0.1, MSE + SGD"),
                    "global_batch": B * dp, "seq_len": S, "parameters": params,
                    "parallelism": (f"dp{dp}" + (f" x tp{tp}" if tp > 1 else "")) if world > 1 else "single",
-                   "l2": "activations of one layer exceed L2 (>= 0.5 GB)"},
-        "roofline": {"kernel": "whole step (model FLOPs, all kernels)", "bound": "tensor", "achieved": achieved,
-                     "peak": tf_peak, "peak_source": f"{peak_src} bf16_tflops (burst)", "unit": "TFLOP/s",
-                     "frac": achieved / tf_peak, "traffic": None},
+                   "grad_sync": grad_sync,
+                   "l2": "inputs larger than L2: one layer's activations are >= 0.5 GB against 126 MB of L2, no explicit flush"},
+        "roofline": {"kernel": f"gemm_tc_pair_kernel (tcgen05 cta_group::2): feed-forward Linear forward "
+                               f"{ff1.batch}x{ff1.out_dim}x{ff1.in_dim} bf16 with bias + activation epilogue, "
+                               f"timed in every timed step; the GEMM family is ~77 % of the step (profiles/)",
+                     "bound": "tensor", "achieved": achieved, "peak": sustained,
+                     "peak_source": f"{peak_src} bf16_tflops_sustained (kernel timed inside a long step)",
+                     "unit": "TFLOP/s", "frac": achieved / sustained, "traffic": traffic,
+                     "avg_launch_ms": gemm_avg_ms, "launches_timed": len(gemm_ms),
+                     "flop_per_launch": gemm_flop,
+                     "whole_step": {"model_tflops_per_gpu": step_tflops, "frac_of_sustained": step_tflops / sustained,
+                                    "frac_of_burst": step_tflops / burst, "flop_per_sample": flops_per_sample}},
         "e2e": {"value": B * dp / (ms_e2e / args.steps * 1e-3), "unit": "samples/s",
                 "h2d_bytes_per_step": hx.numel() * 2, "d2h_bytes_per_step": 28,
                 "ms_per_step": ms_e2e / args.steps},
-        "gpu_launches": None, "abi_calls_timed": abi_calls, "clocks": clock_info,
+        "gpu_launches": launches,
+        "gpu_launches_how": (f"{counted[0]} kernel nodes (+{counted[1]} other nodes) in one step captured as a CUDA "
+                             f"graph, + {sync_launches_per_step} gradient-sum launches, x {args.steps} steps")
+                            if counted is not None else "not counted (capture failed or tensor-parallel run)",
+        "abi_calls_timed": abi_calls, "clocks": clock_info,
     }
+    if check is not None:
+        out["grad_sync_check"] = check
+    if strategy_note is not None:
+        out["config"]["strategy"] = strategy_note
+    if world == 1 and not args.no_per_op:
+        del model, opt
+        torch.cuda.empty_cache()
+        out["per_op"] = per_op_table(torch, Kmod, device)
+    if world == 1 and not args.no_cpu_baseline:
+        out["cpu_baseline"] = cpu_encoder_baseline(os.cpu_count() or 1, repeats=2, bert=bert)
     print(json.dumps(out), flush=True)
     if world > 1:
+        dist.barrier()
+        if hasattr(pops, "close"):
+            pops.close()
         dist.destroy_process_group()
 
 
@@ -861,6 +1188,49 @@ def cpu_baseline(threads, budget_s, kind_note):
                       f"{dt:.2f} s each"}
 
 
+ENC = dict(D=1024, H=16, hd=256, FF=4096, S=512, L=12, B=64)   # configs[2]
+
+
+def cpu_encoder_sample(o, np, layers, enc=None, state=None):
+    """One sample (512 tokens) through `layers` encoder layers on the CPU oracle: forward, MSE
+    gradient, backward, SGD. Attention, LayerNorm and the Linears treat samples independently, so
+    one sample of the batch is a faithful 1/64 of a step; layers are identical, so `layers` of 12
+    is a faithful fraction of a sample."""
+    sys.path.insert(0, str(ROOT / "tests"))
+    from oracle_encoder import OracleEncoder
+    if state is None:
+        W = OracleEncoder.random_weights(layers, ENC["D"], ENC["H"], ENC["hd"], ENC["FF"], seed=4321)
+        rng = np.random.default_rng(1234)
+        x = rng.uniform(-1, 1, (1, ENC["S"], ENC["D"])).astype(np.float32)
+        t = rng.uniform(-1, 1, (1, ENC["S"], ENC["D"])).astype(np.float32)
+        words = lambda n: rng.integers(0, 2 ** 32, (n + 31) // 32, dtype=np.uint32)
+        masks = [(words(ENC["S"] * ENC["FF"]), words(ENC["S"] * ENC["D"])) for _ in range(layers)]
+        state = (OracleEncoder(o, W, 1, ENC["S"], ENC["D"], ENC["H"], ENC["hd"], ENC["FF"], rate=0.1), x, t, masks)
+    encm, x, t, masks = state
+    encm.step(x, t, 1e-3, 1e-4, masks=masks, global_volume=ENC["B"] * ENC["S"] * ENC["D"])
+    return state
+
+
+def cpu_encoder_baseline(threads, repeats, bert=False, layers=1):
+    import numpy as np
+    sys.path.insert(0, str(ROOT / "tests"))
+    import oracle as oracle_mod
+
+    os.environ["OMP_NUM_THREADS"] = str(threads)
+    o = oracle_mod.load()
+    state = cpu_encoder_sample(o, np, layers)          # warm-up + allocation
+    t0 = time.perf_counter()
+    for _ in range(repeats):
+        cpu_encoder_sample(o, np, layers, state=state)
+    dt = (time.perf_counter() - t0) / repeats
+    value = 1.0 / (dt * ENC["L"] / layers)
+    return {"value": value, "unit": "samples/s", "cores": threads, "kind": "port",
+            "sample": f"1 of 64 samples (512 tokens) through {layers} of 12 encoder layers (forward, MSE gradient, "
+                      f"backward, SGD; d 1024, 16 heads of 256, dim_ff 4096) on the CPU oracle (OpenMP, {threads} "
+                      f"threads), {repeats} repeats of {dt:.1f} s; samples/s = 1 / (time x 12 / {layers})"
+                      + (" [BERT run: the encoder sample stands in]" if bert else "")}
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -872,6 +1242,38 @@ def run_reference(args):
     threads = os.cpu_count() or 1
     os.environ["OMP_NUM_THREADS"] = str(threads)
     o = oracle_mod.load()
+    note = ("the reference has no CPU op kernels and cannot be compiled here (SURVEY F1/F2): this arm times "
+            "oracle/cpu_ref.cc, the CPU restatement of its .cu bodies")
+    if args.workload != "microbench":
+        # configs[2]: each step = one sample through one encoder layer (about 10 s of CPU work)
+        layers = 1
+        state = cpu_encoder_sample(o, np, layers)
+        warm = min(args.warmup, 1)
+        for _ in range(warm):
+            cpu_encoder_sample(o, np, layers, state=state)
+        steps = max(1, min(args.steps, 3))
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            cpu_encoder_sample(o, np, layers, state=state)
+        dt = (time.perf_counter() - t0) / steps
+        value = 1.0 / (dt * ENC["L"] / layers)
+        sample = (f"each step = 1 of 64 samples (512 tokens) through {layers} of 12 encoder layers, forward + MSE "
+                  f"gradient + backward + SGD; {steps} timed steps of {dt:.1f} s; samples/s = 1 / (time x 12 / {layers})")
+        out = {
+            "impl": "reference",
+            "metric": "training samples/sec (transformer encoder, fwd+bwd+SGD)",
+            "value": value, "unit": "samples/s", "n_gpus": args.gpus, "steps": steps, "warmup": warm,
+            "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32 (double accumulation)", "data": "synthetic",
+            "config": {"workload": "BASELINE configs[2]: transformer encoder 12 layers, d 1024, 16 heads, head dim 256, "
+                                   "dim_ff 4096, seq 512, dropout 0.1, MSE + SGD — bounded sample on host cores",
+                       "global_batch": 64, "seq_len": 512},
+            "cpu_baseline": {"value": value, "unit": "samples/s", "cores": threads, "kind": "port", "sample": sample},
+            "e2e": {"value": value, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "note": note,
+        }
+        print(json.dumps(out), flush=True)
+        return
     rows = 128
     bufs = oracle_step(o, np, rows, rows * 8)
     for _ in range(min(args.warmup, 1)):
@@ -893,8 +1295,7 @@ def run_reference(args):
         "config": {"workload": "BASELINE configs[1] step, bounded sample on host cores", "samples_per_step": rows},
         "cpu_baseline": {"value": value, "unit": "samples/s", "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "note": "the reference has no CPU op kernels and cannot be compiled here (SURVEY F1/F2): this arm times "
-                "oracle/cpu_ref.cc, the CPU restatement of its .cu bodies",
+        "note": note,
     }
     print(json.dumps(out), flush=True)
 
@@ -906,7 +1307,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--workload", default="microbench", choices=["microbench", "encoder", "bert", "dlrm", "mlp"])
+    ap.add_argument("--no-per-op", action="store_true", help="skip the per-op table of the default workload")
+    ap.add_argument("--workload", default="encoder", choices=["encoder", "microbench", "bert", "dlrm", "mlp"])
     ap.add_argument("--layers", type=int, default=12)
     ap.add_argument("--batch", type=int, default=64)
     ap.add_argument("--head-dim", type=int, default=0, help="0 = the reference's dim_ff/heads (256)")

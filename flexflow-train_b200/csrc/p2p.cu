@@ -151,10 +151,15 @@ template <typename T> struct Acc16 {
 
 // in_off / out_off: byte offsets of the summed range and of the result inside every region's data
 // part; npk = number of 16-byte packets. two_shot: packets are split into `world` chunks.
-template <typename T>
-__global__ void __launch_bounds__(512)
+// THREADS / MINB: 512 x 1 is the stand-alone kernel (two packets from every peer in flight per
+// thread). 128 x 6 is the background form: at most 80 registers per thread and no shared memory,
+// so that one CTA fits beside a resident tcgen05 GEMM CTA (166 registers x 320 threads of the
+// 64 K register file) and the sum proceeds UNDER the backward GEMMs instead of between them.
+template <typename T, int THREADS, int MINB>
+__global__ void __launch_bounds__(THREADS, MINB)
     p2p_all_reduce_kernel(PeerTable t, int rank, int world, size_t in_off, size_t out_off,
                           size_t npk, int two_shot, unsigned long long timeout_ns) {
+  constexpr int PEERS = THREADS >= 512 ? 8 : 4;  // peers whose loads are in flight together
   Control *mine = reinterpret_cast<Control *>(t.base[rank]);
   unsigned const epoch = mine->epoch + 1;  // every block reads it before the last block bumps it
   size_t const tid = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -177,13 +182,13 @@ __global__ void __launch_bounds__(512)
     for (size_t i = tid; i < npk; i += nthreads) {
       Acc16<T> acc;
       acc.zero();
-      for (int p0 = 0; p0 < world; p0 += 8) {  // all peers' loads go out before the first add
-        uint4 raw[8];
+      for (int p0 = 0; p0 < world; p0 += PEERS) {  // the peers' loads go out before the first add
+        uint4 raw[PEERS];
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
+        for (int j = 0; j < PEERS; ++j)
           if (p0 + j < world) raw[j] = ld_peer16(t.base[p0 + j] + kFlagBytes + in_off + i * 16);
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
+        for (int j = 0; j < PEERS; ++j)
           if (p0 + j < world) acc.add(raw[j]);
       }
       *reinterpret_cast<uint4 *>(out_local + i * 16) = acc.pack();
@@ -200,10 +205,10 @@ __global__ void __launch_bounds__(512)
       acc[0].zero();
       acc[1].zero();
       bool const ok1 = i0 + bstride < hi;
-      for (int p0 = 0; p0 < world; p0 += 8) {
-        uint4 raw[8][2];
+      for (int p0 = 0; p0 < world; p0 += PEERS) {
+        uint4 raw[PEERS][2];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
+        for (int j = 0; j < PEERS; ++j) {
           if (p0 + j < world) {
             unsigned char const *src = t.base[p0 + j] + kFlagBytes + in_off;
             raw[j][0] = ld_peer16(src + i0 * 16);
@@ -211,7 +216,7 @@ __global__ void __launch_bounds__(512)
           }
         }
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
+        for (int j = 0; j < PEERS; ++j) {
           if (p0 + j < world) {
             acc[0].add(raw[j][0]);
             acc[1].add(raw[j][1]);
@@ -250,15 +255,15 @@ __global__ void __launch_bounds__(512)
       int const p = (rank + q) % world;  // spread the ranks over different peers at any moment
       size_t const plo = size_t(p) * per, phi = min(npk, plo + per);
       unsigned char const *src = t.base[p] + kFlagBytes + out_off;
-      for (size_t i0 = plo + size_t(blockIdx.x) * bstride * 8 + threadIdx.x; i0 < phi;
-           i0 += nthreads * 8) {
-        uint4 raw[8];
+      for (size_t i0 = plo + size_t(blockIdx.x) * bstride * PEERS + threadIdx.x; i0 < phi;
+           i0 += nthreads * PEERS) {
+        uint4 raw[PEERS];
 #pragma unroll
-        for (int u = 0; u < 8; ++u)
+        for (int u = 0; u < PEERS; ++u)
           raw[u] = (i0 + u * bstride < phi) ? ld_peer16(src + (i0 + u * bstride) * 16)
                                             : make_uint4(0, 0, 0, 0);
 #pragma unroll
-        for (int u = 0; u < 8; ++u)
+        for (int u = 0; u < PEERS; ++u)
           if (i0 + u * bstride < phi)
             *reinterpret_cast<uint4 *>(out_local + (i0 + u * bstride) * 16) = raw[u];
       }
@@ -400,8 +405,30 @@ int ffk_p2p_local_buffer(void *group, void **data_out, size_t *bytes_out) {
   return FFK_OK;
 }
 
-int ffk_p2p_all_reduce_sum(void *stream, void *group, size_t in_offset, size_t out_offset,
-                           size_t count, int dtype) {
+}  // extern "C"
+
+namespace {
+template <int THREADS, int MINB>
+void launch_all_reduce(int dtype, unsigned blocks, cudaStream_t s, Group *g, size_t in_offset,
+                       size_t out_offset, size_t npk, int two_shot) {
+  switch (dtype) {
+    case FFK_FLOAT:
+      p2p_all_reduce_kernel<float, THREADS, MINB><<<blocks, THREADS, 0, s>>>(
+          g->table, g->rank, g->world, in_offset, out_offset, npk, two_shot, g->timeout_ns);
+      break;
+    case FFK_HALF:
+      p2p_all_reduce_kernel<__half, THREADS, MINB><<<blocks, THREADS, 0, s>>>(
+          g->table, g->rank, g->world, in_offset, out_offset, npk, two_shot, g->timeout_ns);
+      break;
+    default:
+      p2p_all_reduce_kernel<__nv_bfloat16, THREADS, MINB><<<blocks, THREADS, 0, s>>>(
+          g->table, g->rank, g->world, in_offset, out_offset, npk, two_shot, g->timeout_ns);
+      break;
+  }
+}
+
+int all_reduce_impl(void *stream, void *group, size_t in_offset, size_t out_offset, size_t count,
+                    int dtype, int background_blocks) {
   Group *g = reinterpret_cast<Group *>(group);
   FFK_REQUIRE(g, "p2p: null group");
   FFK_REQUIRE(g->connected || g->world == 1, "p2p: ffk_p2p_connect has not been called");
@@ -418,7 +445,7 @@ int ffk_p2p_all_reduce_sum(void *stream, void *group, size_t in_offset, size_t o
               "p2p all-reduce: input and output ranges overlap");
   size_t npk = bytes / 16;
   cudaStream_t s = as_stream(stream);
-  if (bytes <= kPushLimit) {
+  if (bytes <= kPushLimit && background_blocks <= 0) {
     unsigned blocks = unsigned(g->world);
     switch (dtype) {
       case FFK_FLOAT:
@@ -435,25 +462,35 @@ int ffk_p2p_all_reduce_sum(void *stream, void *group, size_t in_offset, size_t o
     return FFK_OK;
   }
   int two_shot = bytes > kOneShotLimit && g->world > 1;
+  if (background_blocks > 0) {
+    unsigned blocks = unsigned(std::min<size_t>(size_t(background_blocks), (npk + 127) / 128));
+    launch_all_reduce<128, 6>(dtype, blocks, s, g, in_offset, out_offset, npk, two_shot);
+    FFK_LAUNCH_CHECK();
+    return FFK_OK;
+  }
   // measured inside bench.py at 2 GPUs (32 MiB bucket under the memory-bound tail of the step):
   // 24 blocks 1.221 ms/step, 48 1.182, 96 1.156, 148 1.165, NCCL 1.168. FFK_P2P_BLOCKS overrides.
   unsigned blocks = two_shot ? 96u : unsigned(std::min<size_t>(16, (npk + 511) / 512));
   if (two_shot) {
     if (char const *e = std::getenv("FFK_P2P_BLOCKS")) blocks = unsigned(std::max(1, atoi(e)));
   }
-  switch (dtype) {
-    case FFK_FLOAT:
-      p2p_all_reduce_kernel<float><<<blocks, 512, 0, s>>>(g->table, g->rank, g->world, in_offset, out_offset, npk, two_shot, g->timeout_ns);
-      break;
-    case FFK_HALF:
-      p2p_all_reduce_kernel<__half><<<blocks, 512, 0, s>>>(g->table, g->rank, g->world, in_offset, out_offset, npk, two_shot, g->timeout_ns);
-      break;
-    default:
-      p2p_all_reduce_kernel<__nv_bfloat16><<<blocks, 512, 0, s>>>(g->table, g->rank, g->world, in_offset, out_offset, npk, two_shot, g->timeout_ns);
-      break;
-  }
+  launch_all_reduce<512, 1>(dtype, blocks, s, g, in_offset, out_offset, npk, two_shot);
   FFK_LAUNCH_CHECK();
   return FFK_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int ffk_p2p_all_reduce_sum(void *stream, void *group, size_t in_offset, size_t out_offset,
+                           size_t count, int dtype) {
+  return all_reduce_impl(stream, group, in_offset, out_offset, count, dtype, 0);
+}
+
+int ffk_p2p_all_reduce_sum_background(void *stream, void *group, size_t in_offset,
+                                      size_t out_offset, size_t count, int dtype, int blocks) {
+  FFK_REQUIRE(blocks > 0 && blocks <= 1024, "p2p background all-reduce: blocks must be in 1..1024");
+  return all_reduce_impl(stream, group, in_offset, out_offset, count, dtype, blocks);
 }
 
 int ffk_p2p_status(void *group) {

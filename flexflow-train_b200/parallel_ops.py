@@ -201,10 +201,17 @@ class PeerMemoryGroup:
         assert offset_bytes % 16 == 0 and offset_bytes + nb <= self.nbytes
         return self.bytes[offset_bytes:offset_bytes + nb].view(dtype).view(tuple(shape))
 
-    def all_reduce_sum(self, in_offset: int, out_offset: int, count: int, dtype, stream=None) -> None:
+    def all_reduce_sum(self, in_offset: int, out_offset: int, count: int, dtype, stream=None,
+                       background_blocks: int = 0) -> None:
+        """background_blocks > 0 selects the slim kernel that shares SMs with a running GEMM
+        (ffk_p2p_all_reduce_sum_background); every rank must pass the same value."""
         K = self.K
-        K._call("ffk_p2p_all_reduce_sum", K._stream(stream), self.handle, in_offset, out_offset, count,
-                K._DT[dtype])
+        if background_blocks > 0:
+            K._call("ffk_p2p_all_reduce_sum_background", K._stream(stream), self.handle, in_offset, out_offset,
+                    count, K._DT[dtype], int(background_blocks))
+        else:
+            K._call("ffk_p2p_all_reduce_sum", K._stream(stream), self.handle, in_offset, out_offset, count,
+                    K._DT[dtype])
 
     def check(self) -> None:
         self.K._call("ffk_p2p_status", self.handle)
@@ -213,3 +220,96 @@ class PeerMemoryGroup:
         if self.handle:
             self.K._call("ffk_p2p_destroy", self.handle)
             self.handle = None
+
+
+class PeerGradSync:
+    """Data-parallel gradient sums (the Replicate-backward / `*_nccl_update` exchange: SUM over
+    ranks, no division, optimizer_kernel.cu:83-89) over NVLink peer memory, issued slice by slice
+    WHILE the backward pass is still running.
+
+    The model's flat gradient buckets are re-homed into a peer-mapped region ([grads | sums] per
+    bucket). Backward visits the layers in reverse, so the tail of each bucket is final first:
+    whenever `min_bytes` more of it are complete, one background all-reduce of that slice goes out
+    on a high-priority side stream behind an event; `finish()` sends the remainder and makes the
+    main stream wait. The optimizer then reads `summed(g)`."""
+
+    def __init__(self, model, group: Optional[dist.ProcessGroup] = None, min_bytes: int = 48 << 20,
+                 background_blocks: int = 32):
+        self.model, self.min_bytes, self.blocks = model, int(min_bytes), int(background_blocks)
+        buckets = model.grad_buckets
+        sizes = [(b.numel() * b.element_size() + 255) // 256 * 256 for b in buckets]
+        self.peer = PeerMemoryGroup(2 * sum(sizes), group)
+        self.world = self.peer.world
+        self.slots = []   # per bucket: (grad offset, sum offset, dtype, element size, numel)
+        off = 0
+        flats, self.sums = [], []
+        for b, sz in zip(buckets, sizes):
+            g = self.peer.tensor(off, (b.numel(),), b.dtype).zero_()
+            sm = self.peer.tensor(off + sz, (b.numel(),), b.dtype).zero_()
+            self.slots.append((off, off + sz, b.dtype, b.element_size(), b.numel()))
+            flats.append(g)
+            self.sums.append(sm)
+            off += 2 * sz
+        model.rehome_gradients(flats)
+        # where each layer's gradients start inside its bucket (bytes), for the progress tracking
+        self._layer_lo = {}
+        for l in model.layers:
+            for g in l.grads:
+                for bi, flat in enumerate(model.grad_buckets):
+                    if g.untyped_storage().data_ptr() == flat.untyped_storage().data_ptr() and g.dtype == flat.dtype:
+                        lo = (g.data_ptr() - flat.data_ptr()) // 16 * 16
+                        key = (id(l), bi)
+                        self._layer_lo[key] = min(self._layer_lo.get(key, lo), lo)
+        self.side = torch.cuda.Stream(priority=-1)
+        self.ready = torch.cuda.Event()
+        self.done = torch.cuda.Event()
+        self.launches = 0
+        self.summed_grads = [self.summed(g) for g in model.grads]
+        self.begin()
+
+    def begin(self):
+        self._sent_lo = [n * es for (_, _, _, es, n) in self.slots]  # bytes [sent_lo, end) are on their way
+        self._done_lo = list(self._sent_lo)
+
+    def summed(self, grad: torch.Tensor) -> torch.Tensor:
+        """The view of the summed bucket that corresponds to the gradient view `grad`."""
+        for flat, sm in zip(self.model.grad_buckets, self.sums):
+            if grad.dtype == flat.dtype and flat.data_ptr() <= grad.data_ptr() < flat.data_ptr() + flat.numel() * flat.element_size():
+                o = (grad.data_ptr() - flat.data_ptr()) // flat.element_size()
+                return sm[o:o + grad.numel()].view(grad.shape)
+        raise ValueError("gradient does not live in a synchronised bucket")
+
+    def _send(self, bi: int, lo: int, hi: int):
+        if hi <= lo:
+            return
+        goff, soff, dt, es, _ = self.slots[bi]
+        self.ready.record()
+        self.side.wait_event(self.ready)
+        self.peer.all_reduce_sum(goff + lo, soff + lo, (hi - lo) // es, dt, stream=self.side,
+                                 background_blocks=self.blocks)
+        self.launches += 1
+
+    def after_layer(self, layer):
+        """Called by Model.backward after `layer`'s backward has been queued."""
+        for bi in range(len(self.slots)):
+            lo = self._layer_lo.get((id(layer), bi))
+            if lo is None:
+                continue
+            self._done_lo[bi] = min(self._done_lo[bi], lo)
+            if self._sent_lo[bi] - self._done_lo[bi] >= self.min_bytes:
+                self._send(bi, self._done_lo[bi], self._sent_lo[bi])
+                self._sent_lo[bi] = self._done_lo[bi]
+
+    def finish(self):
+        for bi in range(len(self.slots)):
+            self._send(bi, 0, self._sent_lo[bi])
+            self._sent_lo[bi] = 0
+        self.done.record(self.side)
+        torch.cuda.current_stream().wait_event(self.done)
+        self.begin()
+
+    def check(self):
+        self.peer.check()
+
+    def close(self):
+        self.peer.close()

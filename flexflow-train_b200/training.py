@@ -296,7 +296,16 @@ class Model:
         self.params = [p for l in layers for p in l.params]
         self.grads = [g for l in layers for g in l.grads]
 
-    def _flatten_gradients(self):
+    def rehome_gradients(self, flats: List[torch.Tensor]):
+        """Move the flat gradient buckets into caller-provided storage of the same sizes (e.g. views
+        of a peer-mapped region, so that the data-parallel sum can read them over NVLink)."""
+        assert len(flats) == len(self.grad_buckets)
+        for old, new in zip(self.grad_buckets, flats):
+            assert old.dtype == new.dtype and old.numel() == new.numel()
+        self._flatten_gradients(flats)
+        self.grads = [g for l in self.layers for g in l.grads]
+
+    def _flatten_gradients(self, flats: Optional[List[torch.Tensor]] = None):
         """Re-home every weight gradient in one flat bucket per dtype (16-byte aligned slots),
         so that zeroing is one fill and data-parallel sync is one all-reduce per bucket."""
         by_dtype: Dict[torch.dtype, List] = {}
@@ -304,10 +313,11 @@ class Model:
             for g in l.grads:
                 by_dtype.setdefault(g.dtype, []).append((l, g))
         self.grad_buckets: List[torch.Tensor] = []
-        for dt, items in by_dtype.items():
+        for bi, (dt, items) in enumerate(by_dtype.items()):
             align = 16 // torch.empty(0, dtype=dt).element_size()
             total = sum((g.numel() + align - 1) // align * align for _, g in items)
-            flat = torch.zeros(total, dtype=dt, device=items[0][1].device)
+            flat = flats[bi] if flats is not None else torch.zeros(total, dtype=dt, device=items[0][1].device)
+            assert flat.numel() == total
             off = 0
             for l, g in items:
                 view = flat[off:off + g.numel()].view(g.shape)
@@ -339,9 +349,11 @@ class Model:
         for l in self.layers:
             l.forward()
 
-    def backward(self):
+    def backward(self, after_layer=None):
         for l in reversed(self.layers):
             l.backward()
+            if after_layer is not None and l.grads:
+                after_layer(l)
 
 
 def sparse_cce_step(model: Model, labels: torch.Tensor, opt: SGD, pops=None, global_batch=None):
@@ -355,25 +367,35 @@ def sparse_cce_step(model: Model, labels: torch.Tensor, opt: SGD, pops=None, glo
     scale = 1.0 / float(global_batch or rows)
     K.sparse_categorical_crossentropy_loss_backward_kernel(None, probs.grad, probs.data, labels, rows,
                                                            probs.shape[-1], 1, scale)
+    _backward_sync_update(model, opt, pops)
+
+
+def _backward_sync_update(model: Model, opt: SGD, pops):
+    """backward, data-parallel gradient sum (SUM over ranks, no division), optimizer. `pops` is a
+    ParallelOps (NCCL all-reduce of the flat buckets after backward) or a PeerGradSync (peer-memory
+    sums issued under the backward pass; the optimizer reads the summed buckets)."""
+    if pops is not None and hasattr(pops, "after_layer"):
+        model.backward(pops.after_layer)
+        pops.finish()
+        opt.step(model.params, pops.summed_grads)
+        return
     model.backward()
     if pops is not None:
         pops.allreduce_gradients(model.grad_buckets)
     opt.step(model.params, model.grads)
 
 
-def mse_step(model: Model, target: torch.Tensor, opt: SGD, pops=None, global_batch=None):
-    """One step with the mean-squared-error (avg) loss: scale = 2 / global volume."""
+def mse_step(model: Model, target: torch.Tensor, opt: SGD, pops=None, replicas=None):
+    """One step with the mean-squared-error (avg) loss: scale = 2 / global volume (the volume of
+    all `replicas` data-parallel batches; default: the size of `pops`' group)."""
     model.zero_gradients()
     model.forward()
     out = model.output
     per_rank = out.data.numel()
-    world = 1 if pops is None else pops.world
+    world = replicas if replicas else (1 if pops is None else pops.world)
     scale = 2.0 / float(per_rank * world)
     K.mean_squared_error_avg_loss_backward_kernel(None, out.grad, out.data, target, scale)
-    model.backward()
-    if pops is not None:
-        pops.allreduce_gradients(model.grad_buckets)
-    opt.step(model.params, model.grads)
+    _backward_sync_update(model, opt, pops)
 
 
 def build_mlp(batch=64, dims=(784, 512, 512, 10), dtype=torch.float32, device="cuda"):

@@ -69,6 +69,15 @@ int ffk_p2p_local_buffer(void *group, void **data_out, size_t *bytes_out);
  * and ffk_p2p_status returns FFK_ERR_CUDA on all ranks until the group is destroyed. */
 int ffk_p2p_all_reduce_sum(void *stream, void *group, size_t in_offset, size_t out_offset,
                            size_t count, int dtype);
+/* The same sum (same rank-order fp32 arithmetic, bit-identical results) by a kernel shaped to
+ * run UNDERNEATH other work: `blocks` CTAs of 128 threads, at most 80 registers per thread and
+ * no shared memory, so that a CTA fits on an SM beside a resident tcgen05 GEMM CTA. Meant for
+ * the data-parallel gradient sum of optimizer_kernel.cu:83-89 launched on a side stream while
+ * the backward pass is still producing the next bucket; the all-reduce of a layer's gradients
+ * then costs no step time as long as NVLink keeps up (32 blocks move ~150 GB/s). Every rank
+ * must pass the same `blocks`. */
+int ffk_p2p_all_reduce_sum_background(void *stream, void *group, size_t in_offset,
+                                      size_t out_offset, size_t count, int dtype, int blocks);
 int ffk_p2p_status(void *group);
 int ffk_p2p_destroy(void *group);
 

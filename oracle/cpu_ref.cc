@@ -946,20 +946,26 @@ ORACLE_API void oracle_mha_backward(long long const *dims, float const *q, float
   float const *wq = w + oq, *wk = w + ok, *wv = w + ov, *wo = w + oo;
   size_t Rq = (size_t)d.N * d.Sq, Rk = (size_t)d.N * d.Sk;
   std::vector<double> doc(Rq * HV, 0.0), dqp(Rq * HQ, 0.0), dkp(Rk * HK, 0.0), dvp(Rk * HV, 0.0);
-  // through the output projection
+  // through the output projection (every sum below runs over its index in ascending order; the
+  // loops are only arranged so that rows stream through the cache and threads own whole outputs)
+#pragma omp parallel for schedule(static)
   for (size_t r = 0; r < Rq; ++r)
     for (int c = 0; c < HV; ++c) {
       double acc = 0.0;
       for (int o = 0; o < d.oP; ++o) acc += (double)dout[r * d.oP + o] * wo[(size_t)c * d.oP + o];
       doc[r * HV + c] = acc;
     }
-  for (int c = 0; c < HV; ++c)
-    for (int o = 0; o < d.oP; ++o) {
-      double acc = 0.0;
-      for (size_t r = 0; r < Rq; ++r) acc += f.oc[r * HV + c] * dout[r * d.oP + o];
-      dw[oo + (size_t)c * d.oP + o] += (float)acc;
+#pragma omp parallel for schedule(static)
+  for (int c = 0; c < HV; ++c) {
+    std::vector<double> acc(d.oP, 0.0);
+    for (size_t r = 0; r < Rq; ++r) {
+      double a = f.oc[r * HV + c];
+      for (int o = 0; o < d.oP; ++o) acc[o] += a * dout[r * d.oP + o];
     }
-  // attention core
+    for (int o = 0; o < d.oP; ++o) dw[oo + (size_t)c * d.oP + o] += (float)acc[o];
+  }
+  // attention core: a (sample, head) pair owns its columns of dqp / dkp / dvp
+#pragma omp parallel for collapse(2) schedule(static)
   for (int n = 0; n < d.N; ++n)
     for (int h = 0; h < d.H; ++h)
       for (int s = 0; s < d.Sq; ++s) {
@@ -990,19 +996,24 @@ ORACLE_API void oracle_mha_backward(long long const *dims, float const *q, float
   // through the input projections: data gradients overwrite, weight gradients accumulate
   auto back = [](float const *x, float *dx, float const *wm, float *dwm, std::vector<double> const &dproj,
                  size_t rows, int in, int cols) {
-    if (dx)
+    if (dx) {
+#pragma omp parallel for schedule(static)
       for (size_t r = 0; r < rows; ++r)
         for (int i = 0; i < in; ++i) {
           double acc = 0.0;
           for (int c = 0; c < cols; ++c) acc += dproj[r * cols + c] * wm[(size_t)i * cols + c];
           dx[r * in + i] = (float)acc;
         }
-    for (int i = 0; i < in; ++i)
-      for (int c = 0; c < cols; ++c) {
-        double acc = 0.0;
-        for (size_t r = 0; r < rows; ++r) acc += (double)x[r * in + i] * dproj[r * cols + c];
-        dwm[(size_t)i * cols + c] += (float)acc;
+    }
+#pragma omp parallel for schedule(static)
+    for (int i = 0; i < in; ++i) {
+      std::vector<double> acc(cols, 0.0);
+      for (size_t r = 0; r < rows; ++r) {
+        double xv = (double)x[r * in + i];
+        for (int c = 0; c < cols; ++c) acc[c] += xv * dproj[r * cols + c];
       }
+      for (int c = 0; c < cols; ++c) dwm[(size_t)i * cols + c] += (float)acc[c];
+    }
   };
   back(q, dq, wq, dw + oq, dqp, Rq, d.qS, HQ);
   back(k, dk, wk, dw + ok, dkp, Rk, d.kS, HK);

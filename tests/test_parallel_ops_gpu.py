@@ -1,5 +1,8 @@
-"""GPU, 2 ranks over NCCL (skipped on a single-GPU box): the multi-GPU parallel operators with
-the real local kernels, checked against the single-process statement of the same math."""
+"""GPU, 2 / 4 / 8 ranks over NCCL (each skipped when the box has fewer GPUs): the multi-GPU
+parallel operators with the real local kernels, checked against the single-process statement of
+the same math — bit-exact for Replicate forward and every Repartition / Combine direction along
+every dimension (the reference's exact-equality tests: lib/kernels/test/src/
+test_partition_kernel.cc:30-58, test_replicate_kernel.cc:28-34, test_combine_kernel.cc)."""
 import os
 import socket
 import sys
@@ -28,17 +31,18 @@ def _worker(rank, world, port, results):
     P = ParallelOps()
     ok = {}
     g = torch.Generator(device="cuda").manual_seed(1234)
+    tri = world * (world + 1) // 2
     for dtype in (torch.float32, torch.bfloat16):
-        full = torch.rand(8, 6, 64, generator=g, device="cuda").to(dtype)
+        full = torch.rand(8, 16, 64, generator=g, device="cuda").to(dtype)
         x = full.clone() if rank == 0 else torch.zeros_like(full)
         P.replicate_forward(x)
         ok[f"replicate_fwd_{dtype}"] = torch.equal(x, full)
         dx = torch.ones_like(full)
         P.replicate_backward(dx, (full * (rank + 1)).contiguous())
-        ok[f"replicate_bwd_{dtype}"] = torch.allclose(dx.float(), 1 + full.float() * 3, rtol=2e-2)
+        ok[f"replicate_bwd_{dtype}"] = torch.allclose(dx.float(), 1 + full.float() * tri, rtol=2e-2)
         out = torch.zeros_like(full)
         P.reduction_forward((full * (rank + 1)).contiguous(), out)
-        ok[f"reduction_fwd_{dtype}"] = torch.allclose(out.float(), full.float() * 3, rtol=2e-2)
+        ok[f"reduction_fwd_{dtype}"] = torch.allclose(out.float(), full.float() * tri, rtol=2e-2)
         for dim in (0, 1, 2):
             slab = torch.zeros(P.slab_shape(full.shape, dim), dtype=dtype, device="cuda")
             P.repartition_forward(full, slab, dim)
@@ -58,15 +62,17 @@ def _worker(rank, world, port, results):
     dist.destroy_process_group()
 
 
-def test_parallel_ops_two_gpus_nccl():
-    if torch.cuda.device_count() < 2:
-        pytest.skip("needs 2 GPUs (run with gpurun --gpus 2)")
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_parallel_ops_nccl(world):
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs (run with gpurun --gpus {world})")
     with socket.socket() as s:
         s.bind(("127.0.0.1", 0))
         port = s.getsockname()[1]
     mgr = mp.Manager()
     results = mgr.dict()
-    mp.spawn(_worker, args=(2, port, results), nprocs=2, join=True)
+    mp.spawn(_worker, args=(world, port, results), nprocs=world, join=True)
+    assert len(results) == world
     for rank, ok in results.items():
         bad = [k for k, v in ok.items() if not v]
         assert not bad, f"rank {rank}: {bad}"

@@ -6,7 +6,7 @@ import numpy as np
 import pytest
 import torch
 
-from helpers import assert_close, uniform
+from helpers import assert_close, assert_close_l2, uniform
 
 pytestmark = pytest.mark.gpu
 
@@ -58,6 +58,53 @@ def test_mlp_config0_three_steps_match_the_oracle(ffk, oracle):
         for l, (w, b) in zip(lin, P):
             assert_close(l.w, w, rtol=1e-4, what=f"step {step} weights")
             assert_close(l.b, b, rtol=1e-4, what=f"step {step} bias")
+
+
+@pytest.mark.parametrize("dtype,rate", [(torch.float32, 0.0), (torch.float32, 0.1), (torch.bfloat16, 0.1)])
+def test_encoder_step_matches_the_oracle(ffk, oracle, dtype, rate):
+    """BASELINE configs[2] at toy size: one full training step (forward, MSE gradient, backward with
+    dq + dk + dv, SGD) of the transformer-encoder graph against the same step composed from the
+    CPU oracle (tests/oracle_encoder.py), with the dropout masks the GPU drew. fp32: rtol 1e-4;
+    bf16: the model output within 2e-2, updated weights within one bf16 rounding of the update."""
+    import importlib
+    from oracle_encoder import OracleEncoder
+    T = importlib.import_module("flexflow_train_b200.training")
+    B, S, D, H, hd, FF, L = 4, 16, 64, 4, 24, 128, 2
+    model = T.build_transformer_encoder(num_layers=L, d_model=D, heads=H, seq=S, batch=B, dim_ff=FF, head_dim=hd,
+                                        dropout=rate, dtype=dtype)
+    per = len(model.layers) // L
+    names = ("mha", "g1", "b1", "w1", "c1", "w2", "c2", "g2", "b2")
+
+    def params(i):
+        att, _, ln1, ff1, dp1, ff2, dp2, _, ln2 = model.layers[i * per:(i + 1) * per]
+        return (att.w, ln1.gamma, ln1.beta, ff1.w, ff1.b, ff2.w, ff2.b, ln2.gamma, ln2.beta), (dp1, dp2)
+
+    g = torch.Generator(device="cuda").manual_seed(11)
+    for i in range(L):   # non-trivial affine parameters and biases
+        for t in params(i)[0][1:]:
+            if t.dim() == 1:
+                t.add_(((torch.rand(t.shape, device="cuda", generator=g) - 0.5) * 0.4).to(dtype))
+    W = [{n: t.float().cpu().numpy().copy() for n, t in zip(names, params(i)[0])} for i in range(L)]
+    x = (torch.rand(B, S, D, device="cuda", generator=g) * 2 - 1).to(dtype)
+    target = (torch.rand(B, S, D, device="cuda", generator=g) * 2 - 1).to(dtype)
+    opt = T.SGD(lr=0.05, weight_decay=1e-3)
+    model.input.data.copy_(x)
+    T.mse_step(model, target, opt)
+    torch.cuda.synchronize()
+    masks = [tuple(d.state.mask.cpu().numpy().view(np.uint32).copy() for d in params(i)[1]) for i in range(L)]
+    enc = OracleEncoder(oracle, W, B, S, D, H, hd, FF, rate=rate)
+    out = enc.step(x.float().cpu().numpy(), target.float().cpu().numpy(), 0.05, 1e-3, masks=masks)
+    if dtype == torch.float32:
+        assert_close(model.output.data, out, what="encoder output")
+    else:   # chains of 16-bit GEMMs: bounded in relative L2 (helpers.assert_close_l2)
+        assert_close_l2(model.output.data, out, what="encoder output")
+    for i in range(L):
+        for n, t in zip(names, params(i)[0]):
+            if dtype == torch.float32:
+                assert_close(t, W[i][n], rtol=1e-4, what=f"layer {i} {n} after SGD")
+            else:
+                # master weights are fp32; the bf16 copy is within one rounding of the oracle's value
+                assert_close(t, W[i][n], dtype, what=f"layer {i} {n} after SGD")
 
 
 def test_small_encoder_trains(ffk):
