@@ -772,7 +772,9 @@ def run_encoder(args):
         P = importlib.import_module("flexflow_train_b200.parallel_ops")
         if os.environ.get("FFK_BENCH_GRAD_SYNC", "peer") == "peer":
             try:
-                pops = P.PeerGradSync(model, group=dp_group)   # raises the same error on every rank
+                pops = P.PeerGradSync(model, group=dp_group,   # raises the same error on every rank
+                                      min_bytes=int(os.environ.get("FFK_BENCH_SYNC_MIN_MB", "48")) << 20,
+                                      background_blocks=int(os.environ.get("FFK_BENCH_SYNC_BLOCKS", "32")))
                 grad_sync = ("peer-memory all-reduce (ffk_p2p_all_reduce_sum_background: SUM over ranks, no "
                              "division), one launch per >= 48 MiB of finished gradients on a high-priority side "
                              "stream under the backward pass; SGD reads the summed buckets")

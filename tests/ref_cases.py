@@ -52,8 +52,9 @@ def inputs():
     I["act"] = dict(y=u(18, 500), dy=u(19, 500))
     I["stride"] = dict(inp=u(20, 6, 10), out=u(21, 6, 4), blocks=6, out_blk=4, in_blk=10)
     I["unary"] = dict(x=u(22, 400, lo=0.2, hi=2.0), dy=u(23, 400), scalar=1.7)
-    I["metrics"] = dict(logits=u(24, 32, 10, lo=0.0), labels=rng.integers(0, 10, 32).astype(np.int32),
-                        dense=u(25, 32, 10, lo=0.0))
+    mlab = rng.integers(0, 10, 32).astype(np.int32)
+    # the label-metrics kernel asserts exactly one entry > 0.9 per row (metrics_functions.cu:95-102)
+    I["metrics"] = dict(logits=u(24, 32, 10, lo=0.0), labels=mlab, dense=np.eye(10, dtype=np.float32)[mlab])
     I["topk"] = dict(x=u(26, 4, 50), k=5, dout=u(27, 4, 5))
     I["replicas"] = dict(x=u(28, 5, 100), n=100, reps=5)
     I["linear"] = dict(x=u(29, 64, 40), w=u(30, 48, 40) / np.sqrt(40).astype(np.float32))
@@ -159,9 +160,10 @@ def run_ref(lib, torch):
     call("ref_gelu_forward_inplace", st, P(gx), ctypes.c_size_t(500))
     O["gelu_tanh_fwd"] = gx.cpu().numpy()
     c = I["stride"]
+    inp = dev(c["inp"])
     for add in (0, 1):
         out = dev(c["out"])
-        call("ref_copy_with_stride", st, P(out), P(dev(c["inp"])), c["blocks"], c["out_blk"], c["in_blk"], add)
+        call("ref_copy_with_stride", st, P(out), P(inp), c["blocks"], c["out_blk"], c["in_blk"], add)
         O[f"stride_{'add' if add else 'copy'}"] = out.cpu().numpy()
     c = I["unary"]
     x, dy = dev(c["x"]), dev(c["dy"])
@@ -171,24 +173,27 @@ def run_ref(lib, torch):
         call("ref_element_unary_backward", st, REF_UNARY[op], F(c["scalar"]), P(y), P(dy), P(x), P(dx), ctypes.c_longlong(400))
         O[f"unary_{op}_y"], O[f"unary_{op}_dx"] = y.cpu().numpy(), dx.cpu().numpy()
     c = I["metrics"]
+    # (operands are held in variables: a temporary would be freed, and its memory reused, before the launch)
+    logits, labels, dense = dev(c["logits"]), dev(c["labels"]), dev(c["dense"])
     perf = z(7, dt=torch.int32)
-    call("ref_metrics_sparse", st, 1 | 4 | 8 | 16 | 32, P(dev(c["logits"])), P(dev(c["labels"])), 32, 10, P(perf))
+    call("ref_metrics_sparse", st, 1 | 4 | 8 | 16 | 32, P(logits), P(labels), 32, 10, P(perf))
     O["metrics_sparse"] = perf.cpu().numpy()
     perf = z(7, dt=torch.int32)
-    call("ref_metrics_label", st, 1 | 2 | 8 | 16 | 32, P(dev(c["logits"])), P(dev(c["dense"])), 32, 10, P(perf))
+    call("ref_metrics_label", st, 1 | 2 | 8 | 16 | 32, P(logits), P(dense), 32, 10, P(perf))
     O["metrics_label"] = perf.cpu().numpy()
     c = I["topk"]
     x = dev(c["x"])
     out, ind, din = z(4, 5), z(4, 5, dt=torch.int32), z(4, 50)
     call("ref_topk_forward", st, P(x), P(out), P(ind), ctypes.c_size_t(4), 50, 5, 1)
-    call("ref_topk_backward", st, P(dev(c["dout"])), P(ind), P(din), ctypes.c_size_t(4), 50, 5)
+    tdout = dev(c["dout"])
+    call("ref_topk_backward", st, P(tdout), P(ind), P(din), ctypes.c_size_t(4), 50, 5)
     O["topk_values"], O["topk_indices"], O["topk_din"] = out.cpu().numpy(), ind.cpu().numpy(), din.cpu().numpy()
     c = I["replicas"]
-    acc = dev(np.ones(100, np.float32))
-    call("ref_replicate_backward", st, P(acc), P(dev(c["x"])), ctypes.c_size_t(100), ctypes.c_size_t(5))
+    acc, rx = dev(np.ones(100, np.float32)), dev(c["x"])
+    call("ref_replicate_backward", st, P(acc), P(rx), ctypes.c_size_t(100), ctypes.c_size_t(5))
     O["replicate_bwd"] = acc.cpu().numpy()
     red = z(100)
-    call("ref_reduction_forward", st, P(dev(c["x"])), P(red), ctypes.c_size_t(100), ctypes.c_size_t(5))
+    call("ref_reduction_forward", st, P(rx), P(red), ctypes.c_size_t(100), ctypes.c_size_t(5))
     O["reduction_fwd"] = red.cpu().numpy()
     c = I["linear"]
     for code, name, dt in ((0, "f32", torch.float32), (1, "f16", torch.float16), (2, "bf16", torch.bfloat16)):
@@ -197,8 +202,8 @@ def run_ref(lib, torch):
         call("ref_linear_forward_gemm", st, P(x), P(w), P(y), 40, 48, 64, code)
         O[f"linear_{name}_y"] = y.float().cpu().numpy()
     c = I["bmm"]
-    o = z(10, 10, 10)
-    call("ref_batch_matmul_forward", st, P(o), P(dev(c["a"])), P(dev(c["b"])), 10, 10, 5, 10)
+    o, ba, bb = z(10, 10, 10), dev(c["a"]), dev(c["b"])
+    call("ref_batch_matmul_forward", st, P(o), P(ba), P(bb), 10, 10, 5, 10)
     O["bmm_o"] = o.cpu().numpy()
     return O
 
@@ -404,10 +409,11 @@ def run_ffk(K, torch):
     K.Linear.forward_kernel(None, lin, torch.ones(1, 1, device="cuda"), yg, dev(c["y"] * 3).view(500, 1).contiguous(), None, 1, 500, 1)
     O["gelu_tanh_fwd"] = yg.cpu().numpy().reshape(500)
     c = I["stride"]
+    inp = dev(c["inp"])
     for add in (0, 1):
         out = dev(c["out"])
         K._call("ffk_add_with_stride" if add else "ffk_copy_with_stride", K._stream(None), out.data_ptr(),
-                dev(c["inp"]).data_ptr(), c["blocks"], c["out_blk"], c["in_blk"], K.dtype_code(out))
+                inp.data_ptr(), c["blocks"], c["out_blk"], c["in_blk"], K.dtype_code(out))
         O[f"stride_{'add' if add else 'copy'}"] = out.cpu().numpy()
     c = I["unary"]
     x, dy = dev(c["x"]), dev(c["dy"])
