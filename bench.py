@@ -759,14 +759,17 @@ def run_encoder(args):
     D, H, FF, V = (768, 12, 3072, 30522) if bert else (1024, 16, 4096, 0)
     hd = args.head_dim if args.head_dim > 0 else FF // H
     g = torch.Generator(device=device).manual_seed(1234 + rank // tp)  # one batch per data-parallel replica
+    # fused-operator execution is the default; FFK_BENCH_NO_FUSE=1 runs one kernel per operator
+    fuse = os.environ.get("FFK_BENCH_NO_FUSE") is None
     if bert:
         # the vocabulary head's gradients go through repacked operands: that needs scratch
         Kmod.set_gemm_workspace(int(B * S * ((V + 7) // 8 * 8) * 2 * 1.05))
         model = T.build_bert(L, D, H, FF, S, B, V, dropout=0.1, dtype=torch.bfloat16, device=device,
-                             tp_rank=tp_rank, tp_world=tp, tp_group=tp_group)
+                             tp_rank=tp_rank, tp_world=tp, tp_group=tp_group, fuse=fuse)
         labels = torch.randint(0, V, (B * S,), generator=g, device=device, dtype=torch.int32)
     else:
-        model = T.build_transformer_encoder(L, D, H, S, B, FF, hd, dropout=0.1, dtype=torch.bfloat16, device=device)
+        model = T.build_transformer_encoder(L, D, H, S, B, FF, hd, dropout=0.1, dtype=torch.bfloat16, device=device,
+                                            fuse=fuse)
     sync_launches_per_step = 0
     if dp > 1:
         P = importlib.import_module("flexflow_train_b200.parallel_ops")
@@ -887,6 +890,7 @@ def run_encoder(args):
             dist.destroy_process_group()
         return
     ms_per_step = ms_total / args.steps
+    model_fused = bool(getattr(model, "fuse", False))
     params = sum(p.numel() for p in model.params)
     # fwd+bwd FLOPs per sample: 3 x (projections + scores + FFN), SURVEY §8d
     per_tok = 2 * (3 * D * H * hd + H * hd * D + 2 * S * H * hd + 2 * D * FF)
@@ -920,6 +924,9 @@ def run_encoder(args):
                    "global_batch": B * dp, "seq_len": S, "parameters": params,
                    "parallelism": (f"dp{dp}" + (f" x tp{tp}" if tp > 1 else "")) if world > 1 else "single",
                    "grad_sync": grad_sync,
+                   "execution": ("fused operators: MHA+residual, dense+activation+dropout, dense+dropout+residual as "
+                                 "single GEMM launches; first-writer gradients (no zero fills), shared residual "
+                                 "gradient buffers, gated data gradients") if model_fused else "one kernel per operator",
                    "l2": "inputs larger than L2: one layer's activations are >= 0.5 GB against 126 MB of L2, no explicit flush"},
         "roofline": {"kernel": f"gemm_tc_pair_kernel (tcgen05 cta_group::2): feed-forward Linear forward "
                                f"{ff1.batch}x{ff1.out_dim}x{ff1.in_dim} bf16 with bias + activation epilogue, "

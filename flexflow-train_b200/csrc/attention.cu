@@ -69,7 +69,8 @@ struct Ctx {
 int mm(Ctx const &c, void const *a, long long lda, bool a_mn, void const *b, long long ldb,
        bool b_mn, void *d, long long ldd, long long M, long long N, long long K, bool accumulate,
        long long batch = 1, long long batch2 = 1, long long a_b = 0, long long a_b2 = 0,
-       long long b_b = 0, long long b_b2 = 0, long long d_b = 0, long long d_b2 = 0) {
+       long long b_b = 0, long long b_b2 = 0, long long d_b = 0, long long d_b2 = 0,
+       void const *residual = nullptr) {
   if (M == 0 || N == 0 || batch == 0) return FFK_OK;
   gemm::Problem p{a, b, lda, ldb, a_b, b_b, (int)M, (int)N, (int)K, (int)batch, c.dtype, c.dtype,
                   a_mn, b_mn};
@@ -78,6 +79,10 @@ int mm(Ctx const &c, void const *a, long long lda, bool a_mn, void const *b, lon
   p.b_batch2 = b_b2;
   gemm::Epilogue e{d, ldd, d_b, nullptr, gemm::ACT_NONE, accumulate ? 1 : 0, 1.f, 0.f, nullptr};
   e.d_batch2 = d_b2;
+  if (residual) {  // D = A B + residual, through the epilogue's `lambda * R` term
+    e.r = residual;
+    e.lambda = 1.f;
+  }
   switch (c.path) {
     case FFK_GEMM_TENSOR: return gemm::launch_tc(p, e, c.s);
     case FFK_GEMM_SIMT: return gemm::launch_simt(p, e, c.s);
@@ -109,9 +114,12 @@ size_t ffk_mha_workspace_bytes(ffk_mha_config_t const *cfg_host, int dtype) {
   return size_t(g.w_total) * dtype_size(dtype);
 }
 
-int ffk_mha_forward(void *stream, ffk_mha_config_t const *cfg_host, void const *query,
-                    void const *key, void const *value, void const *weight, void *output,
-                    void *reserve, int dtype, int path) {
+}  // extern "C"
+
+namespace {
+int mha_forward_impl(void *stream, ffk_mha_config_t const *cfg_host, void const *query,
+                     void const *key, void const *value, void const *weight, void *output,
+                     void *reserve, int dtype, int path, void const *residual) {
   Geo g;
   int rc = make_geo(cfg_host, dtype, g);
   if (rc) return rc;
@@ -150,15 +158,17 @@ int ffk_mha_forward(void *stream, ffk_mha_config_t const *cfg_host, void const *
   if ((rc = mm(c, pp, g.Sk, false, vp, g.HV, true, oc, g.HV, g.Sq, g.vP, g.Sk, false, g.N * g.H, g.H,
                g.H * g.Sq * g.Sk, g.Sq * g.Sk, g.Sk * g.HV, g.vP, g.Sq * g.HV, g.vP)))
     return rc;
-  // output projection
-  return mm(c, oc, g.HV, false, c.at(weight, g.wo), g.oP, true, output, g.oP, g.Rq, g.oP, g.HV, false);
+  // output projection (+ residual)
+  return mm(c, oc, g.HV, false, c.at(weight, g.wo), g.oP, true, output, g.oP, g.Rq, g.oP, g.HV, false,
+            1, 1, 0, 0, 0, 0, 0, 0, residual);
 }
 
-int ffk_mha_backward(void *stream, ffk_mha_config_t const *cfg_host, void const *query,
-                     void *query_grad, void const *key, void *key_grad, void const *value,
-                     void *value_grad, void const *weight, void *weight_grad,
-                     void const *output_grad, void const *reserve, void *workspace,
-                     size_t workspace_bytes, int dtype, int path) {
+// acc_*: 0 = the gradient is overwritten (cuDNN's BackwardData semantics), 1 = added to.
+int mha_backward_impl(void *stream, ffk_mha_config_t const *cfg_host, void const *query,
+                      void *query_grad, void const *key, void *key_grad, void const *value,
+                      void *value_grad, void const *weight, void *weight_grad,
+                      void const *output_grad, void const *reserve, void *workspace,
+                      size_t workspace_bytes, int dtype, int path, bool acc_q, bool acc_k, bool acc_v) {
   Geo g;
   int rc = make_geo(cfg_host, dtype, g);
   if (rc) return rc;
@@ -196,12 +206,48 @@ int ffk_mha_backward(void *stream, ffk_mha_config_t const *cfg_host, void const 
                g.H * g.Sq * g.Sk, g.Sq * g.Sk, g.Sq * g.HQ, g.qP, g.Sk * g.HK, g.kP)))
     return rc;
   // input projections: dX = dXp W^T (overwrite) ; dW += X^T dXp
-  if (query_grad && (rc = mm(c, dqp, g.HQ, false, wq, g.HQ, false, query_grad, g.qS, g.Rq, g.qS, g.HQ, false))) return rc;
-  if (key_grad && (rc = mm(c, dkp, g.HK, false, wk, g.HK, false, key_grad, g.kS, g.Rk, g.kS, g.HK, false))) return rc;
-  if (value_grad && (rc = mm(c, dvp, g.HV, false, wv, g.HV, false, value_grad, g.vS, g.Rk, g.vS, g.HV, false))) return rc;
+  if (query_grad && (rc = mm(c, dqp, g.HQ, false, wq, g.HQ, false, query_grad, g.qS, g.Rq, g.qS, g.HQ, acc_q))) return rc;
+  if (key_grad && (rc = mm(c, dkp, g.HK, false, wk, g.HK, false, key_grad, g.kS, g.Rk, g.kS, g.HK, acc_k))) return rc;
+  if (value_grad && (rc = mm(c, dvp, g.HV, false, wv, g.HV, false, value_grad, g.vS, g.Rk, g.vS, g.HV, acc_v))) return rc;
   if ((rc = mm(c, query, g.qS, true, dqp, g.HQ, true, c.at(weight_grad, g.wq), g.HQ, g.qS, g.HQ, g.Rq, true))) return rc;
   if ((rc = mm(c, key, g.kS, true, dkp, g.HK, true, c.at(weight_grad, g.wk), g.HK, g.kS, g.HK, g.Rk, true))) return rc;
   return mm(c, value, g.vS, true, dvp, g.HV, true, c.at(weight_grad, g.wv), g.HV, g.vS, g.HV, g.Rk, true);
+}
+}  // namespace
+
+extern "C" {
+
+int ffk_mha_forward(void *stream, ffk_mha_config_t const *cfg_host, void const *query,
+                    void const *key, void const *value, void const *weight, void *output,
+                    void *reserve, int dtype, int path) {
+  return mha_forward_impl(stream, cfg_host, query, key, value, weight, output, reserve, dtype, path, nullptr);
+}
+
+int ffk_mha_forward_residual(void *stream, ffk_mha_config_t const *cfg_host, void const *query,
+                             void const *key, void const *value, void const *weight, void *output,
+                             void *reserve, int dtype, int path, void const *residual) {
+  return mha_forward_impl(stream, cfg_host, query, key, value, weight, output, reserve, dtype, path, residual);
+}
+
+int ffk_mha_backward(void *stream, ffk_mha_config_t const *cfg_host, void const *query,
+                     void *query_grad, void const *key, void *key_grad, void const *value,
+                     void *value_grad, void const *weight, void *weight_grad,
+                     void const *output_grad, void const *reserve, void *workspace,
+                     size_t workspace_bytes, int dtype, int path) {
+  return mha_backward_impl(stream, cfg_host, query, query_grad, key, key_grad, value, value_grad, weight,
+                           weight_grad, output_grad, reserve, workspace, workspace_bytes, dtype, path, false,
+                           false, false);
+}
+
+int ffk_mha_backward_accumulate(void *stream, ffk_mha_config_t const *cfg_host, void const *query,
+                                void *query_grad, void const *key, void *key_grad, void const *value,
+                                void *value_grad, void const *weight, void *weight_grad,
+                                void const *output_grad, void const *reserve, void *workspace,
+                                size_t workspace_bytes, int dtype, int path, int accumulate_query_grad,
+                                int accumulate_key_grad, int accumulate_value_grad) {
+  return mha_backward_impl(stream, cfg_host, query, query_grad, key, key_grad, value, value_grad, weight,
+                           weight_grad, output_grad, reserve, workspace, workspace_bytes, dtype, path,
+                           accumulate_query_grad != 0, accumulate_key_grad != 0, accumulate_value_grad != 0);
 }
 
 }  // extern "C"

@@ -1,5 +1,6 @@
 // Linear and BatchMatmul on top of the GEMM engine (gemm_sm100.cu).
 #include "gemm_sm100.cuh"
+#include "philox.cuh"
 
 namespace ffk {
 namespace {
@@ -16,6 +17,62 @@ int run_gemm(gemm::Problem const &p, gemm::Epilogue const &e, cudaStream_t s, in
 
 // dY <- dY * act'(.) in place. `ref` is Y for relu/sigmoid/tanh and the
 // pre-activation for gelu.
+// With `mask` (the keep bits of a dropout that followed the activation, 1 bit per element) the
+// dropout gradient is folded in: dY <- dY * keep * scale * act'(.), one pass instead of two.
+template <typename T>
+__global__ void __launch_bounds__(256)
+    dropout_act_backward_kernel(T *__restrict__ dy, T const *__restrict__ ref,
+                                uint32_t const *__restrict__ mask, size_t n, int act, float scale) {
+  constexpr int VN = Vec16<T>::N;
+  size_t nvec = n / VN;
+  size_t stride = size_t(gridDim.x) * blockDim.x;
+  auto grad = [&](float gv, float yv) -> float {
+    if (act == FFK_ACT_NONE) return gv;
+    if (act == FFK_ACT_RELU) return yv > 0.f ? gv : 0.f;
+    if (act == FFK_ACT_SIGMOID) return gv * yv * (1.f - yv);
+    if (act == FFK_ACT_TANH) return gv * (1.f - yv * yv);
+    constexpr float B = 0.7978845608028654f, C = 0.035677408136300125f;
+    float u = yv * (C * yv * yv + B);
+    float t = tanhf(u);
+    float du = B + 3.f * C * yv * yv;
+    return gv * (0.5f + 0.5f * t + 0.5f * yv * (1.f - t * t) * du);
+  };
+  for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < nvec; i += stride) {
+    size_t const e0 = i * VN;
+    uint32_t const bits = __ldg(mask + e0 / 32) >> (e0 % 32);
+    Vec16<T> g = ld_vec(dy + e0);
+    Vec16<T> y;
+    if (act != FFK_ACT_NONE) y = ld_stream(ref + e0);
+#pragma unroll
+    for (int j = 0; j < VN; ++j) {
+      float gv = ((bits >> j) & 1u) ? to_f32(g.v[j]) * scale : 0.f;
+      g.v[j] = from_f32<T>(grad(gv, act != FFK_ACT_NONE ? to_f32(y.v[j]) : 0.f));
+    }
+    st_vec(dy + e0, g);
+  }
+  for (size_t e = nvec * VN + size_t(blockIdx.x) * blockDim.x + threadIdx.x; e < n; e += stride) {
+    float gv = ((mask[e / 32] >> (e % 32)) & 1u) ? to_f32(dy[e]) * scale : 0.f;
+    dy[e] = from_f32<T>(grad(gv, act != FFK_ACT_NONE ? to_f32(ref[e]) : 0.f));
+  }
+}
+
+// dx <- gate > 0 ? dx * scale : 0 (the gradient through a ReLU, or ReLU + dropout, whose stored
+// OUTPUT is `gate`): the stand-alone form of the data-gradient epilogue's gate mode.
+template <typename T>
+__global__ void __launch_bounds__(256)
+    gate_kernel(T *__restrict__ dx, T const *__restrict__ gate, size_t n, float scale) {
+  constexpr int VN = Vec16<T>::N;
+  size_t nvec = n / VN, stride = size_t(gridDim.x) * blockDim.x;
+  for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < nvec; i += stride) {
+    Vec16<T> g = ld_vec(dx + i * VN), y = ld_stream(gate + i * VN);
+#pragma unroll
+    for (int j = 0; j < VN; ++j) g.v[j] = from_f32<T>(to_f32(y.v[j]) > 0.f ? to_f32(g.v[j]) * scale : 0.f);
+    st_vec(dx + i * VN, g);
+  }
+  for (size_t e = nvec * VN + size_t(blockIdx.x) * blockDim.x + threadIdx.x; e < n; e += stride)
+    dx[e] = from_f32<T>(to_f32(gate[e]) > 0.f ? to_f32(dx[e]) * scale : 0.f);
+}
+
 template <typename T>
 __global__ void __launch_bounds__(256)
     act_backward_kernel(T *__restrict__ dy, T const *__restrict__ ref, size_t n, int act) {
@@ -179,18 +236,42 @@ int ffk_linear_forward(void *stream, void const *input, void *output, void const
   return run_gemm(p, e, as_stream(stream), path);
 }
 
-int ffk_linear_backward(void *stream, void const *input, void *input_grad, void const *output,
-                        void *output_grad, void const *weight, void *weight_grad,
-                        void *bias_grad, int in_dim, int out_dim, int batch_size, int dtype,
-                        int activation, float l2_lambda, void const *preact, int path,
-                        void *workspace, size_t workspace_bytes) {
+}  // extern "C"
+
+namespace {
+int linear_backward_impl(void *stream, void const *input, void *input_grad, void const *output,
+                         void *output_grad, void const *weight, void *weight_grad,
+                         void *bias_grad, int in_dim, int out_dim, int batch_size, int dtype,
+                         int activation, float l2_lambda, void const *preact, int path,
+                         void *workspace, size_t workspace_bytes,
+                         ffk_linear_backward_fusion_t const &fu) {
   FFK_REQUIRE(in_dim > 0 && out_dim > 0 && batch_size >= 0, "linear backward: bad extents");
   if (batch_size == 0) return FFK_OK;
   FFK_REQUIRE(input && output_grad && weight && weight_grad, "linear backward: null tensor");
   cudaStream_t s = as_stream(stream);
   size_t n_out = size_t(out_dim) * batch_size;
 
-  if (activation != FFK_ACT_NONE) {
+  if (fu.output_grad_is_preactivation) {
+    // a gated data-gradient epilogue upstream already applied this layer's activation (and
+    // dropout) gradient: nothing to do here
+  } else if (fu.dropout_mask != nullptr && fu.dropout_rate > 0.f) {
+    void const *ref = activation == FFK_ACT_GELU ? preact : output;
+    if (activation == FFK_ACT_GELU && !preact) {
+      set_error("linear backward: GELU gradient needs the pre-activation buffer");
+      return FFK_ERR_UNSUPPORTED;
+    }
+    FFK_REQUIRE(activation == FFK_ACT_NONE || ref, "linear backward: activation gradient needs `output`");
+    FFK_REQUIRE(aligned16(output_grad) && (!ref || aligned16(ref)), "linear backward: unaligned tensor");
+    FFK_REQUIRE(fu.dropout_rate <= 1.f, "linear backward: dropout rate %f outside [0,1]", fu.dropout_rate);
+    float scale = fu.dropout_rate < 1.f ? 1.f / (1.f - fu.dropout_rate) : 0.f;
+    FFK_DISPATCH_FLOAT(dtype, T, {
+      unsigned grid = stream_grid(n_out / Vec16<T>::N + 1, 256, 8);
+      dropout_act_backward_kernel<T><<<grid, 256, 0, s>>>(
+          reinterpret_cast<T *>(output_grad), reinterpret_cast<T const *>(ref),
+          reinterpret_cast<uint32_t const *>(fu.dropout_mask), n_out, activation, scale);
+    });
+    FFK_LAUNCH_CHECK();
+  } else if (activation != FFK_ACT_NONE) {
     void const *ref = output;
     if (activation == FFK_ACT_GELU) {
       if (!preact) {
@@ -242,14 +323,121 @@ int ffk_linear_backward(void *stream, void const *input, void *input_grad, void 
     });
     FFK_LAUNCH_CHECK();
   }
-  if (input_grad) {  // data gradient: dX[b][i] += sum_o dY[b][o] W[o][i]
+  if (input_grad) {  // data gradient: dX[b][i] (+)= sum_o dY[b][o] W[o][i]
     gemm::Problem p{output_grad, weight, out_dim, in_dim, 0, 0, batch_size, in_dim, out_dim, 1,
                     dtype, dtype, false, true};
-    gemm::Epilogue e{input_grad, in_dim, 0, nullptr, gemm::ACT_NONE, 1, 1.f, 0.f, nullptr};
-    int rc = run_gemm(p, e, s, path);
-    if (rc) return rc;
+    gemm::Epilogue e{input_grad, in_dim, 0, nullptr, gemm::ACT_NONE, fu.accumulate_input_grad ? 1 : 0,
+                     1.f, 0.f, nullptr};
+    if (fu.input_gate != nullptr) {
+      gemm::Epilogue g = e;
+      g.r = fu.input_gate;
+      g.r_mode = 1;
+      g.lambda = fu.input_gate_scale;
+      if ((path == FFK_GEMM_AUTO || path == FFK_GEMM_TENSOR) && gemm::fused_eligible(p, g)) {
+        int rc = gemm::launch_tc(p, g, s);
+        if (rc) return rc;
+      } else {
+        if (fu.accumulate_input_grad) {
+          set_error("linear backward: a gated data gradient that accumulates needs the tensor-core "
+                    "epilogue (16-bit tensors, in_dim a multiple of 32, 16-byte aligned rows)");
+          return FFK_ERR_UNSUPPORTED;
+        }
+        int rc = run_gemm(p, e, s, path);
+        if (rc) return rc;
+        size_t n_in = size_t(in_dim) * batch_size;
+        FFK_DISPATCH_FLOAT(dtype, T, {
+          gate_kernel<T><<<stream_grid(n_in / Vec16<T>::N + 1, 256, 8), 256, 0, s>>>(
+              reinterpret_cast<T *>(input_grad), reinterpret_cast<T const *>(fu.input_gate), n_in,
+              fu.input_gate_scale);
+        });
+        FFK_LAUNCH_CHECK();
+      }
+    } else {
+      int rc = run_gemm(p, e, s, path);
+      if (rc) return rc;
+    }
   }
   return FFK_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int ffk_linear_backward(void *stream, void const *input, void *input_grad, void const *output,
+                        void *output_grad, void const *weight, void *weight_grad,
+                        void *bias_grad, int in_dim, int out_dim, int batch_size, int dtype,
+                        int activation, float l2_lambda, void const *preact, int path,
+                        void *workspace, size_t workspace_bytes) {
+  ffk_linear_backward_fusion_t plain{};
+  plain.accumulate_input_grad = 1;
+  return linear_backward_impl(stream, input, input_grad, output, output_grad, weight, weight_grad, bias_grad,
+                              in_dim, out_dim, batch_size, dtype, activation, l2_lambda, preact, path,
+                              workspace, workspace_bytes, plain);
+}
+
+int ffk_linear_backward_fused(void *stream, void const *input, void *input_grad, void const *output,
+                              void *output_grad, void const *weight, void *weight_grad,
+                              void *bias_grad, int in_dim, int out_dim, int batch_size, int dtype,
+                              int activation, float l2_lambda, void const *preact, int path,
+                              void *workspace, size_t workspace_bytes,
+                              ffk_linear_backward_fusion_t const *fusion_host) {
+  FFK_REQUIRE(fusion_host, "linear backward (fused): null fusion record");
+  return linear_backward_impl(stream, input, input_grad, output, output_grad, weight, weight_grad, bias_grad,
+                              in_dim, out_dim, batch_size, dtype, activation, l2_lambda, preact, path,
+                              workspace, workspace_bytes, *fusion_host);
+}
+
+int ffk_linear_forward_fused(void *stream, void const *input, void *output, void const *weight,
+                             void const *bias, int in_dim, int out_dim, int batch_size, int dtype,
+                             int activation, int path, ffk_linear_forward_fusion_t const *fusion_host) {
+  FFK_REQUIRE(fusion_host, "linear forward (fused): null fusion record");
+  ffk_linear_forward_fusion_t const &fu = *fusion_host;
+  FFK_REQUIRE(in_dim > 0 && out_dim > 0 && batch_size >= 0, "linear forward: bad extents");
+  if (batch_size == 0) return FFK_OK;
+  FFK_REQUIRE(input && output && weight, "linear forward: null tensor");
+  FFK_REQUIRE(fu.dropout_rate >= 0.f && fu.dropout_rate <= 1.f, "linear forward: dropout rate %f outside [0,1]",
+              fu.dropout_rate);
+  bool const drop = fu.dropout_rate > 0.f;
+  cudaStream_t s = as_stream(stream);
+  gemm::Problem p{input, weight, in_dim, in_dim, 0, 0, batch_size, out_dim, in_dim, 1,
+                  dtype, dtype, false, false};
+  gemm::Epilogue e{output, out_dim, 0, bias, activation, 0, 1.f, 0.f, nullptr};
+  gemm::Epilogue f = e;
+  f.aux_out = fu.preact_out;
+  if (drop) {
+    f.drop_on = 1;
+    f.drop_mask = reinterpret_cast<unsigned *>(fu.dropout_mask);
+    f.drop_thresh = dropout_thresh16(fu.dropout_rate);
+    f.drop_scale = fu.dropout_rate < 1.f ? 1.f / (1.f - fu.dropout_rate) : 0.f;
+    f.drop_seed = fu.dropout_seed;
+    f.drop_offset = fu.dropout_offset;
+  }
+  if (fu.residual) {
+    f.r = fu.residual;
+    f.lambda = 1.f;
+    f.r_mode = 0;
+  }
+  if ((path == FFK_GEMM_AUTO || path == FFK_GEMM_TENSOR) && gemm::fused_eligible(p, f))
+    return gemm::launch_tc(p, f, s);   // one kernel: product, bias, activation, dropout, residual
+  // the same result from the unfused chain (any dtype, any shape)
+  size_t n_out = size_t(out_dim) * batch_size;
+  if (fu.preact_out) {
+    gemm::Epilogue pre = e;
+    pre.d = fu.preact_out;
+    pre.act = gemm::ACT_NONE;
+    int rc = run_gemm(p, pre, s, path);
+    if (rc) return rc;
+  }
+  int rc = run_gemm(p, e, s, path);
+  if (rc) return rc;
+  if (drop) {
+    FFK_REQUIRE(fu.dropout_mask, "linear forward (fused): the unfused chain needs a dropout mask buffer");
+    rc = ffk_dropout_forward(stream, output, output, fu.dropout_mask, n_out, fu.dropout_rate, fu.dropout_seed,
+                             fu.dropout_offset, dtype);
+    if (rc) return rc;
+  }
+  if (fu.residual) rc = ffk_accumulate(stream, output, fu.residual, n_out, dtype);
+  return rc;
 }
 
 size_t ffk_linear_backward_workspace_bytes(int out_dim) {

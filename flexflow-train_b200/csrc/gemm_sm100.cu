@@ -1,6 +1,7 @@
 // tcgen05 / TMEM / TMA GEMM for sm_100a plus the CUDA-core fp32-exact GEMM.
 // See gemm_sm100.cuh for the contract.
 #include "gemm_sm100.cuh"
+#include "philox.cuh"
 
 #include <cudaTypedefs.h>
 #include <cstdlib>
@@ -170,6 +171,28 @@ __device__ __forceinline__ void epilogue_chunk_staged(uint32_t const (&acc)[32],
       for (int i = 0; i < 32; ++i) v[i] += to_f32(bp[i]);
     }
   }
+  // coalesced side: lane -> (row = it*8 + lane/4, piece = lane%4)
+  int const c_row = lane >> 2, c_piece = lane & 3;
+  int const my_sw = (lane >> 1) & 3;  // row-per-thread side: this thread's row is `lane`
+  // v (row per thread) -> 16 bits -> staging -> 64-byte row segments of `dst`
+  auto store_rows = [&](T *dst) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      Vec16<T> t;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) t.v[i] = from_f32<T>(v[j * 8 + i]);
+      *reinterpret_cast<uint4 *>(stage + lane * 64 + ((j ^ my_sw) << 4)) = *reinterpret_cast<uint4 *>(&t);
+    }
+    __syncwarp();
+#pragma unroll
+    for (int it = 0; it < 4; ++it) {
+      int const r = it * 8 + c_row;
+      uint4 t = *reinterpret_cast<uint4 const *>(stage + r * 64 + ((c_piece ^ ((r >> 1) & 3)) << 4));
+      if (r < rows_valid) *reinterpret_cast<uint4 *>(dst + block_off + r * ep.ldd + col0 + c_piece * 8) = t;
+    }
+    __syncwarp();
+  };
+  if (ep.aux_out != nullptr) store_rows(reinterpret_cast<T *>(ep.aux_out));  // the pre-activation
   if (ep.act == ACT_RELU) {
 #pragma unroll
     for (int i = 0; i < 32; ++i) v[i] = fmaxf(v[i], 0.f);
@@ -177,10 +200,21 @@ __device__ __forceinline__ void epilogue_chunk_staged(uint32_t const (&acc)[32],
 #pragma unroll
     for (int i = 0; i < 32; ++i) v[i] = apply_act_fast(v[i], ep.act);
   }
-  // coalesced side: lane -> (row = it*8 + lane/4, piece = lane%4)
-  int const c_row = lane >> 2, c_piece = lane & 3;
-  int const my_sw = (lane >> 1) & 3;  // row-per-thread side: this thread's row is `lane`
-  auto add_from_global = [&](T const *src, float scale) {
+  if (ep.drop_on) {
+    // this thread's 32 elements are one mask word: element e keeps iff field e % 8 of
+    // Philox(e / 8, offset, seed) >= threshold — the rule of the stand-alone dropout kernel
+    unsigned long long const e0 = (unsigned long long)(block_off + (long long)lane * ep.ldd + col0);
+    uint32_t bits = 0;
+    if (ep.drop_thresh < 0x10000u) {
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+        bits |= philox_keep8(e0 / 8 + q, ep.drop_offset, ep.drop_seed, ep.drop_thresh) << (q * 8);
+    }
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = ((bits >> i) & 1u) ? v[i] * ep.drop_scale : 0.f;
+    if (ep.drop_mask != nullptr && row_ok) ep.drop_mask[e0 / 32] = bits;
+  }
+  auto add_from_global = [&](T const *src, float scale, bool gate) {
     uint4 t[4];
 #pragma unroll
     for (int it = 0; it < 4; ++it) {
@@ -200,30 +234,19 @@ __device__ __forceinline__ void epilogue_chunk_staged(uint32_t const (&acc)[32],
       Vec16<T> t2;
       *reinterpret_cast<uint4 *>(&t2) =
           *reinterpret_cast<uint4 const *>(stage + lane * 64 + ((j ^ my_sw) << 4));
+      if (gate) {
 #pragma unroll
-      for (int i = 0; i < 8; ++i) v[j * 8 + i] += scale * to_f32(t2.v[i]);
+        for (int i = 0; i < 8; ++i) v[j * 8 + i] = to_f32(t2.v[i]) > 0.f ? v[j * 8 + i] * scale : 0.f;
+      } else {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v[j * 8 + i] += scale * to_f32(t2.v[i]);
+      }
     }
     __syncwarp();
   };
-  if (ep.r != nullptr) add_from_global(reinterpret_cast<T const *>(ep.r), ep.lambda);
-  if (ep.accumulate) add_from_global(reinterpret_cast<T const *>(ep.d), 1.f);
-  (void)row_ok;
-#pragma unroll
-  for (int j = 0; j < 4; ++j) {
-    Vec16<T> t;
-#pragma unroll
-    for (int i = 0; i < 8; ++i) t.v[i] = from_f32<T>(v[j * 8 + i]);
-    *reinterpret_cast<uint4 *>(stage + lane * 64 + ((j ^ my_sw) << 4)) = *reinterpret_cast<uint4 *>(&t);
-  }
-  __syncwarp();
-  T *d = reinterpret_cast<T *>(ep.d);
-#pragma unroll
-  for (int it = 0; it < 4; ++it) {
-    int const r = it * 8 + c_row;
-    uint4 t = *reinterpret_cast<uint4 const *>(stage + r * 64 + ((c_piece ^ ((r >> 1) & 3)) << 4));
-    if (r < rows_valid) *reinterpret_cast<uint4 *>(d + block_off + r * ep.ldd + col0 + c_piece * 8) = t;
-  }
-  __syncwarp();
+  if (ep.r != nullptr) add_from_global(reinterpret_cast<T const *>(ep.r), ep.lambda, ep.r_mode == 1);
+  if (ep.accumulate) add_from_global(reinterpret_cast<T const *>(ep.d), 1.f, false);
+  store_rows(reinterpret_cast<T *>(ep.d));
 }
 
 // 16-bit outputs whose rows are NOT 16-byte aligned (a 30522-column vocabulary): same transposition,
@@ -1098,6 +1121,14 @@ int launch_tc(Problem const &p, Epilogue const &e, cudaStream_t stream) {
   if (!no_pair && !narrow && p.M > 128) return launch_tc_pair(p, e, stream);
   return narrow ? launch_tc_layout<2, 128, 6>(p, e, stream)
                 : launch_tc_layout<2, 256, 4>(p, e, stream);
+}
+
+bool fused_eligible(Problem const &p, Epilogue const &e) {
+  size_t os = dtype_size(p.out_dtype);
+  bool sixteen = (p.in_dtype == FFK_BFLOAT16 || p.in_dtype == FFK_HALF) && p.out_dtype == p.in_dtype;
+  return sixteen && p.batch == 1 && p.N % 32 == 0 && e.ldd == p.N && !e.add_d_before_act &&
+         aligned16(e.d) && (e.ldd * os) % 16 == 0 && (!e.r || aligned16(e.r)) &&
+         (!e.aux_out || aligned16(e.aux_out)) && tc_eligible(p, e);
 }
 
 bool softmax_gemm_eligible(Problem const &p, Epilogue const &e) {

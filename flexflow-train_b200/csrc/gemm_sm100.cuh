@@ -33,6 +33,17 @@ struct Epilogue {
   int bias_vec_ok = 0;   // set by the launcher: bias readable as 16-byte packets
   long long d_batch2 = 0;  // elements between inner batches of D (see Problem::batch2)
   int add_d_before_act = 0;  // 1: v = alpha*acc + D, THEN bias / activation (split-precision passes)
+  // ---- fused-operator extras (ffk_linear_forward_fused / ffk_linear_backward_fused, dense.cu).
+  // Only the staged 16-bit epilogue implements them: 16-bit D with 16-byte aligned rows, N a
+  // multiple of 32, one batch; `fused_eligible` checks that before any of them is set. Order:
+  //   v = alpha*acc + bias -> aux_out <- v -> v = act(v) -> v = dropout(v) -> R -> (+ D) -> store
+  void *aux_out = nullptr;        // copy of the pre-activation, same layout as D
+  int r_mode = 0;                 // 0: v += lambda * R;  1: v = R > 0 ? v * lambda : 0 (gate by a ReLU / dropout output)
+  int drop_on = 0;                // dropout behind the activation
+  unsigned *drop_mask = nullptr;  // 1 keep bit per element of D ([M][N] dense), may be null
+  unsigned drop_thresh = 0;       // keep iff the element's 16-bit Philox field >= drop_thresh
+  float drop_scale = 1.f;         // 1 / (1 - rate)
+  unsigned long long drop_seed = 0, drop_offset = 0;
 };
 
 // Problem in "logical" terms. a/b pointers are the stored matrices:
@@ -61,6 +72,9 @@ struct Problem {
 // operands break a TMA constraint (16-byte aligned base and row pitch).
 int launch_tc(Problem const &p, Epilogue const &e, cudaStream_t stream);
 bool tc_eligible(Problem const &p, Epilogue const &e);
+// true when the staged 16-bit epilogue (and therefore Epilogue's fused-operator extras) serves
+// every chunk of this problem
+bool fused_eligible(Problem const &p, Epilogue const &e);
 // D = softmax over each row of (A B^T): 512-column rows, K-major 16-bit operands (the attention
 // scores of a 512-token sequence), normalised in TMEM before they are stored.
 bool softmax_gemm_eligible(Problem const &p, Epilogue const &e);

@@ -450,7 +450,7 @@ __global__ void __launch_bounds__(TPB)
     layer_norm_bwd_rows_kernel(T const *__restrict__ dy, T const *__restrict__ x,
                                T *__restrict__ dx, T const *__restrict__ gamma,
                                float const *__restrict__ mean, float const *__restrict__ rstd,
-                               float *__restrict__ part, long long rows, int nvec) {
+                               float *__restrict__ part, long long rows, int nvec, bool dx_acc) {
   constexpr int VN = Vec16<T>::N;
   constexpr int Q = VN / 4;  // float4 groups per packet
   extern __shared__ float4 ln_smem[];
@@ -516,7 +516,8 @@ __global__ void __launch_bounds__(TPB)
       if (i < nvec) {
         if (dx) {
           T *dxr = dx + r * N;
-          Vec16<T> o = ld_vec(dxr + i * VN);
+          Vec16<T> o = Vec16<T>{};  // dx_acc: dX += ..., else dX = ... (no read of the old value)
+          if (dx_acc) o = ld_vec(dxr + i * VN);
 #pragma unroll
           for (int q = 0; q < Q; ++q) {
             float4 g4 = sg[i * Q + q];
@@ -611,7 +612,7 @@ __global__ void __launch_bounds__(kThreads)
     layer_norm_bwd_generic_kernel(T const *__restrict__ dy, T const *__restrict__ x,
                                   T *__restrict__ dx, T const *__restrict__ gamma,
                                   float const *__restrict__ mean, float const *__restrict__ rstd,
-                                  long long rows, long long N) {
+                                  long long rows, long long N, bool dx_acc) {
   __shared__ float red[64];
   for (long long r = blockIdx.x; r < rows; r += gridDim.x) {
     T const *dyr = dy + r * N;
@@ -630,7 +631,7 @@ __global__ void __launch_bounds__(kThreads)
     T *dxr = dx + r * N;
     for (long long j = threadIdx.x; j < N; j += blockDim.x) {
       float gv = gamma ? to_f32(gamma[j]) : 1.f;
-      dxr[j] = from_f32<T>(to_f32(dxr[j]) + rs * to_f32(dyr[j]) * gv + c1 * to_f32(xr[j]) + c2);
+      dxr[j] = from_f32<T>((dx_acc ? to_f32(dxr[j]) : 0.f) + rs * to_f32(dyr[j]) * gv + c1 * to_f32(xr[j]) + c2);
     }
   }
 }
@@ -825,13 +826,13 @@ __global__ void __launch_bounds__(128)
                                T *__restrict__ dx, T const *__restrict__ gamma,
                                float const *__restrict__ mean, float const *__restrict__ rstd,
                                float *__restrict__ part, long long rows, int nvec,
-                               long long num_warps, int stages) {
+                               long long num_warps, int stages, bool dx_acc) {
   constexpr int VN = Vec16<T>::N;
   extern __shared__ __align__(128) uint8_t ring_smem[];
   int const lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   long long const N = (long long)nvec * VN;
   uint32_t const row_bytes = uint32_t(N * sizeof(T));
-  int const tensors = dx ? 3 : 2;
+  int const tensors = (dx && dx_acc) ? 3 : 2;  // the old dX travels through the ring only when it is added to
   long long const gw = (long long)blockIdx.x * 4 + warp;
   // layout: [4 warps][stages][tensors][row_bytes] then [4 warps][stages] barriers
   uint8_t *my_ring = ring_smem + size_t(warp) * stages * tensors * row_bytes;
@@ -848,7 +849,7 @@ __global__ void __launch_bounds__(128)
     ptx::mbar_arrive_expect_tx(&bars[st], tensors * row_bytes);
     ptx::bulk_load(dst, dy + r * N, row_bytes, &bars[st]);
     ptx::bulk_load(dst + row_bytes, x + r * N, row_bytes, &bars[st]);
-    if (dx) ptx::bulk_load(dst + 2 * row_bytes, dx + r * N, row_bytes, &bars[st]);
+    if (tensors == 3) ptx::bulk_load(dst + 2 * row_bytes, dx + r * N, row_bytes, &bars[st]);
   };
   if (lane == 0) {
     for (int s2 = 0; s2 < stages; ++s2) {
@@ -882,7 +883,8 @@ __global__ void __launch_bounds__(128)
       if (i < nvec) {
         a[p] = *reinterpret_cast<Vec16<T> const *>(src + size_t(i) * 16);
         b[p] = *reinterpret_cast<Vec16<T> const *>(src + row_bytes + size_t(i) * 16);
-        if (dx) o[p] = *reinterpret_cast<Vec16<T> const *>(src + 2 * row_bytes + size_t(i) * 16);
+        o[p] = Vec16<T>{};
+        if (tensors == 3) o[p] = *reinterpret_cast<Vec16<T> const *>(src + 2 * row_bytes + size_t(i) * 16);
       }
     }
     // the row is in registers: hand the stage back and refill it
@@ -960,14 +962,14 @@ __global__ void __launch_bounds__(256, 2)
     layer_norm_bwd_cta_ring_kernel(T const *__restrict__ dy, T const *__restrict__ x,
                                    T *__restrict__ dx, T const *__restrict__ gamma,
                                    float const *__restrict__ mean, float const *__restrict__ rstd,
-                                   float *__restrict__ part, long long rows, int nvec) {
+                                   float *__restrict__ part, long long rows, int nvec, bool dx_acc) {
   constexpr int VN = Vec16<T>::N, STAGES = 2;
   extern __shared__ __align__(128) uint8_t ring_smem[];
   __shared__ float red[64];
   __shared__ __align__(8) uint64_t bars[STAGES];
   long long const N = (long long)nvec * VN;
   uint32_t const row_bytes = uint32_t(N * sizeof(T));
-  int const tensors = dx ? 3 : 2;
+  int const tensors = (dx && dx_acc) ? 3 : 2;  // the old dX travels through the ring only when it is added to
   T *sgamma = reinterpret_cast<T *>(ring_smem + size_t(STAGES) * tensors * row_bytes);
   if (threadIdx.x == 0) {
     for (int s2 = 0; s2 < STAGES; ++s2) ptx::mbar_init(&bars[s2], 1);
@@ -986,7 +988,7 @@ __global__ void __launch_bounds__(256, 2)
     ptx::mbar_arrive_expect_tx(&bars[st], tensors * row_bytes);
     ptx::bulk_load(dst, dy + r * N, row_bytes, &bars[st]);
     ptx::bulk_load(dst + row_bytes, x + r * N, row_bytes, &bars[st]);
-    if (dx) ptx::bulk_load(dst + 2 * row_bytes, dx + r * N, row_bytes, &bars[st]);
+    if (tensors == 3) ptx::bulk_load(dst + 2 * row_bytes, dx + r * N, row_bytes, &bars[st]);
   };
   if (threadIdx.x == 0) {
     for (int s2 = 0; s2 < STAGES; ++s2) {
@@ -1016,7 +1018,8 @@ __global__ void __launch_bounds__(256, 2)
       if (i < nvec) {
         a[p] = *reinterpret_cast<Vec16<T> const *>(src + size_t(i) * 16);
         b[p] = *reinterpret_cast<Vec16<T> const *>(src + row_bytes + size_t(i) * 16);
-        if (dx) o[p] = *reinterpret_cast<Vec16<T> const *>(src + 2 * row_bytes + size_t(i) * 16);
+        o[p] = Vec16<T>{};
+        if (tensors == 3) o[p] = *reinterpret_cast<Vec16<T> const *>(src + 2 * row_bytes + size_t(i) * 16);
         Vec16<T> g = *reinterpret_cast<Vec16<T> const *>(sgamma + i * VN);
 #pragma unroll
         for (int j = 0; j < VN; ++j) {
@@ -1097,7 +1100,7 @@ __global__ void __launch_bounds__(kThreads)
     layer_norm_bwd_warp_rows_kernel(T const *__restrict__ dy, T const *__restrict__ x,
                                     T *__restrict__ dx, T const *__restrict__ gamma,
                                     float const *__restrict__ mean, float const *__restrict__ rstd,
-                                    float *__restrict__ part, long long rows, int nvec) {
+                                    float *__restrict__ part, long long rows, int nvec, bool dx_acc) {
   constexpr int VN = Vec16<T>::N;
   extern __shared__ float4 ln_smem[];  // [2][N] floats, accumulated warp after warp
   int const lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -1132,7 +1135,8 @@ __global__ void __launch_bounds__(kThreads)
       int i = lane + p * 32, ii = i < nvec ? i : 0;
       ak[p] = ld_stream(dyr + ii * VN);
       bk[p] = ld_stream(xr + ii * VN);
-      if (dx) ok[p] = ld_vec(dx + r * N + ii * VN);
+      ok[p] = Vec16<T>{};
+      if (dx && dx_acc) ok[p] = ld_vec(dx + r * N + ii * VN);
     }
 #pragma unroll
     for (int p = 0; p < PW; ++p) {
@@ -1432,11 +1436,16 @@ size_t ffk_layer_norm_backward_workspace_bytes(long long N) {
          sizeof(float);
 }
 
-int ffk_layer_norm_backward(void *stream, void const *output_grad, void const *input,
-                            void *input_grad, void const *gamma, void *gamma_grad,
-                            void *beta_grad, float const *mean, float const *rstd, long long M,
-                            long long N, int dtype, int accumulate_param_grads, void *workspace,
-                            size_t workspace_bytes) {
+}  // extern "C"
+
+namespace {
+// dx_acc: input_grad += ... (the reference's beta = 1 convention) or input_grad = ... (first
+// writer of that gradient: no zero fill before, no read of the old value here)
+int layer_norm_backward_impl(void *stream, void const *output_grad, void const *input,
+                             void *input_grad, void const *gamma, void *gamma_grad,
+                             void *beta_grad, float const *mean, float const *rstd, long long M,
+                             long long N, int dtype, int accumulate_param_grads, void *workspace,
+                             size_t workspace_bytes, bool dx_acc) {
   FFK_REQUIRE(M >= 0 && N >= 0, "layer_norm: negative extent");
   if (M == 0 || N == 0) return FFK_OK;
   FFK_REQUIRE(output_grad && input && mean && rstd, "layer_norm backward: null tensor");
@@ -1448,7 +1457,8 @@ int ffk_layer_norm_backward(void *stream, void const *output_grad, void const *i
                (!input_grad || aligned16(input_grad)) && (!gamma || aligned16(gamma)) &&
                pick_p(N / VN) != 0;
     size_t per_part = size_t(2) * size_t(N) * sizeof(float);
-    size_t parts_fit = (workspace && want_params) ? workspace_bytes / per_part : 0;
+    // partial slabs are stored with float4: a workspace that is not 16-byte aligned is not used
+    size_t parts_fit = (workspace && want_params && aligned16(workspace)) ? workspace_bytes / per_part : 0;
     bool fused = vec && want_params && parts_fit >= 1;
     bool short_rows = vec && pick_pw(N / VN) != 0 && pick_pw(N / VN) <= 2;
     static bool const no_ring = std::getenv("FFK_LN_NO_RING") != nullptr;
@@ -1459,7 +1469,7 @@ int ffk_layer_norm_backward(void *stream, void const *output_grad, void const *i
     if (ring_rows && (input_grad || fused)) {
       int nvec = int(N / VN);
       size_t row_bytes = size_t(N) * sizeof(T);
-      int tensors = input_grad ? 3 : 2;
+      int tensors = (input_grad && dx_acc) ? 3 : 2;
       int stages = (int)std::max<size_t>(2, std::min<size_t>(6, (24 * 1024) / (tensors * row_bytes)));
       size_t smem = size_t(4) * stages * tensors * row_bytes + size_t(4) * stages * 8;
       float *wpart = fused ? reinterpret_cast<float *>(workspace) : nullptr;
@@ -1474,7 +1484,7 @@ int ffk_layer_norm_backward(void *stream, void const *output_grad, void const *i
         kern<<<unsigned((warps + 3) / 4), 128, smem, s>>>(
             reinterpret_cast<T const *>(output_grad), reinterpret_cast<T const *>(input),
             reinterpret_cast<T *>(input_grad), reinterpret_cast<T const *>(gamma), mean, rstd, wpart, M,
-            nvec, warps, stages);
+            nvec, warps, stages, dx_acc);
         return FFK_OK;
       };
       int rc = FFK_OK;
@@ -1498,7 +1508,7 @@ int ffk_layer_norm_backward(void *stream, void const *output_grad, void const *i
       // long rows: CTA-level ring (N <= 4096 at 16 columns per thread)
       int nvec = int(N / VN), pp = pick_p(nvec);
       size_t row_bytes = size_t(N) * sizeof(T);
-      int tensors = input_grad ? 3 : 2;
+      int tensors = (input_grad && dx_acc) ? 3 : 2;
       size_t smem = size_t(2) * tensors * row_bytes + row_bytes;
       float *wpart = fused ? reinterpret_cast<float *>(workspace) : nullptr;
       unsigned grid = 0;
@@ -1510,7 +1520,7 @@ int ffk_layer_norm_backward(void *stream, void const *output_grad, void const *i
         if (fused) grid = (unsigned)std::min<size_t>(grid, parts_fit);
         kern<<<grid, 256, smem, s>>>(
             reinterpret_cast<T const *>(output_grad), reinterpret_cast<T const *>(input),
-            reinterpret_cast<T *>(input_grad), reinterpret_cast<T const *>(gamma), mean, rstd, wpart, M, nvec);
+            reinterpret_cast<T *>(input_grad), reinterpret_cast<T const *>(gamma), mean, rstd, wpart, M, nvec, dx_acc);
         return FFK_OK;
       };
       int rc = FFK_OK;
@@ -1537,11 +1547,11 @@ int ffk_layer_norm_backward(void *stream, void const *output_grad, void const *i
       if (p == 1) {
         layer_norm_bwd_warp_rows_kernel<T, 1><<<grid, kThreads, smem, s>>>(
             reinterpret_cast<T const *>(output_grad), reinterpret_cast<T const *>(input),
-            reinterpret_cast<T *>(input_grad), reinterpret_cast<T const *>(gamma), mean, rstd, wpart, M, nvec);
+            reinterpret_cast<T *>(input_grad), reinterpret_cast<T const *>(gamma), mean, rstd, wpart, M, nvec, dx_acc);
       } else {
         layer_norm_bwd_warp_rows_kernel<T, 2><<<grid, kThreads, smem, s>>>(
             reinterpret_cast<T const *>(output_grad), reinterpret_cast<T const *>(input),
-            reinterpret_cast<T *>(input_grad), reinterpret_cast<T const *>(gamma), mean, rstd, wpart, M, nvec);
+            reinterpret_cast<T *>(input_grad), reinterpret_cast<T const *>(gamma), mean, rstd, wpart, M, nvec, dx_acc);
       }
       FFK_LAUNCH_CHECK();
       if (fused) {
@@ -1565,14 +1575,14 @@ int ffk_layer_norm_backward(void *stream, void const *output_grad, void const *i
                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         layer_norm_bwd_rows_kernel<T, 1, 128><<<grid, 128, smem, s>>>(
             reinterpret_cast<T const *>(output_grad), reinterpret_cast<T const *>(input),
-            reinterpret_cast<T *>(input_grad), reinterpret_cast<T const *>(gamma), mean, rstd, part, M, nvec);
+            reinterpret_cast<T *>(input_grad), reinterpret_cast<T const *>(gamma), mean, rstd, part, M, nvec, dx_acc);
       } else {
         FFK_DISPATCH_P(p, P, {
           FFK_CUDA(cudaFuncSetAttribute(layer_norm_bwd_rows_kernel<T, P, kThreads>,
                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
           layer_norm_bwd_rows_kernel<T, P, kThreads><<<grid, kThreads, smem, s>>>(
               reinterpret_cast<T const *>(output_grad), reinterpret_cast<T const *>(input),
-              reinterpret_cast<T *>(input_grad), reinterpret_cast<T const *>(gamma), mean, rstd, part, M, nvec);
+              reinterpret_cast<T *>(input_grad), reinterpret_cast<T const *>(gamma), mean, rstd, part, M, nvec, dx_acc);
         });
       }
       FFK_LAUNCH_CHECK();
@@ -1586,7 +1596,7 @@ int ffk_layer_norm_backward(void *stream, void const *output_grad, void const *i
     } else if (input_grad) {
       layer_norm_bwd_generic_kernel<T><<<rows_grid(M, 8), kThreads, 0, s>>>(
           reinterpret_cast<T const *>(output_grad), reinterpret_cast<T const *>(input),
-          reinterpret_cast<T *>(input_grad), reinterpret_cast<T const *>(gamma), mean, rstd, M, N);
+          reinterpret_cast<T *>(input_grad), reinterpret_cast<T const *>(gamma), mean, rstd, M, N, dx_acc);
       FFK_LAUNCH_CHECK();
     }
     if (want_params && !fused) {
@@ -1598,6 +1608,28 @@ int ffk_layer_norm_backward(void *stream, void const *output_grad, void const *i
     }
   });
   return FFK_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int ffk_layer_norm_backward(void *stream, void const *output_grad, void const *input,
+                            void *input_grad, void const *gamma, void *gamma_grad,
+                            void *beta_grad, float const *mean, float const *rstd, long long M,
+                            long long N, int dtype, int accumulate_param_grads, void *workspace,
+                            size_t workspace_bytes) {
+  return layer_norm_backward_impl(stream, output_grad, input, input_grad, gamma, gamma_grad, beta_grad, mean,
+                                  rstd, M, N, dtype, accumulate_param_grads, workspace, workspace_bytes, true);
+}
+
+int ffk_layer_norm_backward_ex(void *stream, void const *output_grad, void const *input,
+                               void *input_grad, void const *gamma, void *gamma_grad,
+                               void *beta_grad, float const *mean, float const *rstd, long long M,
+                               long long N, int dtype, int accumulate_param_grads,
+                               int accumulate_input_grad, void *workspace, size_t workspace_bytes) {
+  return layer_norm_backward_impl(stream, output_grad, input, input_grad, gamma, gamma_grad, beta_grad, mean,
+                                  rstd, M, N, dtype, accumulate_param_grads, workspace, workspace_bytes,
+                                  accumulate_input_grad != 0);
 }
 
 int ffk_batch_norm_forward(void *stream, float const *input, float *output, float const *scale,

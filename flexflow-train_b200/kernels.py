@@ -139,6 +139,49 @@ class Linear:
               _ptr(m.workspace), m.workspace.numel() * 4 if m.workspace is not None else 0)
 
 
+class _LinearForwardFusion(ctypes.Structure):      # ffk_linear_forward_fusion_t
+    _fields_ = [("preact_out", ctypes.c_void_p), ("residual", ctypes.c_void_p), ("dropout_mask", ctypes.c_void_p),
+                ("dropout_rate", ctypes.c_float), ("dropout_seed", ctypes.c_ulonglong),
+                ("dropout_offset", ctypes.c_ulonglong)]
+
+
+class _LinearBackwardFusion(ctypes.Structure):     # ffk_linear_backward_fusion_t
+    _fields_ = [("accumulate_input_grad", ctypes.c_int), ("output_grad_is_preactivation", ctypes.c_int),
+                ("dropout_mask", ctypes.c_void_p), ("dropout_rate", ctypes.c_float),
+                ("input_gate", ctypes.c_void_p), ("input_gate_scale", ctypes.c_float)]
+
+
+class FusedLinear:
+    """Fused-operator forms of Linear (ffk_linear_forward_fused / ffk_linear_backward_fused):
+    Linear -> activation -> Dropout -> + residual as one GEMM; backward with the dropout / activation
+    gradient in one pass, a first-writer (overwrite) data gradient, and a data gradient gated by the
+    stored ReLU(+dropout) output of the layer before."""
+
+    @staticmethod
+    def forward_kernel(stream, m, input, output, weight, bias, in_dim, out_dim, batch_size, preact_out=None,
+                       residual=None, dropout=None):
+        """dropout: a DropoutPerDeviceState (rate, seed, mask, offset); its offset advances per call."""
+        fu = _LinearForwardFusion(_ptr(preact_out), _ptr(residual), _ptr(dropout.mask) if dropout else None,
+                                  dropout.rate if dropout else 0.0, dropout.seed if dropout else 0,
+                                  dropout.offset if dropout else 0)
+        _call("ffk_linear_forward_fused", _stream(stream), _ptr(input), _ptr(output), _ptr(weight), _ptr(bias),
+              in_dim, out_dim, batch_size, dtype_code(input), m.activation, m.path, ctypes.byref(fu))
+        if dropout:
+            dropout.offset += 1
+
+    @staticmethod
+    def backward_kernel(stream, m, input, input_grad, output, output_grad, weight, weight_grad, bias_grad, in_dim,
+                        out_dim, batch_size, preact=None, accumulate_input_grad=True,
+                        output_grad_is_preactivation=False, dropout=None, input_gate=None, input_gate_scale=1.0):
+        fu = _LinearBackwardFusion(int(accumulate_input_grad), int(output_grad_is_preactivation),
+                                   _ptr(dropout.mask) if dropout else None, dropout.rate if dropout else 0.0,
+                                   _ptr(input_gate), float(input_gate_scale))
+        _call("ffk_linear_backward_fused", _stream(stream), _ptr(input), _ptr(input_grad), _ptr(output),
+              _ptr(output_grad), _ptr(weight), _ptr(weight_grad), _ptr(bias_grad), in_dim, out_dim, batch_size,
+              dtype_code(input), m.activation, m.l2_lambda, _ptr(preact), m.path, _ptr(m.workspace),
+              m.workspace.numel() * 4 if m.workspace is not None else 0, ctypes.byref(fu))
+
+
 class BatchMatmul:
     """batch_matmul_kernels.h"""
 
@@ -345,13 +388,22 @@ class LayerNorm:
 
     @staticmethod
     def backward_kernel(stream, m, output_grad, input, input_grad, gamma, gamma_grad, beta_grad,
-                        accumulate_param_grads=False):
+                        accumulate_param_grads=False, accumulate_input_grad=True):
+        """accumulate_input_grad=False (ffk_layer_norm_backward_ex) WRITES input_grad: for the first
+        writer of that gradient under fused-operator execution."""
         ws = m.workspace
-        _call("ffk_layer_norm_backward", _stream(stream), _ptr(output_grad), _ptr(input),
-              _ptr(input_grad), _ptr(gamma), _ptr(gamma_grad), _ptr(beta_grad), _ptr(m.mean),
-              _ptr(m.rstd), m.effective_batch_size, m.effective_num_elements,
-              dtype_code(input), int(accumulate_param_grads), _ptr(ws),
-              ws.numel() * 4 if ws is not None else 0)
+        if accumulate_input_grad:
+            _call("ffk_layer_norm_backward", _stream(stream), _ptr(output_grad), _ptr(input),
+                  _ptr(input_grad), _ptr(gamma), _ptr(gamma_grad), _ptr(beta_grad), _ptr(m.mean),
+                  _ptr(m.rstd), m.effective_batch_size, m.effective_num_elements,
+                  dtype_code(input), int(accumulate_param_grads), _ptr(ws),
+                  ws.numel() * 4 if ws is not None else 0)
+        else:
+            _call("ffk_layer_norm_backward_ex", _stream(stream), _ptr(output_grad), _ptr(input),
+                  _ptr(input_grad), _ptr(gamma), _ptr(gamma_grad), _ptr(beta_grad), _ptr(m.mean),
+                  _ptr(m.rstd), m.effective_batch_size, m.effective_num_elements,
+                  dtype_code(input), int(accumulate_param_grads), 0, _ptr(ws),
+                  ws.numel() * 4 if ws is not None else 0)
 
 
 @dataclass
@@ -698,6 +750,24 @@ class MultiHeadAttention:
     def forward_kernel(stream, m, query, key, value, weight, output):
         _call("ffk_mha_forward", _stream(stream), ctypes.byref(m.cfg), _ptr(query), _ptr(key),
               _ptr(value), _ptr(weight), _ptr(output), _ptr(m.reserveSpace), _DT[m.dtype], m.path)
+
+    @staticmethod
+    def forward_residual_kernel(stream, m, query, key, value, weight, output, residual):
+        """output = MHA(q, k, v) + residual (ffk_mha_forward_residual)."""
+        _call("ffk_mha_forward_residual", _stream(stream), ctypes.byref(m.cfg), _ptr(query), _ptr(key),
+              _ptr(value), _ptr(weight), _ptr(output), _ptr(m.reserveSpace), _DT[m.dtype], m.path,
+              _ptr(residual))
+
+    @staticmethod
+    def backward_accumulate_kernel(stream, m, query, query_grad, key, key_grad, value, value_grad, weight,
+                                   weight_grad, output_grad, accumulate=(True, True, True)):
+        """ffk_mha_backward_accumulate: data gradients are added where `accumulate` says so; the three
+        gradient pointers may be one buffer (self-attention)."""
+        _call("ffk_mha_backward_accumulate", _stream(stream), ctypes.byref(m.cfg), _ptr(query),
+              _ptr(query_grad), _ptr(key), _ptr(key_grad), _ptr(value), _ptr(value_grad),
+              _ptr(weight), _ptr(weight_grad), _ptr(output_grad), _ptr(m.reserveSpace),
+              _ptr(m.workSpace), m.workSpace.numel(), _DT[m.dtype], m.path, int(accumulate[0]),
+              int(accumulate[1]), int(accumulate[2]))
 
     @staticmethod
     def backward_kernel(stream, m, query, query_grad, key, key_grad, value, value_grad, weight,

@@ -40,6 +40,32 @@ def _fill0(t: torch.Tensor):
 class Layer:
     params: List[torch.Tensor] = []
     grads: List[torch.Tensor] = []
+    # fused-operator execution (Model(fuse=True)): a layer that is the FIRST writer of an input's
+    # gradient in backward order may write it instead of adding to it, which removes the zero fill
+    # of that gradient and the read of its old value
+    supports_overwrite = False
+    # backward finishes reading y.grad before it writes x.grad, so the two may share one buffer
+    safe_inplace = False
+    _first: Dict[int, bool] = {}
+
+    def input_tensors(self) -> List["Tensor"]:
+        """Every activation this layer reads (and sends a gradient to)."""
+        out = [getattr(self, n, None) for n in ("x", "a", "b", "residual")]
+        out += list(getattr(self, "inputs", []) or [])
+        seen, uniq = set(), []
+        for t in out:
+            if isinstance(t, Tensor) and id(t) not in seen:
+                seen.add(id(t))
+                uniq.append(t)
+        return uniq
+
+    def output_tensors(self) -> List["Tensor"]:
+        y = getattr(self, "y", None)
+        return [y] if isinstance(y, Tensor) else []
+
+    def first(self, t: "Tensor") -> bool:
+        """This layer is the first writer of t.grad in backward order (set by Model when fusing)."""
+        return self._first.get(id(t), False)
 
     def forward(self):
         raise NotImplementedError
@@ -48,13 +74,31 @@ class Layer:
         raise NotImplementedError
 
 
+_scratch_pool: Dict = {}
+
+
+def _scratch_like(t: torch.Tensor, tag: str) -> torch.Tensor:
+    """Backward scratch that is dead between layers: one buffer per (device, shape, dtype, tag)."""
+    key = (str(t.device), tuple(t.shape), t.dtype, tag)
+    buf = _scratch_pool.get(key)
+    if buf is None:
+        buf = _scratch_pool[key] = torch.empty_like(t)
+    return buf
+
+
 class Linear(Layer):
+    supports_overwrite = True
+
     def __init__(self, x: Tensor, out_dim: int, activation=K.ACT_NONE, bias=True, seed=0,
-                 shard_out=None, shard_in=None):
+                 shard_out=None, shard_in=None, dropout=None, residual: Optional[Tensor] = None):
         """shard_out = (index, count): this rank holds rows [index*out_dim, ...) of a weight with
         count*out_dim outputs (column-parallel layer); shard_in = (index, count): it holds the
         matching slice of the input features (row-parallel layer, partial sums out). The full
-        weight is drawn from the seed and sliced, so that a sharded model equals the unsharded one."""
+        weight is drawn from the seed and sliced, so that a sharded model equals the unsharded one.
+
+        Fused-operator form: dropout = (rate, seed) and / or residual make this layer
+        y = dropout(act(x W^T + b)) + residual, ONE GEMM whose epilogue does the rest
+        (ffk_linear_forward_fused) instead of Linear, Dropout and ElementBinary layers."""
         self.x = x
         dt, dev = x.data.dtype, x.data.device
         self.in_dim = x.shape[-1]
@@ -79,8 +123,20 @@ class Linear(Layer):
         self.plain = K.Linear.init_kernel(K.ACT_NONE, 0.0, bias, K.GEMM_AUTO)
         self.params = [self.w] + ([self.b] if bias else [])
         self.grads = [self.dw] + ([self.db] if bias else [])
+        self.drop = K.Dropout.init_kernel(dropout[0], dropout[1], self.y.data.numel(), device=dev) if dropout else None
+        self.residual = residual
+        self.residual_mode = "acc"       # "alias" | "copy" | "acc": how y.grad reaches residual.grad (Model)
+        self.gate_src: Optional["Linear"] = None  # producer of x whose ReLU(+dropout) gradient this dgrad applies
+        self.grad_is_preact = False      # y.grad arrives as the pre-activation gradient (a consumer gated it)
+        self.fused_preact = False        # the pre-activation is stored by the same GEMM (Model(fuse=True))
 
     def forward(self):
+        if self.drop is not None or self.residual is not None or (self.preact is not None and self.fused_preact):
+            K.FusedLinear.forward_kernel(None, self.state, self.x.data, self.y.data, self.w, self.b, self.in_dim,
+                                         self.out_dim, self.batch, preact_out=self.preact,
+                                         residual=self.residual.data if self.residual is not None else None,
+                                         dropout=self.drop)
+            return
         if self.preact is not None:
             # GELU's gradient needs the pre-activation: one extra plain projection kept beside
             # the activated output (the reference's Linear cannot differentiate GELU at all)
@@ -90,11 +146,40 @@ class Linear(Layer):
                                 self.out_dim, self.batch)
 
     def backward(self):
-        K.Linear.backward_kernel(None, self.state, self.x.data, self.x.grad, self.y.data, self.y.grad,
-                                 self.w, self.dw, self.db, self.in_dim, self.out_dim, self.batch, self.preact)
+        G = self.y.grad
+        if self.residual is not None and self.residual.grad is not None:
+            if self.residual_mode == "copy":
+                K.copy(None, self.residual.grad, G)
+            elif self.residual_mode == "acc":
+                K.accumulate(None, self.residual.grad, G)
+            # "alias": residual.grad IS y.grad
+        dy, fused_drop = G, None
+        act = self.state.activation
+        shared = self.residual is not None          # G also serves as the residual's gradient: keep it intact
+        if self.drop is not None and not self.grad_is_preact:
+            if shared or act == K.ACT_NONE:
+                dy = _scratch_like(G, "dz")
+                K.Dropout.backward_kernel(None, self.drop, G, dy)
+            else:
+                fused_drop = self.drop               # dropout + activation gradient, one pass in place on G
+        elif shared and act != K.ACT_NONE and not self.grad_is_preact:
+            dy = _scratch_like(G, "dz")
+            K.copy(None, dy, G)
+        gate = self.gate_src
+        gate_scale = 1.0
+        if gate is not None and gate.drop is not None:
+            gate_scale = 1.0 / (1.0 - gate.drop.rate) if gate.drop.rate < 1.0 else 0.0
+        K.FusedLinear.backward_kernel(None, self.state, self.x.data, self.x.grad, self.y.data, dy, self.w, self.dw,
+                                      self.db, self.in_dim, self.out_dim, self.batch, self.preact,
+                                      accumulate_input_grad=not self.first(self.x),
+                                      output_grad_is_preactivation=self.grad_is_preact, dropout=fused_drop,
+                                      input_gate=gate.y.data if gate is not None else None,
+                                      input_gate_scale=gate_scale)
 
 
 class LayerNorm(Layer):
+    supports_overwrite = True
+
     def __init__(self, x: Tensor, eps=1e-5):
         self.x = x
         dt, dev = x.data.dtype, x.data.device
@@ -114,23 +199,36 @@ class LayerNorm(Layer):
 
     def backward(self):
         K.LayerNorm.backward_kernel(None, self.state, self.y.grad, self.x.data, self.x.grad, self.gamma,
-                                    self.dgamma, self.dbeta, accumulate_param_grads=True)
+                                    self.dgamma, self.dbeta, accumulate_param_grads=True,
+                                    accumulate_input_grad=not self.first(self.x))
 
 
 class Add(Layer):
+    supports_overwrite = True
+
     def __init__(self, a: Tensor, b: Tensor):
         self.a, self.b = a, b
         self.y = Tensor(a.shape, a.data.dtype, a.data.device)
+        # set by Model(fuse=True) per operand: "alias" (operand.grad IS y.grad), "copy", or "acc"
+        self.mode = {"a": "acc", "b": "acc"}
 
     def forward(self):
         K.ElementBinary.forward_kernel(None, K.OperatorType.EW_ADD, self.a.data, self.b.data, self.y.data)
 
     def backward(self):
-        K.ElementBinary.backward_kernel(None, K.OperatorType.EW_ADD, self.y.grad, self.a.data, self.b.data,
-                                        self.a.grad, self.b.grad)
+        if self.mode["a"] == "acc" and self.mode["b"] == "acc":
+            K.ElementBinary.backward_kernel(None, K.OperatorType.EW_ADD, self.y.grad, self.a.data, self.b.data,
+                                            self.a.grad, self.b.grad)
+            return
+        for name, t in (("a", self.a), ("b", self.b)):
+            if t.grad is None or self.mode[name] == "alias":
+                continue
+            (K.copy if self.mode[name] == "copy" else K.accumulate)(None, t.grad, self.y.grad)
 
 
 class Dropout(Layer):
+    supports_overwrite = True
+
     def __init__(self, x: Tensor, rate: float, seed: int):
         self.x = x
         self.y = Tensor(x.shape, x.data.dtype, x.data.device)
@@ -144,7 +242,7 @@ class Dropout(Layer):
     def backward(self):
         # the kernel overwrites (reference semantics). When this layer is the only reader of x the
         # result IS x's gradient; otherwise the driver accumulates it into x.grad.
-        if self.sole_reader:
+        if self.sole_reader or self.first(self.x):
             K.Dropout.backward_kernel(None, self.state, self.y.grad, self.x.grad)
             return
         if self.scratch is None:
@@ -156,11 +254,16 @@ class Dropout(Layer):
 class SelfAttention(Layer):
     """MultiHeadAttention with q = k = v = x (what lib/models' encoder layer builds:
     transformer.cc:32-45). The reference's wrapper passes NULL for dK/dV in this case and
-    thereby drops two thirds of the input gradient; the driver asks for all three and sums them."""
+    thereby drops two thirds of the input gradient; the driver asks for all three and sums them.
 
+    residual=True is the fused-operator form y = MHA(x, x, x) + x (the residual add that follows
+    the attention block in lib/models runs in the output projection's epilogue)."""
+
+    supports_overwrite = True
+    safe_inplace = True   # y.grad is read by the first GEMMs of the backward pass, x.grad written by the last
     _shared_ws: Dict = {}  # backward scratch is dead between layers: one buffer per (device, size)
 
-    def __init__(self, x: Tensor, heads: int, kdim: int, vdim: int, seed=0, shard=None):
+    def __init__(self, x: Tensor, heads: int, kdim: int, vdim: int, seed=0, shard=None, residual=False):
         """shard = (index, count): this rank computes `heads` of the count*heads heads (its slice of
         the packed weight Wq[E][H][kdim] | Wk | Wv | Wo[H][vdim][E]); its output is a partial sum."""
         self.x = x
@@ -183,18 +286,42 @@ class SelfAttention(Layer):
         self.w = full.to(dt).contiguous()
         self.dw = torch.zeros_like(self.w)
         self.y = Tensor(x.shape, dt, dev)
-        # dq | dk | dv stacked like the replicas of a Replicate op: their sum is one kernel
-        self.dqkv = torch.zeros((3,) + tuple(x.data.shape), dtype=dt, device=dev)
-        self.dq, self.dk, self.dv = self.dqkv[0], self.dqkv[1], self.dqkv[2]
+        self.with_residual = bool(residual)
+        self.fused = False        # Model(fuse=True): dq, dk, dv are accumulated straight into x.grad
+        self.alias_x = False      # Model(fuse=True): x.grad IS y.grad (residual form, first writer)
+        self._dqkv = None
         self.params, self.grads = [self.w], [self.dw]
 
     def forward(self):
-        K.MultiHeadAttention.forward_kernel(None, self.state, self.x.data, self.x.data, self.x.data, self.w, self.y.data)
+        if self.with_residual:
+            K.MultiHeadAttention.forward_residual_kernel(None, self.state, self.x.data, self.x.data, self.x.data,
+                                                         self.w, self.y.data, self.x.data)
+        else:
+            K.MultiHeadAttention.forward_kernel(None, self.state, self.x.data, self.x.data, self.x.data, self.w,
+                                                self.y.data)
 
     def backward(self):
-        K.MultiHeadAttention.backward_kernel(None, self.state, self.x.data, self.dq, self.x.data, self.dk,
-                                             self.x.data, self.dv, self.w, self.dw, self.y.grad)
-        K.Replicate.backward_kernel(None, self.x.grad, self.dqkv, 3)  # x.grad += dq + dk + dv
+        G, xg = self.y.grad, self.x.grad
+        if self.fused:
+            acc_q = True
+            if self.with_residual:
+                if not self.alias_x:   # x.grad (+)= y.grad, the residual branch
+                    (K.copy if self.first(self.x) else K.accumulate)(None, xg, G)
+            else:
+                acc_q = not self.first(self.x)
+            K.MultiHeadAttention.backward_accumulate_kernel(None, self.state, self.x.data, xg, self.x.data, xg,
+                                                            self.x.data, xg, self.w, self.dw, G,
+                                                            accumulate=(acc_q, True, True))
+            return
+        if self._dqkv is None:
+            # dq | dk | dv stacked like the replicas of a Replicate op: their sum is one kernel
+            self._dqkv = torch.zeros((3,) + tuple(self.x.data.shape), dtype=self.x.data.dtype, device=self.x.data.device)
+        dq, dk, dv = self._dqkv[0], self._dqkv[1], self._dqkv[2]
+        if self.with_residual:
+            K.accumulate(None, xg, G)
+        K.MultiHeadAttention.backward_kernel(None, self.state, self.x.data, dq, self.x.data, dk,
+                                             self.x.data, dv, self.w, self.dw, G)
+        K.Replicate.backward_kernel(None, xg, self._dqkv, 3)  # x.grad += dq + dk + dv
 
 
 class ReduceSum(Layer):
@@ -232,9 +359,13 @@ class ReplicateIn(Layer):
 
 
 class Softmax(Layer):
+    supports_overwrite = True
+
     def __init__(self, x: Tensor):
         self.x = x
         self.y = Tensor(x.shape, x.data.dtype, x.data.device)
+        self.overwrites = True   # legacy (unfused) mode: Model zero-fills x.grad unless this layer is x's sole reader
+        self.alias = False       # fused mode: x.grad IS y.grad, nothing to do in backward
 
     def forward(self):
         C = self.x.shape[-1]
@@ -242,7 +373,12 @@ class Softmax(Layer):
 
     def backward(self):
         # the reference's softmax backward is a copy (it relies on the fused CE loss gradient)
-        K.Softmax.backward_kernel(None, self.x.grad, self.y.grad)
+        if self.alias:
+            return
+        if self.overwrites or self.first(self.x):
+            K.Softmax.backward_kernel(None, self.x.grad, self.y.grad)
+        else:
+            K.accumulate(None, self.x.grad, self.y.grad)
 
 
 @dataclass
@@ -271,30 +407,131 @@ class SGD:
 
 
 class Model:
-    def __init__(self, inp: Tensor, layers: List[Layer], out: Tensor):
-        self.input, self.layers, self.output = inp, layers, out
-        # gradients that a backward kernel overwrites need no zero fill and no accumulate pass:
-        # a Dropout whose input nobody else reads writes its result straight into x.grad
-        readers: Dict[int, int] = {}
+    def __init__(self, inp: Tensor, layers: List[Layer], out: Tensor, fuse: bool = False):
+        """fuse=False runs the reference's per-operator convention to the letter: every backward kernel
+        ADDS to its input gradients and the driver zero-fills them first. fuse=True is fused-operator
+        execution (the reference's `perform_fusion`, config.h:80): the gradient plan below decides,
+        per tensor, which layer writes its gradient first (that layer overwrites: no fill, no read of
+        the old value), lets the operands of a residual add SHARE the add's output-gradient buffer
+        where the order of reads and writes allows it, and wires the ReLU(+dropout) gradient of a
+        feed-forward layer into the data-gradient GEMM of the layer behind it."""
+        self.input, self.layers, self.output, self.fuse = inp, layers, out, fuse
+        readers: Dict[int, List[Layer]] = {}
         for l in layers:
-            for name in ("x", "a", "b"):
-                t = getattr(l, name, None)
-                if isinstance(t, Tensor):
-                    readers[id(t)] = readers.get(id(t), 0) + 1
+            for t in l.input_tensors():
+                readers.setdefault(id(t), []).append(l)
         self._overwritten = set()
         for l in layers:
-            if isinstance(l, Dropout) and readers.get(id(l.x), 0) == 1 and l.x.grad is not None:
-                l.sole_reader = True
-                self._overwritten.add(id(l.x))
-            # the reference's softmax backward is a copy: it overwrites its input gradient
-            if isinstance(l, Softmax) and readers.get(id(l.x), 0) == 1 and l.x.grad is not None:
-                self._overwritten.add(id(l.x))
+            l._first = {}
+        if fuse:
+            self._plan_gradients(readers)
+        else:
+            # gradients that a backward kernel overwrites need no zero fill and no accumulate pass:
+            # a Dropout whose input nobody else reads writes its result straight into x.grad
+            for l in layers:
+                sole = len(readers.get(id(l.x), [])) == 1 if isinstance(getattr(l, "x", None), Tensor) else False
+                if isinstance(l, Dropout) and sole and l.x.grad is not None:
+                    l.sole_reader = True
+                    self._overwritten.add(id(l.x))
+                # the reference's softmax backward is a copy: it overwrites its input gradient
+                if isinstance(l, Softmax):
+                    l.overwrites = sole
+                    if sole and l.x.grad is not None:
+                        self._overwritten.add(id(l.x))
         # every loss kernel writes the whole gradient of the model output
-        if out.grad is not None and readers.get(id(out), 0) == 0:
+        if out.grad is not None and not readers.get(id(out)):
             self._overwritten.add(id(out))
+        for tid in self._overwritten:
+            assert len(readers.get(tid, [])) <= 1 or fuse, "an overwritten gradient must have a single writer"
         self._flatten_gradients()
         self.params = [p for l in layers for p in l.params]
         self.grads = [g for l in layers for g in l.grads]
+
+    def _plan_gradients(self, readers: Dict[int, List[Layer]]):
+        """Fused-operator execution: first writers, shared gradient buffers, gated data gradients."""
+        order = list(reversed(self.layers))                   # backward order
+        pos = {id(l): i for i, l in enumerate(order)}
+        producer: Dict[int, Layer] = {}
+        tensors: Dict[int, Tensor] = {}
+        for l in self.layers:
+            for t in l.output_tensors():
+                producer[id(t)] = l
+            for t in l.input_tensors() + l.output_tensors():
+                tensors[id(t)] = t
+        writers = {tid: sorted(ls, key=lambda l: pos[id(l)]) for tid, ls in readers.items()}
+        for tid, ls in writers.items():
+            t = tensors[tid]
+            if t.grad is None:
+                continue
+            if ls[0].supports_overwrite:
+                ls[0]._first[tid] = True
+                self._overwritten.add(tid)                    # no zero fill: its first writer overwrites
+
+        def later_writers_ok(z: Tensor, me: Layer, x_producer: Optional[Layer]) -> bool:
+            """z.grad may share a buffer that x's producer still reads: every OTHER writer of z.grad must
+            run after that read — or be that producer itself, if it reads before it writes."""
+            if x_producer is None:
+                return True
+            for w in writers[id(z)]:
+                if w is me:
+                    continue
+                if pos[id(w)] < pos[id(x_producer)]:
+                    return False
+                if pos[id(w)] == pos[id(x_producer)] and not w.safe_inplace:
+                    return False
+            return True
+
+        def share(t: Tensor, buf_owner: Tensor):
+            t.grad = buf_owner.grad
+
+        for l in order:
+            if isinstance(l, Add):
+                ops = {"a": l.a, "b": l.b}
+                first = {n: t.grad is not None and l._first.get(id(t), False) for n, t in ops.items()}
+                sole = {n: len(readers[id(t)]) == 1 for n, t in ops.items()}
+                for n in ops:
+                    l.mode[n] = "copy" if first[n] else "acc"
+                if l.a is l.b:
+                    continue
+                for n, m in (("a", "b"), ("b", "a")):
+                    x, z = ops[n], ops[m]
+                    if not (first[n] and sole[n]):
+                        continue
+                    # x is read only by this add: its gradient IS y.grad
+                    l.mode[n] = "alias"
+                    share(x, l.y)
+                    if first[m] and later_writers_ok(z, l, producer.get(id(x))):
+                        l.mode[m] = "alias"      # later writers add into the shared buffer after x's producer read it
+                        share(z, l.y)
+                    break
+            elif isinstance(l, Linear):
+                if l.residual is not None and l.residual.grad is not None:
+                    # y.grad is only read by this layer's backward: the residual's gradient can be that buffer
+                    if l._first.get(id(l.residual), False):
+                        l.residual_mode = "alias"
+                        share(l.residual, l.y)
+                    else:
+                        l.residual_mode = "acc"
+                if l.preact is not None:
+                    l.fused_preact = True
+                src = producer.get(id(l.x))
+                if (isinstance(src, Linear) and src.state.activation == K.ACT_RELU and src.residual is None
+                        and len(readers[id(l.x)]) == 1 and l.x.grad is not None and l._first.get(id(l.x), False)
+                        and l.x.data.dtype in (torch.bfloat16, torch.float16) and l.in_dim % 32 == 0):
+                    l.gate_src = src                 # dX of this layer = pre-activation gradient of `src`
+                    src.grad_is_preact = True
+            elif isinstance(l, Softmax):
+                # backward is a copy (softmax fused with the cross-entropy gradient): let the loss
+                # kernel write the logits' gradient in place instead
+                if l.x.grad is not None and l._first.get(id(l.x), False) and l.y.grad is not None:
+                    l.alias = True
+                    share(l.x, l.y)
+            elif isinstance(l, SelfAttention):
+                l.fused = True
+                l._dqkv = None
+                if l.with_residual and l.x.grad is not None and l._first.get(id(l.x), False):
+                    l.alias_x = True
+                    share(l.x, l.y)
 
     def rehome_gradients(self, flats: List[torch.Tensor]):
         """Move the flat gradient buckets into caller-provided storage of the same sizes (e.g. views
@@ -331,9 +568,8 @@ class Model:
     def activations(self):
         seen, out = set(), []
         for l in self.layers:
-            for name in ("x", "a", "b", "y"):
-                t = getattr(l, name, None)
-                if isinstance(t, Tensor) and id(t) not in seen:
+            for t in l.input_tensors() + l.output_tensors():
+                if id(t) not in seen:
                     seen.add(id(t))
                     out.append(t)
         return out
@@ -398,7 +634,7 @@ def mse_step(model: Model, target: torch.Tensor, opt: SGD, pops=None, replicas=N
     _backward_sync_update(model, opt, pops)
 
 
-def build_mlp(batch=64, dims=(784, 512, 512, 10), dtype=torch.float32, device="cuda"):
+def build_mlp(batch=64, dims=(784, 512, 512, 10), dtype=torch.float32, device="cuda", fuse=False):
     """BASELINE configs[0]: MLP 784-512-512-10, ReLU, softmax head."""
     x = Tensor((batch, dims[0]), dtype, device, requires_grad=True)
     layers: List[Layer] = []
@@ -410,20 +646,37 @@ def build_mlp(batch=64, dims=(784, 512, 512, 10), dtype=torch.float32, device="c
         cur = lin.y
     sm = Softmax(cur)
     layers.append(sm)
-    return Model(x, layers, sm.y)
+    return Model(x, layers, sm.y, fuse=fuse)
 
 
 def build_transformer_encoder(num_layers=12, d_model=1024, heads=16, seq=512, batch=64, dim_ff=4096,
                               head_dim: Optional[int] = None, dropout=0.1, dtype=torch.bfloat16,
-                              device="cuda", seed=0):
+                              device="cuda", seed=0, fuse=False):
     """BASELINE configs[2]: the encoder stack lib/models builds
     (lib/models/src/models/transformer/transformer.cc:32-65): MHA(x,x,x) -> add -> LayerNorm ->
     dense(dim_ff, ReLU) -> dropout -> dense(d_model) -> dropout -> add -> LayerNorm.
-    head_dim None reproduces the reference's kdim = vdim = dim_ff / heads."""
+    head_dim None reproduces the reference's kdim = vdim = dim_ff / heads.
+
+    fuse=True builds the same graph for fused-operator execution: per layer
+    [MHA + residual] -> LayerNorm -> [dense + ReLU + dropout] -> [dense + dropout + residual] ->
+    LayerNorm — five launches' worth of layers instead of nine, same seeds, same dropout masks, same
+    results up to the rounding of the intermediates that are no longer stored."""
     hd = head_dim if head_dim is not None else dim_ff // heads
     x = Tensor((batch, seq, d_model), dtype, device)
     layers: List[Layer] = []
     cur = x
+    if fuse:
+        for i in range(num_layers):
+            att = SelfAttention(cur, heads, hd, hd, seed=seed + i, residual=True)
+            ln1 = LayerNorm(att.y)
+            ff1 = Linear(ln1.y, dim_ff, K.ACT_RELU, True, seed=100 + i,
+                         dropout=(dropout, 12345 + 2 * i) if dropout > 0 else None)
+            ff2 = Linear(ff1.y, d_model, K.ACT_NONE, True, seed=200 + i,
+                         dropout=(dropout, 12346 + 2 * i) if dropout > 0 else None, residual=ln1.y)
+            ln2 = LayerNorm(ff2.y)
+            layers += [att, ln1, ff1, ff2, ln2]
+            cur = ln2.y
+        return Model(x, layers, cur, fuse=True)
     for i in range(num_layers):
         att = SelfAttention(cur, heads, hd, hd, seed=seed + i)
         add1 = Add(cur, att.y)
@@ -441,7 +694,7 @@ def build_transformer_encoder(num_layers=12, d_model=1024, heads=16, seq=512, ba
 
 def build_bert(num_layers=12, hidden=768, heads=12, dim_ff=3072, seq=512, batch=64, vocab=30522,
                dropout=0.1, layer_norm_eps=1e-12, dtype=torch.bfloat16, device="cuda", seed=0,
-               tp_rank=0, tp_world=1, tp_group=None):
+               tp_rank=0, tp_world=1, tp_group=None, fuse=False):
     """BASELINE configs[3] (data-parallel form): the graph lib/models builds for BERT
     (lib/models/src/models/bert/bert.cc:52-155) — the input is the already embedded sequence
     [batch, seq, hidden]; each layer is MHA(x,x,x) with kdim = vdim = dim_ff / heads -> add ->
@@ -453,6 +706,23 @@ def build_bert(num_layers=12, hidden=768, heads=12, dim_ff=3072, seq=512, batch=
     layers: List[Layer] = []
     cur = x
     tp = tp_world > 1
+    if fuse and not tp:
+        # fused-operator execution: [MHA + residual] -> LayerNorm -> [dense + GELU + dropout, the
+        # pre-activation stored by the same GEMM] -> [dense + dropout + residual] -> LayerNorm
+        for i in range(num_layers):
+            att = SelfAttention(cur, heads, hd, hd, seed=seed + i, residual=True)
+            ln1 = LayerNorm(att.y, eps=layer_norm_eps)
+            ff1 = Linear(ln1.y, dim_ff, K.ACT_GELU, True, seed=100 + i,
+                         dropout=(dropout, 22345 + 2 * i) if dropout > 0 else None)
+            ff2 = Linear(ff1.y, hidden, K.ACT_NONE, True, seed=200 + i,
+                         dropout=(dropout, 22346 + 2 * i) if dropout > 0 else None, residual=ln1.y)
+            ln2 = LayerNorm(ff2.y, eps=layer_norm_eps)
+            layers += [att, ln1, ff1, ff2, ln2]
+            cur = ln2.y
+        head = Linear(cur, vocab, K.ACT_GELU, True, seed=300)
+        sm = Softmax(head.y)
+        layers += [head, sm]
+        return Model(x, layers, sm.y, fuse=True)
     if tp:
         assert heads % tp_world == 0 and dim_ff % tp_world == 0
     sh = (tp_rank, tp_world) if tp else None

@@ -75,6 +75,57 @@ int ffk_linear_backward(void *stream, void const *input, void *input_grad, void 
                         int activation, float l2_lambda, void const *preact, int path,
                         void *workspace, size_t workspace_bytes);
 
+/* ---- Fused-operator execution (the reference's `perform_fusion` switch,
+ * lib/local-execution/include/local-execution/config.h:80, and the legacy FusedOp,
+ * lib/runtime/src/ops/fused.cc: consecutive operators run as one task). These entry points are
+ * ADDITIVE: each equals a chain of the per-operator entry points above and falls back to exactly
+ * that chain when a shape or dtype cannot take the one-kernel path (16-bit tensors, out_dim a
+ * multiple of 32, 16-byte aligned rows). */
+
+/* Linear -> [activation] -> [Dropout] -> [+ residual], the feed-forward and projection blocks of
+ * lib/models (transformer.cc:46-60, bert.cc:98-120), as ONE GEMM whose epilogue does the rest:
+ *   v = X W^T + bias;  preact_out <- v (optional; the GELU gradient needs it);  v = act(v);
+ *   v = keep ? v / (1 - rate) : 0 with the keep bit of ffk_dropout_forward's generator for the
+ *   same (seed, offset, element) — the bit mask is also written when dropout_mask != NULL;
+ *   output <- v + residual (optional).
+ * Replaces linear_kernels.cu:109-190 + dropout_kernels.cu:64-80 + element_binary_kernels.cu:141-243. */
+typedef struct {
+  void *preact_out;            /* optional, same shape and dtype as output */
+  void const *residual;        /* optional, same shape and dtype as output */
+  void *dropout_mask;          /* ffk_dropout_mask_bytes(batch*out_dim) bytes; needed by the backward pass unless the activation is RELU */
+  float dropout_rate;          /* 0 = no dropout */
+  unsigned long long dropout_seed, dropout_offset;
+} ffk_linear_forward_fusion_t;
+int ffk_linear_forward_fused(void *stream, void const *input, void *output, void const *weight,
+                             void const *bias, int in_dim, int out_dim, int batch_size, int dtype,
+                             int activation, int path, ffk_linear_forward_fusion_t const *fusion_host);
+
+/* ffk_linear_backward with the operators around it folded in:
+ *   accumulate_input_grad   1: dX += (the reference's convention); 0: dX = — the caller knows this
+ *                           Linear is the first writer of that gradient, so no zero fill is needed;
+ *   dropout_mask / rate     a dropout followed the activation (fused forward above): its gradient
+ *                           and the activation gradient are applied to dY in one pass;
+ *   output_grad_is_preactivation   dY already holds the pre-activation gradient (it was produced by
+ *                           a gated data-gradient epilogue, below): skip that pass;
+ *   input_gate / scale      X is the stored output of ReLU (+ dropout, scale = 1/(1-rate)) of the
+ *                           layer before: the data-gradient GEMM's epilogue writes
+ *                           dX = X > 0 ? (dY W) * scale : 0, i.e. the pre-activation gradient of that
+ *                           layer, without a separate pass over the [batch][in_dim] tensor. */
+typedef struct {
+  int accumulate_input_grad;
+  int output_grad_is_preactivation;
+  void const *dropout_mask;
+  float dropout_rate;
+  void const *input_gate;
+  float input_gate_scale;
+} ffk_linear_backward_fusion_t;
+int ffk_linear_backward_fused(void *stream, void const *input, void *input_grad, void const *output,
+                              void *output_grad, void const *weight, void *weight_grad,
+                              void *bias_grad, int in_dim, int out_dim, int batch_size, int dtype,
+                              int activation, float l2_lambda, void const *preact, int path,
+                              void *workspace, size_t workspace_bytes,
+                              ffk_linear_backward_fusion_t const *fusion_host);
+
 /* Kernels::BatchMatmul::forward_kernel — include/kernels/batch_matmul_kernels.h:12,
  * src/cuda/ops/batch_matmul_kernels.cu:23-84 (argument order of the DEFINITION).
  *   O[b] (n x m) = A[b] (n x k) * B[b] (k x m), all row-major; a/b_seq_length_dim and
@@ -129,6 +180,24 @@ int ffk_mha_backward(void *stream, ffk_mha_config_t const *cfg_host, void const 
                      void *value_grad, void const *weight, void *weight_grad,
                      void const *output_grad, void const *reserve, void *workspace,
                      size_t workspace_bytes, int dtype, int path);
+
+/* Fused-operator forms of MultiHeadAttention (additive, see "Fused-operator execution" above):
+ *  - forward with the residual of the encoder layer folded into the output projection's epilogue:
+ *    out = MHA(q, k, v) + residual (lib/models transformer.cc:32-45 adds the layer input right
+ *    behind the attention block);
+ *  - backward whose data gradients are ADDED to query_grad / key_grad / value_grad where the flag
+ *    says so, instead of cuDNN's overwrite. With q = k = v = x (self-attention) the three pointers
+ *    may be the same buffer: accumulate flags (first-writer?, 1, 1) leave dq + dk + dv in it
+ *    without three separate tensors and a sum pass. */
+int ffk_mha_forward_residual(void *stream, ffk_mha_config_t const *cfg_host, void const *query,
+                             void const *key, void const *value, void const *weight, void *output,
+                             void *reserve, int dtype, int path, void const *residual);
+int ffk_mha_backward_accumulate(void *stream, ffk_mha_config_t const *cfg_host, void const *query,
+                                void *query_grad, void const *key, void *key_grad, void const *value,
+                                void *value_grad, void const *weight, void *weight_grad,
+                                void const *output_grad, void const *reserve, void *workspace,
+                                size_t workspace_bytes, int dtype, int path, int accumulate_query_grad,
+                                int accumulate_key_grad, int accumulate_value_grad);
 
 #ifdef __cplusplus
 }

@@ -49,6 +49,16 @@ int ffk_layer_norm_backward(void *stream, void const *output_grad, void const *i
                             long long N, int dtype, int accumulate_param_grads, void *workspace,
                             size_t workspace_bytes);
 
+/* ffk_layer_norm_backward with the choice the reference's convention does not offer:
+ * accumulate_input_grad == 0 WRITES input_grad instead of adding to it (one HBM pass less, and no
+ * zero fill before it) for callers that know this op is the first writer of that gradient —
+ * the step driver's fused-operator execution. 1 = ffk_layer_norm_backward. */
+int ffk_layer_norm_backward_ex(void *stream, void const *output_grad, void const *input,
+                               void *input_grad, void const *gamma, void *gamma_grad,
+                               void *beta_grad, float const *mean, float const *rstd, long long M,
+                               long long N, int dtype, int accumulate_param_grads,
+                               int accumulate_input_grad, void *workspace, size_t workspace_bytes);
+
 /* No counterpart in the reference. LayerNorm backward for callers that cannot allocate device
  * memory and have no workspace to pass: tasks running under a runtime that has already claimed
  * the GPU's memory for its own pool (the reference's legacy Legion/Realm runtime does so at

@@ -60,8 +60,9 @@ def test_mlp_config0_three_steps_match_the_oracle(ffk, oracle):
             assert_close(l.b, b, rtol=1e-4, what=f"step {step} bias")
 
 
+@pytest.mark.parametrize("fuse", [False, True])
 @pytest.mark.parametrize("dtype,rate", [(torch.float32, 0.0), (torch.float32, 0.1), (torch.bfloat16, 0.1)])
-def test_encoder_step_matches_the_oracle(ffk, oracle, dtype, rate):
+def test_encoder_step_matches_the_oracle(ffk, oracle, dtype, rate, fuse):
     """BASELINE configs[2] at toy size: one full training step (forward, MSE gradient, backward with
     dq + dk + dv, SGD) of the transformer-encoder graph against the same step composed from the
     CPU oracle (tests/oracle_encoder.py), with the dropout masks the GPU drew. fp32: rtol 1e-4;
@@ -71,13 +72,18 @@ def test_encoder_step_matches_the_oracle(ffk, oracle, dtype, rate):
     T = importlib.import_module("flexflow_train_b200.training")
     B, S, D, H, hd, FF, L = 4, 16, 64, 4, 24, 128, 2
     model = T.build_transformer_encoder(num_layers=L, d_model=D, heads=H, seq=S, batch=B, dim_ff=FF, head_dim=hd,
-                                        dropout=rate, dtype=dtype)
+                                        dropout=rate, dtype=dtype, fuse=fuse)
     per = len(model.layers) // L
     names = ("mha", "g1", "b1", "w1", "c1", "w2", "c2", "g2", "b2")
 
     def params(i):
-        att, _, ln1, ff1, dp1, ff2, dp2, _, ln2 = model.layers[i * per:(i + 1) * per]
-        return (att.w, ln1.gamma, ln1.beta, ff1.w, ff1.b, ff2.w, ff2.b, ln2.gamma, ln2.beta), (dp1, dp2)
+        if fuse:   # fused-operator execution: the dropout states live inside the two dense layers
+            att, ln1, ff1, ff2, ln2 = model.layers[i * per:(i + 1) * per]
+            drops = (ff1.drop, ff2.drop)
+        else:
+            att, _, ln1, ff1, dp1, ff2, dp2, _, ln2 = model.layers[i * per:(i + 1) * per]
+            drops = (dp1.state, dp2.state)
+        return (att.w, ln1.gamma, ln1.beta, ff1.w, ff1.b, ff2.w, ff2.b, ln2.gamma, ln2.beta), drops
 
     g = torch.Generator(device="cuda").manual_seed(11)
     for i in range(L):   # non-trivial affine parameters and biases
@@ -91,7 +97,7 @@ def test_encoder_step_matches_the_oracle(ffk, oracle, dtype, rate):
     model.input.data.copy_(x)
     T.mse_step(model, target, opt)
     torch.cuda.synchronize()
-    masks = [tuple(d.state.mask.cpu().numpy().view(np.uint32).copy() for d in params(i)[1]) for i in range(L)]
+    masks = [tuple(d.mask.cpu().numpy().view(np.uint32).copy() for d in params(i)[1]) for i in range(L)] if rate > 0 else None
     enc = OracleEncoder(oracle, W, B, S, D, H, hd, FF, rate=rate)
     out = enc.step(x.float().cpu().numpy(), target.float().cpu().numpy(), 0.05, 1e-3, masks=masks)
     if dtype == torch.float32:
