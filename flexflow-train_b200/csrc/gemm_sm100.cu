@@ -148,7 +148,9 @@ __device__ __forceinline__ void epilogue_row_chunk(uint32_t const (&acc)[32], Ep
 // of 32 lanes touching 32 different rows with 16 bytes each. Row r keeps its four 16-byte
 // pieces at piece ^ ((r >> 1) & 3): conflict-free for both the row-per-thread and the
 // 8-rows-by-4-pieces access. Warp-collective: every lane calls it, `row_ok` masks dead rows.
-template <typename T>
+// EXTRAS compiles in the fused-operator steps (pre-activation copy, dropout, gate); the plain
+// instantiation is the epilogue every other GEMM runs and carries none of their code.
+template <typename T, bool EXTRAS>
 __device__ __forceinline__ void epilogue_chunk_staged(uint32_t const (&acc)[32], Epilogue const &ep,
                                                       uint8_t *stage, long long block_off,
                                                       int rows_valid, int col0, bool row_ok) {
@@ -192,7 +194,9 @@ __device__ __forceinline__ void epilogue_chunk_staged(uint32_t const (&acc)[32],
     }
     __syncwarp();
   };
-  if (ep.aux_out != nullptr) store_rows(reinterpret_cast<T *>(ep.aux_out));  // the pre-activation
+  if constexpr (EXTRAS) {
+    if (ep.aux_out != nullptr) store_rows(reinterpret_cast<T *>(ep.aux_out));  // the pre-activation
+  }
   if (ep.act == ACT_RELU) {
 #pragma unroll
     for (int i = 0; i < 32; ++i) v[i] = fmaxf(v[i], 0.f);
@@ -200,7 +204,7 @@ __device__ __forceinline__ void epilogue_chunk_staged(uint32_t const (&acc)[32],
 #pragma unroll
     for (int i = 0; i < 32; ++i) v[i] = apply_act_fast(v[i], ep.act);
   }
-  if (ep.drop_on) {
+  if (EXTRAS && ep.drop_on) {
     // this thread's 32 elements are one mask word: element e keeps iff field e % 8 of
     // Philox(e / 8, offset, seed) >= threshold — the rule of the stand-alone dropout kernel
     unsigned long long const e0 = (unsigned long long)(block_off + (long long)lane * ep.ldd + col0);
@@ -234,7 +238,7 @@ __device__ __forceinline__ void epilogue_chunk_staged(uint32_t const (&acc)[32],
       Vec16<T> t2;
       *reinterpret_cast<uint4 *>(&t2) =
           *reinterpret_cast<uint4 const *>(stage + lane * 64 + ((j ^ my_sw) << 4));
-      if (gate) {
+      if (EXTRAS && gate) {
 #pragma unroll
         for (int i = 0; i < 8; ++i) v[j * 8 + i] = to_f32(t2.v[i]) > 0.f ? v[j * 8 + i] * scale : 0.f;
       } else {
@@ -302,7 +306,7 @@ __device__ __forceinline__ void epilogue_chunk_staged_unaligned(uint32_t const (
 // (TMEM lanes) of its quadrant. The TMEM load of chunk c+1 is in flight while chunk c is
 // converted and stored; `release` runs once the last load has landed (the accumulator buffer
 // may then be overwritten by the next tile's MMAs).
-template <int NCHUNK, typename Release>
+template <int NCHUNK, bool EXTRAS, typename Release>
 __device__ __forceinline__ void epilogue_columns(uint32_t taddr, Epilogue const &ep, long long block_off,
                                                  int rows_valid, int N, int col_first, int out_dtype,
                                                  int vec_ok, uint8_t *stage, Release release) {
@@ -332,9 +336,9 @@ __device__ __forceinline__ void epilogue_columns(uint32_t taddr, Epilogue const 
         epilogue_chunk_staged_unaligned<__half>(r[c & 1], ep, stage, block_off, rows_valid, col0, valid);
     } else if (staged_ok && valid == 32) {  // warp-uniform
       if (out_dtype == FFK_BFLOAT16)
-        epilogue_chunk_staged<__nv_bfloat16>(r[c & 1], ep, stage, block_off, rows_valid, col0, row_ok);
+        epilogue_chunk_staged<__nv_bfloat16, EXTRAS>(r[c & 1], ep, stage, block_off, rows_valid, col0, row_ok);
       else
-        epilogue_chunk_staged<__half>(r[c & 1], ep, stage, block_off, rows_valid, col0, row_ok);
+        epilogue_chunk_staged<__half, EXTRAS>(r[c & 1], ep, stage, block_off, rows_valid, col0, row_ok);
     } else if (row_ok) {
       switch (out_dtype) {
         case FFK_FLOAT: epilogue_row_chunk<float>(r[c & 1], ep, row_off, col0, valid, vec_ok); break;
@@ -494,7 +498,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
                                   static_cast<long long>(tc.b % batch2) * ep.d_batch2 +
                                   static_cast<long long>(row0) * ep.ldd;
       int const col_off = half * (BLOCK_N / 2);
-      epilogue_columns<NCHUNK>(
+      epilogue_columns<NCHUNK, false>(
           tmem_base + (uint32_t(q * 32) << 16) + acc * BLOCK_N + col_off, ep, block_off,
           min(32, M - row0), N, tc.n_idx + col_off, out_dtype, vec_ok,
           smem + Plan::STAGING_OFFSET + (warp - 2) * EPI_STAGE_PER_WARP, [&] {
@@ -525,7 +529,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
 // tcgen05.mma.cta_group::2 for both; TMA completions of both CTAs are counted on the
 // leader's full barrier; commits are multicast to both CTAs' empty / tmem-full barriers;
 // both epilogues release the accumulator through the leader's tmem-empty barrier.
-template <bool A_MN, bool B_MN, int STAGES>
+template <bool A_MN, bool B_MN, int STAGES, bool EXTRAS>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
     gemm_tc_pair_kernel(const __grid_constant__ CUtensorMap map_a,
                         const __grid_constant__ CUtensorMap map_b, Epilogue ep, int M, int N, int K,
@@ -680,7 +684,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
                                   static_cast<long long>(b % batch2) * ep.d_batch2 +
                                   static_cast<long long>(row0) * ep.ldd;
       int const col_off = half * (BLOCK_N / 2);
-      epilogue_columns<BLOCK_N / 64>(
+      epilogue_columns<BLOCK_N / 64, EXTRAS>(
           tmem_base + (uint32_t(q * 32) << 16) + acc * BLOCK_N + col_off, ep, block_off,
           min(32, M - row0), N, n_idx + col_off, out_dtype, vec_ok,
           smem + STAGES * STAGE_BYTES + 256 + (warp - 2) * EPI_STAGE_PER_WARP, [&] {
@@ -896,7 +900,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
                                   static_cast<long long>(row0) * ep.ldd;
 #pragma unroll 1
       for (int cc = 0; cc < 4; ++cc) {
-        epilogue_columns<2>(taddr + cc * 64, row_ep, block_off, min(32, M - row0), N,
+        epilogue_columns<2, false>(taddr + cc * 64, row_ep, block_off, min(32, M - row0), N,
                             half * 256 + cc * 64, out_dtype, 1, stage_buf, [&] {
                               if (cc == 3) {
                                 ptx::tc_fence_before();
@@ -1035,7 +1039,9 @@ int launch_tc_pair_inst(Problem const &p, Epilogue const &e, cudaStream_t stream
   else
     rc = make_map(&mb, p.b, p.in_dtype, p.N, p.K, bo, b2, p.ldb, p.b_batch, p.b_batch2, ATOM, BLOCK_K);
   if (rc) return rc;
-  auto kern = gemm_tc_pair_kernel<A_MN, B_MN, STAGES>;
+  // the fused-operator epilogue is its own instantiation: plain GEMMs do not carry its code
+  bool const extras = e.aux_out != nullptr || e.drop_on || e.r_mode == 1;
+  auto kern = extras ? gemm_tc_pair_kernel<A_MN, B_MN, STAGES, true> : gemm_tc_pair_kernel<A_MN, B_MN, STAGES, false>;
   FFK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
   uint32_t fmt = p.in_dtype == FFK_BFLOAT16 ? ptx::kFmtBF16 : ptx::kFmtF16;
   uint32_t idesc = ptx::make_idesc(fmt, A_MN, B_MN, 256, 256);
@@ -1126,7 +1132,10 @@ int launch_tc(Problem const &p, Epilogue const &e, cudaStream_t stream) {
 bool fused_eligible(Problem const &p, Epilogue const &e) {
   size_t os = dtype_size(p.out_dtype);
   bool sixteen = (p.in_dtype == FFK_BFLOAT16 || p.in_dtype == FFK_HALF) && p.out_dtype == p.in_dtype;
-  return sixteen && p.batch == 1 && p.N % 32 == 0 && e.ldd == p.N && !e.add_d_before_act &&
+  static bool const no_pair = std::getenv("FFK_GEMM_NO_PAIR") != nullptr;
+  // only the CTA-pair kernel (outputs of more than 128 x 128) instantiates the fused epilogue
+  bool const pair = !no_pair && p.N > 128 && p.M > 128;
+  return pair && sixteen && p.batch == 1 && p.N % 32 == 0 && e.ldd == p.N && !e.add_d_before_act &&
          aligned16(e.d) && (e.ldd * os) % 16 == 0 && (!e.r || aligned16(e.r)) &&
          (!e.aux_out || aligned16(e.aux_out)) && tc_eligible(p, e);
 }
