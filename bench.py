@@ -724,15 +724,25 @@ def run_encoder(args):
     bert = args.workload == "bert"
     tp = 1
     strategy_note = None
+    st = None
     if args.strategy:
         # "imported search strategy": {"tensor_parallel": T}, or a parallel computation graph in the
         # reference's v1 JSON layout (flexflow-train_b200/strategy.py reads its edges and places the
-        # parallel ops per layer); the rest of the world size is data parallel
-        st = importlib.import_module("flexflow_train_b200.strategy").load_strategy(args.strategy, world)
+        # parallel ops per layer); the rest of the world size is data parallel. "auto:tpT" writes the
+        # BERT graph with a tensor-parallel placement of degree T for this world size and reads it back.
+        S = importlib.import_module("flexflow_train_b200.strategy")
+        if args.strategy.startswith("auto:tp"):
+            X = importlib.import_module("flexflow_train_b200.pcg_export")
+            t_ = int(args.strategy[len("auto:tp"):])
+            st = S.parse_strategy(X.bert_pcg(batch=args.batch * (world // t_), vocab=30528, tensor_parallel=t_,
+                                             data_parallel=world // t_), world)
+        else:
+            st = S.load_strategy(args.strategy, world)
         tp = st.tensor_parallel
         strategy_note = {"file": os.path.basename(args.strategy), "tensor_parallel": st.tensor_parallel,
                          "data_parallel": st.data_parallel or world // st.tensor_parallel,
-                         "placed_layers": len(st.placements)}
+                         "placed_layers": len(st.placements),
+                         "parallel_ops_on_activations": len(st.parallel_ops)}
     if args.tp:
         tp = args.tp
     if not bert or world % tp != 0:
@@ -761,7 +771,16 @@ def run_encoder(args):
     g = torch.Generator(device=device).manual_seed(1234 + rank // tp)  # one batch per data-parallel replica
     # fused-operator execution is the default; FFK_BENCH_NO_FUSE=1 runs one kernel per operator
     fuse = os.environ.get("FFK_BENCH_NO_FUSE") is None
-    if bert:
+    from_pcg = bert and st is not None and len(st.placements) > 0
+    if from_pcg:
+        # the layer list comes from the graph: Replicate / Reduction / Combine placed where the file says
+        V = max(int(pl.attrs.get("out_channels", 0)) for pl in st.placements if pl.kind == "linear")
+        L = len([pl for pl in st.placements if pl.kind == "multi_head_attention"])
+        Kmod.set_gemm_workspace(int(B * S * ((V + 7) // 8 * 8) * 2 * 1.05))
+        model = T.build_from_strategy(st, batch=B, dtype=torch.bfloat16, device=device, tp_rank=tp_rank,
+                                      tp_group=tp_group)
+        labels = torch.randint(0, V, (B * S,), generator=g, device=device, dtype=torch.int32)
+    elif bert:
         # the vocabulary head's gradients go through repacked operands: that needs scratch
         Kmod.set_gemm_workspace(int(B * S * ((V + 7) // 8 * 8) * 2 * 1.05))
         model = T.build_bert(L, D, H, FF, S, B, V, dropout=0.1, dtype=torch.bfloat16, device=device,
@@ -1322,7 +1341,8 @@ def main():
     ap.add_argument("--batch", type=int, default=64)
     ap.add_argument("--head-dim", type=int, default=0, help="0 = the reference's dim_ff/heads (256)")
     ap.add_argument("--tp", type=int, default=0, help="bert: tensor-parallel degree (divides --gpus)")
-    ap.add_argument("--strategy", default="", help='bert: JSON file with {"tensor_parallel": T}')
+    ap.add_argument("--strategy", default="", help='bert: {"tensor_parallel": T} file, a parallel computation graph '
+                    'in the reference v1 JSON layout (strategies/*.v1.json), or auto:tpT')
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3  # timing rule: at least 3 warm-up steps

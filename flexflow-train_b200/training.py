@@ -358,6 +358,40 @@ class ReplicateIn(Layer):
         K.accumulate(None, self.x.grad, self.y.grad)
 
 
+class CombineGather(Layer):
+    """Combine over the tensor-parallel group (lib/op-attrs .../ops/combine.cc; kernel
+    combine_kernels.cu:50-61): forward concatenates the ranks' slabs along `dim` (all-gather,
+    bit-exact), backward adds this rank's slab of the output gradient to the slab gradient."""
+
+    def __init__(self, x: Tensor, dim: int, pops):
+        self.x, self.dim, self.pops = x, dim % len(x.shape), pops
+        shape = list(x.shape)
+        shape[self.dim] *= pops.world
+        self.y = Tensor(tuple(shape), x.data.dtype, x.data.device)
+
+    def forward(self):
+        self.pops.combine_forward(self.x.data, self.y.data, self.dim)
+
+    def backward(self):
+        self.pops.combine_backward(self.y.grad, self.x.grad, self.dim)
+
+
+class RepartitionSlice(Layer):
+    """Repartition over the tensor-parallel group (.../ops/repartition.cc; kernel
+    partition_kernels.cu:53-72): forward keeps this rank's slab of the replicated input along `dim`
+    (bit-exact), backward all-gathers the slab gradients and adds them to the input gradient."""
+
+    def __init__(self, x: Tensor, dim: int, pops):
+        self.x, self.dim, self.pops = x, dim % len(x.shape), pops
+        self.y = Tensor(tuple(pops.slab_shape(x.shape, self.dim)), x.data.dtype, x.data.device)
+
+    def forward(self):
+        self.pops.repartition_forward(self.x.data, self.y.data, self.dim)
+
+    def backward(self):
+        self.pops.repartition_backward(self.x.grad, self.y.grad, self.dim)
+
+
 class Softmax(Layer):
     supports_overwrite = True
 
@@ -749,6 +783,124 @@ def build_bert(num_layers=12, hidden=768, heads=12, dim_ff=3072, seq=512, batch=
     sm = Softmax(head.y)
     layers += [head, sm]
     return Model(x, layers, sm.y)
+
+
+# ------------------------------------------------------------------ models from a parallel computation graph
+def build_from_strategy(strategy, batch: int, dtype=torch.bfloat16, device="cuda", tp_rank=0, tp_group=None,
+                        seed=0, input_shape=None):
+    """The layer list of a model described by a parallel computation graph in the reference's v1
+    file format (strategy.load_strategy -> Strategy.placements): every compute layer of the graph
+    becomes a step-driver layer, every parallel operator on an ACTIVATION becomes the matching
+    collective layer of the tensor-parallel group —
+
+        Replicate   -> ReplicateIn   (identity forward, all-reduce backward)
+        Reduction   -> ReduceSum     (all-reduce forward, copy backward)
+        Repartition -> RepartitionSlice along a feature dimension (local slab / all-gather + add)
+        Combine     -> CombineGather along a feature dimension (all-gather / local slab)
+
+    — and the Repartition operators found on a WEIGHT chain shard that weight: heads for
+    multi_head_attention, in- or out-channels for linear (the reference lays a projection out as
+    [in_channels][out_channels], op-attrs/ops/linear.cc:42-50, so ff dim 0 is the row-parallel and
+    ff dim 1 the column-parallel split). Batch-dimension Repartition / Combine and weight Replicate
+    are data parallelism: each rank simply holds its `batch` samples. Supported layers:
+    multi_head_attention (self-attention), linear, layer_norm, dropout, element_binary(add), softmax."""
+    from .parallel_ops import ParallelOps
+    tp = strategy.tensor_parallel
+    pops = ParallelOps(group=tp_group) if tp > 1 else None
+    tensors: Dict[int, Tensor] = {}      # compute / input node id -> its output activation
+    par_cache: Dict[int, Tensor] = {}    # parallel-op node id -> the activation behind it
+    layers: List[Layer] = []
+    model_input = None
+    counters = {"linear": 0, "multi_head_attention": 0, "dropout": 0}
+
+    def through(chain, t: Tensor) -> Tensor:
+        for op in chain:
+            if op.node in par_cache:
+                t = par_cache[op.node]
+                continue
+            if op.op in ("repartition", "combine") and op.dim == 0:
+                pass                                   # the batch split: this rank's samples are `t`
+            elif tp == 1 or op.degree == 1:
+                pass
+            elif op.op == "replicate":
+                l = ReplicateIn(t, tp_group)
+                layers.append(l)
+                t = l.y
+            elif op.op == "reduction":
+                l = ReduceSum(t, tp_group)
+                layers.append(l)
+                t = l.y
+            elif op.op == "combine":
+                l = CombineGather(t, op.dim, pops)
+                layers.append(l)
+                t = l.y
+            else:
+                l = RepartitionSlice(t, op.dim, pops)
+                layers.append(l)
+                t = l.y
+            par_cache[op.node] = t
+        return t
+
+    def weight_shard(chain, dim):
+        for op in chain:
+            if op.op == "repartition" and op.dim == dim and op.degree > 1:
+                assert op.degree == tp, f"weight shard degree {op.degree} != tensor-parallel degree {tp}"
+                return (tp_rank, tp)
+        return None
+
+    out = None
+    for pl in strategy.placements:
+        a = pl.attrs
+        if pl.kind == "input":
+            shape = input_shape
+            if shape is None:
+                dims = (((a.get("tensor_shape") or {}).get("dims") or {}).get("ff_ordered")) or []
+                shape = (batch,) + tuple(int(d) for d in dims[1:])
+            model_input = Tensor(tuple(shape), dtype, device)
+            tensors[pl.node] = model_input
+            out = model_input
+            continue
+        ins = [through(chain, tensors[src]) for chain, src in zip(pl.inputs, pl.producers)]
+        if pl.kind == "multi_head_attention":
+            assert all(t is ins[0] for t in ins), "only self-attention (q = k = v) is supported"
+            heads = int(a["num_heads"])
+            sh = weight_shard(pl.weights[0], 1) if pl.weights else None
+            i = counters["multi_head_attention"]
+            counters["multi_head_attention"] += 1
+            l = SelfAttention(ins[0], heads // (tp if sh else 1), int(a["kdim"]), int(a["vdim"]), seed=seed + i, shard=sh)
+        elif pl.kind == "linear":
+            act = a.get("activation")
+            act = {None: K.ACT_NONE, "RELU": K.ACT_RELU, "SIGMOID": K.ACT_SIGMOID, "TANH": K.ACT_TANH,
+                   "GELU": K.ACT_GELU}[act.upper() if isinstance(act, str) else act]
+            w = pl.weights[0] if pl.weights else []
+            col, row = weight_shard(w, 1), weight_shard(w, 0)
+            i = counters["linear"]
+            counters["linear"] += 1
+            out_ch = int(a["out_channels"])
+            use_bias = bool(a.get("use_bias", True))
+            if row is not None and tp_rank != 0:
+                use_bias = False                      # the bias of a row-parallel layer is added once
+            l = Linear(ins[0], out_ch // (tp if col else 1), act, use_bias, seed=int(a.get("seed", 100 + i)),
+                       shard_out=col, shard_in=row)
+        elif pl.kind == "layer_norm":
+            l = LayerNorm(ins[0], eps=float(a.get("eps", 1e-5)))
+        elif pl.kind == "dropout":
+            i = counters["dropout"]
+            counters["dropout"] += 1
+            # dropout on a tensor every tensor-parallel rank holds in full must draw the same mask everywhere
+            l = Dropout(ins[0], float(a["rate"]), int(a.get("seed", 12345 + i)))
+        elif pl.kind == "element_binary":
+            assert str(a.get("type", "EW_ADD")).upper().endswith("ADD"), "only element_binary add is supported"
+            l = Add(ins[0], ins[1])
+        elif pl.kind == "softmax":
+            l = Softmax(ins[0])
+        else:
+            raise ValueError(f"parallel computation graph: layer kind {pl.kind!r} is not supported by the step driver")
+        layers.append(l)
+        tensors[pl.node] = l.y
+        out = through(pl.output, l.y)
+        # later consumers reach this output through its trailing parallel ops, which are cached by node id
+    return Model(model_input, layers, out)
 
 
 # ------------------------------------------------------------------ DLRM (BASELINE configs[4])

@@ -134,3 +134,38 @@ def test_tensor_parallel_block_is_placed_per_layer(ffk):
     doc["raw_graph"]["node_labels"][11][1]["op_attrs"] = {"index": S.PCG_OPERATOR_KEYS.index("reduce_distributed"),
                                                          "value": {"reduction_degree": 2}}
     assert S.parse_strategy(doc).tensor_parallel == 2
+
+
+def test_exported_bert_graph_reads_back_with_its_placement(ffk, tmp_path):
+    """pcg_export.bert_pcg writes the BERT graph of lib/models in the reference's v1 layout with a
+    tensor-parallel placement; strategy.load_strategy must recover the degrees and, layer by layer,
+    where the parallel operators sit."""
+    S = importlib.import_module("flexflow_train_b200.strategy")
+    X = importlib.import_module("flexflow_train_b200.pcg_export")
+    doc = X.bert_pcg(num_layers=3, hidden=64, heads=4, dim_ff=128, seq=16, batch=32, vocab=208, tensor_parallel=2,
+                     data_parallel=4)
+    p = tmp_path / "bert_tp2_dp4.v1.json"
+    X.write(p, doc)
+    st = S.load_strategy(p, world_size=8)
+    assert (st.tensor_parallel, st.data_parallel) == (2, 4)
+    kinds = [pl.kind for pl in st.placements]
+    assert kinds.count("multi_head_attention") == 3 and kinds.count("linear") == 7 and kinds.count("layer_norm") == 6
+    att = next(pl for pl in st.placements if pl.kind == "multi_head_attention")
+    assert [(o.op, o.degree) for o in att.inputs[0]] == [("repartition", 4), ("replicate", 2)]
+    assert [(o.op, o.dim, o.degree) for o in att.weights[0]] == [("repartition", 1, 2), ("replicate", 0, 4)]
+    assert [(o.op, o.degree) for o in att.output] == [("reduction", 2)]
+    lins = [pl for pl in st.placements if pl.kind == "linear"]
+    assert [(o.op, o.dim) for o in lins[0].weights[0]][0] == ("repartition", 1)      # column-parallel
+    assert [(o.op, o.dim) for o in lins[1].weights[0]][0] == ("repartition", 0)      # row-parallel
+    assert [(o.op, o.degree) for o in lins[1].output] == [("reduction", 2)]
+    assert [(o.op, o.dim, o.degree) for o in lins[-1].output] == [("combine", 2, 2)]  # vocabulary-parallel head
+    ln = next(pl for pl in st.placements if pl.kind == "layer_norm")
+    assert [[(o.op, o.degree) for o in w] for w in ln.weights] == [[("replicate", 8)], [("replicate", 8)]]
+    # the committed strategy files are such graphs
+    for name, world in (("bert_base_tp2_dp1.v1.json", 2), ("bert_base_tp2_dp4.v1.json", 8)):
+        st = S.load_strategy(ROOT / "strategies" / name, world_size=world)
+        assert st.tensor_parallel == 2 and len([pl for pl in st.placements if pl.kind == "multi_head_attention"]) == 12
+    # pure data parallelism exported the same way is not mistaken for tensor parallelism
+    st = S.parse_strategy(X.bert_pcg(num_layers=1, hidden=64, heads=4, dim_ff=128, seq=16, batch=32, vocab=208,
+                                     tensor_parallel=1, data_parallel=8), world_size=8)
+    assert (st.tensor_parallel, st.data_parallel) == (1, 8)

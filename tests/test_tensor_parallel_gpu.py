@@ -13,14 +13,16 @@ pytestmark = pytest.mark.gpu
 WORKER = Path(__file__).resolve().parent / "tp_worker.py"
 
 
-@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs on one node")
-def test_bert_tensor_parallel_matches_unsharded():
+@pytest.mark.parametrize("world", [2, 4])
+def test_bert_tensor_parallel_matches_unsharded(world):
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs on one node")
     with socket.socket() as s:
         s.bind(("127.0.0.1", 0))
         port = s.getsockname()[1]
     procs = []
-    for rank in range(2):
-        env = dict(os.environ, RANK=str(rank), LOCAL_RANK=str(rank), WORLD_SIZE="2",
+    for rank in range(world):
+        env = dict(os.environ, RANK=str(rank), LOCAL_RANK=str(rank), WORLD_SIZE=str(world),
                    MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
         procs.append(subprocess.Popen([sys.executable, str(WORKER)], env=env, stdout=subprocess.PIPE,
                                       stderr=subprocess.STDOUT, text=True))

@@ -41,6 +41,41 @@ def main():
     full = train(T.build_bert(**cfg))
     part = train(T.build_bert(**cfg, tp_rank=rank, tp_world=world))
     ok = True
+    # the same model built from a parallel computation graph in the reference's v1 file format:
+    # Replicate / Reduction around attention and feed-forward, a vocabulary-parallel head whose
+    # logits are Combine'd along the feature dimension (vocabulary padded to divide by the degree)
+    S = importlib.import_module("flexflow_train_b200.strategy")
+    X = importlib.import_module("flexflow_train_b200.pcg_export")
+    vocab = 208
+    pcfg = dict(cfg, vocab=vocab)
+    labels_p = labels % vocab
+    doc = X.bert_pcg(num_layers=2, hidden=64, heads=4, dim_ff=128, seq=16, batch=4, vocab=vocab, dropout=0.0,
+                     tensor_parallel=world, data_parallel=1)
+    st = S.parse_strategy(doc, world_size=world)
+
+    def train_p(model, steps=3):
+        opt = T.SGD(lr=0.2, weight_decay=0.0)
+        for _ in range(steps):
+            model.input.data.copy_(x)
+            T.sparse_cce_step(model, labels_p, opt)
+        torch.cuda.synchronize()
+        return model
+
+    full_p = train_p(T.build_bert(**pcfg))
+    from_pcg = train_p(T.build_from_strategy(st, batch=4, tp_rank=rank))
+    try:
+        assert st.tensor_parallel == world
+        kinds = [type(l).__name__ for l in from_pcg.layers]
+        assert "CombineGather" in kinds and "ReduceSum" in kinds and "ReplicateIn" in kinds, kinds
+        assert_close_l2(from_pcg.output.data, full_p.output.data.float().cpu().numpy(), what="probabilities (PCG build)")
+        head_full = [l for l in full_p.layers if isinstance(l, T.Linear)][-1]
+        head_part = [l for l in from_pcg.layers if isinstance(l, T.Linear)][-1]
+        n = head_part.out_dim
+        assert n == vocab // world
+        assert_close_l2(head_part.w, head_full.w[rank * n:(rank + 1) * n].float().cpu().numpy(), what="vocabulary shard")
+    except AssertionError as e:
+        print(f"rank {rank}: {e}", flush=True)
+        ok = False
     try:
         assert_close_l2(part.output.data, full.output.data.float().cpu().numpy(), what="probabilities")
         ff1_full = [l for l in full.layers if isinstance(l, T.Linear)][0]
