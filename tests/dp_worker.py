@@ -54,7 +54,9 @@ def main():
         if not torch.isfinite(pf).all():
             print(f"rank {rank}: parameter {i} is not finite", flush=True)
             ok = False
-        tol = torch.maximum(pf.abs(), qf.abs()) * 2.0 ** -7 + 1e-6
+        # NCCL rounds every partial sum of its ring to bf16, the peer-memory kernel sums in fp32 and
+        # rounds once: after three steps the weights agree to a bf16 ulp of the tensor's scale
+        tol = torch.maximum(pf.abs(), qf.abs()) * 2.0 ** -6 + qf.abs().max() * 2.0 ** -8 + 1e-6
         if ((pf - qf).abs() > tol).any():
             print(f"rank {rank}: parameter {i} differs from the NCCL run by {(pf - qf).abs().max().item()}", flush=True)
             ok = False

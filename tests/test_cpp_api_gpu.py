@@ -30,3 +30,14 @@ def test_reference_kernel_tests_on_the_cpp_veneer():
     r = subprocess.run([str(BIN)], capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert "0 failed" in r.stdout
+
+
+@pytest.mark.gpu
+def test_cost_estimator_bridge():
+    """tests/cpp/cost_estimator_test.cc: ICostEstimator::estimate_cost(OpCostEstimateKey) for fifteen
+    operator families and estimate_cost(TensorSetMovement), through the C++ veneer."""
+    exe = ROOT / "tests" / "cpp" / "cost_estimator_test"
+    assert exe.exists(), "build it with __graft_entry__.build()"
+    r = subprocess.run([str(exe)], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert "0 failed" in r.stdout
