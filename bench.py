@@ -785,7 +785,7 @@ def run_encoder(args):
         L = len([pl for pl in st.placements if pl.kind == "multi_head_attention"])
         Kmod.set_gemm_workspace(int(B * S * ((V + 7) // 8 * 8) * 2 * 1.05))
         model = T.build_from_strategy(st, batch=B, dtype=torch.bfloat16, device=device, tp_rank=tp_rank,
-                                      tp_group=tp_group)
+                                      tp_group=tp_group, fuse=fuse)
         labels = torch.randint(0, V, (B * S,), generator=g, device=device, dtype=torch.int32)
     elif bert:
         # the vocabulary head's gradients go through repacked operands: that needs scratch

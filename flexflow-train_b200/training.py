@@ -13,7 +13,7 @@ legacy loop, examples/cpp/Transformer/transformer.cc:192-197).
 from __future__ import annotations
 
 from dataclasses import dataclass, field
-from typing import Dict, List, Optional
+from typing import Any, Dict, List, Optional
 
 import torch
 import torch.distributed as dist
@@ -328,6 +328,8 @@ class ReduceSum(Layer):
     """Reduction over the tensor-parallel group (lib/op-attrs .../ops/reduction.cc): forward sums
     the ranks' partial tensors (all-reduce), backward hands the gradient through unchanged."""
 
+    supports_overwrite = True
+
     def __init__(self, x: Tensor, group=None):
         self.x, self.group = x, group
         self.y = Tensor(x.shape, x.data.dtype, x.data.device)
@@ -337,7 +339,7 @@ class ReduceSum(Layer):
         dist.all_reduce(self.y.data, op=dist.ReduceOp.SUM, group=self.group)
 
     def backward(self):
-        K.accumulate(None, self.x.grad, self.y.grad)
+        (K.copy if self.first(self.x) else K.accumulate)(None, self.x.grad, self.y.grad)
 
 
 class ReplicateIn(Layer):
@@ -787,7 +789,7 @@ def build_bert(num_layers=12, hidden=768, heads=12, dim_ff=3072, seq=512, batch=
 
 # ------------------------------------------------------------------ models from a parallel computation graph
 def build_from_strategy(strategy, batch: int, dtype=torch.bfloat16, device="cuda", tp_rank=0, tp_group=None,
-                        seed=0, input_shape=None):
+                        seed=0, input_shape=None, fuse=False):
     """The layer list of a model described by a parallel computation graph in the reference's v1
     file format (strategy.load_strategy -> Strategy.placements): every compute layer of the graph
     becomes a step-driver layer, every parallel operator on an ACTIVATION becomes the matching
@@ -848,9 +850,28 @@ def build_from_strategy(strategy, batch: int, dtype=torch.bfloat16, device="cuda
                 return (tp_rank, tp)
         return None
 
+    # fused-operator execution on the imported graph: a dropout that is the only reader of a dense
+    # layer's output (no parallel operator between them) runs in that layer's GEMM epilogue
+    readers: Dict[int, List] = {}
+    for pl in strategy.placements:
+        for src in pl.producers:
+            readers.setdefault(src, []).append(pl)
+    by_node = {pl.node: pl for pl in strategy.placements}
+    fused_dropout: Dict[int, Any] = {}     # linear node -> the dropout placement folded into it
+    skip_nodes = set()
+    if fuse:
+        for pl in strategy.placements:
+            if pl.kind == "dropout" and len(pl.producers) == 1 and not pl.inputs[0]:
+                src = by_node.get(pl.producers[0])
+                if src is not None and src.kind == "linear" and len(readers.get(src.node, [])) == 1 and not src.output:
+                    fused_dropout[src.node] = pl
+                    skip_nodes.add(pl.node)
+
     out = None
     for pl in strategy.placements:
         a = pl.attrs
+        if pl.node in skip_nodes:
+            continue
         if pl.kind == "input":
             shape = input_shape
             if shape is None:
@@ -880,8 +901,14 @@ def build_from_strategy(strategy, batch: int, dtype=torch.bfloat16, device="cuda
             use_bias = bool(a.get("use_bias", True))
             if row is not None and tp_rank != 0:
                 use_bias = False                      # the bias of a row-parallel layer is added once
+            drop = None
+            dpl = fused_dropout.get(pl.node)
+            if dpl is not None and float(dpl.attrs["rate"]) > 0:
+                j = counters["dropout"]
+                counters["dropout"] += 1
+                drop = (float(dpl.attrs["rate"]), int(dpl.attrs.get("seed", 12345 + j)))
             l = Linear(ins[0], out_ch // (tp if col else 1), act, use_bias, seed=int(a.get("seed", 100 + i)),
-                       shard_out=col, shard_in=row)
+                       shard_out=col, shard_in=row, dropout=drop)
         elif pl.kind == "layer_norm":
             l = LayerNorm(ins[0], eps=float(a.get("eps", 1e-5)))
         elif pl.kind == "dropout":
@@ -899,8 +926,12 @@ def build_from_strategy(strategy, batch: int, dtype=torch.bfloat16, device="cuda
         layers.append(l)
         tensors[pl.node] = l.y
         out = through(pl.output, l.y)
+        dpl = fused_dropout.get(pl.node)
+        if dpl is not None:                 # the folded dropout's readers see this layer's output
+            tensors[dpl.node] = l.y
+            out = through(dpl.output, l.y)
         # later consumers reach this output through its trailing parallel ops, which are cached by node id
-    return Model(model_input, layers, out)
+    return Model(model_input, layers, out, fuse=fuse)
 
 
 # ------------------------------------------------------------------ DLRM (BASELINE configs[4])

@@ -45,7 +45,7 @@ int main() {
   cases.push_back({"batch_norm", key(BatchNormAttrs{true}, {P({4, 8, 12, 12})}, {}, {P({4, 8, 12, 12})})});
   cases.push_back({"dropout", key(DropoutAttrs{0.1f, 12345ull}, {P({128, 256})}, {}, {P({128, 256})})});
   cases.push_back({"embedding", key(EmbeddingAttrs{1000, 64, std::nullopt}, {P({512}, DataType::INT64)}, {P({1000, 64})}, {P({512, 64})})});
-  cases.push_back({"reduce", key(ReduceAttrs{{ff_dim_t{1}}, OperatorType::REDUCE_SUM}, {P({128, 256})}, {}, {P({128})})});
+  cases.push_back({"reduce", key(ReduceAttrs{{ff_dim_t{1}}, OperatorType::REDUCE_SUM}, {P({128, 256})}, {}, {P({128, 1})})});
   cases.push_back({"pool2d", key(Pool2DAttrs{2, 2, 2, 2, 0, 0, PoolOp::MAX, std::nullopt}, {P({4, 8, 12, 12})}, {}, {P({4, 8, 6, 6})})});
   cases.push_back({"conv2d", key(Conv2DAttrs{16, 3, 3, 1, 1, 1, 1, 1, std::nullopt, true}, {P({4, 8, 12, 12})},
                                  {P({16, 8, 3, 3}), P({16})}, {P({4, 16, 12, 12})})});

@@ -62,7 +62,7 @@ def main():
         return model
 
     full_p = train_p(T.build_bert(**pcfg))
-    from_pcg = train_p(T.build_from_strategy(st, batch=4, tp_rank=rank))
+    from_pcg = train_p(T.build_from_strategy(st, batch=4, tp_rank=rank, fuse=True))
     try:
         assert st.tensor_parallel == world
         kinds = [type(l).__name__ for l in from_pcg.layers]
