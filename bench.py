@@ -615,8 +615,11 @@ def per_op_table(torch, Kmod, device, iters=10):
     K.LayerNorm.forward_kernel(None, ln, x_ln, torch.empty_like(x_ln), gamma, beta)  # mean / rstd of x_ln
     mk_lb = lambda: (r(ROWS, COLS), x_ln.clone(), torch.zeros(ROWS, COLS, device=device))
     timed("LayerNorm bwd (dX, dgamma, dbeta) 8192x4096 fp32", "hbm", 3 * t, 3 * t, mk_lb,
+          lambda s: K.LayerNorm.backward_kernel(None, ln, s[0], s[1], s[2], gamma, dg, db, accumulate_input_grad=False),
+          note="first-writer form (ffk_layer_norm_backward_ex): read dY, X, write dX = SURVEY a9's 3 passes")
+    timed("LayerNorm bwd, accumulating dX (reference convention)", "hbm", 4 * t, 3 * t, mk_lb,
           lambda s: K.LayerNorm.backward_kernel(None, ln, s[0], s[1], s[2], gamma, dg, db),
-          note="algorithmic = read dY, X + write dX (SURVEY a9); the kernel accumulates into dX (reads it), 4 passes in fact")
+          note="dX += ...: the old dX is read as well, 4 passes")
     mk3 = lambda: (r(ROWS, COLS), r(ROWS, COLS), torch.empty(ROWS, COLS, device=device))
     timed("ElementBinary add fwd 8192x4096 fp32", "hbm", 3 * t, 3 * t, mk3,
           lambda s: K.ElementBinary.forward_kernel(None, K.OperatorType.EW_ADD, s[0], s[1], s[2]))
@@ -799,14 +802,18 @@ def run_encoder(args):
     sync_launches_per_step = 0
     if dp > 1:
         P = importlib.import_module("flexflow_train_b200.parallel_ops")
-        if os.environ.get("FFK_BENCH_GRAD_SYNC", "peer") == "peer":
+        # tensor-parallel runs keep ONE communication library: their activation all-reduces are NCCL's, and
+        # a spinning peer-memory kernel of the data-parallel group on a side stream could wait on a rank whose
+        # NCCL kernel waits on a third (a cycle across two libraries)
+        if os.environ.get("FFK_BENCH_GRAD_SYNC", "peer") == "peer" and tp == 1:
             try:
+                min_mb = int(os.environ.get("FFK_BENCH_SYNC_MIN_MB", "150"))
+                blocks = int(os.environ.get("FFK_BENCH_SYNC_BLOCKS", "0"))
                 pops = P.PeerGradSync(model, group=dp_group,   # raises the same error on every rank
-                                      min_bytes=int(os.environ.get("FFK_BENCH_SYNC_MIN_MB", "48")) << 20,
-                                      background_blocks=int(os.environ.get("FFK_BENCH_SYNC_BLOCKS", "32")))
-                grad_sync = ("peer-memory all-reduce (ffk_p2p_all_reduce_sum_background: SUM over ranks, no "
-                             "division), one launch per >= 48 MiB of finished gradients on a high-priority side "
-                             "stream under the backward pass; SGD reads the summed buckets")
+                                      min_bytes=min_mb << 20, background_blocks=blocks)
+                grad_sync = (f"peer-memory all-reduce over NVLink ({'ffk_p2p_all_reduce_sum_background, ' + str(blocks) + ' CTAs' if blocks else 'ffk_p2p_all_reduce_sum'}: "
+                             f"SUM over ranks in fp32 rank order, no division), one launch per >= {min_mb} MiB of "
+                             f"finished gradients on a side stream while backward continues; SGD reads the summed buckets")
             except RuntimeError as e:
                 grad_sync = "NCCL all-reduce [peer-memory path unavailable on this box: " + str(e)[:200] + "]"
         if pops is None:

@@ -42,14 +42,36 @@ __global__ void __launch_bounds__(kThreads)
   long long const total = batch * ppr;
   long long const stride = (long long)gridDim.x * blockDim.x;
   long long const out_dim = (long long)ppr * VN;
+  if (!aggregate) {
+    // plain gather: four packets per thread and trip, a grid stride apart — the four index loads
+    // go out together, then the four row loads, then the stores, so that every thread keeps four
+    // independent 16-byte requests to the (randomly placed) table rows in flight
+    constexpr int U = 4;
+    for (long long i0 = (long long)blockIdx.x * blockDim.x + threadIdx.x; i0 < total; i0 += stride * U) {
+      long long b[U];
+      int pk[U];
+      long long row[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        long long const i = i0 + u * stride;
+        b[u] = i / ppr;
+        pk[u] = int(i - b[u] * ppr);
+        row[u] = i < total ? (long long)idx[b[u]] : 0;
+      }
+      Vec16<T> v[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+        if (i0 + u * stride < total) v[u] = ld_vec(table + row[u] * out_dim + pk[u] * VN);  // rows may be re-read: keep in L2
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+        if (i0 + u * stride < total) st_stream(out + b[u] * out_dim + pk[u] * VN, v[u]);
+    }
+    return;
+  }
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
     long long const b = i / ppr;
     int const pk = int(i - b * ppr);
-    if (!aggregate) {
-      long long const row = (long long)idx[b];
-      Vec16<T> v = ld_vec(table + row * out_dim + pk * VN);  // table rows may be re-read: keep in L2
-      st_stream(out + b * out_dim + pk * VN, v);
-    } else {
+    {
       float acc[VN];
 #pragma unroll
       for (int j = 0; j < VN; ++j) acc[j] = 0.f;
