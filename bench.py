@@ -1000,10 +1000,11 @@ def run_encoder(args):
 
 # ----------------------------------------------------------------------------- DLRM workload
 def run_dlrm(args):
-    """BASELINE configs[4]: the DLRM of examples/cpp/DLRM (8 tables of 1 M x 64 fp32 here, so that
-    8 GPUs own one each; bag size 1; bottom MLP 4-64-64, "cat" interaction, top MLP 64-64-2, MSE +
-    SGD), tables sharded over the ranks, lookups repartitioned with an all-to-all, MLPs data parallel.
-    `--workload dlrm [--batch B]` (B per GPU, default 8192)."""
+    """BASELINE configs[4]: the DLRM of examples/cpp/DLRM at the shapes of its run script
+    (run_random.sh:9): 8 tables of 1 M x 64 fp32, bag size 1, bottom MLP 64-512-512-64, "cat"
+    interaction, top MLP 576-1024-1024-1024-1, MSE + SGD; tables sharded over the ranks, lookups
+    repartitioned with an all-to-all, MLPs data parallel; the tables are updated row-sparsely
+    (ffk_embedding_sgd_update). `--workload dlrm [--batch B]` (B per GPU, default 8192)."""
     import importlib
 
     import torch
@@ -1028,9 +1029,9 @@ def run_dlrm(args):
     net = T.DLRM(batch=B, embedding_size=(1000000,) * tables, rank=rank, world=world, device=device)
     opt = T.SGD(lr=0.01, weight_decay=0.0)
     g = torch.Generator(device=device).manual_seed(77 + rank)
-    hdense = torch.rand(B, 4, generator=g, device=device).cpu().pin_memory()
-    target = (torch.rand(B, 2, generator=g, device=device) > 0.5).float()
-    hout = torch.empty(B, 2).pin_memory()
+    hdense = torch.rand(B, 64, generator=g, device=device).cpu().pin_memory()
+    target = (torch.rand(B, 1, generator=g, device=device) > 0.5).float()
+    hout = torch.empty(B, 1).pin_memory()
     net.dense.data.copy_(hdense)
     lib = ffk_import.load().lib()
 
@@ -1077,13 +1078,13 @@ def run_dlrm(args):
         ms_total, ms_e2e = t.tolist()
     if rank == 0:
         ms = ms_total / args.steps
-        # bytes one step must move per GPU: for each local table, gather + scatter of the global
-        # batch's rows, zero fill and SGD pass over table and gradient
+        # bytes one step must move per GPU for the tables: gather of the global batch's rows, and the
+        # row-sparse update (dOut read, row read-modify-write); the MLPs (2.6 M parameters) add
+        # 3 x 2 x B x params FLOP on the tensor-core side, small next to the table traffic
         tl = tables // world
         row = 64 * 4
         lookups = tl * B * world
-        table_bytes = tl * 1000000 * row
-        algo = lookups * (8 + 2 * row) + lookups * (8 + 3 * row) + table_bytes * (1 + 3)
+        algo = lookups * (8 + 2 * row) + lookups * (8 + 3 * row)
         _, hbm_peak, peak_src = load_peaks()
         print(json.dumps({
             "metric": "training samples/sec (DLRM, fwd+bwd+SGD)", "value": B * world / (ms * 1e-3),
@@ -1091,14 +1092,15 @@ def run_dlrm(args):
             "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "fp32", "data": "synthetic",
             "config": {"workload": f"BASELINE configs[4]: DLRM, {tables} tables of 1M x 64 fp32 sharded over {world} "
-                                   f"rank(s), bag 1, bottom 4-64-64, cat, top 64-64-2, batch {B} per GPU, MSE + SGD",
+                                   f"rank(s), bag 1, bottom 64-512-512-64, cat, top 576-1024-1024-1024-1, batch {B} per GPU, "
+                                   f"MSE + SGD, row-sparse table update",
                        "global_batch": B * world, "parallelism": f"tables/{world} x dp{world}" if world > 1 else "single",
                        "l2": "tables exceed L2 (256 MB each)"},
-            "roofline": {"kernel": "whole step (embedding traffic + dense table passes)", "bound": "hbm",
+            "roofline": {"kernel": "whole step against the embedding traffic alone (gather + row-sparse update)", "bound": "hbm",
                          "achieved": algo / (ms * 1e-3) / 1e9, "peak": hbm_peak, "peak_source": peak_src,
                          "unit": "GB/s", "frac": algo / (ms * 1e-3) / 1e9 / hbm_peak, "traffic": None},
             "e2e": {"value": B * world / (ms_e2e / args.steps * 1e-3), "unit": "samples/s",
-                    "h2d_bytes_per_step": B * 4 * 4, "d2h_bytes_per_step": B * 2 * 4,
+                    "h2d_bytes_per_step": B * 64 * 4, "d2h_bytes_per_step": B * 1 * 4,
                     "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": None, "abi_calls_timed": abi_calls, "clocks": clock_info}), flush=True)
     if world > 1:

@@ -290,11 +290,13 @@ int embedding_fwd_t(cudaStream_t s, void const *input, void *output, void const 
   return FFK_OK;
 }
 
+// `alpha` scales what is scattered: 1 for the gradient itself, -lr for the row-sparse SGD update
+// (the table is the target then).
 template <typename TI>
 int embedding_bwd_t(cudaStream_t s, void const *input, void const *dout, void *dtable, int dtype,
-                    int aggr, int in_dim, int out_dim, long long batch) {
+                    int aggr, int in_dim, int out_dim, long long batch, double alpha = 1.0) {
   int bag = aggr == FFK_AGGR_NONE ? 1 : in_dim;
-  double scale = aggr == FFK_AGGR_AVG ? 1.0 / double(bag) : 1.0;
+  double scale = (aggr == FFK_AGGR_AVG ? 1.0 / double(bag) : 1.0) * alpha;
   if (dtype == FFK_DOUBLE) {
     unsigned grid = stream_grid(size_t(batch) * out_dim, kThreads, 8);
     embed_bwd_scalar_kernel<TI, double><<<grid, kThreads, 0, s>>>(
@@ -309,7 +311,7 @@ int embedding_bwd_t(cudaStream_t s, void const *input, void const *dout, void *d
       unsigned grid = stream_grid(size_t(batch) * ppr, kThreads, 8);
       embed_bwd_vec_kernel<TI, T><<<grid, kThreads, 0, s>>>((TI const *)input, (T const *)dout,
                                                             (T *)dtable, ppr, bag, batch,
-                                                            (float)scale, aggr == FFK_AGGR_AVG);
+                                                            (float)scale, scale != 1.0);
     } else {
       if constexpr (std::is_same<T, float>::value) {
         unsigned grid = stream_grid(size_t(batch) * out_dim, kThreads, 8);
@@ -360,6 +362,22 @@ int ffk_embedding_backward(void *stream, void const *input, void const *output_g
     return embedding_bwd_t<int32_t>(as_stream(stream), input, output_grad, weight_grad, dtype, aggr, in_dim, out_dim, batch_size);
   if (index_dtype == FFK_INT64)
     return embedding_bwd_t<int64_t>(as_stream(stream), input, output_grad, weight_grad, dtype, aggr, in_dim, out_dim, batch_size);
+  set_error("embedding: indices must be INT32 or INT64");
+  return FFK_ERR_DTYPE;
+}
+
+int ffk_embedding_sgd_update(void *stream, void const *input, void const *output_grad, void *weight,
+                             float lr, int index_dtype, int dtype, int aggr, int in_dim, int out_dim,
+                             int batch_size) {
+  FFK_REQUIRE(out_dim > 0 && batch_size >= 0, "embedding: bad extents");
+  FFK_REQUIRE(aggr >= FFK_AGGR_NONE && aggr <= FFK_AGGR_AVG, "embedding: bad aggr %d", aggr);
+  FFK_REQUIRE(aggr == FFK_AGGR_NONE || in_dim > 0, "embedding: bag size must be positive");
+  if (batch_size == 0) return FFK_OK;
+  FFK_REQUIRE(input && output_grad && weight, "embedding update: null tensor");
+  if (index_dtype == FFK_INT32)
+    return embedding_bwd_t<int32_t>(as_stream(stream), input, output_grad, weight, dtype, aggr, in_dim, out_dim, batch_size, -double(lr));
+  if (index_dtype == FFK_INT64)
+    return embedding_bwd_t<int64_t>(as_stream(stream), input, output_grad, weight, dtype, aggr, in_dim, out_dim, batch_size, -double(lr));
   set_error("embedding: indices must be INT32 or INT64");
   return FFK_ERR_DTYPE;
 }

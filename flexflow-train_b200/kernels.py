@@ -461,6 +461,12 @@ class Embedding:
               batch_size)
 
     @staticmethod
+    def sgd_update_kernel(stream, input, output_grad, weight, lr, aggr, in_dim, out_dim, batch_size):
+        """Row-sparse SGD on the table (ffk_embedding_sgd_update): W[idx] -= lr * dOut."""
+        _call("ffk_embedding_sgd_update", _stream(stream), _ptr(input), _ptr(output_grad), _ptr(weight),
+              float(lr), dtype_code(input), dtype_code(weight), aggr, in_dim, out_dim, batch_size)
+
+    @staticmethod
     def rand_generate_int(stream, t, p):
         _call("ffk_rand_generate_int", _stream(stream), _ptr(t), t.numel(), p, dtype_code(t))
 

@@ -960,8 +960,12 @@ class ShardedEmbeddings(Layer):
     Tables and their gradients stay out of the data-parallel gradient buckets."""
 
     def __init__(self, indices: torch.Tensor, entries: int, dim: int, batch: int, tables: int, rank=0,
-                 world=1, group=None, seed=0, device="cuda"):
+                 world=1, group=None, seed=0, device="cuda", sparse_update=True):
+        """sparse_update: plain SGD touches only the looked-up rows (ffk_embedding_sgd_update scatters
+        -lr * dOut straight into the table): no gradient table, no zero fill, no dense optimizer pass.
+        With momentum or weight decay the dense path (gradient table + ffk_sgd_update) is used."""
         assert tables % world == 0
+        self.sparse_update = sparse_update
         self.tl, self.T, self.B, self.W, self.rank, self.group = tables // world, tables, batch, world, rank, group
         self.dim, self.bag = dim, indices.shape[-1]
         assert tuple(indices.shape[:2]) == (self.tl, world * batch)
@@ -971,7 +975,8 @@ class ShardedEmbeddings(Layer):
             g = torch.Generator(device=device).manual_seed(5000 + seed + rank * self.tl + j)
             bound = (1.0 / entries) ** 0.5
             self.tables.append((torch.rand(entries, dim, device=device, generator=g) * 2 - 1) * bound)
-            self.dtables.append(torch.zeros(entries, dim, device=device))
+            self.dtables.append(None if sparse_update else torch.zeros(entries, dim, device=device))
+        self._grad_src = None
         self.y = Tensor((tables, batch, dim), torch.float32, device)          # [table][row][dim] for MY rows
         self.send = torch.zeros(world, self.tl, batch, dim, device=device)    # [dest rank][local table][row][dim]
         self.gsend = torch.zeros_like(self.send) if world > 1 else None
@@ -1001,6 +1006,9 @@ class ShardedEmbeddings(Layer):
             src = self.gsend
         else:
             src = self.y.grad.view(1, self.tl, self.B, self.dim)
+        self._grad_src = src
+        if self.sparse_update:
+            return                      # the rows are updated straight from dOut in update()
         for j in range(self.tl):
             _fill0(self.dtables[j])
             for q in range(self.W):
@@ -1008,6 +1016,14 @@ class ShardedEmbeddings(Layer):
                                             self.dtables[j], K.AGGR_SUM, self.bag, self.dim, self.B)
 
     def update(self, opt: "SGD"):
+        if self.sparse_update:
+            assert opt.momentum == 0 and opt.weight_decay == 0, "row-sparse update is plain SGD only"
+            src = self._grad_src
+            for j in range(self.tl):
+                for q in range(self.W):
+                    K.Embedding.sgd_update_kernel(None, self.idx[j, q * self.B:(q + 1) * self.B], src[q, j],
+                                                  self.tables[j], opt.lr, K.AGGR_SUM, self.bag, self.dim, self.B)
+            return
         for w, g in zip(self.tables, self.dtables):
             K.sgd_ps_update_task_gpu(None, opt.lr, 0.0, False, opt.weight_decay, g, w.numel(), 1, w, None, None)
 
@@ -1015,11 +1031,13 @@ class ShardedEmbeddings(Layer):
 class DLRM:
     """examples/cpp/DLRM/dlrm.cc:139-166: dense features -> bottom MLP; one embedding lookup per
     sparse feature; "cat" interaction; top MLP (sigmoid on its last layer); MSE loss.
-    Defaults are the example's: 4 tables of 1 M x 64, bag size 1, bottom 4-64-64, top 64-64-2."""
+    Defaults are those of the example's run script (examples/cpp/DLRM/run_random.sh:9): 8 tables of
+    1 M x 64, bag size 1, bottom MLP 64-512-512-64, top MLP 576-1024-1024-1024-1 (576 = 64 + 8 x 64
+    is the width of the concatenation, so mlp_top lists the layer widths behind it)."""
 
-    def __init__(self, batch=8192, embedding_size=(1000000,) * 4, sparse_feature_size=64, bag=1,
-                 mlp_bot=(4, 64, 64), mlp_top=(64, 64, 2), rank=0, world=1, group=None, device="cuda",
-                 seed=0):
+    def __init__(self, batch=8192, embedding_size=(1000000,) * 8, sparse_feature_size=64, bag=1,
+                 mlp_bot=(64, 512, 512, 64), mlp_top=(1024, 1024, 1024, 1), rank=0, world=1, group=None,
+                 device="cuda", seed=0, sparse_update=True):
         self.batch, self.world, self.rank = batch, world, rank
         T = len(embedding_size)
         assert len(set(embedding_size)) == 1, "one table size (the example's default)"
@@ -1037,7 +1055,7 @@ class DLRM:
             layers.append(lin)
             cur = lin.y
         self.emb = ShardedEmbeddings(all_idx[rank * tl:(rank + 1) * tl], embedding_size[0], sparse_feature_size,
-                                     batch, T, rank, world, group, seed, device)
+                                     batch, T, rank, world, group, seed, device, sparse_update=sparse_update)
         layers.append(self.emb)
         cat = Concat([cur] + self.emb.views())
         layers.append(cat)

@@ -33,6 +33,17 @@ int ffk_embedding_backward(void *stream, void const *input, void const *output_g
                            void *weight_grad, int index_dtype, int dtype, int aggr, int in_dim,
                            int out_dim, int batch_size);
 
+/* Fused-operator form of Embedding backward + SGD for tables (additive): the
+ * reference scatters dOut into a dense weight gradient (embedding_kernels.cu:144-335) and then
+ * runs the dense optimizer over the whole table (optimizer_kernel.cu:20-41) — three passes over
+ * a table of which a step touches a handful of rows. With plain SGD (no momentum, no weight decay,
+ * which is how examples/cpp/DLRM trains its tables) W -= lr * scatter_add(dOut) is the same as
+ * scattering -lr * dOut straight into W: only the looked-up rows move, no gradient table, no zero
+ * fill, no dense pass. Same index / aggregation rules as ffk_embedding_backward. */
+int ffk_embedding_sgd_update(void *stream, void const *input, void const *output_grad, void *weight,
+                             float lr, int index_dtype, int dtype, int aggr, int in_dim, int out_dim,
+                             int batch_size);
+
 /* Kernels::Embedding::rand_generate_int{32,64}_wrapper — include/kernels/embedding_kernels.h:32-33,
  * src/cuda/embedding_kernels.cu:24-38,337-342: ptr[i] = i % p. */
 int ffk_rand_generate_int(void *stream, void *ptr, size_t size, long long p, int index_dtype);

@@ -15,6 +15,43 @@ import torch.distributed as dist
 import ffk_import
 
 
+def exact_sum_case(T, P, rank, world, B, S, D, H, FF, L):
+    """The peer-memory sum itself, without a training step around it: every rank fills its gradient
+    buckets with its own data, the slices go out the way a backward pass would send them, and the
+    result must equal, BIT FOR BIT, the fp32 sum in rank order of all ranks' buckets rounded once."""
+    model = T.build_transformer_encoder(num_layers=L, d_model=D, heads=H, seq=S, batch=B, dim_ff=FF, dropout=0.0,
+                                        dtype=torch.bfloat16)
+    sync = P.PeerGradSync(model, min_bytes=64 << 10, background_blocks=8 if rank >= 0 else 0)
+    ok = True
+    for trial, blocks in enumerate((8, 0)):     # the background kernel and the full-size one
+        sync.blocks = blocks
+        for b in model.grad_buckets:
+            gen = torch.Generator(device=b.device).manual_seed(1000 * trial + 17 + rank)
+            b.copy_(((torch.rand(b.numel(), device=b.device, generator=gen) - 0.5) * 0.3).to(b.dtype))
+        torch.cuda.synchronize()
+        dist.barrier()
+        for l in reversed(model.layers):
+            if l.grads:
+                sync.after_layer(l)
+        sync.finish()
+        torch.cuda.synchronize()
+        for b, got in zip(model.grad_buckets, sync.sums):
+            every = [torch.empty_like(b) for _ in range(world)]
+            dist.all_gather(every, b)
+            acc = torch.zeros(b.numel(), dtype=torch.float32, device=b.device)
+            for e in every:                      # rank order, fp32
+                acc += e.float()
+            want = acc.to(b.dtype)
+            if not torch.equal(got, want):
+                n = (got != want).sum().item()
+                print(f"rank {rank}: peer sum (blocks={blocks}) differs from the fp32 rank-order sum in {n} elements", flush=True)
+                ok = False
+    sync.check()
+    dist.barrier()
+    sync.close()
+    return ok
+
+
 def main():
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", rank)))
@@ -44,19 +81,24 @@ def main():
             sync.close()
         return [p.clone() for p in model.params], launches
 
+    ok = exact_sum_case(T, P, rank, world, B, S, D, H, FF, L)
+    p0 = [p.clone().float() for p in T.build_transformer_encoder(num_layers=L, d_model=D, heads=H, seq=S, batch=B,
+                                                                 dim_ff=FF, dropout=0.0, dtype=torch.bfloat16).params]
     a, launches = train("peer")
     b, _ = train("nccl")
-    ok = launches >= 6          # more than one slice per step went out
-    if not ok:
+    if launches < 6:            # more than one slice per step went out
         print(f"rank {rank}: only {launches} background launches", flush=True)
+        ok = False
     for i, (p, q) in enumerate(zip(a, b)):
         pf, qf = p.float(), q.float()
         if not torch.isfinite(pf).all():
             print(f"rank {rank}: parameter {i} is not finite", flush=True)
             ok = False
         # NCCL rounds every partial sum of its ring to bf16, the peer-memory kernel sums in fp32 and
-        # rounds once: after three steps the weights agree to a bf16 ulp of the tensor's scale
-        tol = torch.maximum(pf.abs(), qf.abs()) * 2.0 ** -6 + qf.abs().max() * 2.0 ** -6 + 1e-6
+        # rounds once (exact_sum_case pins that bit for bit). Where the ranks' gradients cancel, the two
+        # sums differ by a sizeable fraction of the RESULT, so the trained weights are compared on the
+        # scale of what three steps changed: a bf16 ulp of the weight plus 15 % of the largest update.
+        tol = torch.maximum(pf.abs(), qf.abs()) * 2.0 ** -6 + (qf - p0[i]).abs().max() * 0.15 + 1e-7
         if ((pf - qf).abs() > tol).any():
             print(f"rank {rank}: parameter {i} differs from the NCCL run by {(pf - qf).abs().max().item()}", flush=True)
             ok = False

@@ -246,3 +246,29 @@ def test_small_dlrm_trains(ffk):
         touched = torch.zeros(1000, dtype=torch.bool, device="cuda")
         touched[net.emb.idx[j].reshape(-1)] = True
         assert torch.equal(a[~touched], b[~touched]) and not torch.equal(a[touched], b[touched])
+
+
+def test_row_sparse_table_update_equals_the_dense_path(ffk):
+    """DLRM tables: scattering -lr * dOut straight into the table (ffk_embedding_sgd_update) must leave
+    the same tables, MLP weights and outputs as gradient table + zero fill + dense SGD."""
+    import importlib
+    T = importlib.import_module("flexflow_train_b200.training")
+    cfg = dict(batch=512, embedding_size=(2000,) * 4, sparse_feature_size=32, bag=3, mlp_bot=(8, 64, 32),
+               mlp_top=(64, 32, 1))
+    g = torch.Generator(device="cuda").manual_seed(4)
+    dense = torch.rand(512, 8, device="cuda", generator=g)
+    target = (torch.rand(512, 1, device="cuda", generator=g) > 0.5).float()
+    nets = []
+    for sparse in (False, True):
+        net = T.DLRM(sparse_update=sparse, **cfg)
+        opt = T.SGD(lr=0.3, weight_decay=0.0)
+        net.dense.data.copy_(dense)
+        for _ in range(4):
+            T.dlrm_step(net, target, opt)
+        torch.cuda.synchronize()
+        nets.append(net)
+    a, b = nets
+    assert a.emb.dtables[0] is not None and b.emb.dtables[0] is None
+    for ta, tb in zip(a.emb.tables, b.emb.tables):
+        assert_close(tb, ta.cpu().numpy(), rtol=1e-5, what="table after row-sparse updates")
+    assert_close(b.model.output.data, a.model.output.data.cpu().numpy(), rtol=1e-4, what="output")
