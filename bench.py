@@ -1026,6 +1026,10 @@ def run_dlrm(args):
         pops = importlib.import_module("flexflow_train_b200.parallel_ops").ParallelOps()
     B = args.batch if args.batch != 64 else 8192
     tables = 8
+    # what the veneer's ManagedPerDeviceFFHandle does for an fp32 caller of the reference API: GEMM
+    # scratch registered and allowTensorOpMathConversion on, so the fp32 MLPs run on the tensor cores
+    Kd = importlib.import_module("flexflow_train_b200.kernels")
+    Kd.set_gemm_workspace(256 << 20, fp32_tensor_math=True)
     net = T.DLRM(batch=B, embedding_size=(1000000,) * tables, rank=rank, world=world, device=device)
     opt = T.SGD(lr=0.01, weight_decay=0.0)
     g = torch.Generator(device=device).manual_seed(77 + rank)
