@@ -844,19 +844,23 @@ def run_encoder(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    # the dominant kernel, timed live: the first feed-forward Linear (one tcgen05 GEMM launch with
-    # the bias + activation epilogue) of every timed step
-    ff1 = next(l for l in model.layers if isinstance(l, T.Linear))
-    gemm_flop = 2.0 * ff1.batch * ff1.in_dim * ff1.out_dim
-    gemm_events = []
-    plain_forward = ff1.forward
+    # the dominant kernel, timed live: the plain CTA-pair tcgen05 GEMM (40 of a layer's 46 GEMM launches).
+    # ffk_gemm_time_next brackets the NEXT such launch with an event pair: set right before the first
+    # attention layer's forward, that is its query projection — tokens x (heads*head_dim) x d_model.
+    import ctypes
+    att0 = next(l for l in model.layers if isinstance(l, T.SelfAttention))
+    tok = B * S
+    proj_n, proj_k = (H // tp) * hd, D
+    gemm_flop = 2.0 * tok * proj_n * proj_k
+    gemm_timers = []
+    plain_att_forward = att0.forward
 
     def timed_forward():
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a.record()
-        plain_forward()
-        b.record()
-        gemm_events.append((a, b))
+        t = ctypes.c_void_p()
+        lib.call("ffk_timer_create", ctypes.byref(t))
+        lib.call("ffk_gemm_time_next", t)
+        plain_att_forward()
+        gemm_timers.append(t)
 
     for _ in range(args.warmup):
         step()
@@ -875,7 +879,7 @@ def run_encoder(args):
     if rank == 0:
         clocks.start()
     calls0 = lib.launches
-    ff1.forward = timed_forward
+    att0.forward = timed_forward
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     e0.record()
@@ -883,11 +887,16 @@ def run_encoder(args):
         step()
     e1.record()
     barrier()
-    ff1.forward = plain_forward
+    att0.forward = plain_att_forward
     ms_total = e0.elapsed_time(e1)
-    abi_calls = lib.launches - calls0
+    abi_calls = lib.launches - calls0 - 2 * len(gemm_timers)
     clock_info = clocks.stop() if rank == 0 else None
-    gemm_ms = [a.elapsed_time(b) for a, b in gemm_events]
+    gemm_ms = []
+    for t in gemm_timers:
+        ms = ctypes.c_float()
+        lib.call("ffk_timer_read", t, ctypes.byref(ms))
+        lib.call("ffk_timer_destroy", t)
+        gemm_ms.append(ms.value)
 
     def e2e_step():
         model.input.data.copy_(hx, non_blocking=True)          # the batch arrives from the host
@@ -936,7 +945,7 @@ def run_encoder(args):
     tr = ROOT / "profiles" / "gemm_traffic_bytes.json"
     if tr.exists():
         try:
-            traffic = json.loads(tr.read_text()).get(f"{ff1.batch}x{ff1.out_dim}x{ff1.in_dim}")
+            traffic = json.loads(tr.read_text()).get(f"{tok}x{proj_n}x{proj_k}")
         except Exception:
             traffic = None
     launches = None
@@ -961,9 +970,10 @@ def run_encoder(args):
                                  "single GEMM launches; first-writer gradients (no zero fills), shared residual "
                                  "gradient buffers, gated data gradients") if model_fused else "one kernel per operator",
                    "l2": "inputs larger than L2: one layer's activations are >= 0.5 GB against 126 MB of L2, no explicit flush"},
-        "roofline": {"kernel": f"gemm_tc_pair_kernel (tcgen05 cta_group::2): feed-forward Linear forward "
-                               f"{ff1.batch}x{ff1.out_dim}x{ff1.in_dim} bf16 with bias + activation epilogue, "
-                               f"timed in every timed step; the GEMM family is ~77 % of the step (profiles/)",
+        "roofline": {"kernel": f"gemm_tc_pair_kernel (tcgen05 cta_group::2, plain epilogue): query projection of the first "
+                               f"attention layer, {tok}x{proj_n}x{proj_k} bf16, one launch per timed step bracketed by "
+                               f"ffk_gemm_time_next; this instantiation is 40 of a layer's 46 GEMM launches and the GEMM "
+                               f"family is 88 % of the step (profiles/r02_summary.md)",
                      "bound": "tensor", "achieved": achieved, "peak": sustained,
                      "peak_source": f"{peak_src} bf16_tflops_sustained (kernel timed inside a long step)",
                      "unit": "TFLOP/s", "frac": achieved / sustained, "traffic": traffic,

@@ -11,6 +11,11 @@
 
 #include "../../include/ffk.h"
 
+// Event pair of ffk_timer_* (include/ffk_runtime.h).
+struct ffk_timer {
+  cudaEvent_t start, stop;
+};
+
 namespace ffk {
 
 // ---------------------------------------------------------------- errors
@@ -36,6 +41,10 @@ int cuda_fail(cudaError_t e, char const *what, char const *file, int line);
   } while (0)
 
 #define FFK_LAUNCH_CHECK() FFK_CUDA(cudaGetLastError())
+
+// ffk_gemm_time_next: the timer (of the calling host thread) that the next tensor-core GEMM launch
+// brackets with its start / stop events; cleared by that launch.
+::ffk_timer *&gemm_timer_slot();
 
 // ---------------------------------------------------------------- device
 struct DeviceInfo {

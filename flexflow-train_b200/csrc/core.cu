@@ -23,6 +23,11 @@ int cuda_fail(cudaError_t e, char const *what, char const *file, int line) {
   return FFK_ERR_CUDA;
 }
 
+::ffk_timer *&gemm_timer_slot() {
+  thread_local ::ffk_timer *slot = nullptr;
+  return slot;
+}
+
 DeviceInfo const &device_info() {
   // one process per GPU: the device current at first use is the device of the process
   static DeviceInfo info = [] {

@@ -1052,8 +1052,14 @@ int launch_tc_pair_inst(Problem const &p, Epilogue const &e, cudaStream_t stream
                ((e.d_batch2 * os) % 16 == 0) && (e.r == nullptr || aligned16(e.r));
   Epilogue e2 = e;
   e2.bias_vec_ok = e.bias != nullptr && aligned16(e.bias) && vec_ok;
+  ::ffk_timer *const timer = ::ffk::gemm_timer_slot();   // ffk_gemm_time_next: bracket THIS launch with the timer's events
+  if (timer) cudaEventRecord(timer->start, stream);
   kern<<<clusters * 2, NUM_THREADS, SMEM, stream>>>(ma, mb, e2, p.M, p.N, p.K, p.batch, b2, idesc,
                                                     p.out_dtype, vec_ok);
+  if (timer) {
+    cudaEventRecord(timer->stop, stream);
+    ::ffk::gemm_timer_slot() = nullptr;
+  }
   FFK_LAUNCH_CHECK();
   return FFK_OK;
 }

@@ -47,6 +47,7 @@ __global__ void __launch_bounds__(kThreads)
     // go out together, then the four row loads, then the stores, so that every thread keeps four
     // independent 16-byte requests to the (randomly placed) table rows in flight
     constexpr int U = 4;
+    bool const small = total < (1ll << 31);   // 32-bit divisions (64-bit ones run on the slow XU path)
     for (long long i0 = (long long)blockIdx.x * blockDim.x + threadIdx.x; i0 < total; i0 += stride * U) {
       long long b[U];
       int pk[U];
@@ -54,7 +55,7 @@ __global__ void __launch_bounds__(kThreads)
 #pragma unroll
       for (int u = 0; u < U; ++u) {
         long long const i = i0 + u * stride;
-        b[u] = i / ppr;
+        b[u] = small ? (long long)(unsigned(i) / unsigned(ppr)) : i / ppr;
         pk[u] = int(i - b[u] * ppr);
         row[u] = i < total ? (long long)idx[b[u]] : 0;
       }

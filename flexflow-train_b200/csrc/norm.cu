@@ -672,7 +672,7 @@ __global__ void __launch_bounds__(kThreads)
 
 // Short rows: one warp per row for LayerNorm as well (a d_model = 1024 bf16 row is 128 packets).
 template <typename T, int PW>
-__global__ void __launch_bounds__(kThreads, (PW <= 4 ? 3 : 1))
+__global__ void __launch_bounds__(kThreads, (PW <= 2 ? 3 : PW <= 4 ? 2 : 1))
     layer_norm_fwd_warp_rows_kernel(T const *__restrict__ x, T *__restrict__ y,
                                     T const *__restrict__ gamma, T const *__restrict__ beta,
                                     float *__restrict__ mean, float *__restrict__ rstd,
@@ -682,16 +682,41 @@ __global__ void __launch_bounds__(kThreads, (PW <= 4 ? 3 : 1))
   long long const warp0 = (long long)blockIdx.x * (kThreads / 32) + (threadIdx.x >> 5);
   long long const wstride = (long long)gridDim.x * (kThreads / 32);
   float const invn = 1.f / float(nvec * VN);
-  for (long long r = warp0; r < rows; r += wstride) {
-    T const *xr = x + r * (long long)nvec * VN;
-    T *yr = y + r * (long long)nvec * VN;
-    // the row stays PACKED in registers (widened where used): 4 registers per packet instead of
-    // VN, which is what keeps three 256-thread CTAs resident per SM at 32 columns per lane
-    Vec16<T> t[PW];
+  // gamma / beta of this lane's columns stay packed in registers for every row the warp visits
+  Vec16<T> gk[PW], bk[PW];
+#pragma unroll
+  for (int p = 0; p < PW; ++p) {
+    int i = lane + p * 32;
+#pragma unroll
+    for (int j = 0; j < VN; ++j) {
+      gk[p].v[j] = from_f32<T>(1.f);
+      bk[p].v[j] = from_f32<T>(0.f);
+    }
+    if (gamma && i < nvec) gk[p] = ld_vec(gamma + i * VN);
+    if (beta && i < nvec) bk[p] = ld_vec(beta + i * VN);
+  }
+  // the row stays PACKED in registers (widened where used): 4 registers per packet instead of VN.
+  // The NEXT row's packets are requested before this row is reduced, so that a warp always has
+  // two rows of loads in flight.
+  Vec16<T> t[PW], tn[PW];
+  if (warp0 < rows) {
+    T const *xr = x + warp0 * (long long)nvec * VN;
 #pragma unroll
     for (int p = 0; p < PW; ++p) {
       int i = lane + p * 32;
       t[p] = ld_stream(xr + (i < nvec ? i : 0) * VN);
+    }
+  }
+  for (long long r = warp0; r < rows; r += wstride) {
+    T *yr = y + r * (long long)nvec * VN;
+    long long const rn = r + wstride;
+    if (rn < rows) {
+      T const *xn = x + rn * (long long)nvec * VN;
+#pragma unroll
+      for (int p = 0; p < PW; ++p) {
+        int i = lane + p * 32;
+        tn[p] = ld_stream(xn + (i < nvec ? i : 0) * VN);
+      }
     }
     float s1 = 0.f, s2 = 0.f;
 #pragma unroll
@@ -718,26 +743,25 @@ __global__ void __launch_bounds__(kThreads, (PW <= 4 ? 3 : 1))
     for (int p = 0; p < PW; ++p) {
       int i = lane + p * 32;
       if (i < nvec) {
-        Vec16<T> o, g, b;
-        if (gamma) g = ld_vec(gamma + i * VN);
-        if (beta) b = ld_vec(beta + i * VN);
+        Vec16<T> o;
 #pragma unroll
         for (int j = 0; j < VN; ++j) {
           float u = (to_f32(t[p].v[j]) - mu) * rs;
-          if (gamma) u *= to_f32(g.v[j]);
-          if (beta) u += to_f32(b.v[j]);
+          u = u * to_f32(gk[p].v[j]) + to_f32(bk[p].v[j]);
           o.v[j] = from_f32<T>(u);
         }
         st_stream(yr + i * VN, o);
       }
     }
+#pragma unroll
+    for (int p = 0; p < PW; ++p) t[p] = tn[p];
   }
 }
 
 // Forward for long rows through a bulk-copy ring: three rows in flight per CTA, the row is read
 // from shared memory twice (statistics, then normalisation), so nothing of it lives in registers
 // and four CTAs stay resident per SM at 16 KB rows.
-template <typename T>
+template <typename T, int P>
 __global__ void __launch_bounds__(256)
     layer_norm_fwd_cta_ring_kernel(T const *__restrict__ x, T *__restrict__ y,
                                    T const *__restrict__ gamma, T const *__restrict__ beta,
@@ -762,6 +786,21 @@ __global__ void __launch_bounds__(256)
   }
   __syncthreads();
   float const invn = 1.f / float(N);
+  // gamma / beta of this thread's (at most P) packets, packed, for every row the CTA visits: the
+  // normalisation pass then touches shared memory only (they used to be re-read through L1 per row,
+  // which is where the pass stalled)
+  Vec16<T> gk[P], bk[P];
+#pragma unroll
+  for (int p = 0; p < P; ++p) {
+    int const i = threadIdx.x + p * 256;
+#pragma unroll
+    for (int j = 0; j < VN; ++j) {
+      gk[p].v[j] = from_f32<T>(1.f);
+      bk[p].v[j] = from_f32<T>(0.f);
+    }
+    if (gamma && i < nvec) gk[p] = ld_vec(gamma + i * VN);
+    if (beta && i < nvec) bk[p] = ld_vec(beta + i * VN);
+  }
   int st = 0;
   uint32_t phase = 0;
   for (long long r = blockIdx.x; r < rows; r += gridDim.x) {
@@ -786,18 +825,18 @@ __global__ void __launch_bounds__(256)
       rstd[r] = rs;
     }
     T *yr = y + r * N;
-    for (int i = threadIdx.x; i < nvec; i += 256) {
-      Vec16<T> t = *reinterpret_cast<Vec16<T> const *>(src + size_t(i) * 16), o, g, b;
-      if (gamma) g = ld_vec(gamma + i * VN);
-      if (beta) b = ld_vec(beta + i * VN);
 #pragma unroll
-      for (int j = 0; j < VN; ++j) {
-        float u = (to_f32(t.v[j]) - mu) * rs;
-        if (gamma) u *= to_f32(g.v[j]);
-        if (beta) u += to_f32(b.v[j]);
-        o.v[j] = from_f32<T>(u);
+    for (int p = 0; p < P; ++p) {
+      int const i = threadIdx.x + p * 256;
+      if (i < nvec) {
+        Vec16<T> t = *reinterpret_cast<Vec16<T> const *>(src + size_t(i) * 16), o;
+#pragma unroll
+        for (int j = 0; j < VN; ++j) {
+          float u = (to_f32(t.v[j]) - mu) * rs;
+          o.v[j] = from_f32<T>(u * to_f32(gk[p].v[j]) + to_f32(bk[p].v[j]));
+        }
+        st_stream(yr + i * VN, o);
       }
-      st_stream(yr + i * VN, o);
     }
     __syncthreads();  // the stage has been read for the last time
     if (threadIdx.x == 0) {
@@ -1404,13 +1443,20 @@ int ffk_layer_norm_forward(void *stream, void const *input, void *output, void c
                N * sizeof(T) <= 32768) {
       int nvec = int(N / VN);
       size_t smem = size_t(3) * size_t(N) * sizeof(T);
-      auto kern = layer_norm_fwd_cta_ring_kernel<T>;
-      FFK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      int per_sm = 0;
-      FFK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 256, smem));
-      kern<<<rows_grid(M, std::max(1, per_sm)), 256, smem, s>>>(
-          reinterpret_cast<T const *>(input), reinterpret_cast<T *>(output),
-          reinterpret_cast<T const *>(gamma), reinterpret_cast<T const *>(beta), mean, rstd, M, nvec, eps);
+      auto launch = [&](auto kern) -> int {
+        FFK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        int per_sm = 0;
+        FFK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 256, smem));
+        kern<<<rows_grid(M, std::max(1, per_sm)), 256, smem, s>>>(
+            reinterpret_cast<T const *>(input), reinterpret_cast<T *>(output),
+            reinterpret_cast<T const *>(gamma), reinterpret_cast<T const *>(beta), mean, rstd, M, nvec, eps);
+        return FFK_OK;
+      };
+      int const packets_per_thread = (nvec + 255) / 256;   // rows of 8 .. 32 KB: 2 .. 8 packets of 16 bytes
+      int rc = packets_per_thread <= 2   ? launch(layer_norm_fwd_cta_ring_kernel<T, 2>)
+               : packets_per_thread <= 4 ? launch(layer_norm_fwd_cta_ring_kernel<T, 4>)
+                                         : launch(layer_norm_fwd_cta_ring_kernel<T, 8>);
+      if (rc) return rc;
     } else if (vec) {
       int nvec = int(N / VN), p = pick_p(nvec);
       FFK_DISPATCH_P(p, P, {

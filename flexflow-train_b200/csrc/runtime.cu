@@ -20,9 +20,7 @@ struct ffk_arena {
   size_t in_use = 0, reserved = 0, driver_allocs = 0;
 };
 
-struct ffk_timer {
-  cudaEvent_t start, stop;
-};
+// struct ffk_timer lives in common.cuh (the GEMM launcher records into it for ffk_gemm_time_next)
 
 namespace ffk {
 namespace {
@@ -166,6 +164,16 @@ int ffk_timer_end(ffk_timer_t *t, void *stream, float *elapsed_ms) {
   FFK_CUDA(cudaEventRecord(t->stop, as_stream(stream)));
   FFK_CUDA(cudaEventSynchronize(t->stop));
   FFK_CUDA(cudaEventElapsedTime(elapsed_ms, t->start, t->stop));
+  return FFK_OK;
+}
+int ffk_timer_read(ffk_timer_t *t, float *elapsed_ms) {
+  FFK_REQUIRE(t && elapsed_ms, "timer_read: null argument");
+  FFK_CUDA(cudaEventSynchronize(t->stop));
+  FFK_CUDA(cudaEventElapsedTime(elapsed_ms, t->start, t->stop));
+  return FFK_OK;
+}
+int ffk_gemm_time_next(ffk_timer_t *t) {
+  ffk::gemm_timer_slot() = t;
   return FFK_OK;
 }
 int ffk_timer_destroy(ffk_timer_t *t) {

@@ -55,6 +55,14 @@ int ffk_timer_create(ffk_timer_t **out);
 int ffk_timer_begin(ffk_timer_t *timer, void *stream);
 int ffk_timer_end(ffk_timer_t *timer, void *stream, float *elapsed_ms);
 int ffk_timer_destroy(ffk_timer_t *timer);
+/* Profiling hook in the spirit of profiling_wrapper, at the granularity of ONE kernel: the next
+ * launch of the CTA-pair tcgen05 GEMM issued by the calling host thread (inside whatever entry
+ * point issues it — Linear, MultiHeadAttention, ...) records the timer's start event in front of
+ * the kernel and its stop event behind it, on the kernel's own stream. ffk_timer_read waits for
+ * the stop event and returns the milliseconds between the two. bench.py uses it to time the
+ * dominant kernel live inside its timed steps. */
+int ffk_gemm_time_next(ffk_timer_t *timer);
+int ffk_timer_read(ffk_timer_t *timer, float *elapsed_ms);
 
 /* zero_init_kernel / constant fill on the device — include/kernels/initializer_kernels.h:10-28
  * (declared there; the reference defines only the CPU zero/constant versions,
