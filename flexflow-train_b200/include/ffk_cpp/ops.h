@@ -3,6 +3,7 @@
 // forwards to the C ABI (include/ffk*.h). Per-op state structs keep the reference's names;
 // instead of cuDNN descriptors they carry the plain numbers the sm_100a kernels need.
 #pragma once
+#include <cstddef>
 #include "runtime.h"
 
 namespace FlexFlow {
@@ -51,21 +52,43 @@ struct LayerNormPerDeviceState {
   float *mean, *rstd, *ds, *db, *scale, *bias;
   DataType data_type;
 };
+// cuDNN descriptor handles of the reference's state structs (include/kernels/device.h typedefs):
+// kept as opaque pointers so that the member layout and the cleanup_kernel signatures stay the
+// reference's; nothing here creates or reads a cuDNN descriptor, the slots are null.
+using ffTensorDescriptor_t = struct ffk_opaque_tensor_descriptor *;
+using ffActivationDescriptor_t = struct ffk_opaque_activation_descriptor *;
+using ffDropoutDescriptor_t = struct ffk_opaque_dropout_descriptor *;
+using ffBatchNormMode_t = int;
+
+// batch_norm_kernels.h:11-27, member for member
 struct BatchNormPerDeviceState {
   PerDeviceFFHandle handle;
+  ffTensorDescriptor_t inputTensor, outputTensor, biasTensor;
+  ffActivationDescriptor_t actiDesc;
+  ffBatchNormMode_t mode;
   float *runningMean, *runningVar, *saveMean, *saveVar;  // saveVar holds 1/sqrt(var+eps)
   int output_n, output_c, output_h, output_w;
   bool relu;
 };
+// dropout_kernels.h:12-22, member for member; the generator state of this library follows them
 struct DropoutPerDeviceState {
   PerDeviceFFHandle handle;
+  ffTensorDescriptor_t inputTensor, outputTensor;
+  ffDropoutDescriptor_t dropoutDesc;
+  void *reserveSpace;                 // 1 bit per element keep-mask
+  void *dropoutStates;                // unused: the Philox stream is keyed by (seed, offset)
+  size_t reserveSpaceSize;
+  size_t dropoutStateSize;
   float rate;
   unsigned long long seed;
   mutable unsigned long long offset;  // advances once per forward call (fresh mask each step)
-  void *reserveSpace;                 // 1 bit per element keep-mask
-  size_t reserveSpaceSize;
   size_t num_elements;
 };
+static_assert(offsetof(BatchNormPerDeviceState, runningMean) ==
+                  sizeof(PerDeviceFFHandle) + 4 * sizeof(void *) + sizeof(void *),
+              "BatchNormPerDeviceState: descriptors and mode sit between the handle and runningMean, as in the reference");
+static_assert(offsetof(DropoutPerDeviceState, reserveSpace) == sizeof(PerDeviceFFHandle) + 3 * sizeof(void *),
+              "DropoutPerDeviceState: three descriptor slots between the handle and reserveSpace, as in the reference");
 struct ReducePerDeviceState {
   PerDeviceFFHandle handle;
   OperatorType op_type;
@@ -317,8 +340,8 @@ inline BatchNormPerDeviceState init_kernel(PerDeviceFFHandle handle, Allocator a
   cudaStream_t s;
   checkCUDA(get_legion_stream(&s));
   FFK_CHECK(ffk_fill(s, runningMean, size_t(output_c) * 2, 0.0, FFK_FLOAT));
-  return BatchNormPerDeviceState{handle, runningMean, runningVar, saveMean, saveVar,
-                                 output_n, output_c, output_h, output_w, relu};
+  return BatchNormPerDeviceState{handle, nullptr, nullptr, nullptr, nullptr, 0, runningMean, runningVar, saveMean,
+                                 saveVar, output_n, output_c, output_h, output_w, relu};
 }
 inline void forward_kernel(ffStream_t stream, BatchNormPerDeviceState const &m, float const *input_ptr,
                            float *output_ptr, float const *scale_ptr, float const *bias_ptr) {
@@ -338,6 +361,11 @@ inline void backward_kernel(ffStream_t stream, BatchNormPerDeviceState const &m,
 inline void cleanup_kernel(Allocator allocator, BatchNormPerDeviceState const &m) {
   allocator.deallocate(m.runningMean);
 }
+// batch_norm_kernels.h:76-82: the reference's signature (descriptor handles are ignored here)
+inline void cleanup_kernel(Allocator allocator, ffTensorDescriptor_t, ffTensorDescriptor_t, ffTensorDescriptor_t,
+                           ffActivationDescriptor_t, bool /*relu*/, float *runningMean) {
+  allocator.deallocate(runningMean);
+}
 }  // namespace BatchNorm
 
 // ------------------------------------------------------------------ dropout_kernels.h
@@ -347,7 +375,7 @@ inline DropoutPerDeviceState init_kernel(PerDeviceFFHandle handle, float rate, u
   size_t n = output_domain.num_elements();
   size_t bytes = ffk_dropout_mask_bytes(n);
   void *mask = allocator.allocate(bytes ? bytes : 4);
-  return DropoutPerDeviceState{handle, rate, seed, 0ull, mask, bytes, n};
+  return DropoutPerDeviceState{handle, nullptr, nullptr, nullptr, mask, nullptr, bytes, 0, rate, seed, 0ull, n};
 }
 inline void forward_kernel(ffStream_t stream, DropoutPerDeviceState const &m, float const *input_ptr,
                            float *output_ptr) {
@@ -362,6 +390,12 @@ inline void backward_kernel(ffStream_t stream, DropoutPerDeviceState const &m,
 }
 inline void cleanup_kernel(Allocator allocator, DropoutPerDeviceState const &m) {
   allocator.deallocate(m.reserveSpace);
+}
+// dropout_kernels.h:53-57: the reference's signature. The reference frees `dropoutStates` here; this
+// library keeps no generator state, and the mask (reserveSpace) stays with the allocator.
+inline void cleanup_kernel(Allocator allocator, ffTensorDescriptor_t, ffTensorDescriptor_t, ffDropoutDescriptor_t,
+                           void *dropoutStates) {
+  if (dropoutStates) allocator.deallocate(dropoutStates);
 }
 }  // namespace Dropout
 

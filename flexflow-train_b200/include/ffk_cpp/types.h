@@ -120,12 +120,15 @@ inline int act_code(std::optional<Activation> const &a) {
 // ---- dimension indices
 struct ff_dim_t {
   int value;
+  constexpr ff_dim_t(int v = 0) : value(v) {}
   bool operator==(ff_dim_t o) const { return value == o.value; }
 };
 struct legion_dim_t {
   int value;
+  constexpr legion_dim_t(int v = 0) : value(v) {}
   bool operator==(legion_dim_t o) const { return value == o.value; }
 };
+using LegionTensorDims = std::vector<size_t>;  // what ArrayShape::dims holds (array_shape.h:50)
 inline legion_dim_t add_to_legion_dim(legion_dim_t d, int v) { return legion_dim_t{d.value + v}; }
 inline legion_dim_t legion_dim_from_ff_dim(ff_dim_t d, int num_dims) {
   return legion_dim_t{num_dims - d.value - 1};
@@ -153,9 +156,11 @@ inline TensorShape make_tensor_shape_from_legion_dims(std::vector<size_t> legion
   TensorShape s{{std::vector<size_t>(legion.rbegin(), legion.rend())}, dt};
   return s;
 }
+#ifndef FFK_NO_TEST_SHAPE_HELPERS  // the reference's kernel tests bring their own (test/src/test_utils.cc)
 inline TensorShape make_float_tensor_shape_from_legion_dims(std::vector<size_t> legion) {
   return make_tensor_shape_from_legion_dims(std::move(legion), DataType::FLOAT);
 }
+#endif
 
 // ArrayShape — include/kernels/array_shape.h:14-52. Dims are held in legion order
 // (innermost first); rank-0 shapes have 0 elements, as in the reference.

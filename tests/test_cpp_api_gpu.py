@@ -41,3 +41,35 @@ def test_cost_estimator_bridge():
     r = subprocess.run([str(exe)], capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert "0 failed" in r.stdout
+
+
+# Reference test cases that cannot pass on ANY implementation of the API, with the reason:
+REFERENCE_TESTS_BROKEN_UPSTREAM = {
+    "Test Gather Forward and Backward Kernel":
+        "passes a FLOAT tensor as the index accessor and legion_dim 2 for a rank-1 tensor: the reference's own "
+        "assert(index.data_type == INT32 || INT64) (gather_kernels.cu:138-139) fires",
+}
+
+
+@pytest.mark.gpu
+def test_reference_kernel_test_files_run_unmodified():
+    """tests/cpp/reference_kernel_tests = the reference's lib/kernels/test/src/test_*.cc compiled
+    verbatim against the veneer (built where /root/reference exists; the binary travels). Every test
+    case runs in its own process (the API aborts on error, like the reference's checkCUDA); all of
+    them must pass except the ones that are broken upstream, which are listed above with the reason."""
+    exe = ROOT / "tests" / "cpp" / "reference_kernel_tests"
+    if not exe.exists():
+        pytest.skip("not built: needs the reference checkout at build time (__graft_entry__.build())")
+    listing = subprocess.run([str(exe), "--list-test-cases"], capture_output=True, text=True, timeout=120).stdout
+    cases = [l.strip() for l in listing.splitlines()
+             if l.strip() and not l.startswith("[doctest]") and not l.startswith("====")]
+    assert len(cases) == 20, listing
+    failed = {}
+    for name in cases:
+        r = subprocess.run([str(exe), f"--test-case={name}"], capture_output=True, text=True, timeout=300)
+        if r.returncode != 0:
+            failed[name] = (r.stdout[-600:] + r.stderr[-400:]).strip()
+    unexpected = {k: v for k, v in failed.items() if k not in REFERENCE_TESTS_BROKEN_UPSTREAM}
+    print(f"reference kernel tests: {len(cases) - len(failed)} of {len(cases)} cases pass; failing: {sorted(failed)}")
+    assert not unexpected, "\n\n".join(f"{k}:\n{v}" for k, v in unexpected.items())
+    assert len(cases) - len(failed) >= 15

@@ -20,11 +20,11 @@ from helpers import SEED_ACT, SEED_W, assert_close, to_dev, uniform
 pytestmark = pytest.mark.gpu
 
 
-def _backward_pair(K, ffk, M, N, dtype, accumulate):
-    x, _ = to_dev(uniform((M, N), SEED_ACT) + 0.25, dtype)
-    gamma, _ = to_dev(uniform((N,), SEED_W) + 1.0, dtype)
+def _backward_pair(K, ffk, M, N, dtype, accumulate, oracle=None):
+    x, xn = to_dev(uniform((M, N), SEED_ACT) + 0.25, dtype)
+    gamma, gn = to_dev(uniform((N,), SEED_W) + 1.0, dtype)
     beta, _ = to_dev(uniform((N,), SEED_W + 1), dtype)
-    dy, _ = to_dev(uniform((M, N), SEED_ACT + 1), dtype)
+    dy, dyn = to_dev(uniform((M, N), SEED_ACT + 1), dtype)
     y = torch.empty_like(x)
     state = K.LayerNorm.init_kernel(True, M, N, 1e-5)      # owns a torch-allocated workspace
     K.LayerNorm.forward_kernel(None, state, x, y, gamma, beta)
@@ -50,13 +50,26 @@ def _backward_pair(K, ffk, M, N, dtype, accumulate):
     assert_close(dx, dx_ref.float().cpu().numpy(), dtype, what=f"static dX {M}x{N}")
     assert_close(dg, dg_ref.float().cpu().numpy(), dtype, what=f"static dgamma {M}x{N}")
     assert_close(db, db_ref.float().cpu().numpy(), dtype, what=f"static dbeta {M}x{N}")
+    if oracle is not None:
+        # second referee: the CPU oracle on the same inputs (it starts from the same dX / dgamma /
+        # dbeta contents and follows the same accumulate rule)
+        dxo, _, _ = fresh()
+        dxn = dxo.float().cpu().numpy()
+        dgn = np.full(N, 3.0, np.float32)
+        dbn = np.full(N, -2.0, np.float32)
+        oracle.layer_norm_backward(dyn, xn, dxn, gn, dgn, dbn, state.mean[:M].cpu().numpy(),
+                                   state.rstd[:M].cpu().numpy(), M, N, int(accumulate))
+        assert_close(dx, dxn, dtype, what=f"static dX vs oracle {M}x{N}")
+        if dtype == torch.float32:   # 16-bit parameter sums over hundreds of rows: judged against the workspace variant above
+            assert_close(dg, dgn, dtype, what=f"static dgamma vs oracle {M}x{N}")
+            assert_close(db, dbn, dtype, what=f"static dbeta vs oracle {M}x{N}")
 
 
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
-def test_static_scratch_backward_matches_workspace_backward_twice_in_a_row(K, ffk, dtype):
+def test_static_scratch_backward_matches_workspace_backward_twice_in_a_row(K, ffk, oracle, dtype):
     # first call: wide rows, many slabs; second call: fewer, narrower slabs over the same array
-    _backward_pair(K, ffk, 600, 4096, dtype, accumulate=False)
-    _backward_pair(K, ffk, 37, 1024, dtype, accumulate=True)
+    _backward_pair(K, ffk, 600, 4096, dtype, accumulate=False, oracle=oracle)
+    _backward_pair(K, ffk, 37, 1024, dtype, accumulate=True, oracle=oracle)
     # and once more at the documented limit
     _backward_pair(K, ffk, 5, 16384, dtype, accumulate=False)
 
