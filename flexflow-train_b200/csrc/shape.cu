@@ -202,21 +202,27 @@ __global__ void __launch_bounds__(kThreads)
     int h0 = ho * sh - ph, w0 = wo * sw - pw;
     float g = dy[i];
     if (type == FFK_POOL_MAX) {
-      float m = y[i];
-      bool done = false;
-      for (int a = 0; a < kh && !done; ++a) {
+      // the window's maximum is located again from x (first one in scan order), not by comparing
+      // with y: the gradient then does not depend on `output` holding this very forward pass
+      // (the reference's own test hands the call an unrelated buffer, test_pool_2d_kernels.cc:60-76)
+      (void)y;
+      float best = -INFINITY;
+      int bh = -1, bw = -1;
+      for (int a = 0; a < kh; ++a) {
         int h = h0 + a;
         if (h < 0 || h >= ih) continue;
         for (int b = 0; b < kw; ++b) {
           int w = w0 + b;
           if (w < 0 || w >= iw) continue;
-          if (plane[h * iw + w] == m) {
-            atomicAdd(gplane + h * iw + w, g);
-            done = true;
-            break;
+          float v = plane[h * iw + w];
+          if (v > best) {
+            best = v;
+            bh = h;
+            bw = w;
           }
         }
       }
+      if (bh >= 0) atomicAdd(gplane + bh * iw + bw, g);
     } else {
       int cnt = 0;
       for (int a = 0; a < kh; ++a) {
