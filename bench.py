@@ -797,6 +797,9 @@ def run_encoder(args):
                              tp_rank=tp_rank, tp_world=tp, tp_group=tp_group, fuse=fuse)
         labels = torch.randint(0, V, (B * S,), generator=g, device=device, dtype=torch.int32)
     else:
+        # scratch for the K-cut GEMM schedule (configs[1]'s weight-gradient product in the per-op table: 256 tiles
+        # = 3.46 waves of 74 CTA pairs; the encoder's own 64-tile weight gradients measured faster whole)
+        Kmod.set_gemm_workspace(32 << 20)
         model = T.build_transformer_encoder(L, D, H, S, B, FF, hd, dropout=0.1, dtype=torch.bfloat16, device=device,
                                             fuse=fuse)
     sync_launches_per_step = 0

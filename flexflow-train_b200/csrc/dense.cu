@@ -210,6 +210,17 @@ int ffk_set_gemm_workspace(void *workspace, size_t workspace_bytes) {
 
 int ffk_set_gemm_fp32_tensor_math(int allow) { return gemm::set_fp32_tensor_math(allow); }
 
+int ffk_gemm_kcut_plan(int M, int N, int K, int pairs, int *plan5) {
+  return gemm::kcut_plan(M, N, K, pairs, plan5);
+}
+int ffk_gemm_kcut_segments(int M, int N, int K, int pairs, int pair, int *six, int max_segments) {
+  if (pairs <= 0 || pair < 0 || pair >= pairs || max_segments < 0) {
+    set_error("ffk_gemm_kcut_segments: pair %d of %d", pair, pairs);
+    return FFK_ERR_INVALID;
+  }
+  return gemm::kcut_segments(M, N, K, pairs, pair, six, max_segments);
+}
+
 int ffk_gemm(void *stream, void const *a, void const *b, void *d, int M, int N, int K, int batch,
              long long lda, long long ldb, long long ldd, long long a_batch_stride,
              long long b_batch_stride, long long d_batch_stride, int in_dtype, int out_dtype,

@@ -302,6 +302,133 @@ __device__ __forceinline__ void epilogue_chunk_staged_unaligned(uint32_t const (
   __syncwarp();
 }
 
+// ---- K ranges of one output tile shared between CTA pairs (see gemm_tc_pair_kernel) ----
+// A pair that computed a K range NOT starting at 0 parks its raw fp32 accumulators in its own
+// slot of the scratch; the pair that computed the range starting at 0 adds them (in slot order,
+// so the sum is reproducible) before the ordinary epilogue. One slot = 16 warp positions
+// (2 CTAs x 8 epilogue warps) x 16 KB; float4 index (chunk * 8 + i) * 32 + lane inside a
+// position, so that every instruction of a warp touches 512 contiguous bytes.
+constexpr int SK_POSITIONS = 2 * EPI_WARPS;
+constexpr int SK_POS_FLOAT4 = 4 * 8 * 32;                      // 4 chunks of 32 columns x 32 rows
+constexpr size_t SK_FLAG_BYTES = 16384;                        // flags of up to 256 slots
+constexpr size_t SK_SLOT_BYTES = size_t(SK_POSITIONS) * SK_POS_FLOAT4 * sizeof(float4);
+
+struct SkEpilogue {
+  int mode = 0;                    // 0 whole tile, 1 park the partial, 2 add `count` parked partials
+  float4 *park = nullptr;          // mode 1: this warp position inside this pair's slot
+  uint32_t *park_flag = nullptr;
+  float4 const *take = nullptr;    // mode 2: this warp position inside the first contributor's slot
+  uint32_t const *take_flag = nullptr;
+  int count = 0;                   // mode 2: contributors occupy consecutive slots
+  uint32_t wait_ms = 0;            // mode 2: bound of the wait for each contributor
+};
+
+// K-cut schedule. A launch whose tile count does not fill its last wave of CTA pairs keeps the
+// leading `whole_tiles` tiles (a multiple of the pair count) whole, dealt round the pairs, and
+// cuts the `cut_tiles` tiles of the last wave along K so that every pair works to the end:
+//  * few tiles (2 x cut_tiles <= pairs): every cut tile is cut at the same k-blocks into
+//    `pieces` runs of `piece_k`, one pair per piece (pair = tile * pieces + piece);
+//  * many tiles: pair t < cut_tiles computes k-blocks [0, piece_k) of tile t, and each of the
+//    remaining pairs computes the tails [piece_k, num_k) of `tails` consecutive tiles.
+// Either way all pairs that share an operand panel sweep it at the same k at the same time —
+// the property that lets one read from HBM serve them all, and that a split into equal runs of
+// the linearised (tile, k) space does not have (measured: 64 tiles of 512 k-blocks on 74 pairs
+// ran 32 % SLOWER that way, HBM-bound on re-reads). A run that does not start at k = 0 is
+// parked (role 1) in slot `slot`; the run that does (role 2) adds `count` parked partials
+// from consecutive slots. A pair never parks after it has waited, so waits cannot chain.
+struct SkArgs {
+  int whole_tiles = 0, cut_tiles = 0;
+  int pieces = 0;   // >= 2: uniform pieces; 0: heads and tails
+  int piece_k = 0;  // k-blocks per piece, or the length of the head
+  int tails = 0;    // heads and tails: tails per helper pair
+};
+struct SkSegment {
+  int tile, kb0, kb1;
+  int role;         // 0 whole tile, 1 park, 2 own the tile and take `count` partials
+  int slot, count;
+};
+// Host-callable: the CPU tests walk the same code (ffk_gemm_kcut_segments). One `next` per
+// segment, so that the three role loops of the kernel keep a single body each.
+struct SkWalk {
+  SkArgs a;
+  int pair, pairs, num_k, next_tile, whole_end, cut_i, cut_end;
+  __host__ __device__ SkWalk(int pair_, int pairs_, int num_tiles, int num_k_, SkArgs const &args)
+      : a(args), pair(pair_), pairs(pairs_), num_k(num_k_), next_tile(pair_) {
+    whole_end = a.cut_tiles > 0 ? a.whole_tiles : num_tiles;
+    cut_i = cut_end = 0;
+    if (a.cut_tiles > 0) {
+      if (a.pieces >= 2) {
+        cut_end = pair < a.cut_tiles * a.pieces ? 1 : 0;
+      } else if (pair < a.cut_tiles) {
+        cut_end = 1;
+      } else {
+        cut_i = (pair - a.cut_tiles) * a.tails;
+        cut_end = cut_i + a.tails < a.cut_tiles ? cut_i + a.tails : a.cut_tiles;
+      }
+    }
+  }
+  __host__ __device__ __forceinline__ bool next(SkSegment &g) {
+    if (next_tile < whole_end) {
+      g.tile = next_tile;
+      g.kb0 = 0;
+      g.kb1 = num_k;
+      g.role = 0;
+      g.slot = g.count = 0;
+      next_tile += pairs;
+      return true;
+    }
+    if (cut_i >= cut_end) return false;
+    if (a.pieces >= 2) {
+      int const t = pair / a.pieces, j = pair - t * a.pieces;
+      g.tile = a.whole_tiles + t;
+      g.kb0 = j * a.piece_k;
+      g.kb1 = g.kb0 + a.piece_k < num_k ? g.kb0 + a.piece_k : num_k;
+      g.role = j == 0 ? 2 : 1;
+      g.slot = t * (a.pieces - 1) + (j == 0 ? 0 : j - 1);
+      g.count = j == 0 ? a.pieces - 1 : 0;
+    } else if (pair < a.cut_tiles) {
+      g.tile = a.whole_tiles + pair;
+      g.kb0 = 0;
+      g.kb1 = a.piece_k;
+      g.role = 2;
+      g.slot = pair;
+      g.count = 1;
+    } else {
+      g.tile = a.whole_tiles + cut_i;
+      g.kb0 = a.piece_k;
+      g.kb1 = num_k;
+      g.role = 1;
+      g.slot = cut_i;
+      g.count = 0;
+    }
+    ++cut_i;
+    return true;
+  }
+};
+
+__device__ __forceinline__ void sk_publish(uint32_t *flag) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(flag), "r"(1u) : "memory");
+}
+// Bounded wait: a contributor that does not arrive within `wait_ms` turns the tile into NaN
+// instead of hanging the device. The bound is long (FFK_GEMM_STREAMK_WAIT_MS, default 120 s):
+// a contributor pair may not even be resident yet while another kernel holds its SMs — e.g. a
+// peer-memory collective waiting up to its own 30 s limit for a late rank.
+__device__ __forceinline__ bool sk_arrived(uint32_t const *flag, uint32_t wait_ms) {
+  uint32_t v;
+  unsigned long long t0 = 0;
+  for (uint32_t spin = 0;; ++spin) {
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(flag) : "memory");
+    if (v != 0u) return true;
+    if ((spin & 1023u) == 1023u) {
+      unsigned long long now;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > 1000000ull * wait_ms) return false;
+    }
+    __nanosleep(64);
+  }
+}
+
 // One warp's share of a tile epilogue: NCHUNK chunks of 32 accumulator columns for the 32 rows
 // (TMEM lanes) of its quadrant. The TMEM load of chunk c+1 is in flight while chunk c is
 // converted and stored; `release` runs once the last load has landed (the accumulator buffer
@@ -309,7 +436,8 @@ __device__ __forceinline__ void epilogue_chunk_staged_unaligned(uint32_t const (
 template <int NCHUNK, bool EXTRAS, typename Release>
 __device__ __forceinline__ void epilogue_columns(uint32_t taddr, Epilogue const &ep, long long block_off,
                                                  int rows_valid, int N, int col_first, int out_dtype,
-                                                 int vec_ok, uint8_t *stage, Release release) {
+                                                 int vec_ok, uint8_t *stage, Release release,
+                                                 SkEpilogue const *sk = nullptr) {
   int const lane = threadIdx.x & 31;
   bool const row_ok = lane < rows_valid;
   long long const row_off = block_off + static_cast<long long>(lane) * ep.ldd;
@@ -318,6 +446,13 @@ __device__ __forceinline__ void epilogue_columns(uint32_t taddr, Epilogue const 
                             !ep.accumulate && ep.r == nullptr;
   uint32_t r[2][32];
   ptx::tmem_ld_32x32(taddr, r[0]);
+  bool sk_lost = false;
+  if (sk != nullptr && sk->mode == 2) {
+    int ok = 1;
+    if (lane == 0)
+      for (int j = 0; j < sk->count; ++j) ok &= sk_arrived(sk->take_flag + j * SK_POSITIONS, sk->wait_ms) ? 1 : 0;
+    sk_lost = __shfl_sync(0xffffffffu, ok, 0) == 0;
+  }
 #pragma unroll
   for (int c = 0; c < NCHUNK; ++c) {
     ptx::tmem_ld_wait_for(r[c & 1]);
@@ -325,6 +460,32 @@ __device__ __forceinline__ void epilogue_columns(uint32_t taddr, Epilogue const 
       ptx::tmem_ld_32x32(taddr + (c + 1) * 32, r[(c + 1) & 1]);
     } else {
       release();
+    }
+    if (sk != nullptr && sk->mode == 1) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+        __stcg(reinterpret_cast<uint4 *>(sk->park) + (c * 8 + i) * 32 + lane,
+               make_uint4(r[c & 1][4 * i], r[c & 1][4 * i + 1], r[c & 1][4 * i + 2], r[c & 1][4 * i + 3]));
+      continue;
+    }
+    if (sk != nullptr && sk->mode == 2) {
+      for (int j = 0; j < sk->count; ++j) {
+        float4 const *src = sk->take + size_t(j) * (SK_POSITIONS * SK_POS_FLOAT4) + c * 8 * 32 + lane;
+        float4 t[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) t[i] = __ldcg(src + i * 32);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          r[c & 1][4 * i] = __float_as_uint(__uint_as_float(r[c & 1][4 * i]) + t[i].x);
+          r[c & 1][4 * i + 1] = __float_as_uint(__uint_as_float(r[c & 1][4 * i + 1]) + t[i].y);
+          r[c & 1][4 * i + 2] = __float_as_uint(__uint_as_float(r[c & 1][4 * i + 2]) + t[i].z);
+          r[c & 1][4 * i + 3] = __float_as_uint(__uint_as_float(r[c & 1][4 * i + 3]) + t[i].w);
+        }
+      }
+      if (sk_lost) {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) r[c & 1][i] = 0x7fc00000u;
+      }
     }
     int const col0 = col_first + c * 32;
     int const valid = min(32, N - col0);
@@ -348,6 +509,11 @@ __device__ __forceinline__ void epilogue_columns(uint32_t taddr, Epilogue const 
         default: epilogue_row_chunk<__half>(r[c & 1], ep, row_off, col0, valid, vec_ok); break;
       }
     }
+  }
+  if (sk != nullptr && sk->mode == 1) {
+    __threadfence();
+    __syncwarp();
+    if (lane == 0) sk_publish(sk->park_flag);
   }
 }
 
@@ -533,7 +699,8 @@ template <bool A_MN, bool B_MN, int STAGES, bool EXTRAS>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
     gemm_tc_pair_kernel(const __grid_constant__ CUtensorMap map_a,
                         const __grid_constant__ CUtensorMap map_b, Epilogue ep, int M, int N, int K,
-                        int batch, int batch2, uint32_t idesc, int out_dtype, int vec_ok) {
+                        int batch, int batch2, uint32_t idesc, int out_dtype, int vec_ok,
+                        SkArgs sk_args, uint8_t *sk_ws, uint32_t sk_wait_ms) {
   constexpr int BLOCK_N = 256, HALF_N = 128, PAIR_M = 256, ESIZE = 2;
   constexpr int BLOCK_K = SWIZZLE_BYTES / ESIZE, ATOM_MN = SWIZZLE_BYTES / ESIZE;
   constexpr int A_BYTES = BLOCK_M * SWIZZLE_BYTES, B_BYTES = HALF_N * SWIZZLE_BYTES;
@@ -594,17 +761,21 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
     m_idx = (first + in_g % gsize) * PAIR_M;
     n_idx = (in_g / gsize) * BLOCK_N;
   };
+  // all three roles walk the same list of (tile, k range) segments
+  SkWalk walk(tile0, tile_step, num_tiles, num_k, sk_args);
+  SkSegment seg;
 
   if (warp == 0 && lane == 0) {
     // ------------------------------------------------------------ TMA producer (both CTAs)
     int stage = 0;
     uint32_t phase = 0;
-    for (int tile = tile0; tile < num_tiles; tile += tile_step) {
+    while (walk.next(seg)) {
+      int const kb0 = seg.kb0, kb1 = seg.kb1;
       int b, m_idx, n_idx;
-      decode(tile, b, m_idx, n_idx);
+      decode(seg.tile, b, m_idx, n_idx);
       int const my_m = m_idx + rank * BLOCK_M, my_n = n_idx + rank * HALF_N;
       int const b_in = b % batch2, b_out = b / batch2;
-      for (int kb = 0; kb < num_k; ++kb) {
+      for (int kb = kb0; kb < kb1; ++kb) {
         ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
         uint8_t *sa = smem + stage * STAGE_BYTES;
         uint8_t *sb = sa + A_BYTES;
@@ -641,11 +812,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
     constexpr uint32_t B_KSTEP = B_MN ? (MMA_K_BYTES / ESIZE) * SWIZZLE_BYTES : MMA_K_BYTES;
     int stage = 0, acc = 0;
     uint32_t phase = 0, acc_phase = 0;
-    for (int tile = tile0; tile < num_tiles; tile += tile_step) {
+    while (walk.next(seg)) {
+      int const kb0 = seg.kb0, kb1 = seg.kb1;
       ptx::mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
       ptx::tc_fence_after();
       uint32_t const d_tmem = tmem_base + acc * BLOCK_N;
-      for (int kb = 0; kb < num_k; ++kb) {
+      for (int kb = kb0; kb < kb1; ++kb) {
         ptx::mbar_wait(&full_bar[stage], phase);
         ptx::tc_fence_after();
         uint32_t const sa = ptx::smem_u32(smem + stage * STAGE_BYTES);
@@ -654,10 +826,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
         for (int k = 0; k < K_STEPS; ++k) {
           uint64_t da = ptx::make_smem_desc_sw128(sa + k * A_KSTEP, A_LBO, 1024);
           uint64_t db = ptx::make_smem_desc_sw128(sb + k * B_KSTEP, B_LBO, 1024);
-          ptx::mma_f16_ss_2cta(d_tmem, da, db, idesc, (kb | k) != 0);
+          ptx::mma_f16_ss_2cta(d_tmem, da, db, idesc, ((kb - kb0) | k) != 0);
         }
         ptx::mma_commit_2cta(&empty_bar[stage], 0b11);
-        if (kb == num_k - 1) ptx::mma_commit_2cta(&tmem_full[acc], 0b11);
+        if (kb == kb1 - 1) ptx::mma_commit_2cta(&tmem_full[acc], 0b11);
         if (++stage == STAGES) {
           stage = 0;
           phase ^= 1;
@@ -674,9 +846,28 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
     int const half = (warp - 2) >> 2;
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int tile = tile0; tile < num_tiles; tile += tile_step) {
+    while (walk.next(seg)) {
       int b, m_idx, n_idx;
-      decode(tile, b, m_idx, n_idx);
+      decode(seg.tile, b, m_idx, n_idx);
+      // a K range that does not start at 0 is parked in its slot of the scratch; the range that
+      // does collects the slots that hold the rest of the tile
+      SkEpilogue sk;
+      if (seg.role != 0) {
+        int const pos = int(rank) * EPI_WARPS + (warp - 2);
+        uint32_t *const flag = reinterpret_cast<uint32_t *>(sk_ws) + seg.slot * SK_POSITIONS + pos;
+        float4 *const slot = reinterpret_cast<float4 *>(sk_ws + SK_FLAG_BYTES) +
+                             (size_t(seg.slot) * SK_POSITIONS + pos) * SK_POS_FLOAT4;
+        sk.mode = seg.role;
+        if (seg.role == 1) {
+          sk.park = slot;
+          sk.park_flag = flag;
+        } else {
+          sk.take = slot;
+          sk.take_flag = flag;
+          sk.count = seg.count;
+          sk.wait_ms = sk_wait_ms;
+        }
+      }
       ptx::mbar_wait(&tmem_full[acc], acc_phase);
       ptx::tc_fence_after();
       int const row0 = m_idx + rank * BLOCK_M + q * 32;
@@ -692,7 +883,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
             __syncwarp();
             if (lane == 0)
               ptx::mbar_arrive_cluster(ptx::map_to_cta(ptx::smem_u32(&tmem_empty[acc]), 0));
-          });
+          }, EXTRAS ? nullptr : &sk);
       if (++acc == 2) {
         acc = 0;
         acc_phase ^= 1;
@@ -1021,6 +1212,15 @@ int launch_tc_layout(Problem const &p, Epilogue const &e, cudaStream_t s) {
   return launch_tc_inst<ESIZE, true, true, BLOCK_N, STAGES>(p, e, s);
 }
 
+struct SkPlan {
+  SkArgs args;
+  uint8_t *ws = nullptr;
+  uint32_t wait_ms = 0;
+};
+// defined with the registered scratch below
+bool sk_begin(Problem const &p, bool extras, long long tiles, int pairs, cudaStream_t stream, SkPlan &plan);
+void sk_end(cudaStream_t stream);
+
 template <bool A_MN, bool B_MN>
 int launch_tc_pair_inst(Problem const &p, Epilogue const &e, cudaStream_t stream) {
   constexpr int STAGES = 6, BLOCK_K = 64, ATOM = 64, HALF_N = 128;
@@ -1046,20 +1246,26 @@ int launch_tc_pair_inst(Problem const &p, Epilogue const &e, cudaStream_t stream
   uint32_t fmt = p.in_dtype == FFK_BFLOAT16 ? ptx::kFmtBF16 : ptx::kFmtF16;
   uint32_t idesc = ptx::make_idesc(fmt, A_MN, B_MN, 256, 256);
   long long tiles = 1LL * ((p.M + 255) / 256) * ((p.N + 255) / 256) * p.batch;
-  int clusters = (int)std::min<long long>(tiles, device_info().sm_count / 2);
+  int const pairs = device_info().sm_count / 2;
+  int clusters = (int)std::min<long long>(tiles, pairs);
   size_t os = dtype_size(p.out_dtype);
   int vec_ok = aligned16(e.d) && ((e.ldd * os) % 16 == 0) && ((e.d_batch * os) % 16 == 0) &&
                ((e.d_batch2 * os) % 16 == 0) && (e.r == nullptr || aligned16(e.r));
   Epilogue e2 = e;
   e2.bias_vec_ok = e.bias != nullptr && aligned16(e.bias) && vec_ok;
+  // a tile count that leaves the last wave of pairs mostly idle: cut the tiles of that wave along K
+  SkPlan sk;
+  bool const cut = sk_begin(p, extras, tiles, pairs, stream, sk);
+  if (cut) clusters = pairs;
   ::ffk_timer *const timer = ::ffk::gemm_timer_slot();   // ffk_gemm_time_next: bracket THIS launch with the timer's events
   if (timer) cudaEventRecord(timer->start, stream);
   kern<<<clusters * 2, NUM_THREADS, SMEM, stream>>>(ma, mb, e2, p.M, p.N, p.K, p.batch, b2, idesc,
-                                                    p.out_dtype, vec_ok);
+                                                    p.out_dtype, vec_ok, sk.args, sk.ws, sk.wait_ms);
   if (timer) {
     cudaEventRecord(timer->stop, stream);
     ::ffk::gemm_timer_slot() = nullptr;
   }
+  if (cut) sk_end(stream);
   FFK_LAUNCH_CHECK();
   return FFK_OK;
 }
@@ -1463,6 +1669,113 @@ int set_fp32_tensor_math(int allow) {
   return FFK_OK;
 }
 
+namespace {
+
+// K-cut schedule of the CTA-pair kernel (gemm_tc_pair_kernel, `SkWalk`). Taken when
+//  * a scratch is registered for this device and can be ordered behind its last user,
+//  * the plain epilogue runs, one batch, and the scratch is not holding this GEMM's operands,
+//  * the last wave of 256 x 256 tiles would leave >= 5 % of the whole launch idle
+//    (256 tiles on 74 pairs: 13.5 %; 512 tiles: 1.2 % -> left alone), and, when that wave is
+//    more than half full, >= 25 % of the pairs idle in it (see below).
+// FFK_GEMM_NO_STREAMK=1 turns it off. sk_begin .. sk_end hold g_scratch_mu.
+bool sk_arithmetic(long long tiles, int num_k, int pairs, SkArgs &a) {
+  a = SkArgs{};
+  if (pairs <= 1 || pairs > 256 || tiles <= 0 || num_k < 8) return false;
+  long long const waves = (tiles + pairs - 1) / pairs;
+  int const rem = int(tiles % pairs);
+  if (rem == 0 || tiles - rem > (1 << 30)) return false;
+  if ((pairs - rem) * 100LL < 5LL * pairs * waves) return false;
+  SkArgs r;
+  r.whole_tiles = int(tiles - rem);
+  r.cut_tiles = rem;
+  if (2 * rem <= pairs) {
+    int const want = pairs / rem;                    // pairs available per tile
+    int piece_k = (num_k + want - 1) / want;
+    if (piece_k < 4) piece_k = 4;                    // a piece shorter than 4 k-blocks is all epilogue
+    r.piece_k = piece_k;
+    r.pieces = (num_k + piece_k - 1) / piece_k;      // every piece non-empty
+    if (r.pieces < 2) return false;
+  } else {
+    // Heads and tails pay only when a good part of the wave is idle: with 64 tiles on 74 pairs
+    // (13.5 % idle) the cut launch measured 4 % SLOWER than the whole tiles (207.6 against
+    // 200.1 us) — the device runs under its power cap, so 64 busy pairs clock higher than 74,
+    // and the tails' operands are extra HBM traffic. Taken from 25 % idle pairs upwards.
+    int const helpers = pairs - rem;
+    if (helpers * 4 < pairs) return false;
+    r.tails = (rem + helpers - 1) / helpers;
+    int head = int((1LL * num_k * r.tails + r.tails) / (r.tails + 1));   // ceil(num_k q / (q + 1))
+    if (head >= num_k) head = num_k - 1;
+    if (head < 1) return false;
+    r.pieces = 0;
+    r.piece_k = head;
+  }
+  a = r;
+  return true;
+}
+
+bool sk_begin(Problem const &p, bool extras, long long tiles, int pairs, cudaStream_t stream, SkPlan &plan) {
+  static bool const off = std::getenv("FFK_GEMM_NO_STREAMK") != nullptr;
+  if (off || extras || p.batch != 1 || p.scratch_busy) return false;
+  SkArgs args;
+  if (!sk_arithmetic(tiles, (p.K + 63) / 64, pairs, args)) return false;
+  size_t const need = SK_FLAG_BYTES + size_t(pairs) * SK_SLOT_BYTES;   // never more slots than pairs
+  g_scratch_mu.lock();
+  Scratch *sc = scratch_slot();
+  if (!sc || !sc->ptr || !aligned16(sc->ptr) || sc->bytes < need || scratch_acquire(*sc, stream) != FFK_OK ||
+      cudaMemsetAsync(sc->ptr, 0, size_t(pairs) * SK_POSITIONS * sizeof(uint32_t), stream) != cudaSuccess) {
+    cudaGetLastError();
+    g_scratch_mu.unlock();
+    return false;
+  }
+  static uint32_t const wait_ms = [] {
+    char const *v = std::getenv("FFK_GEMM_STREAMK_WAIT_MS");
+    long ms = v ? std::atol(v) : 0;
+    return uint32_t(ms > 0 ? ms : 120000);
+  }();
+  plan.wait_ms = wait_ms;
+  plan.args = args;
+  plan.ws = static_cast<uint8_t *>(sc->ptr);
+  return true;
+}
+void sk_end(cudaStream_t stream) {
+  Scratch *sc = scratch_slot();
+  if (sc) scratch_release(*sc, stream);
+  g_scratch_mu.unlock();
+}
+
+}  // namespace
+
+int kcut_plan(int M, int N, int K, int pairs, int *plan5) {
+  long long const tiles = 1LL * ((M + 255) / 256) * ((N + 255) / 256);
+  SkArgs a;
+  bool const taken = M > 128 && N > 128 && K > 0 && sk_arithmetic(tiles, (K + 63) / 64, pairs, a);
+  if (plan5) {
+    plan5[0] = a.whole_tiles;
+    plan5[1] = a.cut_tiles;
+    plan5[2] = a.pieces;
+    plan5[3] = a.piece_k;
+    plan5[4] = a.tails;
+  }
+  return taken ? 1 : 0;
+}
+
+int kcut_segments(int M, int N, int K, int pairs, int pair, int *six, int max_segments) {
+  long long const tiles = 1LL * ((M + 255) / 256) * ((N + 255) / 256);
+  SkArgs a;
+  if (!(M > 128 && N > 128 && K > 0 && sk_arithmetic(tiles, (K + 63) / 64, pairs, a))) a = SkArgs{};
+  int n = 0;
+  SkWalk walk(pair, pairs, int(tiles), (K + 63) / 64, a);
+  SkSegment g;
+  while (walk.next(g)) {
+    if (n < max_segments && six) {
+      int *o = six + 6 * n;
+      o[0] = g.tile; o[1] = g.kb0; o[2] = g.kb1; o[3] = g.role; o[4] = g.slot; o[5] = g.count;
+    }
+    ++n;
+  }
+  return n;
+}
+
 size_t split_workspace_bytes(Problem const &p) {
   size_t ea = operand_elems(p.a_mn_major ? p.K : p.M, p.lda, p.a_batch, p.a_batch2, p.batch, p.batch2);
   size_t eb = operand_elems(p.b_mn_major ? p.K : p.N, p.ldb, p.b_batch, p.b_batch2, p.batch, p.batch2);
@@ -1491,6 +1804,7 @@ int launch_split_bf16(Problem const &p, Epilogue const &e, cudaStream_t stream, 
   FFK_LAUNCH_CHECK();
   Problem q = p;
   q.in_dtype = FFK_BFLOAT16;
+  q.scratch_busy = true;   // the registered scratch may be this workspace (and its lock is held)
   if (!tc_eligible(q, e)) {
     set_error("split-bf16 gemm: operands do not satisfy TMA alignment");
     return FFK_ERR_UNSUPPORTED;

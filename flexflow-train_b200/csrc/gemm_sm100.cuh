@@ -100,6 +100,15 @@ int set_workspace(void *ptr, size_t bytes);
 int set_fp32_tensor_math(int allow);
 int launch_split_bf16_registered(Problem const &p, Epilogue const &e, cudaStream_t stream);
 
+// K-cut schedule of the CTA-pair kernel (see gemm_sm100.cu `SkWalk`, `sk_begin`): the arithmetic
+// alone, for introspection and the CPU tests. kcut_plan returns 1 when an M x N x K 16-bit
+// product on `pairs` CTA pairs would be cut (given scratch) and fills plan5 = {whole tiles,
+// cut tiles, pieces per cut tile (0 = heads and tails), k-blocks per piece / per head, tails per
+// helper pair}; kcut_segments lists pair `pair`'s work as (tile, first k-block, end k-block,
+// role, slot, count) and returns the number of segments.
+int kcut_plan(int M, int N, int K, int pairs, int *plan5);
+int kcut_segments(int M, int N, int K, int pairs, int pair, int *six, int max_segments);
+
 // Picks the tensor path for 16-bit inputs when eligible; large fp32 products take the
 // split-bf16 tensor path when scratch is registered; everything else runs SIMT.
 int launch(Problem const &p, Epilogue const &e, cudaStream_t stream);

@@ -32,6 +32,27 @@ int ffk_set_gemm_workspace(void *workspace, size_t workspace_bytes);
  * registered. FFK_GEMM_SPLIT_BF16 as an explicit path needs only the scratch. */
 int ffk_set_gemm_fp32_tensor_math(int allow);
 
+/* The K-cut schedule of the 16-bit tensor-core product, as arithmetic (no device work; no
+ * reference counterpart — cuBLAS picks its own split-K heuristics behind cublasGemmEx,
+ * linear_kernels.cu:127-149). A product of more than 128 x 128 outputs runs as 256 x 256 tiles
+ * on `pairs` CTA pairs (SM count / 2). When the tile count leaves >= 5 % of the launch idle in
+ * its last wave AND scratch is registered (ffk_set_gemm_workspace, >= 16 KB + pairs x 256 KB),
+ * the tiles of that wave are cut along K (k-blocks of 64): into equal pieces, one pair each,
+ * when the wave is at most half full; otherwise into a head computed by the tile's own pair and
+ * a tail, with the idle pairs taking several tails each. Partial sums are parked in the scratch
+ * in fp32 and added by the tile's owner in a fixed order (results are reproducible run to run;
+ * they differ from the uncut schedule by fp32 summation order only). FFK_GEMM_NO_STREAMK=1
+ * disables it.
+ *   ffk_gemm_kcut_plan     -> 1 if M x N x K would be cut; plan5 = {whole tiles, cut tiles,
+ *                             pieces per cut tile (0 = heads and tails), k-blocks per piece or
+ *                             per head, tails per helper pair} (all 0 when not cut);
+ *   ffk_gemm_kcut_segments -> pair `pair`'s work as (tile, first k-block, end k-block, role,
+ *                             slot, count) written to six[6 * max_segments]; role 0 = whole
+ *                             tile, 1 = partial parked in `slot`, 2 = owner adding `count`
+ *                             partials from `slot` on; returns the segment count. */
+int ffk_gemm_kcut_plan(int M, int N, int K, int pairs, int *plan5);
+int ffk_gemm_kcut_segments(int M, int N, int K, int pairs, int pair, int *six, int max_segments);
+
 /* General strided-batched product, the building block under Linear / BatchMatmul / MHA:
  *   D[b][m][n] = alpha * sum_k A(b,m,k) * B(b,n,k)  (+ bias[n]) (act)  (+ D if accumulate)
  * A is stored [batch][M][lda>=K] when a_mn_major == 0 (k contiguous) or [batch][K][lda>=M]

@@ -169,3 +169,78 @@ def test_exported_bert_graph_reads_back_with_its_placement(ffk, tmp_path):
     st = S.parse_strategy(X.bert_pcg(num_layers=1, hidden=64, heads=4, dim_ff=128, seq=16, batch=32, vocab=208,
                                      tensor_parallel=1, data_parallel=8), world_size=8)
     assert (st.tensor_parallel, st.data_parallel) == (1, 8)
+
+
+def _kcut(ffk, M, N, K, pairs):
+    import ctypes
+
+    L = ffk.lib()
+    plan = (ctypes.c_int * 5)()
+    taken = L.call("ffk_gemm_kcut_plan", M, N, K, pairs, plan)
+    segs = []
+    for pair in range(pairs):
+        buf = (ctypes.c_int * (6 * 1024))()
+        n = L.call("ffk_gemm_kcut_segments", M, N, K, pairs, pair, buf, 1024)
+        assert n <= 1024
+        segs.append([tuple(buf[6 * i + j] for j in range(6)) for i in range(n)])
+    return taken, tuple(plan), segs
+
+
+def test_gemm_k_cut_schedule_covers_every_k_block_once(ffk):
+    """The segment lists the CTA pairs walk (the kernel and this test call the same code):
+    every (tile, k-block) exactly once; each parked partial has its own slot, below the pair
+    count (the scratch holds one slot per pair); the slots a tile's owner reads are exactly the
+    slots parked for that tile; a pair never parks after it has waited (so waits cannot chain);
+    pairs that share a tile row / column start their pieces at the same k-block (one read from
+    HBM serves them); and the longest pair is within a few k-blocks of the ideal share."""
+    import random
+
+    rng = random.Random(5)
+    shapes = [(4096, 4096, 8192, 74), (4096, 1024, 32768, 74), (768, 768, 32768, 74), (3072, 768, 32768, 74),
+              (512, 512, 4096, 74), (4096, 512, 512, 74), (1000, 1304, 4104, 74), (8192, 4096, 4096, 74)]
+    shapes += [(rng.randint(129, 6000), rng.randint(129, 6000), rng.randint(8, 40000), rng.choice([74, 66, 10, 2, 128]))
+               for _ in range(80)]
+    cut_seen = 0
+    for M, N, K, pairs in shapes:
+        taken, plan, segs = _kcut(ffk, M, N, K, pairs)
+        whole, cut, pieces, piece_k, tails = plan
+        tiles, num_k = ((M + 255) // 256) * ((N + 255) // 256), (K + 63) // 64
+        cover, parked, owned, slots = set(), {}, {}, set()
+        for pair, lst in enumerate(segs):
+            waited = False
+            for (t, a, b, role, slot, count) in lst:
+                assert 0 <= t < tiles and 0 <= a < b <= num_k, (M, N, K, pairs, t, a, b)
+                for kb in range(a, b):
+                    assert (t, kb) not in cover
+                    cover.add((t, kb))
+                if role == 0:
+                    assert (a, b) == (0, num_k)
+                elif role == 1:
+                    assert a > 0 and not waited, "a pair parks after it has waited"
+                    assert 0 <= slot < pairs and slot not in slots
+                    slots.add(slot)
+                    parked.setdefault(t, []).append(slot)
+                else:
+                    assert role == 2 and a == 0 and b < num_k and count >= 1
+                    owned[t] = list(range(slot, slot + count))
+                    waited = True
+        assert len(cover) == tiles * num_k
+        assert {t: sorted(v) for t, v in parked.items()} == owned
+        if not taken:
+            assert plan == (0, 0, 0, 0, 0) and not parked
+            continue
+        cut_seen += 1
+        assert whole % pairs == 0 and whole + cut == tiles and 0 < cut < pairs
+        # cut points are the same for every cut tile
+        starts = {a for lst in segs for (t, a, b, role, _, _) in lst if role != 0}
+        assert starts == ({j * piece_k for j in range(pieces)} if pieces else {0, piece_k})
+        loads = [sum(b - a for (_, a, b, _, _, _) in lst) for lst in segs]
+        uncut = -(-tiles // pairs) * num_k
+        assert max(loads) < uncut, (M, N, K, pairs, max(loads), uncut)
+    assert cut_seen >= 25
+    # the shapes the schedule exists for, and one it must leave alone
+    assert _kcut(ffk, 4096, 1024, 32768, 74)[0] == 0                             # encoder weight gradient, 64 tiles on 74 pairs: measured slower when cut
+    assert _kcut(ffk, 2000, 1304, 1032, 74)[:2] == (1, (0, 48, 0, 12, 2))        # 48 tiles: heads of 12 k-blocks, two tails per helper
+    assert _kcut(ffk, 4096, 4096, 8192, 74)[:2] == (1, (222, 34, 2, 64, 0))      # configs[1] weight gradient: 3.46 waves
+    assert _kcut(ffk, 768, 768, 32768, 74)[:2] == (1, (0, 9, 8, 64, 0))          # BERT-base weight gradient: 9 tiles
+    assert _kcut(ffk, 8192, 4096, 4096, 74)[0] == 0                              # 512 tiles = 6.92 waves
