@@ -4,7 +4,8 @@
 // the sm_100a kernels a second referee that IS the reference's code, for every op family whose
 // arithmetic the reference wrote itself (LayerNorm, Embedding, losses, optimizers, Gather, Cast,
 // TopK, the element-unary custom ops, the helper kernels, metrics, Replicate / Reduction sums),
-// plus the two cuBLAS calls of Linear and BatchMatmul configured as the reference configures them.
+// plus the cuBLAS calls of Linear and BatchMatmul (forward and backward) configured as the reference
+// configures them.
 //
 // Each wrapper restates the launch configuration of the reference's host function (cited), which
 // cannot be compiled here (generated *.dtg.h headers, cuDNN / cuBLAS handle types, Legion).
@@ -387,4 +388,50 @@ REF_API int ref_batch_matmul_forward(void *stream, float *o, float const *a, flo
   cublasStatus_t st = cublasSgemmStridedBatched(blas(), CUBLAS_OP_N, CUBLAS_OP_N, m, n, k, &alpha, b, m, (long long)k * m,
                                                 a, k, (long long)n * k, &beta, o, m, (long long)n * m, batch);
   return st == CUBLAS_STATUS_SUCCESS ? 0 : -(int)st - 100;
+}
+
+// linear_kernels.cu:229-327 — the three products of Linear's backward, all with alpha = beta = 1 (the
+// gradients ACCUMULATE), column-major views of the row-major tensors:
+//   dW[out][in] += dY[batch][out]^T X[batch][in]     cublasGemmEx(OP_N, OP_T, in, out, batch, X, in, dY, out, dW, in)
+//   db[out]     += 1^T dY                            cublasGemmEx(OP_N, OP_T, 1, out, batch, ones, 1, dY, out, db, 1)
+//   dX[batch][in] += dY W[out][in]                   cublasGemmEx(OP_N, OP_N, in, batch, out, W, in, dY, out, dX, in)
+// dtype as in ref_linear_forward_gemm. `ones` has `batch` elements OF THE DATA TYPE: the reference
+// passes its fp32 one_ptr with CUDA_R_32F beside 16-bit dY, a combination cublasGemmEx rejects
+// (CUBLAS_STATUS_NOT_SUPPORTED) — the ledger's deviation for 16-bit bias gradients.
+REF_API int ref_linear_backward_gemm(void *stream, void const *x, void *dx, void const *dy, void const *w, void *dw,
+                                     void *db, void const *ones, int in_dim, int out_dim, int batch, int dtype) {
+  cublasSetStream(blas(), S(stream));
+  cudaDataType_t t = dtype == 0 ? CUDA_R_32F : dtype == 1 ? CUDA_R_16F : CUDA_R_16BF;
+  cublasComputeType_t ct = dtype == 1 ? CUBLAS_COMPUTE_16F : CUBLAS_COMPUTE_32F;
+  __half const h1 = __float2half(1.f);
+  float const f1 = 1.f;
+  void const *one = dtype == 1 ? static_cast<void const *>(&h1) : static_cast<void const *>(&f1);
+  cublasStatus_t st = cublasGemmEx(blas(), CUBLAS_OP_N, CUBLAS_OP_T, in_dim, out_dim, batch, one, x, t, in_dim, dy, t,
+                                   out_dim, one, dw, t, in_dim, ct, CUBLAS_GEMM_DEFAULT_TENSOR_OP);
+  if (st != CUBLAS_STATUS_SUCCESS) return -(int)st - 100;
+  if (db != nullptr) {
+    st = cublasGemmEx(blas(), CUBLAS_OP_N, CUBLAS_OP_T, 1, out_dim, batch, one, ones, t, 1, dy, t, out_dim, one, db, t,
+                      1, ct, CUBLAS_GEMM_DEFAULT_TENSOR_OP);
+    if (st != CUBLAS_STATUS_SUCCESS) return -(int)st - 200;
+  }
+  if (dx != nullptr) {
+    st = cublasGemmEx(blas(), CUBLAS_OP_N, CUBLAS_OP_N, in_dim, batch, out_dim, one, w, t, in_dim, dy, t, out_dim, one,
+                      dx, t, in_dim, ct, CUBLAS_GEMM_DEFAULT_TENSOR_OP);
+    if (st != CUBLAS_STATUS_SUCCESS) return -(int)st - 300;
+  }
+  return 0;
+}
+// batch_matmul_kernels.cu:85-139: dA[b] (n x k) += dO[b] (n x m) B[b]^T (m x k), dB[b] (k x m) += A[b]^T dO[b],
+// both cublasSgemmStridedBatched with alpha = beta = 1
+REF_API int ref_batch_matmul_backward(void *stream, float const *o_grad, float const *a, float *a_grad, float const *b,
+                                      float *b_grad, int m, int n, int k, int batch) {
+  cublasSetStream(blas(), S(stream));
+  float alpha = 1.f;
+  long long const a_stride = (long long)n * k, b_stride = (long long)m * k, o_stride = (long long)n * m;
+  cublasStatus_t st = cublasSgemmStridedBatched(blas(), CUBLAS_OP_T, CUBLAS_OP_N, k, n, m, &alpha, b, m, b_stride, o_grad,
+                                                m, o_stride, &alpha, a_grad, k, a_stride, batch);
+  if (st != CUBLAS_STATUS_SUCCESS) return -(int)st - 100;
+  st = cublasSgemmStridedBatched(blas(), CUBLAS_OP_N, CUBLAS_OP_T, m, k, n, &alpha, o_grad, m, o_stride, a, k, a_stride,
+                                 &alpha, b_grad, m, b_stride, batch);
+  return st == CUBLAS_STATUS_SUCCESS ? 0 : -(int)st - 200;
 }

@@ -57,8 +57,11 @@ def inputs():
     I["metrics"] = dict(logits=u(24, 32, 10, lo=0.0), labels=mlab, dense=np.eye(10, dtype=np.float32)[mlab])
     I["topk"] = dict(x=u(26, 4, 50), k=5, dout=u(27, 4, 5))
     I["replicas"] = dict(x=u(28, 5, 100), n=100, reps=5)
-    I["linear"] = dict(x=u(29, 64, 40), w=u(30, 48, 40) / np.sqrt(40).astype(np.float32))
-    I["bmm"] = dict(a=u(31, 10, 10, 5), b=u(32, 10, 5, 10), m=10, n=10, k=5, batch=10)   # test_batch_matmul_kernel.cc
+    I["linear"] = dict(x=u(29, 64, 40), w=u(30, 48, 40) / np.sqrt(40).astype(np.float32),
+                       # backward: the gradients start non-zero (the reference accumulates with beta = 1)
+                       dy=u(33, 64, 48), dx0=u(34, 64, 40) * 0.5, dw0=u(35, 48, 40) * 0.5, db0=u(36, 48) * 0.5)
+    I["bmm"] = dict(a=u(31, 10, 10, 5), b=u(32, 10, 5, 10), m=10, n=10, k=5, batch=10,   # test_batch_matmul_kernel.cc
+                    do=u(37, 10, 10, 10), da0=u(38, 10, 10, 5) * 0.5, db0=u(39, 10, 5, 10) * 0.5)
     return I
 
 
@@ -201,10 +204,18 @@ def run_ref(lib, torch):
         y = z(64, 48, dt=dt)
         call("ref_linear_forward_gemm", st, P(x), P(w), P(y), 40, 48, 64, code)
         O[f"linear_{name}_y"] = y.float().cpu().numpy()
+        dy, dx, dw, db = dev(c["dy"], dt), dev(c["dx0"], dt), dev(c["dw0"], dt), dev(c["db0"], dt)
+        ones = torch.ones(64, dtype=dt, device="cuda")
+        call("ref_linear_backward_gemm", st, P(x), P(dx), P(dy), P(w), P(dw), P(db), P(ones), 40, 48, 64, code)
+        O[f"linear_{name}_dx"], O[f"linear_{name}_dw"], O[f"linear_{name}_db"] = (
+            dx.float().cpu().numpy(), dw.float().cpu().numpy(), db.float().cpu().numpy())
     c = I["bmm"]
     o, ba, bb = z(10, 10, 10), dev(c["a"]), dev(c["b"])
     call("ref_batch_matmul_forward", st, P(o), P(ba), P(bb), 10, 10, 5, 10)
     O["bmm_o"] = o.cpu().numpy()
+    do, da, db = dev(c["do"]), dev(c["da0"]), dev(c["db0"])
+    call("ref_batch_matmul_backward", st, P(do), P(ba), P(da), P(bb), P(db), 10, 10, 5, 10)
+    O["bmm_da"], O["bmm_db"] = da.cpu().numpy(), db.cpu().numpy()
     return O
 
 
@@ -314,10 +325,17 @@ def run_oracle(o):
         y = z(64, 48)
         o.linear_forward(np.ascontiguousarray(x), np.ascontiguousarray(w), None, y, 40, 48, 64, -1)
         O[f"linear_{name}_y"] = y
+        rnd = (lambda a: a.astype(np.float16).astype(np.float32)) if dt is np.float16 else _bf16 if dt is None else (lambda a: a)
+        dy, dx, dw, db = (np.ascontiguousarray(rnd(c[k])).copy() for k in ("dy", "dx0", "dw0", "db0"))
+        o.linear_backward(np.ascontiguousarray(x), dx, y, dy, np.ascontiguousarray(w), dw, db, 40, 48, 64, -1, 0.0, None)
+        O[f"linear_{name}_dx"], O[f"linear_{name}_dw"], O[f"linear_{name}_db"] = dx, dw, db
     c = I["bmm"]
     out = z(10, 10, 10)
     o.batch_matmul_forward(out, c["a"], c["b"], 10, 10, 5, 10, -1, -1, -1)
     O["bmm_o"] = out
+    da, db = c["da0"].copy(), c["db0"].copy()
+    o.batch_matmul_backward(c["do"], c["a"], da, c["b"], db, 10, 10, 5, 10)
+    O["bmm_da"], O["bmm_db"] = da, db
     return O
 
 
@@ -449,10 +467,18 @@ def run_ffk(K, torch):
         y = z(64, 48, dt=dt)
         K.Linear.forward_kernel(None, lin, x, y, w, None, 40, 48, 64)
         O[f"linear_{name}_y"] = y.float().cpu().numpy()
+        linb = K.Linear.init_kernel(K.ACT_NONE, 0.0, True, K.GEMM_AUTO, out_dim=48)
+        dy, dx, dw, db = dev(c["dy"], dt), dev(c["dx0"], dt), dev(c["dw0"], dt), dev(c["db0"], dt)
+        K.Linear.backward_kernel(None, linb, x, dx, y, dy, w, dw, db, 40, 48, 64)
+        O[f"linear_{name}_dx"], O[f"linear_{name}_dw"], O[f"linear_{name}_db"] = (
+            dx.float().cpu().numpy(), dw.float().cpu().numpy(), db.float().cpu().numpy())
     c = I["bmm"]
     o = z(10, 10, 10)
     K.BatchMatmul.forward_kernel(None, o, dev(c["a"]), dev(c["b"]), 10, 10, 5, 10)
     O["bmm_o"] = o.cpu().numpy()
+    da, db = dev(c["da0"]), dev(c["db0"])
+    K.BatchMatmul.backward_kernel(None, o, dev(c["do"]), dev(c["a"]), da, dev(c["b"]), db, 10, 10, 5, 10)
+    O["bmm_da"], O["bmm_db"] = da.cpu().numpy(), db.cpu().numpy()
     torch.cuda.synchronize()
     return O
 
@@ -462,6 +488,7 @@ EXACT = ("emb_none_", "gather_i32_out", "gather_i64_out", "transpose_out", "cast
          "topk_values", "loss_identity")
 # fp16 with CUBLAS_COMPUTE_16F (the reference's choice) accumulates in half: compare at half resolution
 RTOL = {"linear_f16_y": 2e-2, "linear_bf16_y": 2e-2, "unary_POW_y": 1e-5, "unary_POW_dx": 1e-5}
+RTOL.update({f"linear_{t}_{g}": 2e-2 for t in ("f16", "bf16") for g in ("dx", "dw", "db")})
 
 
 def compare(name, got, ref):

@@ -5,7 +5,8 @@ writes gpurun_out/ref_kernels.npz. Run on the GPU box:
 
     gpurun -- python tools/make_ref_golden.py
 
-then copy the file to tests/golden/ref_kernels.npz and commit it. /root/reference is not read at
+then copy the file to tests/golden/ref_kernels.npz and commit it (`--merge` keeps the arrays that
+are already committed and only adds new cases). /root/reference is not read at
 run time: the .so travels with the snapshot."""
 import ctypes
 import sys
@@ -22,6 +23,12 @@ import ref_cases  # noqa: E402
 def main():
     lib = ctypes.CDLL(str(ref_cases.REF_SO))
     out = ref_cases.run_ref(lib, torch)
+    if "--merge" in sys.argv:
+        # cases added later: arrays already committed stay byte for byte, only new names are added
+        old = dict(np.load(ROOT / "tests" / "golden" / "ref_kernels.npz"))
+        added = sorted(set(out) - set(old))
+        out = {**out, **old}
+        print(f"merge: kept {len(old)} committed arrays, added {added}")
     dest = ROOT / "gpurun_out" / "ref_kernels.npz"
     dest.parent.mkdir(exist_ok=True)
     np.savez_compressed(dest, **out)
