@@ -212,3 +212,32 @@ def test_oracle_against_the_reference_tests_exact_vectors(oracle, case):
     else:
         oracle.sum_replicas(dst, src, n, case["reps"], case["accumulate"])
     assert (dst == np.float32(case["expect_fill"])).all()
+
+
+# ---------------------------------------------------------------------------------------------
+# tests/golden/cudnn_conv.npz: Conv2D through the cuDNN calls of conv_2d_kernels.cu:276-388
+# (forward + bias + ReLU; ReLU gradient in place on dY; filter / bias / data gradients with
+# beta = 1) on four geometries incl. groups, recorded on a B200 by oracle/cudnn_ref/conv_golden.cu
+# with CUDNN_FMA_MATH and fixed algorithms (see the header of that file).
+CONV_CASES = ["conv_a", "conv_b", "conv_c", "conv_d"]
+
+
+@pytest.fixture(scope="module")
+def GC():
+    return np.load(GOLD / "cudnn_conv.npz")
+
+
+@pytest.mark.parametrize("name", CONV_CASES)
+def test_oracle_conv2d_vs_cudnn(oracle, GC, name):
+    geo = [int(v) for v in GC[name + "_geo"]]
+    relu = geo.pop()
+    x, w, b = (np.ascontiguousarray(GC[f"{name}_{k}"]) for k in ("x", "w", "b"))
+    y = np.zeros_like(GC[name + "_y"])
+    oracle.conv2d_forward(geo, x, y, w, b, relu)
+    near(y, GC[name + "_y"], rtol=1e-5, atol=1e-5)
+    dy, dx, dw, db = (np.array(GC[f"{name}_{k}"], copy=True) for k in ("dy", "dx0", "dw0", "db0"))
+    oracle.conv2d_backward(geo, x, dx, np.ascontiguousarray(GC[name + "_y"]), dy, w, dw, db, relu)
+    near(dy, GC[name + "_dy_after"], rtol=0, atol=0)          # the ReLU gradient is applied to dY in place
+    near(dw, GC[name + "_dw"], rtol=1e-4, atol=1e-4)
+    near(db, GC[name + "_db"], rtol=1e-4, atol=1e-4)
+    near(dx, GC[name + "_dx"], rtol=1e-4, atol=1e-5)

@@ -95,6 +95,25 @@ def test_pool2d(K, G, name, ptype):
     near(dx, G[name + "_dx"], atol=1e-5)
 
 
+@pytest.mark.parametrize("name", ["conv_a", "conv_b", "conv_c", "conv_d"])
+def test_conv2d(K, name):
+    """Conv2D against the cuDNN calls of conv_2d_kernels.cu:276-388 (tests/golden/cudnn_conv.npz,
+    oracle/cudnn_ref/conv_golden.cu): forward + bias + ReLU, gradients accumulating onto dX / dW / db."""
+    GC = np.load(GOLD / "cudnn_conv.npz")
+    n, ci, ih, iw, co, oh, ow, k, _, p, _, s, _, g, relu = (int(v) for v in GC[name + "_geo"])
+    x, w, b = dev(GC[name + "_x"]), dev(GC[name + "_w"]), dev(GC[name + "_b"])
+    m = K.Conv2D.init_kernel(K.ACT_RELU if relu else None, k, k, g, p, p, s, s, (n, ci, ih, iw), (n, co, oh, ow))
+    y = torch.zeros(n, co, oh, ow, device="cuda")
+    K.Conv2D.forward_kernel(None, m, x, y, w, b)
+    near(y, GC[name + "_y"], rtol=1e-4, atol=1e-5)
+    dy, dx, dw, db = dev(GC[name + "_dy"]), dev(GC[name + "_dx0"]), dev(GC[name + "_dw0"]), dev(GC[name + "_db0"])
+    K.Conv2D.backward_kernel(None, m, x, dx, dev(GC[name + "_y"]), dy, w, dw, db)
+    near(dw, GC[name + "_dw"], rtol=1e-4, atol=1e-4)
+    near(db, GC[name + "_db"], rtol=1e-4, atol=1e-4)
+    near(dx, GC[name + "_dx"], rtol=1e-4, atol=1e-4)
+    near(dy, GC[name + "_dy_after"], rtol=0, atol=0)   # the ReLU gradient is applied to dY in place
+
+
 import json
 
 
