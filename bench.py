@@ -592,7 +592,10 @@ def per_op_table(torch, Kmod, device, iters=10):
     mk_w = lambda: (r(M, N).to(bf), r(M, KDIM).to(bf), torch.zeros(N, KDIM, dtype=bf, device=device))
     timed("Linear wgrad (TN, beta=1)", "tensor", flop, 2 * M * N * 2 + N * KDIM * 2, mk_w,
           lambda s: K.Gemm.run(s[0], s[1], s[2], N, KDIM, M, a_mn=True, b_mn=True, accumulate=True,
-                               path=K.GEMM_TENSOR))
+                               path=K.GEMM_TENSOR),
+          note="256 tiles = 3.46 waves of 74 CTA pairs: with scratch registered the 34 tiles of the last wave are cut "
+               "along K in two (DESIGN 3.1); the rest of the gap to the forward product is the power cap — filling "
+               "idle pairs lowers the clock of the busy ones (profiles/r02_kcut_timing.txt)")
     mk_b = lambda: (r(M, KDIM).to(bf), torch.zeros(M, KDIM, dtype=bf, device=device), r(M, N).relu().to(bf),
                     r(M, N).to(bf), torch.zeros(N, KDIM, dtype=bf, device=device), torch.zeros(N, dtype=bf, device=device))
     timed("Linear bwd (ReLU grad + wgrad + bias grad + dgrad)", "tensor", 2 * flop, 4 * M * N * 2 + N * KDIM * 2, mk_b,
@@ -636,7 +639,9 @@ def per_op_table(torch, Kmod, device, iters=10):
                     torch.empty(EBATCH, EDIM, device=device))
     timed("Embedding fwd 1Mx256 fp32, 65536 i64 indices", "hbm", EBATCH * (8 + 2 * EDIM * 4),
           EBATCH * (8 + 2 * EDIM * 4), mk_e,
-          lambda s: K.Embedding.forward_kernel(None, s[0], s[1], table, K.AGGR_NONE, 1, EDIM, EBATCH))
+          lambda s: K.Embedding.forward_kernel(None, s[0], s[1], table, K.AGGR_NONE, 1, EDIM, EBATCH),
+          note="random 1 KB rows of a 1 GB table: every row is a DRAM page miss; 4 rows in flight per thread "
+               "(ncu: profiles/r02_perop_full_subset.csv)")
     dtable = table.zero_()
     mk_eb = lambda: (torch.randint(0, ENTRIES, (EBATCH,), device=device, generator=g, dtype=torch.int64),
                      r(EBATCH, EDIM))
@@ -652,11 +657,15 @@ def per_op_table(torch, Kmod, device, iters=10):
     gb, bb = (r(D) + 1).to(bf), r(D).to(bf)
     lnb = K.LayerNorm.init_kernel(True, TOK, D, 1e-5, device=device)
     timed("LayerNorm fwd 32768x1024 bf16", "hbm", 2 * TOK * D * 2, 2 * TOK * D * 2, mk2b,
-          lambda s: K.LayerNorm.forward_kernel(None, lnb, s[0], s[1], gb, bb))
+          lambda s: K.LayerNorm.forward_kernel(None, lnb, s[0], s[1], gb, bb),
+          note="2 KB rows, one warp per row: 30 us launches are latency-bound (two dependent reductions per row, "
+               "next row prefetched); ncu in profiles/r02_perop_full_subset.csv")
     dpo = K.Dropout.init_kernel(0.1, 12345, TOK * 4096, device=device)
     mk_dp = lambda: (r(TOK, 4096).to(bf), torch.empty(TOK, 4096, dtype=bf, device=device))
     timed("Dropout fwd 32768x4096 bf16", "hbm", 2 * TOK * 4096 * 2 + TOK * 4096 // 8, 2 * TOK * 4096 * 2, mk_dp,
-          lambda s: K.Dropout.forward_kernel(None, dpo, s[0], s[1]))
+          lambda s: K.Dropout.forward_kernel(None, dpo, s[0], s[1]),
+          note="ALU-bound, not HBM-bound: Philox4x32-10 per 8 elements, 61 % SM throughput under ncu "
+               "(profiles/r02_perop_full_subset.csv); the fused encoder step runs dropout in the GEMM epilogue instead")
     torch.cuda.synchronize()
     return {"peaks": {"bf16_tflops_burst": burst, "hbm_gbs": hbm, "source": src},
             "l2": "each op rotates through buffer sets of more than 2 x 126 MB in total", "iters": iters, "rows": rows}
