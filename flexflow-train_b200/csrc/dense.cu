@@ -210,6 +210,8 @@ int ffk_set_gemm_workspace(void *workspace, size_t workspace_bytes) {
 
 int ffk_set_gemm_fp32_tensor_math(int allow) { return gemm::set_fp32_tensor_math(allow); }
 
+int ffk_set_gemm_kcut(int enable) { return gemm::set_kcut(enable); }
+
 int ffk_gemm_kcut_plan(int M, int N, int K, int pairs, int *plan5) {
   return gemm::kcut_plan(M, N, K, pairs, plan5);
 }

@@ -1569,6 +1569,7 @@ struct Scratch {
   void *ptr = nullptr;
   size_t bytes = 0;
   int fp32_tensor_math = 0;      // ffk_set_gemm_fp32_tensor_math: AUTO may split fp32 into bf16 terms
+  int kcut_off = 0;              // ffk_set_gemm_kcut(0): whole tiles only on this device
   cudaStream_t last_stream = nullptr;
   bool used = false;             // last_stream is meaningful
   bool last_captured = false;    // the last use was recorded into a CUDA graph
@@ -1658,6 +1659,17 @@ int set_workspace(void *ptr, size_t bytes) {
   return FFK_OK;
 }
 
+int set_kcut(int enable) {
+  std::lock_guard<std::mutex> lock(g_scratch_mu);
+  Scratch *sc = scratch_slot();
+  if (!sc) {
+    set_error("gemm K-cut switch: no current CUDA device");
+    return FFK_ERR_CUDA;
+  }
+  sc->kcut_off = enable ? 0 : 1;
+  return FFK_OK;
+}
+
 int set_fp32_tensor_math(int allow) {
   std::lock_guard<std::mutex> lock(g_scratch_mu);
   Scratch *sc = scratch_slot();
@@ -1721,7 +1733,8 @@ bool sk_begin(Problem const &p, bool extras, long long tiles, int pairs, cudaStr
   size_t const need = SK_FLAG_BYTES + size_t(pairs) * SK_SLOT_BYTES;   // never more slots than pairs
   g_scratch_mu.lock();
   Scratch *sc = scratch_slot();
-  if (!sc || !sc->ptr || !aligned16(sc->ptr) || sc->bytes < need || scratch_acquire(*sc, stream) != FFK_OK ||
+  if (!sc || sc->kcut_off || !sc->ptr || !aligned16(sc->ptr) || sc->bytes < need ||
+      scratch_acquire(*sc, stream) != FFK_OK ||
       cudaMemsetAsync(sc->ptr, 0, size_t(pairs) * SK_POSITIONS * sizeof(uint32_t), stream) != cudaSuccess) {
     cudaGetLastError();
     g_scratch_mu.unlock();

@@ -107,6 +107,8 @@ int launch_split_bf16_registered(Problem const &p, Epilogue const &e, cudaStream
 // helper pair}; kcut_segments lists pair `pair`'s work as (tile, first k-block, end k-block,
 // role, slot, count) and returns the number of segments.
 int kcut_plan(int M, int N, int K, int pairs, int *plan5);
+// Per-device switch of the K-cut schedule (on by default; needs registered scratch to act).
+int set_kcut(int enable);
 int kcut_segments(int M, int N, int K, int pairs, int pair, int *six, int max_segments);
 
 // Picks the tensor path for 16-bit inputs when eligible; large fp32 products take the

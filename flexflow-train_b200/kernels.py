@@ -93,6 +93,11 @@ def set_gemm_workspace(nbytes_or_tensor, fp32_tensor_math=False):
     return t
 
 
+def set_gemm_kcut(enable: bool):
+    """ffk_set_gemm_kcut: the K-cut schedule of 16-bit products on the CURRENT device (default on)."""
+    _call("ffk_set_gemm_kcut", 1 if enable else 0)
+
+
 class Gemm:
     @staticmethod
     def run(a, b, d, M, N, K, batch=1, a_mn=False, b_mn=False, alpha=1.0, accumulate=False,

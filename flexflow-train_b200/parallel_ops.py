@@ -18,6 +18,7 @@ exercise the rank arithmetic over gloo.
 """
 from __future__ import annotations
 
+import os
 from typing import List, Optional, Sequence
 
 import torch
@@ -265,6 +266,13 @@ class PeerGradSync:
         self.done = torch.cuda.Event()
         self.launches = 0
         self.summed_grads = [self.summed(g) for g in model.grads]
+        # The K-cut GEMM schedule waits on CTAs of its own grid, and so does the two-shot collective that
+        # now runs beside the backward GEMMs. The side stream's priority orders the two (DESIGN 3.1,
+        # "Residency"), but that pairing has not been measured on a multi-GPU box yet: whole tiles while
+        # this object lives. FFK_PEER_SYNC_KEEP_KCUT=1 keeps the cut schedule on.
+        self._kcut_off = os.environ.get("FFK_PEER_SYNC_KEEP_KCUT") is None
+        if self._kcut_off:
+            self.peer.K.set_gemm_kcut(False)
         self.begin()
 
     def begin(self):
@@ -312,4 +320,7 @@ class PeerGradSync:
         self.peer.check()
 
     def close(self):
+        if self._kcut_off:
+            self.peer.K.set_gemm_kcut(True)
+            self._kcut_off = False
         self.peer.close()

@@ -51,6 +51,11 @@ int ffk_set_gemm_fp32_tensor_math(int allow);
  *                             tile, 1 = partial parked in `slot`, 2 = owner adding `count`
  *                             partials from `slot` on; returns the segment count. */
 int ffk_gemm_kcut_plan(int M, int N, int K, int pairs, int *plan5);
+/* Per-device switch of the K-cut schedule for the CURRENT device (default on; it acts only with
+ * registered scratch). Off = whole tiles only — for callers that run kernels which wait on their
+ * own grid's CTAs beside 16-bit products at equal stream priority ("Residency").
+ * No reference counterpart (cuBLAS exposes no such switch; linear_kernels.cu:127-149). */
+int ffk_set_gemm_kcut(int enable);
 int ffk_gemm_kcut_segments(int M, int N, int K, int pairs, int pair, int *six, int max_segments);
 
 /* General strided-batched product, the building block under Linear / BatchMatmul / MHA:

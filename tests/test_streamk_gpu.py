@@ -74,6 +74,31 @@ def test_k_cut_gemm_every_layout_ragged(K, a_mn, b_mn, out_dtype, shape):
     assert_close(cut1, whole.float().cpu().numpy(), rtol=rtol, what="k-cut vs whole tiles")
 
 
+def test_k_cut_switch_restores_whole_tiles(K, scratch):
+    """ffk_set_gemm_kcut(0): with scratch registered the product must run whole tiles again, i.e.
+    give the bits of the launch without scratch; switching it back on gives the cut result."""
+    M, N, Kd = 768, 768, 8192
+    a, b, _, _ = _operands(M, N, Kd, True, True, torch.bfloat16, 21)
+
+    def run():
+        d = torch.zeros(M, N, dtype=torch.float32, device="cuda")
+        K.Gemm.run(a, b, d, M, N, Kd, a_mn=True, b_mn=True, path=K.GEMM_TENSOR)
+        return d
+
+    cut = run()
+    K.set_gemm_kcut(False)
+    try:
+        off = run()
+    finally:
+        K.set_gemm_kcut(True)
+    again = run()
+    K.set_gemm_workspace(None)
+    whole = run()
+    assert torch.equal(off, whole), "switch off: not the whole-tile result"
+    assert torch.equal(cut, again), "switch back on: not the cut result"
+    assert_close(cut, whole.cpu().numpy(), rtol=1e-4, what="cut vs whole, fp32 output")
+
+
 SHAPES = [  # M, N, K, a_mn, b_mn, what
     (4096, 4096, 8192, True, True, "configs[1] wgrad: 256 tiles, 3.46 waves"),
     (4096, 1024, 32768, True, True, "encoder wgrad: 64 tiles on 74 pairs, left whole (13.5 % idle: measured slower cut)"),
