@@ -244,3 +244,114 @@ def test_gemm_k_cut_schedule_covers_every_k_block_once(ffk):
     assert _kcut(ffk, 4096, 4096, 8192, 74)[:2] == (1, (222, 34, 2, 64, 0))      # configs[1] weight gradient: 3.46 waves
     assert _kcut(ffk, 768, 768, 32768, 74)[:2] == (1, (0, 9, 8, 64, 0))          # BERT-base weight gradient: 9 tiles
     assert _kcut(ffk, 8192, 4096, 4096, 74)[0] == 0                              # 512 tiles = 6.92 waves
+
+
+def test_peer_grad_sync_slices_tile_every_bucket_once(ffk, monkeypatch):
+    """PeerGradSync's bookkeeping (host logic of the N > 1 path) with the device taken away: a
+    stand-in peer group records the collectives. Over one backward pass (layers in reverse) plus
+    finish(), the slices sent for each bucket must tile [0, bucket) exactly once, from the tail
+    down, on 16-byte boundaries, each at least min_bytes long except the remainder; `summed(g)` is
+    the view of the sum region at g's offset; the K-cut GEMM schedule is off while the object lives."""
+    import torch
+
+    P = importlib.import_module("flexflow_train_b200.parallel_ops")
+    calls, switches = [], []
+
+    class FakeK:
+        @staticmethod
+        def set_gemm_kcut(on):
+            switches.append(bool(on))
+
+    class FakePeer:
+        K = FakeK
+
+        def __init__(self, nbytes, group=None):
+            self.world, self.rank = 2, 0
+            self.nbytes = (int(nbytes) + 255) // 256 * 256
+            self.bytes = torch.zeros(self.nbytes, dtype=torch.uint8)
+
+        def tensor(self, off, shape, dtype):
+            n = 1
+            for s in shape:
+                n *= s
+            nb = n * torch.empty(0, dtype=dtype).element_size()
+            assert off % 16 == 0 and off + nb <= self.nbytes
+            return self.bytes[off:off + nb].view(dtype).view(tuple(shape))
+
+        def all_reduce_sum(self, in_off, out_off, count, dtype, stream=None, background_blocks=0):
+            calls.append((in_off, out_off, count, dtype))
+
+        def check(self):
+            pass
+
+        def close(self):
+            pass
+
+    class Dummy:
+        def __init__(self, *a, **k):
+            pass
+
+        def record(self, *a):
+            pass
+
+        def wait_event(self, *a):
+            pass
+
+    monkeypatch.setattr(P, "PeerMemoryGroup", FakePeer)
+    monkeypatch.setattr(torch.cuda, "Stream", Dummy)
+    monkeypatch.setattr(torch.cuda, "Event", Dummy)
+    monkeypatch.setattr(torch.cuda, "current_stream", lambda *a: Dummy())
+
+    class Layer:
+        def __init__(self, grads):
+            self.grads = grads
+
+    class Model:
+        """Two buckets (bf16 weights, fp32 norms), gradients laid out layer by layer like training.Model."""
+
+        def __init__(self):
+            sizes16 = [4096 * 300, 1000, 4096 * 300, 7, 4096 * 500]
+            sizes32 = [1024, 1024, 3, 1024]
+            self.spec = [(torch.bfloat16, sizes16), (torch.float32, sizes32)]
+            self.layers = [Layer([]) for _ in range(5)]
+            self._lay([torch.zeros(sum((n + 7) // 8 * 8 for n in sizes16), dtype=torch.bfloat16),
+                       torch.zeros(sum((n + 3) // 4 * 4 for n in sizes32), dtype=torch.float32)])
+
+        def _lay(self, flats):
+            self.grad_buckets = flats
+            for l in self.layers:
+                l.grads = []
+            for flat, (dt, sizes) in zip(flats, self.spec):
+                align, off = 16 // flat.element_size(), 0
+                for i, n in enumerate(sizes):
+                    self.layers[i % len(self.layers)].grads.append(flat[off:off + n])
+                    off += (n + align - 1) // align * align
+            self.grads = [g for l in self.layers for g in l.grads]
+
+        def rehome_gradients(self, flats):
+            self._lay(flats)
+
+    model = Model()
+    min_bytes = 1 << 20
+    sync = P.PeerGradSync(model, min_bytes=min_bytes, background_blocks=0)
+    assert switches == [False]
+    for step in range(2):                       # the bookkeeping must reset for the next step
+        calls.clear()
+        for l in reversed(model.layers):
+            sync.after_layer(l)
+        sync.finish()
+        for bi, (goff, soff, dt, es, numel) in enumerate(sync.slots):
+            mine = [(i - goff, o - soff, c) for (i, o, c, d) in calls if d == dt]
+            assert mine and all(i == o and i % 16 == 0 for i, o, _ in mine)
+            spans = [(i, i + c * es) for i, _, c in mine]
+            assert spans[0][1] == numel * es and spans[-1][0] == 0
+            assert all(a[0] == b[1] for a, b in zip(spans, spans[1:])), "slices must follow each other downwards"
+            assert all(hi - lo >= min_bytes for lo, hi in spans[:-1])
+    for g in model.grads:
+        sm = sync.summed(g)
+        bi = next(i for i, f in enumerate(model.grad_buckets)
+                  if f.dtype == g.dtype and f.data_ptr() <= g.data_ptr() < f.data_ptr() + f.numel() * f.element_size())
+        flat, smf = model.grad_buckets[bi], sync.sums[bi]
+        assert sm.shape == g.shape and sm.data_ptr() - smf.data_ptr() == g.data_ptr() - flat.data_ptr()
+    sync.close()
+    assert switches == [False, True]
