@@ -4,6 +4,10 @@
 // instead of cuDNN descriptors they carry the plain numbers the sm_100a kernels need.
 #pragma once
 #include <cstddef>
+#include <cstring>
+#include <stdexcept>
+#include <variant>
+#include <vector>
 #include "runtime.h"
 
 namespace FlexFlow {
@@ -760,6 +764,170 @@ inline void mean_squared_error_avg_loss_backward_kernel(ffStream_t stream, float
 inline void identity_loss_backward_kernel(ffStream_t stream, float *loss_grad_ptr, float const *loss_ptr,
                                           size_t loss_volume, size_t, float scale_factor) {
   FFK_CHECK(ffk_identity_loss_backward(stream, loss_grad_ptr, loss_ptr, loss_volume, scale_factor, FFK_FLOAT));
+}
+
+// ------------------------------------------------------------------ metrics_kernels.h / perf_metrics.h
+// LossFunction (op-attrs/ops/loss_functions) and the metric selection the reference keeps beside it
+// (lib/runtime/src/metrics_functions.h:28-52).
+enum class LossFunction {
+  CATEGORICAL_CROSSENTROPY,
+  SPARSE_CATEGORICAL_CROSSENTROPY,
+  MEAN_SQUARED_ERROR_AVG_REDUCE,
+  MEAN_SQUARED_ERROR_SUM_REDUCE,
+  IDENTITY
+};
+enum class Metric {
+  ACCURACY,
+  CATEGORICAL_CROSSENTROPY,
+  SPARSE_CATEGORICAL_CROSSENTROPY,
+  MEAN_SQUARED_ERROR,
+  ROOT_MEAN_SQUARED_ERROR,
+  MEAN_ABSOLUTE_ERROR,
+};
+class MetricsAttrs {
+public:
+  MetricsAttrs() = delete;
+  MetricsAttrs(LossFunction loss, std::vector<Metric> const &metrics)
+      : loss_type(loss), measure_accuracy(false), measure_categorical_crossentropy(false),
+        measure_sparse_categorical_crossentropy(false), measure_mean_squared_error(false),
+        measure_root_mean_squared_error(false), measure_mean_absolute_error(false) {
+    for (Metric m : metrics) {      // lib/runtime/src/metrics_functions.cc:33-58
+      switch (m) {
+        case Metric::ACCURACY: measure_accuracy = true; break;
+        case Metric::CATEGORICAL_CROSSENTROPY: measure_categorical_crossentropy = true; break;
+        case Metric::SPARSE_CATEGORICAL_CROSSENTROPY: measure_sparse_categorical_crossentropy = true; break;
+        case Metric::MEAN_SQUARED_ERROR: measure_mean_squared_error = true; break;
+        case Metric::ROOT_MEAN_SQUARED_ERROR: measure_root_mean_squared_error = true; break;
+        case Metric::MEAN_ABSOLUTE_ERROR: measure_mean_absolute_error = true; break;
+      }
+    }
+  }
+  LossFunction loss_type;
+  bool measure_accuracy;
+  bool measure_categorical_crossentropy;
+  bool measure_sparse_categorical_crossentropy;
+  bool measure_mean_squared_error;
+  bool measure_root_mean_squared_error;
+  bool measure_mean_absolute_error;
+};
+inline int ffk_metric_flags(MetricsAttrs const &m) {
+  return (m.measure_accuracy ? FFK_METRIC_ACCURACY : 0) | (m.measure_categorical_crossentropy ? FFK_METRIC_CCE : 0) |
+         (m.measure_sparse_categorical_crossentropy ? FFK_METRIC_SPARSE_CCE : 0) |
+         (m.measure_mean_squared_error ? FFK_METRIC_MSE : 0) |
+         (m.measure_root_mean_squared_error ? FFK_METRIC_RMSE : 0) |
+         (m.measure_mean_absolute_error ? FFK_METRIC_MAE : 0);
+}
+// src/perf_metrics.cc:29-68
+inline PerfMetrics update(PerfMetrics const &lhs, PerfMetrics const &rhs) {
+  PerfMetrics out(lhs);
+  auto add = [](std::optional<float> &l, std::optional<float> const &r) {
+    if (l.has_value()) l.value() += r.value_or(0.f);
+  };
+  out.train_all += rhs.train_all;
+  if (out.train_correct.has_value()) out.train_correct.value() += rhs.train_correct.value_or(0);
+  add(out.cce_loss, rhs.cce_loss);
+  add(out.sparse_cce_loss, rhs.sparse_cce_loss);
+  add(out.mse_loss, rhs.mse_loss);
+  add(out.rmse_loss, rhs.rmse_loss);
+  add(out.mae_loss, rhs.mae_loss);
+  out.current_time = rhs.current_time;
+  return out;
+}
+inline PerfMetrics apply_scale(PerfMetrics const &pm, float scale) {
+  PerfMetrics out(pm);
+  for (std::optional<float> *l : {&out.cce_loss, &out.sparse_cce_loss, &out.mse_loss, &out.rmse_loss, &out.mae_loss})
+    if (l->has_value()) l->value() *= scale;
+  return out;
+}
+// The reference's kernels add into a zero-copy (host-mapped) PerfMetrics (metrics_functions.cu:23-137).
+// Here the batch is accumulated in a small device record (one per host thread and device, kept), then
+// read back and added to `perf_zc` — the call returns with `perf_zc` up to date, as a caller that
+// reads its zero-copy record after synchronising would see it.
+namespace detail {
+inline ffk_perf_metrics_t *metrics_scratch() {
+  thread_local ffk_perf_metrics_t *buf[64] = {};
+  int dev = 0;
+  checkCUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) dev = 0;
+  if (!buf[dev]) checkCUDA(cudaMalloc(reinterpret_cast<void **>(&buf[dev]), sizeof(ffk_perf_metrics_t)));
+  return buf[dev];
+}
+inline void metrics_fold(ffStream_t stream, ffk_perf_metrics_t const *dev_rec, PerfMetrics &perf_zc) {
+  ffk_perf_metrics_t h;
+  checkCUDA(cudaMemcpyAsync(&h, dev_rec, sizeof(h), cudaMemcpyDeviceToHost, stream));
+  checkCUDA(cudaStreamSynchronize(stream));
+  perf_zc.train_all += h.train_all;
+  if (perf_zc.train_correct.has_value()) perf_zc.train_correct.value() += h.train_correct;
+  if (perf_zc.cce_loss.has_value()) perf_zc.cce_loss.value() += h.cce_loss;
+  if (perf_zc.sparse_cce_loss.has_value()) perf_zc.sparse_cce_loss.value() += h.sparse_cce_loss;
+  if (perf_zc.mse_loss.has_value()) perf_zc.mse_loss.value() += h.mse_loss;
+  if (perf_zc.rmse_loss.has_value()) perf_zc.rmse_loss.value() += h.rmse_loss;
+  if (perf_zc.mae_loss.has_value()) perf_zc.mae_loss.value() += h.mae_loss;
+}
+}  // namespace detail
+inline void update_metrics_sparse_label_kernel(ffStream_t stream, MetricsAttrs const &metrics, float const *logit_ptr,
+                                               int const *label_ptr, int num_samples, int num_classes,
+                                               PerfMetrics &perf_zc) {
+  ffk_perf_metrics_t *rec = detail::metrics_scratch();
+  checkCUDA(cudaMemsetAsync(rec, 0, sizeof(*rec), stream));
+  FFK_CHECK(ffk_update_metrics_sparse_label(stream, ffk_metric_flags(metrics), logit_ptr, label_ptr, num_samples,
+                                            num_classes, rec));
+  detail::metrics_fold(stream, rec, perf_zc);
+}
+inline void update_metrics_label_kernel(ffStream_t stream, MetricsAttrs const &metrics, float const *logit_ptr,
+                                        float const *label_ptr, int num_samples, int num_classes,
+                                        PerfMetrics &perf_zc) {
+  ffk_perf_metrics_t *rec = detail::metrics_scratch();
+  checkCUDA(cudaMemsetAsync(rec, 0, sizeof(*rec), stream));
+  FFK_CHECK(ffk_update_metrics_label(stream, ffk_metric_flags(metrics), logit_ptr, label_ptr, num_samples,
+                                     num_classes, rec));
+  detail::metrics_fold(stream, rec, perf_zc);
+}
+
+// ------------------------------------------------------------------ initializer_kernels.h, cpu.h
+// zero / constant initialisation (initializer_kernels.h:21-28). The reference has the CPU bodies only
+// (src/cpu/initializer_kernels.cc:1-52; its zero_init_kernel_gpu is NOT_IMPLEMENTED, constant_init_kernel
+// and the three random initialisers are declared and defined nowhere in lib/kernels). The GPU forms here
+// are ffk_fill on the calling thread's stream; the random initialisers are not provided.
+enum class TaskLocation { CPU, GPU };
+struct DataTypeValue {   // op-attrs/datatype_value.dtg.h: one value of any tensor element type
+  std::variant<float, double, int32_t, int64_t, bool> raw;
+  template <typename T> DataTypeValue(T v) : raw(v) {}
+  template <typename T> bool has() const { return std::holds_alternative<T>(raw); }
+  template <typename T> T get() const { return std::get<T>(raw); }
+  double as_double() const {
+    return std::visit([](auto v) { return static_cast<double>(v); }, raw);
+  }
+};
+inline void constant_init_kernel_gpu(GenericTensorAccessorW const &tensor, DataTypeValue value) {
+  ffStream_t stream;
+  checkCUDA(get_legion_stream(&stream));
+  FFK_CHECK(ffk_fill(stream, tensor.ptr, tensor.shape.get_volume(), value.as_double(), ffk_dt(tensor.data_type)));
+  checkCUDA(cudaStreamSynchronize(stream));
+}
+inline void constant_init_kernel_cpu(GenericTensorAccessorW const &tensor, DataTypeValue value) {
+  size_t const n = tensor.shape.get_volume();
+  double const v = value.as_double();
+  switch (tensor.data_type) {
+    case DataType::FLOAT: for (size_t i = 0; i < n; ++i) static_cast<float *>(tensor.ptr)[i] = float(v); break;
+    case DataType::DOUBLE: for (size_t i = 0; i < n; ++i) static_cast<double *>(tensor.ptr)[i] = v; break;
+    case DataType::INT32: for (size_t i = 0; i < n; ++i) static_cast<int32_t *>(tensor.ptr)[i] = int32_t(v); break;
+    case DataType::INT64: for (size_t i = 0; i < n; ++i) static_cast<int64_t *>(tensor.ptr)[i] = int64_t(v); break;
+    case DataType::BOOL: for (size_t i = 0; i < n; ++i) static_cast<bool *>(tensor.ptr)[i] = v != 0.0; break;
+    default: throw std::runtime_error("constant_init_kernel_cpu: 16-bit tensors have no host element type here");
+  }
+}
+inline void constant_init_kernel(TaskLocation const &loc, GenericTensorAccessorW const &tensor, DataTypeValue value) {
+  if (loc == TaskLocation::CPU) constant_init_kernel_cpu(tensor, value);
+  else constant_init_kernel_gpu(tensor, value);
+}
+inline void zero_init_kernel_gpu(GenericTensorAccessorW const &tensor) { constant_init_kernel_gpu(tensor, DataTypeValue(0.f)); }
+inline void zero_init_kernel_cpu(GenericTensorAccessorW const &tensor) {
+  std::memset(tensor.ptr, 0, tensor.shape.get_volume() * size_of_datatype(tensor.data_type));
+}
+inline void zero_init_kernel(TaskLocation const &loc, GenericTensorAccessorW const &tensor) {
+  if (loc == TaskLocation::CPU) zero_init_kernel_cpu(tensor);
+  else zero_init_kernel_gpu(tensor);
 }
 
 // ------------------------------------------------------------------ optimizer_kernels.h
