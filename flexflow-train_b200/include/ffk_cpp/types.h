@@ -58,6 +58,16 @@ using coord_t = long long;
     if ((call) != FFK_OK) { FatalError(std::string("ffk failure: ") + ffk_last_error()); }       \
   } while (0)
 
+// device.h:86,110-114 — the event helpers of profiling_wrapper and the error string
+inline char const *getCudaErrorString(cudaError_t status) { return cudaGetErrorString(status); }
+inline ffError_t ffEventCreate(ffEvent_t *e) { return cudaEventCreate(e); }
+inline ffError_t ffEventDestroy(ffEvent_t &e) { return cudaEventDestroy(e); }
+inline ffError_t ffEventRecord(ffEvent_t &e, ffStream_t stream) { return cudaEventRecord(e, stream); }
+inline ffError_t ffEventSynchronize(ffEvent_t &e) { return cudaEventSynchronize(e); }
+inline ffError_t ffEventElapsedTime(float *elapsed, ffEvent_t &start, ffEvent_t &stop) {
+  return cudaEventElapsedTime(elapsed, start, stop);
+}
+
 inline std::runtime_error mk_runtime_error(std::string const &s) { return std::runtime_error(s); }
 #define NOT_IMPLEMENTED() throw ::FlexFlow::mk_runtime_error("not implemented")
 
@@ -252,6 +262,76 @@ template <typename A> bool shape_and_dtype_matches(A const &a, ArrayShape const 
 }
 inline float *get_float_ptr(GenericTensorAccessorW const &a) { return a.get_float_ptr(); }
 inline float const *get_float_ptr(GenericTensorAccessorR const &a) { return a.get_float_ptr(); }
+// accessor.h:68-167 — the free-function forms: typed pointer of one accessor (throws on a data type
+// mismatch) and of a vector of accessors, per element type
+template <DataType DT> real_type_t<DT> *get(GenericTensorAccessorW const &a) { return a.template get<DT>(); }
+template <DataType DT> real_type_t<DT> const *get(GenericTensorAccessorR const &a) { return a.template get<DT>(); }
+template <DataType DT> std::vector<real_type_t<DT> *> get(std::vector<GenericTensorAccessorW> const &accs) {
+  std::vector<real_type_t<DT> *> out;
+  for (auto const &a : accs) out.push_back(get<DT>(a));
+  return out;
+}
+template <DataType DT> std::vector<real_type_t<DT> const *> get(std::vector<GenericTensorAccessorR> const &accs) {
+  std::vector<real_type_t<DT> const *> out;
+  for (auto const &a : accs) out.push_back(get<DT>(a));
+  return out;
+}
+#define FFK_ACCESSOR_PTRS(name, DT)                                                                               \
+  inline real_type_t<DT> *get_##name##_ptr(GenericTensorAccessorW const &a) { return get<DT>(a); }                  \
+  inline real_type_t<DT> const *get_##name##_ptr(GenericTensorAccessorR const &a) { return get<DT>(a); }            \
+  inline std::vector<real_type_t<DT> *> get_##name##_ptrs(std::vector<GenericTensorAccessorW> const &a) {           \
+    return get<DT>(a);                                                                                              \
+  }                                                                                                                 \
+  inline std::vector<real_type_t<DT> const *> get_##name##_ptrs(std::vector<GenericTensorAccessorR> const &a) {     \
+    return get<DT>(a);                                                                                              \
+  }
+FFK_ACCESSOR_PTRS(int32, DataType::INT32)
+FFK_ACCESSOR_PTRS(int64, DataType::INT64)
+FFK_ACCESSOR_PTRS(double, DataType::DOUBLE)
+FFK_ACCESSOR_PTRS(half, DataType::HALF)
+#undef FFK_ACCESSOR_PTRS
+inline std::vector<float *> get_float_ptrs(std::vector<GenericTensorAccessorW> const &a) { return get<DataType::FLOAT>(a); }
+inline std::vector<float const *> get_float_ptrs(std::vector<GenericTensorAccessorR> const &a) {
+  return get<DataType::FLOAT>(a);
+}
+inline std::pair<ArrayShape, DataType> get_shape_and_datatype(GenericTensorAccessorR const &a) {
+  return {a.shape, a.data_type};
+}
+inline std::pair<ArrayShape, DataType> get_shape_and_datatype(GenericTensorAccessorW const &a) {
+  return {a.shape, a.data_type};
+}
+
+// ---- datatype_dispatch.h:8-88 — run F<DT> (or F<IT, OT>) for data types known at run time
+template <template <DataType> class F, typename... Args>
+auto dispatch(DataType dt, Args &&...args) -> decltype(F<DataType::FLOAT>{}(std::forward<Args>(args)...)) {
+  switch (dt) {
+    case DataType::FLOAT: return F<DataType::FLOAT>{}(std::forward<Args>(args)...);
+    case DataType::DOUBLE: return F<DataType::DOUBLE>{}(std::forward<Args>(args)...);
+    case DataType::INT32: return F<DataType::INT32>{}(std::forward<Args>(args)...);
+    case DataType::INT64: return F<DataType::INT64>{}(std::forward<Args>(args)...);
+    case DataType::BOOL: return F<DataType::BOOL>{}(std::forward<Args>(args)...);
+    default: throw mk_runtime_error(std::string("Unknown datatype ") + format_as(dt));
+  }
+}
+template <template <DataType> class F> struct DataTypeDispatch1 {
+  template <typename... Args>
+  auto operator()(DataType data_type, Args... args) -> decltype(F<DataType::FLOAT>{}(args...)) {
+    return dispatch<F>(data_type, args...);
+  }
+};
+template <template <DataType, DataType> class F> struct DataTypeDispatch2 {
+  template <DataType IT> struct InputType {
+    template <DataType OT> struct OutputType {
+      template <typename... Args> void operator()(Args... args) const { F<IT, OT>{}(args...); }
+    };
+    template <typename... Args> void operator()(DataType output_type, Args... args) const {
+      dispatch<OutputType>(output_type, args...);
+    }
+  };
+  template <typename... Args> void operator()(DataType input_data_type, DataType output_data_type, Args... args) {
+    dispatch<InputType>(input_data_type, output_data_type, args...);
+  }
+};
 
 // ---- attrs consumed by kernels (op-attrs)
 struct L1RegularizerAttrs { float lambda; };

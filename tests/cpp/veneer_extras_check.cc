@@ -21,7 +21,42 @@ void (*const p_const)(TaskLocation const &, GenericTensorAccessorW const &, Data
 void (*const p_const_gpu)(GenericTensorAccessorW const &, DataTypeValue) = &constant_init_kernel_gpu;
 void (*const p_const_cpu)(GenericTensorAccessorW const &, DataTypeValue) = &constant_init_kernel_cpu;
 
+// accessor.h:68-167, datatype_dispatch.h, device.h:110-114
+int32_t *(*const p_i32)(GenericTensorAccessorW const &) = &get_int32_ptr;
+double const *(*const p_f64)(GenericTensorAccessorR const &) = &get_double_ptr;
+std::vector<float *> (*const p_fptrs)(std::vector<GenericTensorAccessorW> const &) = &get_float_ptrs;
+std::vector<int64_t const *> (*const p_i64ptrs)(std::vector<GenericTensorAccessorR> const &) = &get_int64_ptrs;
+std::pair<ArrayShape, DataType> (*const p_sd)(GenericTensorAccessorR const &) = &get_shape_and_datatype;
+ffError_t (*const p_ev)(float *, ffEvent_t &, ffEvent_t &) = &ffEventElapsedTime;
+
+template <DataType DT> struct SizeOf {
+  size_t operator()(size_t n) const { return n * sizeof(real_type_t<DT>); }
+};
+template <DataType IT, DataType OT> struct Widen {
+  void operator()(int *out) const { *out = int(sizeof(real_type_t<OT>)) - int(sizeof(real_type_t<IT>)); }
+};
+
 int host_side_semantics() {
+  if (DataTypeDispatch1<SizeOf>{}(DataType::DOUBLE, size_t(3)) != 24 || dispatch<SizeOf>(DataType::INT32, size_t(2)) != 8) return 10;
+  int widen = 0;
+  DataTypeDispatch2<Widen>{}(DataType::FLOAT, DataType::INT64, &widen);
+  if (widen != 4) return 11;
+  try {
+    DataTypeDispatch1<SizeOf>{}(DataType::HALF, size_t(1));   // not a dispatchable type in the reference either
+    return 12;
+  } catch (std::runtime_error const &) {
+  }
+  {
+    double d[2] = {1.0, 2.0};
+    GenericTensorAccessorW wd{{DataType::DOUBLE, ArrayShape(std::vector<size_t>{2}), d}};
+    if (get<DataType::DOUBLE>(wd) != d || get_double_ptrs(std::vector<GenericTensorAccessorW>{wd, wd}).size() != 2) return 13;
+    if (get_shape_and_datatype(wd).second != DataType::DOUBLE) return 14;
+    try {
+      get_float_ptr(wd);
+      return 15;
+    } catch (std::runtime_error const &) {
+    }
+  }
   // the host-only pieces can be exercised without a device
   MetricsAttrs m(LossFunction::SPARSE_CATEGORICAL_CROSSENTROPY, {Metric::ACCURACY, Metric::SPARSE_CATEGORICAL_CROSSENTROPY});
   if (ffk_metric_flags(m) != (FFK_METRIC_ACCURACY | FFK_METRIC_SPARSE_CCE)) return 1;
