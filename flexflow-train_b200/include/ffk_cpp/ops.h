@@ -473,6 +473,14 @@ inline Pool2DPerDeviceState init_kernel(PerDeviceFFHandle handle, std::optional<
                               kernel_h, kernel_w, stride_h, stride_w, pad_h, pad_w, pool_type,
                               activation == Activation::RELU};
 }
+// pool_2d_kernels.h:49-64 — the in-place form: the state's handle and ReLU flag stay as they are
+inline void init_kernel(Pool2DPerDeviceState *m, int input_w, int input_h, int input_c, int input_n, int output_w,
+                        int output_h, int output_c, int output_n, int pad_h, int pad_w, int kernel_h, int kernel_w,
+                        int stride_h, int stride_w, PoolOp pool_type) {
+  *m = init_kernel(m->handle, m->relu ? std::optional<Activation>(Activation::RELU) : std::nullopt, input_w, input_h,
+                   input_c, input_n, output_w, output_h, output_c, output_n, pad_h, pad_w, kernel_h, kernel_w,
+                   stride_h, stride_w, pool_type);
+}
 inline void forward_kernel(ffStream_t stream, Pool2DPerDeviceState const &m, void const *input_ptr,
                            void *output_ptr) {
   FFK_CHECK(ffk_pool2d_forward(stream, (float const *)input_ptr, (float *)output_ptr, m.n, m.c, m.in_h,
