@@ -58,9 +58,15 @@ typedef enum {
 typedef enum { FFK_ACT_NONE = -1, FFK_ACT_RELU = 0, FFK_ACT_SIGMOID = 1, FFK_ACT_TANH = 2, FFK_ACT_GELU = 3 } ffk_activation_t;
 
 /* ------------------------------------------------------------------ core */
+/* Message of the last failed call on this host thread. The reference prints and aborts instead
+ * (checkCUDA / checkCUDNN / checkCUBLAS, include/kernels/device.h:88-108, src/device.h:31-56); the
+ * C++ veneer restores that behaviour on top of this (FFK_CHECK). */
 char const *ffk_last_error(void);
+/* Version of this C ABI (no reference counterpart: libkernels.so is linked by name,
+ * lib/kernels/CMakeLists.txt:15-19). */
 int ffk_abi_version(void);
-/* Number of SMs of the current device, or a negative status. */
+/* Number of SMs of the current device, or a negative status (the reference sizes its grids with
+ * GET_BLOCKS instead, src/device.h:59-71). */
 int ffk_device_sm_count(void);
 
 #ifdef __cplusplus

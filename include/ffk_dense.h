@@ -126,7 +126,8 @@ int ffk_linear_forward_fused(void *stream, void const *input, void *output, void
                              void const *bias, int in_dim, int out_dim, int batch_size, int dtype,
                              int activation, int path, ffk_linear_forward_fusion_t const *fusion_host);
 
-/* ffk_linear_backward with the operators around it folded in:
+/* ffk_linear_backward (linear_kernels.h:62, linear_kernels.cu:192-323) with the operators around it
+ * folded in (the dropout gradient of dropout_kernels.cu:82-94, the ReLU gradient of the layer before):
  *   accumulate_input_grad   1: dX += (the reference's convention); 0: dX = — the caller knows this
  *                           Linear is the first writer of that gradient, so no zero fill is needed;
  *   dropout_mask / rate     a dropout followed the activation (fused forward above): its gradient
@@ -184,9 +185,11 @@ typedef struct {
  * — verified against cudnnGetMultiHeadAttnWeights on a B200 (tests/golden/mha_*.npz). */
 size_t ffk_mha_weight_bytes(ffk_mha_config_t const *cfg_host, int dtype);
 /* Bytes the forward pass keeps for the backward pass (the role of MHAPerDeviceState::
- * reserveSpace): projected Q/K/V, attention probabilities, concatenated head outputs. */
+ * reserveSpace, sized by cudnnGetMultiHeadAttnBuffers at attention_kernels.cu:127-136): projected
+ * Q/K/V, attention probabilities, concatenated head outputs. */
 size_t ffk_mha_reserve_bytes(ffk_mha_config_t const *cfg_host, int dtype);
-/* Scratch bytes backward needs (the role of PerDeviceFFHandle::workSpace). */
+/* Scratch bytes backward needs (the role of PerDeviceFFHandle::workSpace, include/kernels/ff_handle.h:13-24,
+ * which attention_kernels.cu:292-334 hands to cuDNN). */
 size_t ffk_mha_workspace_bytes(ffk_mha_config_t const *cfg_host, int dtype);
 
 /* MultiHeadAttention::forward_kernel — attention_kernels.h:85, attention_kernels.cu:246-277.

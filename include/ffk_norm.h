@@ -49,7 +49,8 @@ int ffk_layer_norm_backward(void *stream, void const *output_grad, void const *i
                             long long N, int dtype, int accumulate_param_grads, void *workspace,
                             size_t workspace_bytes);
 
-/* ffk_layer_norm_backward with the choice the reference's convention does not offer:
+/* ffk_layer_norm_backward (layer_norm_kernels.h:47, layer_norm_kernels.cu:410-437) with the choice the
+ * reference's convention does not offer:
  * accumulate_input_grad == 0 WRITES input_grad instead of adding to it (one HBM pass less, and no
  * zero fill before it) for callers that know this op is the first writer of that gradient —
  * the step driver's fused-operator execution. 1 = ffk_layer_norm_backward. */

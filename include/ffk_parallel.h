@@ -24,8 +24,10 @@ int ffk_nccl_get_unique_id(void *id_out_host);
 int ffk_nccl_comm_create(void **comm_out, void const *id_host, int num_ranks, int my_rank);
 int ffk_nccl_comm_destroy(void *comm);
 
-/* In-place sum over ranks (ncclAllReduce, ncclSum) of `count` elements: the exchange step of
- * Replicate-backward / Reduction-forward and of the *_nccl_update tasks. FLOAT, HALF, BFLOAT16,
+/* In-place sum over ranks (ncclAllReduce, ncclSum — the call at src/cuda/optimizer_kernel.cu:83-89) of
+ * `count` elements: the exchange step of Replicate-backward / Reduction-forward
+ * (replicate_kernels.cu:66-78, reduction_kernels.cu:67-79 sum stacked replicas on one device) and of
+ * the *_nccl_update tasks. FLOAT, HALF, BFLOAT16,
  * DOUBLE, INT32, INT64. */
 int ffk_all_reduce_sum(void *stream, void *comm, void *buffer, size_t count, int dtype);
 
@@ -44,7 +46,7 @@ int ffk_adam_nccl_update(void *stream, void *comm, float alpha_t, float beta1, f
                          float *master_weight);
 
 /* ---- Sum over ranks through NVLink peer memory (no counterpart in the reference, which only
- * has the NCCL call above). One process per GPU on one node. Each rank creates a region of
+ * has the NCCL call above, src/cuda/optimizer_kernel.cu:83-89; same SUM-without-division contract). One process per GPU on one node. Each rank creates a region of
  * `data_bytes` (device memory, cudaMalloc) and gets a 64-byte handle; the handles of all ranks,
  * concatenated in rank order and shipped by any means, connect the group (cudaIpcOpenMemHandle).
  * Tensors that take part in the collective live inside the region (ffk_p2p_local_buffer). */
@@ -54,7 +56,8 @@ int ffk_p2p_create(void **group_out, int rank, int world, size_t data_bytes,
 int ffk_p2p_connect(void *group, unsigned char const *handles_all /* world * FFK_P2P_HANDLE_BYTES */);
 int ffk_p2p_local_buffer(void *group, void **data_out, size_t *bytes_out);
 
-/* out[i] = sum over ranks of in[i] for `count` elements (FLOAT, HALF, BFLOAT16; fp32
+/* out[i] = sum over ranks of in[i] for `count` elements — what ncclAllReduce(ncclSum) gives the
+ * *_nccl_update tasks (src/cuda/optimizer_kernel.cu:83-89, 191-197) — (FLOAT, HALF, BFLOAT16; fp32
  * accumulation in rank order, so every rank ends with bit-identical results). `in_offset` and
  * `out_offset` are byte offsets into the region, the same on every rank; the two ranges must not
  * overlap; offsets and size are multiples of 16 bytes. Up to 64 KB every rank pushes its input

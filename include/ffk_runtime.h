@@ -19,11 +19,14 @@ int ffk_arena_create(ffk_arena_t **out, size_t slab_bytes);
 int ffk_arena_allocate(ffk_arena_t *arena, size_t bytes, void **out);
 int ffk_arena_deallocate(ffk_arena_t *arena, void *ptr);
 int ffk_arena_destroy(ffk_arena_t *arena);
-/* Bytes handed out and not yet returned / bytes obtained from the driver. */
+/* Bytes handed out and not yet returned / bytes obtained from the driver / driver allocations made so
+ * far (LocalCudaAllocator, src/local_cuda_allocator.cc, makes one per tensor; these counters are how the
+ * tests show the arena does not). */
 size_t ffk_arena_bytes_in_use(ffk_arena_t const *arena);
 size_t ffk_arena_bytes_reserved(ffk_arena_t const *arena);
 /* Number of driver allocations (cudaMalloc calls) made so far — what the cost estimator and
- * the tests use to show that steady state is allocation-free. */
+ * the tests use to show that steady state is allocation-free (src/local_cuda_allocator.cc allocates
+ * per tensor). */
 size_t ffk_arena_driver_allocations(ffk_arena_t const *arena);
 
 /* The data members of PerDeviceFFHandle (include/kernels/ff_handle.h:13-24) that the kernels
@@ -55,7 +58,8 @@ int ffk_timer_create(ffk_timer_t **out);
 int ffk_timer_begin(ffk_timer_t *timer, void *stream);
 int ffk_timer_end(ffk_timer_t *timer, void *stream, float *elapsed_ms);
 int ffk_timer_destroy(ffk_timer_t *timer);
-/* Profiling hook in the spirit of profiling_wrapper, at the granularity of ONE kernel: the next
+/* Profiling hook in the spirit of profiling_wrapper (include/kernels/profiling.h:24-49), at the
+ * granularity of ONE kernel: the next
  * launch of the CTA-pair tcgen05 GEMM issued by the calling host thread (inside whatever entry
  * point issues it — Linear, MultiHeadAttention, ...) records the timer's start event in front of
  * the kernel and its stop event behind it, on the kernel's own stream. ffk_timer_read waits for
