@@ -3,6 +3,7 @@
 // forwards to the C ABI (include/ffk*.h). Per-op state structs keep the reference's names;
 // instead of cuDNN descriptors they carry the plain numbers the sm_100a kernels need.
 #pragma once
+#include <cmath>
 #include <cstddef>
 #include <cstring>
 #include <stdexcept>
@@ -896,7 +897,7 @@ inline void update_metrics_label_kernel(ffStream_t stream, MetricsAttrs const &m
 // zero / constant initialisation (initializer_kernels.h:21-28). The reference has the CPU bodies only
 // (src/cpu/initializer_kernels.cc:1-52; its zero_init_kernel_gpu is NOT_IMPLEMENTED, constant_init_kernel
 // and the three random initialisers are declared and defined nowhere in lib/kernels). The GPU forms here
-// are ffk_fill on the calling thread's stream; the random initialisers are not provided.
+// are ffk_fill on the calling thread's stream; the random initialisers follow below.
 enum class TaskLocation { CPU, GPU };
 struct DataTypeValue {   // op-attrs/datatype_value.dtg.h: one value of any tensor element type
   std::variant<float, double, int32_t, int64_t, bool> raw;
@@ -936,6 +937,59 @@ inline void zero_init_kernel_cpu(GenericTensorAccessorW const &tensor) {
 inline void zero_init_kernel(TaskLocation const &loc, GenericTensorAccessorW const &tensor) {
   if (loc == TaskLocation::CPU) zero_init_kernel_cpu(tensor);
   else zero_init_kernel_gpu(tensor);
+}
+
+// The three random initialisers (initializer_kernels.h:10-20). lib/kernels declares them and defines them
+// nowhere; the callers (lib/runtime/src/initializer.cc:88-108, 203-229) fix the meaning: uniform in
+// [min_val, max_val]; Glorot = uniform in [-scale, scale] with the caller's scale = sqrt(6 / (fan_in +
+// fan_out)); normal(mean, stddev); float tensors only (the legacy cuRAND bodies assert DT_FLOAT,
+// lib/runtime/src/initializer_kernels.cu:35). Initialisation runs once, off the hot path: the values are a
+// function of the seed alone (SplitMix64 counter stream, 24-bit mantissas, Box-Muller), generated on the
+// host and copied to wherever the tensor lives.
+namespace detail {
+inline uint64_t splitmix64(uint64_t &state) {
+  uint64_t z = (state += 0x9E3779B97F4A7C15ULL);
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+  return z ^ (z >> 31);
+}
+inline float unit_float(uint64_t &state) { return float(splitmix64(state) >> 40) * (1.0f / 16777216.0f); }  // [0, 1)
+inline void require_float(GenericTensorAccessorW const &t, char const *who) {
+  if (t.data_type != DataType::FLOAT) throw mk_runtime_error(std::string(who) + ": float tensors only");
+}
+inline void store_floats(GenericTensorAccessorW const &t, std::vector<float> const &host) {
+  cudaPointerAttributes attr{};
+  bool const on_device = cudaPointerGetAttributes(&attr, t.ptr) == cudaSuccess &&
+                         (attr.type == cudaMemoryTypeDevice || attr.type == cudaMemoryTypeManaged);
+  if (!on_device) {
+    cudaGetLastError();  // a plain host pointer (or no driver at all) is not an error here
+    std::memcpy(t.ptr, host.data(), host.size() * sizeof(float));
+    return;
+  }
+  checkCUDA(cudaMemcpy(t.ptr, host.data(), host.size() * sizeof(float), cudaMemcpyHostToDevice));
+}
+}  // namespace detail
+inline void uniform_init_kernel(GenericTensorAccessorW const &tensor, size_t seed, float min_val, float max_val) {
+  detail::require_float(tensor, "uniform_init_kernel");
+  std::vector<float> host(tensor.shape.get_volume());
+  uint64_t state = seed;
+  for (float &v : host) v = min_val + (max_val - min_val) * detail::unit_float(state);
+  detail::store_floats(tensor, host);
+}
+inline void glorot_uniform_init_kernel(GenericTensorAccessorW const &tensor, size_t seed, float scale_factor) {
+  uniform_init_kernel(tensor, seed, -scale_factor, scale_factor);
+}
+inline void norm_init_kernel(GenericTensorAccessorW const &tensor, size_t seed, float mean, float stddev) {
+  detail::require_float(tensor, "norm_init_kernel");
+  std::vector<float> host(tensor.shape.get_volume());
+  uint64_t state = seed;
+  for (size_t i = 0; i < host.size(); i += 2) {
+    float const u1 = 1.0f - detail::unit_float(state), u2 = detail::unit_float(state);   // u1 in (0, 1]
+    float const r = std::sqrt(-2.0f * std::log(u1)), a = 6.28318530717958647692f * u2;
+    host[i] = mean + stddev * r * std::cos(a);
+    if (i + 1 < host.size()) host[i + 1] = mean + stddev * r * std::sin(a);
+  }
+  detail::store_floats(tensor, host);
 }
 
 // ------------------------------------------------------------------ optimizer_kernels.h

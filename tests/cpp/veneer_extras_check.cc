@@ -6,6 +6,8 @@
 #include "kernels/metrics_kernels.h"
 #include "kernels/perf_metrics.h"
 
+#include <cmath>
+
 using namespace FlexFlow;
 
 void (*const p_sparse)(ffStream_t, MetricsAttrs const &, float const *, int const *, int, int, PerfMetrics &) =
@@ -36,7 +38,48 @@ template <DataType IT, DataType OT> struct Widen {
   void operator()(int *out) const { *out = int(sizeof(real_type_t<OT>)) - int(sizeof(real_type_t<IT>)); }
 };
 
+void (*const p_uni)(GenericTensorAccessorW const &, size_t, float, float) = &uniform_init_kernel;
+void (*const p_glo)(GenericTensorAccessorW const &, size_t, float) = &glorot_uniform_init_kernel;
+void (*const p_nrm)(GenericTensorAccessorW const &, size_t, float, float) = &norm_init_kernel;
+
+int random_initialisers() {
+  size_t const n = 20001;   // odd: the Box-Muller tail
+  std::vector<float> a(n), b(n), c(n);
+  auto acc = [&](std::vector<float> &v) {
+    return GenericTensorAccessorW{{DataType::FLOAT, ArrayShape(std::vector<size_t>{v.size()}), v.data()}};
+  };
+  uniform_init_kernel(acc(a), 7, -0.25f, 0.75f);
+  uniform_init_kernel(acc(b), 7, -0.25f, 0.75f);
+  uniform_init_kernel(acc(c), 8, -0.25f, 0.75f);
+  if (a != b || a == c) return 20;                       // a function of the seed
+  double sum = 0;
+  for (float v : a) {
+    if (!(v >= -0.25f && v < 0.75f)) return 21;
+    sum += v;
+  }
+  if (std::fabs(sum / n - 0.25) > 0.01) return 22;
+  glorot_uniform_init_kernel(acc(b), 7, 0.5f);
+  for (size_t i = 0; i < n; ++i)
+    if (std::fabs(b[i] - (a[i] + 0.25f - 0.5f)) > 1e-6f) return 23;   // same stream, range [-0.5, 0.5)
+  norm_init_kernel(acc(c), 11, 2.0f, 0.5f);
+  double m = 0, v2 = 0;
+  for (float v : c) m += v;
+  m /= n;
+  for (float v : c) v2 += (v - m) * (v - m);
+  if (std::fabs(m - 2.0) > 0.02 || std::fabs(std::sqrt(v2 / n) - 0.5) > 0.02) return 24;
+  for (float v : c) if (!std::isfinite(v)) return 25;
+  int32_t ints[4] = {0, 0, 0, 0};
+  GenericTensorAccessorW wi{{DataType::INT32, ArrayShape(std::vector<size_t>{4}), ints}};
+  try {
+    uniform_init_kernel(wi, 1, 0.f, 1.f);
+    return 26;
+  } catch (std::runtime_error const &) {
+  }
+  return 0;
+}
+
 int host_side_semantics() {
+  if (int rc = random_initialisers()) return rc;
   if (DataTypeDispatch1<SizeOf>{}(DataType::DOUBLE, size_t(3)) != 24 || dispatch<SizeOf>(DataType::INT32, size_t(2)) != 8) return 10;
   int widen = 0;
   DataTypeDispatch2<Widen>{}(DataType::FLOAT, DataType::INT64, &widen);

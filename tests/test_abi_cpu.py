@@ -75,9 +75,11 @@ def test_bad_arguments_are_rejected_without_touching_the_device(ffk):
 
 def test_veneer_metrics_and_initialiser_helpers_host_side():
     """tests/cpp/veneer_extras_check.cc (built by __graft_entry__.build()): the veneer has the reference's
-    metrics wrappers, PerfMetrics update / apply_scale and zero / constant initialisers under the reference's
-    names and signatures (checked at compile time through function-pointer types), and the host-only ones
-    behave like src/perf_metrics.cc:29-68 and src/cpu/initializer_kernels.cc:1-52."""
+    metrics wrappers, PerfMetrics update / apply_scale, the zero / constant / random initialisers, the accessor
+    helpers and DataTypeDispatch1/2 under the reference's names and signatures (checked at compile time through
+    function-pointer types), and the host-only ones behave like src/perf_metrics.cc:29-68,
+    src/cpu/initializer_kernels.cc:1-52 and the callers' contract of the random initialisers
+    (lib/runtime/src/initializer.cc:88-108, 203-229: ranges, moments, a function of the seed alone)."""
     import subprocess
     from pathlib import Path
 
@@ -89,8 +91,8 @@ def test_veneer_metrics_and_initialiser_helpers_host_side():
 
 def test_veneer_declares_every_kernel_function_of_the_reference_headers():
     """Every `*_kernel` / `*_task_gpu` function name declared under the reference's
-    lib/kernels/include/kernels appears in the veneer, except the three random initialisers, which the
-    reference declares and defines nowhere in lib/kernels. Needs the reference checkout."""
+    lib/kernels/include/kernels appears in the veneer — including the ones the reference declares and
+    defines nowhere in lib/kernels (the random initialisers). Needs the reference checkout."""
     from pathlib import Path
 
     ref = Path("/root/reference/lib/kernels/include/kernels")
@@ -98,7 +100,7 @@ def test_veneer_declares_every_kernel_function_of_the_reference_headers():
         pytest.skip("the reference checkout is not on this machine")
     veneer = Path(__file__).resolve().parents[1] / "flexflow-train_b200" / "include" / "ffk_cpp"
     vtext = "\n".join(p.read_text() for p in veneer.glob("*.h"))
-    not_provided = {"uniform_init_kernel", "glorot_uniform_init_kernel", "norm_init_kernel"}
+    not_provided = set()
     missing, seen = [], 0
     for h in sorted(ref.glob("*.h")):
         text = re.sub(r"/\*.*?\*/", " ", re.sub(r"//[^\n]*", " ", h.read_text()), flags=re.S)
@@ -111,9 +113,8 @@ def test_veneer_declares_every_kernel_function_of_the_reference_headers():
 
 def test_veneer_signatures_match_the_reference_headers():
     """tools/veneer_signature_diff.py: the parameter lists of all 88 kernel functions declared in the
-    reference's include/kernels/*.h against the veneer's, namespace by namespace. Six differences are
-    known and deliberate: the three random initialisers (declared by the reference, defined nowhere in
-    lib/kernels; not provided), `sgd_nccl_update_task_gpu` (the reference header misses a comma,
+    reference's include/kernels/*.h against the veneer's, namespace by namespace. Three differences are
+    known and deliberate: `sgd_nccl_update_task_gpu` (the reference header misses a comma,
     optimizer_kernels.h:23) and the two Adam updates (the reference header forgets `size` / `num_replicas`,
     which the bodies in src/cuda/optimizer_kernel.cu:147-214 take). Needs the reference checkout."""
     import importlib.util
@@ -129,5 +130,4 @@ def test_veneer_signatures_match_the_reference_headers():
     checked, bad = mod.compare("/root/reference", lines.append)
     flagged = {re.search(r"'([a-z0-9_]+)'\)", l).group(1) for l in lines if l.startswith(("MISSING", "DIFF"))}
     assert checked >= 85
-    assert flagged == {"uniform_init_kernel", "glorot_uniform_init_kernel", "norm_init_kernel",
-                       "sgd_nccl_update_task_gpu", "adam_ps_update_task_gpu", "adam_nccl_update_task_gpu"}, lines
+    assert flagged == {"sgd_nccl_update_task_gpu", "adam_ps_update_task_gpu", "adam_nccl_update_task_gpu"}, lines
