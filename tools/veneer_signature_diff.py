@@ -113,6 +113,40 @@ def _compare(ref, ven, out):
   return len(R), bad
 
 
+def compare_call_sites(ref_root='/root/reference', out=print):
+    """The callers' view: every `profile(<kernel>, settings, "fmt", args...)` in
+    lib/local-execution/src/ops/*.cc must find <kernel> in the veneer — in one of the namespaces the
+    file pulls in with `using namespace FlexFlow::Kernels::<Op>`, or in FlexFlow — with exactly
+    len(args) + 1 parameters (profile() prepends the stream). Returns (call sites, mismatches)."""
+    ven = Path(__file__).resolve().parents[1] / 'flexflow-train_b200' / 'include' / 'ffk_cpp'
+    V = {}
+    for h in sorted(ven.glob('*.h')):
+        for ns, name, params in functions(h.read_text()):
+            V.setdefault((ns, name), []).append(params)
+    total = bad = 0
+    for f in sorted((Path(ref_root) / 'lib' / 'local-execution' / 'src' / 'ops').glob('*.cc')):
+        t = re.sub(r'//[^\n]*', ' ', f.read_text())
+        using = re.findall(r'using namespace FlexFlow::Kernels::([A-Za-z0-9_]+)', t)
+        for m in re.finditer(r'\bprofile\s*\(', t):
+            i, depth = m.end(), 1
+            while depth and i < len(t):
+                depth += {'(': 1, ')': -1}.get(t[i], 0)
+                i += 1
+            args = split_params(t[m.end():i - 1])
+            fn, nargs = args[0].strip(), len(args) - 3
+            total += 1
+            cands = [c for ns in using for c in V.get((f'Kernels::{ns}', fn), [])] + V.get(('', fn), [])
+            if not cands:
+                out(f'{f.name}: {fn} not found in the veneer (namespaces {using})')
+                bad += 1
+            elif not any(len(c) - 1 == nargs for c in cands):
+                out(f'{f.name}: {fn} is called with {nargs} arguments, the veneer takes {[len(c) - 1 for c in cands]}')
+                bad += 1
+    out(f'call sites {total} mismatches {bad}')
+    return total, bad
+
+
 if __name__ == '__main__':
     n, bad = compare(*(sys.argv[1:2]))
-    sys.exit(1 if bad else 0)
+    n2, bad2 = compare_call_sites(*(sys.argv[1:2]))
+    sys.exit(1 if bad or bad2 else 0)
