@@ -142,6 +142,18 @@ def compare_call_sites(ref_root='/root/reference', out=print):
             elif not any(len(c) - 1 == nargs for c in cands):
                 out(f'{f.name}: {fn} is called with {nargs} arguments, the veneer takes {[len(c) - 1 for c in cands]}')
                 bad += 1
+        # init_kernel is called directly (no stream, no profile())
+        for m in re.finditer(r'(?<![A-Za-z_])init_kernel\s*\(', t):
+            i, depth = m.end(), 1
+            while depth and i < len(t):
+                depth += {'(': 1, ')': -1}.get(t[i], 0)
+                i += 1
+            nargs = len(split_params(t[m.end():i - 1]))
+            total += 1
+            cands = [c for ns in using for c in V.get((f'Kernels::{ns}', 'init_kernel'), [])]
+            if not any(len(c) == nargs for c in cands):
+                out(f'{f.name}: init_kernel is called with {nargs} arguments, the veneer takes {[len(c) for c in cands]}')
+                bad += 1
     out(f'call sites {total} mismatches {bad}')
     return total, bad
 
