@@ -133,10 +133,15 @@ struct ff_dim_t {
   constexpr ff_dim_t(int v = 0) : value(v) {}
   bool operator==(ff_dim_t o) const { return value == o.value; }
 };
-struct legion_dim_t {
+struct legion_dim_t {   // kernels/legion_dim_t.struct.toml: eq, ord, hash
   int value;
   constexpr legion_dim_t(int v = 0) : value(v) {}
   bool operator==(legion_dim_t o) const { return value == o.value; }
+  bool operator!=(legion_dim_t o) const { return value != o.value; }
+  bool operator<(legion_dim_t o) const { return value < o.value; }
+  bool operator>(legion_dim_t o) const { return value > o.value; }
+  bool operator<=(legion_dim_t o) const { return value <= o.value; }
+  bool operator>=(legion_dim_t o) const { return value >= o.value; }
 };
 using LegionTensorDims = std::vector<size_t>;  // what ArrayShape::dims holds (array_shape.h:50)
 inline legion_dim_t add_to_legion_dim(legion_dim_t d, int v) { return legion_dim_t{d.value + v}; }
@@ -348,9 +353,16 @@ struct ElementUnaryAttrs {
   std::optional<float> scalar;
 };
 inline OperatorType get_op_type(ElementUnaryAttrs const &a) { return a.op_type; }
-struct ProfilingSettings {
+struct ProfilingSettings {   // kernels/profiling_settings.struct.toml: eq, ord, hash
   int warmup_iters;
   int measure_iters;
+  bool operator==(ProfilingSettings const &o) const {
+    return warmup_iters == o.warmup_iters && measure_iters == o.measure_iters;
+  }
+  bool operator!=(ProfilingSettings const &o) const { return !(*this == o); }
+  bool operator<(ProfilingSettings const &o) const {
+    return warmup_iters != o.warmup_iters ? warmup_iters < o.warmup_iters : measure_iters < o.measure_iters;
+  }
 };
 
 // ---- PerDeviceFFHandle — include/kernels/ff_handle.h:13-24
@@ -364,3 +376,14 @@ struct PerDeviceFFHandle {
 };
 
 }  // namespace FlexFlow
+
+namespace std {
+template <> struct hash<::FlexFlow::legion_dim_t> {
+  size_t operator()(::FlexFlow::legion_dim_t const &d) const { return std::hash<int>{}(d.value); }
+};
+template <> struct hash<::FlexFlow::ProfilingSettings> {
+  size_t operator()(::FlexFlow::ProfilingSettings const &p) const {
+    return std::hash<int>{}(p.warmup_iters) * 1000003u ^ std::hash<int>{}(p.measure_iters);
+  }
+};
+}  // namespace std

@@ -1,0 +1,4 @@
+// Same include path as the header the reference GENERATES from lib/kernels/include/kernels/legion_dim_t.struct.toml
+// (proj dtgen, not vendored); the type lives in ffk_cpp/types.h.
+#pragma once
+#include "../ffk_cpp/ops.h"

@@ -4,7 +4,11 @@
 #include "kernels/cpu.h"
 #include "kernels/initializer_kernels.h"
 #include "kernels/metrics_kernels.h"
+#include "kernels/legion_dim_t.dtg.h"
 #include "kernels/perf_metrics.h"
+#include "kernels/profiling_settings.dtg.h"
+
+#include <unordered_set>
 
 #include <cmath>
 
@@ -80,6 +84,13 @@ int random_initialisers() {
 
 int host_side_semantics() {
   if (int rc = random_initialisers()) return rc;
+  {  // the generated value types (eq, ord, hash)
+    std::unordered_set<legion_dim_t> dims{legion_dim_t{1}, legion_dim_t{1}, legion_dim_t{2}};
+    std::unordered_set<ProfilingSettings> ps{ProfilingSettings{1, 2}, ProfilingSettings{1, 2}};
+    if (dims.size() != 2 || ps.size() != 1 || !(legion_dim_t{1} < legion_dim_t{2}) ||
+        !(ProfilingSettings{1, 2} < ProfilingSettings{1, 3}) || ProfilingSettings{0, 1} != ProfilingSettings{0, 1})
+      return 30;
+  }
   if (DataTypeDispatch1<SizeOf>{}(DataType::DOUBLE, size_t(3)) != 24 || dispatch<SizeOf>(DataType::INT32, size_t(2)) != 8) return 10;
   int widen = 0;
   DataTypeDispatch2<Widen>{}(DataType::FLOAT, DataType::INT64, &widen);

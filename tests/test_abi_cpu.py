@@ -150,3 +150,21 @@ def test_veneer_serves_every_kernel_call_site_of_local_execution():
     lines = []
     total, bad = mod.compare_call_sites("/root/reference", lines.append)
     assert total >= 60 and bad == 0, lines
+
+
+def test_every_kernels_include_path_of_the_reference_resolves():
+    """Every `#include "kernels/..."` that appears anywhere under the reference's lib/ resolves inside
+    flexflow-train_b200/include (the generated *.dtg.h paths included), except kernels/cuda_helper.h, which
+    only the legacy runtime names and the reference's own include directory does not contain either."""
+    import subprocess
+    from pathlib import Path
+
+    ref = Path("/root/reference/lib")
+    if not ref.is_dir():
+        pytest.skip("the reference checkout is not on this machine")
+    out = subprocess.run(["grep", "-rhoE", '#include "kernels/[a-z_0-9./]+"', str(ref), "--include=*.cc",
+                          "--include=*.h", "--include=*.cu"], capture_output=True, text=True).stdout
+    wanted = {l.split('"')[1] for l in out.splitlines()}
+    inc = Path(__file__).resolve().parents[1] / "flexflow-train_b200" / "include"
+    missing = sorted(h for h in wanted if not (inc / h).exists())
+    assert len(wanted) >= 40 and missing == ["kernels/cuda_helper.h"], missing
